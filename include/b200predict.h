@@ -1,0 +1,151 @@
+/*
+ * b200predict.h — C ABI of libb200predict.so, the B200 (sm_100a) implementation of the
+ * batched image `predict` path of CodyRichter/MLMicroserviceTemplate.
+ *
+ * Every entry point is `extern "C"`, takes plain pointers / sizes / a cudaStream_t passed as
+ * `void*`, returns 0 on success or a negative B2P_E_* code, never throws and never calls back
+ * into the host language.  A handle is bound to ONE device and is NOT re-entrant: exactly one
+ * host thread drives a given handle; different handles (different GPUs) are independent.
+ * All compute entry points are stream-ordered and asynchronous; the caller owns every buffer it
+ * passes and keeps it alive until the stream work has completed.
+ *
+ * There is no CPU fallback anywhere behind this header: b2p_create() fails with
+ * B2P_E_DEVICE on anything that is not compute capability 10.x.
+ *
+ * Reference citations are file:line in CodyRichter/MLMicroserviceTemplate.
+ */
+#ifndef B200PREDICT_H_
+#define B200PREDICT_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2P_ABI_VERSION 1
+
+/* error codes */
+#define B2P_OK 0
+#define B2P_E_ARG -1      /* bad argument (null pointer, size out of range, malformed program) */
+#define B2P_E_DEVICE -2   /* not an sm_100 device / device mismatch */
+#define B2P_E_CUDA -3     /* a CUDA runtime/driver call failed; see b2p_last_error() */
+#define B2P_E_NOMEM -4    /* device or pinned allocation failed */
+#define B2P_E_LIMIT -5    /* a size exceeds a documented fixed maximum */
+
+typedef struct b2p_handle b2p_handle;
+
+/* ---- layer program -----------------------------------------------------------------------
+ * The classifier forward is handed over as a flat program of ops over numbered activation
+ * slots.  Slot B2P_SLOT_INPUT is the caller's input tensor, B2P_SLOT_OUTPUT the caller's output;
+ * every other slot is handle-owned workspace sized `slot_elems[i] * max_batch` bf16 elements.
+ * Activations are NHWC bf16.  The host mirror builds the program by walking the torchvision
+ * module tree (ResNet: SP/torchvision/models/resnet.py:266-282).                              */
+#define B2P_SLOT_INPUT 0
+#define B2P_SLOT_OUTPUT -2
+#define B2P_SLOT_NONE -1
+
+enum b2p_op_kind {
+    B2P_OP_CONV = 1,       /* implicit-GEMM conv (+bias, +residual, +ReLU), bf16 NHWC -> bf16 NHWC  */
+    B2P_OP_LINEAR = 2,     /* [n, in_c] bf16 x [out_c, in_c]^T + bias -> fp32 [n, out_c]            */
+    B2P_OP_MAXPOOL = 3,    /* kh x kw / stride / pad_lo max pool, NHWC bf16                          */
+    B2P_OP_AVGPOOL = 4,    /* global average pool NHWC bf16 -> [n, c] bf16                           */
+    B2P_OP_STEM_PACK = 5,  /* NCHW bf16 [n,3,H,W] -> 2x2 space-to-depth NHWC [n,H/2,W/2,16] bf16    */
+    B2P_OP_NCHW_TO_NHWC = 6 /* NCHW bf16 [n,c,H,W] -> NHWC bf16 (test helper, c % 8 == 0)            */
+};
+
+typedef struct b2p_op {
+    int32_t kind;
+    int32_t src, dst, res;          /* slot ids; res = residual added before ReLU, or B2P_SLOT_NONE */
+    int32_t in_h, in_w, in_c;
+    int32_t out_h, out_w, out_c;
+    int32_t kh, kw, stride;
+    int32_t pad_lo, pad_hi;         /* zero padding before / after, same on both axes              */
+    int32_t relu;
+    int32_t weight, bias;           /* blob indices: weight bf16 [out_c_pad][kh][kw][in_c], bias f32 */
+    int32_t reserved[4];
+} b2p_op;
+
+typedef struct b2p_model_desc {
+    int32_t abi_version;            /* B2P_ABI_VERSION */
+    int32_t max_batch;              /* largest n any call will pass                                */
+    int32_t sub_batch;              /* >0: run the program over chunks of this many images so that
+                                       inter-layer activations stay L2-resident; 0 = whole batch   */
+    int32_t n_ops;
+    const b2p_op* ops;
+    int32_t n_slots;                /* slots 0..n_slots-1; slot 0 is the external input            */
+    const int64_t* slot_elems;      /* per-image element count of each slot (bf16 elements)        */
+    int32_t n_blobs;
+    const void* const* blob_ptrs;   /* HOST pointers; copied to the device by b2p_create            */
+    const int64_t* blob_bytes;
+    int64_t in_elems_per_image;     /* elements per image of the external input  (bf16)            */
+    int64_t out_elems_per_image;    /* elements per image of the external output (fp32 or bf16)    */
+} b2p_model_desc;
+
+/* One decoded image inside a batch slab (uint8, HWC, 3 channels, rows densely packed).
+ * The resize geometry follows SP/torchvision/transforms/_presets.py:58-65: the image is resized
+ * (antialiased bilinear) to res_h x res_w, then the 224x224 window at (top, left) is kept.      */
+typedef struct b2p_image {
+    int64_t offset;                 /* byte offset of pixel (0,0,0) from the slab base             */
+    int32_t h, w;                   /* source size                                                 */
+    int32_t res_h, res_w;           /* size after resize                                           */
+    int32_t top, left;              /* crop origin in the resized image                            */
+} b2p_image;
+
+#define B2P_OUT_HW 224              /* model input is 224 x 224                                     */
+#define B2P_MAX_TOPK 8
+
+typedef struct b2p_stats {
+    float ms_h2d, ms_preprocess, ms_forward, ms_epilogue, ms_d2h;   /* last b2p_predict_host call */
+    int64_t calls;
+    int64_t kernel_launches;        /* kernels launched by this handle since create                */
+} b2p_stats;
+
+/* Library-wide: ABI version and a static build string ("sm_100a ..."). */
+int32_t b2p_abi_version(void);
+const char* b2p_build_info(void);
+
+/* Replaces init() (src/model/model.py:6-13): builds one model replica on `device`: copies the
+ * packed weights, allocates workspace, encodes the TMA descriptors.  Synchronous.               */
+int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out);
+int32_t b2p_destroy(b2p_handle* h);
+const char* b2p_last_error(const b2p_handle* h);   /* h may be NULL: last create() failure      */
+int32_t b2p_stats_get(b2p_handle* h, b2p_stats* out);
+
+/* Stage P (K1), the arithmetic predict() would do after Image.open (src/model/model.py:23):
+ * antialiased resize + crop + /255 + (x-mean)/std + HWC->NCHW.  `slab` is a DEVICE pointer to the
+ * uint8 images, `imgs` a HOST array of n descriptors (copied before return).  `out` is a device
+ * tensor [n,3,224,224], bf16 when out_f32 == 0, fp32 otherwise (the fp32 form exists for the
+ * 1e-6 parity gate).                                                                           */
+int32_t b2p_preprocess(b2p_handle* h, const uint8_t* slab, const b2p_image* imgs, int32_t n,
+                       void* out, int32_t out_f32, void* stream);
+
+/* Stage F (K2): runs the layer program on n images. `x` = external input, `out` = external
+ * output (fp32 logits [n, classes] for a classifier program).                                  */
+int32_t b2p_forward(b2p_handle* h, const void* x, int32_t n, void* out, void* stream);
+
+/* Stage E (K3): fp32 softmax over `classes` + top-k (k <= B2P_MAX_TOPK), ties -> lowest index.
+ * logits [n, classes] fp32 device -> probs [n, k] fp32, idx [n, k] int32 (device).             */
+int32_t b2p_softmax_topk(b2p_handle* h, const float* logits, int32_t n, int32_t classes,
+                         int32_t k, float* probs, int32_t* idx, void* stream);
+
+/* The three stages chained on one stream, device buffers in, device buffers out.  This is what
+ * predict() (src/model/model.py:16-31) computes for a batch of n already-decoded images.       */
+int32_t b2p_predict(b2p_handle* h, const uint8_t* slab, const b2p_image* imgs, int32_t n,
+                    int32_t k, float* probs, int32_t* idx, void* stream);
+
+/* Same, end to end from HOST memory: copies `slab_bytes` of (pinned) host slab to the device,
+ * runs the chain, copies probs/idx back to (pinned) host memory.  Asynchronous: synchronise the
+ * stream before reading probs_host / idx_host.  Records per-stage CUDA-event times (b2p_stats). */
+int32_t b2p_predict_host(b2p_handle* h, const uint8_t* slab_host, int64_t slab_bytes,
+                         const b2p_image* imgs, int32_t n, int32_t k, float* probs_host,
+                         int32_t* idx_host, void* stream);
+
+/* Device logits of the most recent b2p_predict / b2p_predict_host call ([n, classes] fp32,
+ * handle-owned, valid until the next call).  Used by the parity tests.                         */
+const float* b2p_last_logits(b2p_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200PREDICT_H_ */

@@ -1,0 +1,443 @@
+// C-ABI layer of libb200predict.so: handle lifetime, the layer-program executor and the chained
+// predict entry points declared in include/b200predict.h.
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+#include "kernels.h"
+
+using namespace b2p;
+
+namespace {
+
+char g_create_error[512] = "";
+
+struct OpPlan {
+    b2p_op op;
+    GemmPlan gemm;        // valid for CONV / LINEAR
+    bool is_gemm = false;
+    bool src_external = false;
+};
+
+}  // namespace
+
+struct b2p_handle {
+    int device = -1;
+    int num_sms = 0;
+    int max_batch = 0;
+    int chunk = 0;                       // images per pass through the program
+    int64_t in_elems = 0, out_elems = 0;
+    int classes = 0;
+    std::vector<OpPlan> ops;
+    std::vector<void*> slots;            // device workspace per slot (slot 0 unused)
+    std::vector<int64_t> slot_elems;
+    std::vector<void*> blobs;            // device copies of the weight blobs
+    std::vector<int64_t> blob_bytes;
+    // predict-chain staging (handle-owned)
+    uint8_t* slab_dev = nullptr;
+    int64_t slab_cap = 0;
+    // descriptor staging: a ring of pinned + device slots so that back-to-back asynchronous calls
+    // never overwrite a descriptor block whose host->device copy is still queued
+    static constexpr int RING = 8;
+    b2p_image* imgs_dev[RING] = {};
+    b2p_image* imgs_pinned[RING] = {};
+    cudaEvent_t imgs_done[RING] = {};
+    bool imgs_used[RING] = {};
+    int ring_pos = 0;
+    b2p_image* cur_imgs_dev = nullptr;
+    void* x_dev = nullptr;               // [max_batch,3,224,224] bf16
+    float* logits_dev = nullptr;         // [max_batch, out_elems]
+    float* probs_dev = nullptr;
+    int32_t* idx_dev = nullptr;
+    cudaEvent_t ev[6] = {};
+    bool ev_valid = false;
+    b2p_stats stats = {};
+    char err[512] = "";
+};
+
+namespace {
+
+void set_error(b2p_handle* h, const char* fmt, ...) {
+    char* dst = h ? h->err : g_create_error;
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(dst, 512, fmt, ap);
+    va_end(ap);
+}
+
+#define B2P_CUDA(h, call)                                                                  \
+    do {                                                                                   \
+        cudaError_t e__ = (call);                                                          \
+        if (e__ != cudaSuccess) {                                                          \
+            set_error(h, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, \
+                      __LINE__);                                                           \
+            return B2P_E_CUDA;                                                             \
+        }                                                                                  \
+    } while (0)
+
+void* slot_ptr(b2p_handle* h, int slot, const void* ext_in, void* ext_out, int64_t chunk_off_imgs) {
+    if (slot == B2P_SLOT_INPUT)
+        return const_cast<uint8_t*>(static_cast<const uint8_t*>(ext_in)) + chunk_off_imgs * h->in_elems * 2;
+    if (slot == B2P_SLOT_OUTPUT) return ext_out;   // offset applied by the caller (element size varies)
+    if (slot < 0 || slot >= static_cast<int>(h->slots.size())) return nullptr;
+    return h->slots[slot];
+}
+
+int validate_desc(const b2p_model_desc* d) {
+    if (!d || d->abi_version != B2P_ABI_VERSION) return B2P_E_ARG;
+    if (d->max_batch <= 0 || d->max_batch > 4096) return B2P_E_LIMIT;
+    if (d->n_ops <= 0 || !d->ops || d->n_slots <= 0 || !d->slot_elems) return B2P_E_ARG;
+    if (d->n_blobs < 0 || (d->n_blobs > 0 && (!d->blob_ptrs || !d->blob_bytes))) return B2P_E_ARG;
+    if (d->sub_batch < 0) return B2P_E_ARG;
+    for (int i = 0; i < d->n_ops; ++i) {
+        const b2p_op& o = d->ops[i];
+        if (o.kind < B2P_OP_CONV || o.kind > B2P_OP_NCHW_TO_NHWC) return B2P_E_ARG;
+        auto ok_slot = [&](int s, bool allow_none) {
+            if (s == B2P_SLOT_NONE) return allow_none;
+            if (s == B2P_SLOT_OUTPUT) return true;
+            return s >= 0 && s < d->n_slots;
+        };
+        if (!ok_slot(o.src, false) || o.src == B2P_SLOT_OUTPUT) return B2P_E_ARG;
+        if (!ok_slot(o.dst, false) || o.dst == B2P_SLOT_INPUT) return B2P_E_ARG;
+        if (!ok_slot(o.res, true) || o.res == B2P_SLOT_OUTPUT) return B2P_E_ARG;
+        if (o.kind == B2P_OP_CONV || o.kind == B2P_OP_LINEAR) {
+            if (o.weight < 0 || o.weight >= d->n_blobs || o.bias < 0 || o.bias >= d->n_blobs) return B2P_E_ARG;
+        }
+    }
+    return B2P_OK;
+}
+
+int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st) {
+    for (int off = 0; off < n; off += h->chunk) {
+        const int nb = (n - off) < h->chunk ? (n - off) : h->chunk;
+        for (OpPlan& p : h->ops) {
+            const b2p_op& o = p.op;
+            const void* src = slot_ptr(h, o.src, x, out, off);
+            void* dst = slot_ptr(h, o.dst, x, out, off);
+            const void* res = o.res == B2P_SLOT_NONE ? nullptr : slot_ptr(h, o.res, x, out, off);
+            if (!src || !dst) { set_error(h, "program references an unallocated slot"); return B2P_E_ARG; }
+            cudaError_t e = cudaSuccess;
+            switch (o.kind) {
+                case B2P_OP_CONV:
+                case B2P_OP_LINEAR: {
+                    if (o.dst == B2P_SLOT_OUTPUT) {
+                        const size_t esz = o.kind == B2P_OP_LINEAR ? 4 : 2;
+                        dst = static_cast<uint8_t*>(dst) + static_cast<size_t>(off) * h->out_elems * esz;
+                    }
+                    if (p.src_external) {
+                        // A-operand map points into the caller's buffer: encode it for this chunk
+                        char eb[256] = "";
+                        if (!gemm_plan_set_src(p.gemm, src, nb, eb, sizeof eb)) {
+                            set_error(h, "%s", eb);
+                            return B2P_E_CUDA;
+                        }
+                    }
+                    const int rows = o.kind == B2P_OP_LINEAR ? nb : nb * o.out_h * o.out_w;
+                    e = gemm_plan_launch(p.gemm, rows, res, dst, h->num_sms, st);
+                    break;
+                }
+                case B2P_OP_MAXPOOL:
+                    e = launch_maxpool(src, dst, nb, o.in_h, o.in_w, o.in_c, o.out_h, o.out_w, o.kh, o.stride,
+                                       o.pad_lo, st);
+                    break;
+                case B2P_OP_AVGPOOL:
+                    e = launch_avgpool(src, dst, nb, o.in_h * o.in_w, o.in_c, st);
+                    break;
+                case B2P_OP_STEM_PACK:
+                    e = launch_stem_pack(src, dst, nb, o.in_h, o.in_w, st);
+                    break;
+                case B2P_OP_NCHW_TO_NHWC:
+                    e = launch_nchw_to_nhwc(src, dst, nb, o.in_c, o.in_h, o.in_w, st);
+                    break;
+                default:
+                    set_error(h, "unknown op kind %d", o.kind);
+                    return B2P_E_ARG;
+            }
+            if (e != cudaSuccess) {
+                set_error(h, "op kind %d launch failed: %s", o.kind, cudaGetErrorString(e));
+                return B2P_E_CUDA;
+            }
+            h->stats.kernel_launches += 1;
+        }
+    }
+    return B2P_OK;
+}
+
+int stage_images(b2p_handle* h, const b2p_image* imgs, int n, cudaStream_t st) {
+    const int r = h->ring_pos;
+    h->ring_pos = (r + 1) % b2p_handle::RING;
+    if (h->imgs_used[r]) B2P_CUDA(h, cudaEventSynchronize(h->imgs_done[r]));
+    memcpy(h->imgs_pinned[r], imgs, sizeof(b2p_image) * static_cast<size_t>(n));
+    B2P_CUDA(h, cudaMemcpyAsync(h->imgs_dev[r], h->imgs_pinned[r], sizeof(b2p_image) * static_cast<size_t>(n),
+                                cudaMemcpyHostToDevice, st));
+    B2P_CUDA(h, cudaEventRecord(h->imgs_done[r], st));
+    h->imgs_used[r] = true;
+    h->cur_imgs_dev = h->imgs_dev[r];
+    return B2P_OK;
+}
+
+int check_images(b2p_handle* h, const b2p_image* imgs, int n) {
+    for (int i = 0; i < n; ++i) {
+        const b2p_image& im = imgs[i];
+        if (im.h <= 0 || im.w <= 0 || im.res_h < B2P_OUT_HW || im.res_w < B2P_OUT_HW || im.top < 0 ||
+            im.left < 0 || im.top + B2P_OUT_HW > im.res_h || im.left + B2P_OUT_HW > im.res_w || im.offset < 0) {
+            set_error(h, "image %d: bad geometry h=%d w=%d res=%dx%d crop=(%d,%d)", i, im.h, im.w, im.res_h,
+                      im.res_w, im.top, im.left);
+            return B2P_E_ARG;
+        }
+    }
+    return B2P_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int32_t b2p_abi_version(void) { return B2P_ABI_VERSION; }
+
+const char* b2p_build_info(void) {
+    return "libb200predict sm_100a (tcgen05/TMA/TMEM), built " __DATE__ " " __TIME__;
+}
+
+const char* b2p_last_error(const b2p_handle* h) { return h ? h->err : g_create_error; }
+
+int32_t b2p_destroy(b2p_handle* h) {
+    if (!h) return B2P_OK;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    for (void* p : h->slots) if (p) cudaFree(p);
+    for (void* p : h->blobs) if (p) cudaFree(p);
+    if (h->slab_dev) cudaFree(h->slab_dev);
+    for (int r = 0; r < b2p_handle::RING; ++r) {
+        if (h->imgs_dev[r]) cudaFree(h->imgs_dev[r]);
+        if (h->imgs_pinned[r]) cudaFreeHost(h->imgs_pinned[r]);
+        if (h->imgs_done[r]) cudaEventDestroy(h->imgs_done[r]);
+    }
+    if (h->x_dev) cudaFree(h->x_dev);
+    if (h->logits_dev) cudaFree(h->logits_dev);
+    if (h->probs_dev) cudaFree(h->probs_dev);
+    if (h->idx_dev) cudaFree(h->idx_dev);
+    if (h->ev_valid) for (auto& e : h->ev) cudaEventDestroy(e);
+    delete h;
+    return B2P_OK;
+}
+
+int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out) {
+    g_create_error[0] = 0;
+    if (!out) return B2P_E_ARG;
+    *out = nullptr;
+    int rc = validate_desc(desc);
+    if (rc != B2P_OK) { set_error(nullptr, "invalid model description (code %d)", rc); return rc; }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        set_error(nullptr, "no such CUDA device %d (%d visible)", device, ndev);
+        return B2P_E_DEVICE;
+    }
+    cudaDeviceProp prop;
+    B2P_CUDA(nullptr, cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        set_error(nullptr, "device %d is sm_%d%d; this library only runs on sm_100 (B200) and has no fallback",
+                  device, prop.major, prop.minor);
+        return B2P_E_DEVICE;
+    }
+    B2P_CUDA(nullptr, cudaSetDevice(device));
+    char eb[256] = "";
+    if (!tma_init(eb, sizeof eb)) { set_error(nullptr, "%s", eb); return B2P_E_CUDA; }
+
+    b2p_handle* h = new (std::nothrow) b2p_handle();
+    if (!h) return B2P_E_NOMEM;
+    h->device = device;
+    h->num_sms = prop.multiProcessorCount;
+    h->max_batch = desc->max_batch;
+    h->chunk = (desc->sub_batch > 0 && desc->sub_batch < desc->max_batch) ? desc->sub_batch : desc->max_batch;
+    h->in_elems = desc->in_elems_per_image;
+    h->out_elems = desc->out_elems_per_image;
+
+#define B2P_FAIL(code, ...)                         \
+    do {                                            \
+        set_error(nullptr, __VA_ARGS__);            \
+        b2p_destroy(h);                             \
+        return code;                                \
+    } while (0)
+
+    // weights
+    h->blobs.assign(desc->n_blobs, nullptr);
+    h->blob_bytes.assign(desc->blob_bytes, desc->blob_bytes + desc->n_blobs);
+    for (int i = 0; i < desc->n_blobs; ++i) {
+        if (desc->blob_bytes[i] <= 0 || !desc->blob_ptrs[i]) B2P_FAIL(B2P_E_ARG, "blob %d is empty", i);
+        if (cudaMalloc(&h->blobs[i], static_cast<size_t>(desc->blob_bytes[i])) != cudaSuccess)
+            B2P_FAIL(B2P_E_NOMEM, "cudaMalloc(%lld) for blob %d failed", (long long)desc->blob_bytes[i], i);
+        if (cudaMemcpy(h->blobs[i], desc->blob_ptrs[i], static_cast<size_t>(desc->blob_bytes[i]),
+                       cudaMemcpyHostToDevice) != cudaSuccess)
+            B2P_FAIL(B2P_E_CUDA, "weight upload of blob %d failed", i);
+    }
+    // workspace slots (sized for one chunk)
+    h->slots.assign(desc->n_slots, nullptr);
+    h->slot_elems.assign(desc->slot_elems, desc->slot_elems + desc->n_slots);
+    for (int i = 1; i < desc->n_slots; ++i) {
+        const size_t bytes = static_cast<size_t>(desc->slot_elems[i]) * 2 * h->chunk;
+        if (bytes == 0) continue;
+        if (cudaMalloc(&h->slots[i], bytes) != cudaSuccess)
+            B2P_FAIL(B2P_E_NOMEM, "cudaMalloc(%zu) for slot %d failed", bytes, i);
+        cudaMemset(h->slots[i], 0, bytes);
+    }
+    // op plans
+    h->ops.resize(desc->n_ops);
+    for (int i = 0; i < desc->n_ops; ++i) {
+        OpPlan& p = h->ops[i];
+        p.op = desc->ops[i];
+        const b2p_op& o = p.op;
+        if (o.kind == B2P_OP_CONV || o.kind == B2P_OP_LINEAR) {
+            p.is_gemm = true;
+            p.src_external = (o.src == B2P_SLOT_INPUT);
+            const int rows_cap = o.kind == B2P_OP_LINEAR ? h->chunk : h->chunk * o.out_h * o.out_w;
+            if (!gemm_plan_init(p.gemm, o, h->blobs[o.weight], h->blob_bytes[o.weight],
+                                static_cast<const float*>(h->blobs[o.bias]), rows_cap, h->num_sms, eb, sizeof eb))
+                B2P_FAIL(B2P_E_ARG, "op %d: %s", i, eb);
+            if (h->blob_bytes[o.bias] < static_cast<int64_t>(p.gemm.n_pad) * 4)
+                B2P_FAIL(B2P_E_ARG, "op %d: bias blob shorter than padded out_c", i);
+            if (!p.src_external) {
+                if (!h->slots[o.src]) B2P_FAIL(B2P_E_ARG, "op %d reads an empty slot", i);
+                if (!gemm_plan_set_src(p.gemm, h->slots[o.src], h->chunk, eb, sizeof eb))
+                    B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
+            }
+        } else if ((o.kind == B2P_OP_MAXPOOL || o.kind == B2P_OP_AVGPOOL) && o.in_c % 8 != 0) {
+            B2P_FAIL(B2P_E_ARG, "op %d: pooling needs channels %% 8 == 0", i);
+        }
+        if (o.kind == B2P_OP_LINEAR && o.dst == B2P_SLOT_OUTPUT) h->classes = o.out_c;
+    }
+    // predict-chain staging
+    const size_t nb = static_cast<size_t>(h->max_batch);
+    for (int r = 0; r < b2p_handle::RING; ++r) {
+        if (cudaMalloc(&h->imgs_dev[r], sizeof(b2p_image) * nb) != cudaSuccess ||
+            cudaMallocHost(&h->imgs_pinned[r], sizeof(b2p_image) * nb) != cudaSuccess ||
+            cudaEventCreateWithFlags(&h->imgs_done[r], cudaEventDisableTiming) != cudaSuccess)
+            B2P_FAIL(B2P_E_NOMEM, "descriptor staging allocation failed");
+    }
+    if (cudaMalloc(&h->x_dev, nb * 3 * B2P_OUT_HW * B2P_OUT_HW * 2) != cudaSuccess ||
+        cudaMalloc(&h->logits_dev, nb * static_cast<size_t>(h->out_elems > 0 ? h->out_elems : 1) * 4) != cudaSuccess ||
+        cudaMalloc(&h->probs_dev, nb * B2P_MAX_TOPK * 4) != cudaSuccess ||
+        cudaMalloc(&h->idx_dev, nb * B2P_MAX_TOPK * 4) != cudaSuccess)
+        B2P_FAIL(B2P_E_NOMEM, "staging allocation failed");
+    for (auto& e : h->ev)
+        if (cudaEventCreate(&e) != cudaSuccess) B2P_FAIL(B2P_E_CUDA, "cudaEventCreate failed");
+    h->ev_valid = true;
+    if (cudaDeviceSynchronize() != cudaSuccess) B2P_FAIL(B2P_E_CUDA, "device sync after create failed");
+#undef B2P_FAIL
+    *out = h;
+    return B2P_OK;
+}
+
+// Per-stage times of the last b2p_predict_host call are resolved here, after the caller has
+// synchronised the stream; events that have not completed yet leave the previous values in place.
+int32_t b2p_stats_get(b2p_handle* h, b2p_stats* out) {
+    if (!h || !out) return B2P_E_ARG;
+    if (h->ev_valid && h->stats.calls > 0) {
+        float ms[5];
+        bool ok = true;
+        for (int i = 0; i < 5 && ok; ++i) ok = cudaEventElapsedTime(&ms[i], h->ev[i], h->ev[i + 1]) == cudaSuccess;
+        if (ok) {
+            h->stats.ms_h2d = ms[0];
+            h->stats.ms_preprocess = ms[1];
+            h->stats.ms_forward = ms[2];
+            h->stats.ms_epilogue = ms[3];
+            h->stats.ms_d2h = ms[4];
+        } else {
+            cudaGetLastError();
+        }
+    }
+    *out = h->stats;
+    return B2P_OK;
+}
+
+int32_t b2p_preprocess(b2p_handle* h, const uint8_t* slab, const b2p_image* imgs, int32_t n, void* out,
+                       int32_t out_f32, void* stream) {
+    if (!h || !slab || !imgs || !out || n <= 0) return B2P_E_ARG;
+    if (n > h->max_batch) { set_error(h, "n=%d exceeds max_batch=%d", n, h->max_batch); return B2P_E_LIMIT; }
+    B2P_CUDA(h, cudaSetDevice(h->device));
+    int rc = check_images(h, imgs, n);
+    if (rc != B2P_OK) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    rc = stage_images(h, imgs, n, st);
+    if (rc != B2P_OK) return rc;
+    int launches = 0;
+    B2P_CUDA(h, launch_preprocess(slab, h->cur_imgs_dev, imgs, n, out, out_f32, st, &launches));
+    h->stats.kernel_launches += launches;
+    return B2P_OK;
+}
+
+int32_t b2p_forward(b2p_handle* h, const void* x, int32_t n, void* out, void* stream) {
+    if (!h || !x || !out || n <= 0) return B2P_E_ARG;
+    if (n > h->max_batch) { set_error(h, "n=%d exceeds max_batch=%d", n, h->max_batch); return B2P_E_LIMIT; }
+    B2P_CUDA(h, cudaSetDevice(h->device));
+    return run_program(h, x, n, out, static_cast<cudaStream_t>(stream));
+}
+
+int32_t b2p_softmax_topk(b2p_handle* h, const float* logits, int32_t n, int32_t classes, int32_t k,
+                         float* probs, int32_t* idx, void* stream) {
+    if (!h || !logits || !probs || !idx || n <= 0 || classes <= 0) return B2P_E_ARG;
+    if (k <= 0 || k > B2P_MAX_TOPK || k > classes) { set_error(h, "k=%d out of range", k); return B2P_E_LIMIT; }
+    B2P_CUDA(h, cudaSetDevice(h->device));
+    B2P_CUDA(h, launch_softmax_topk(logits, n, classes, k, probs, idx, static_cast<cudaStream_t>(stream)));
+    h->stats.kernel_launches += 1;
+    return B2P_OK;
+}
+
+int32_t b2p_predict(b2p_handle* h, const uint8_t* slab, const b2p_image* imgs, int32_t n, int32_t k,
+                    float* probs, int32_t* idx, void* stream) {
+    if (!h || h->classes <= 0) { if (h) set_error(h, "program has no classifier output"); return B2P_E_ARG; }
+    int rc = b2p_preprocess(h, slab, imgs, n, h->x_dev, 0, stream);
+    if (rc != B2P_OK) return rc;
+    rc = b2p_forward(h, h->x_dev, n, h->logits_dev, stream);
+    if (rc != B2P_OK) return rc;
+    return b2p_softmax_topk(h, h->logits_dev, n, h->classes, k, probs, idx, stream);
+}
+
+int32_t b2p_predict_host(b2p_handle* h, const uint8_t* slab_host, int64_t slab_bytes, const b2p_image* imgs,
+                         int32_t n, int32_t k, float* probs_host, int32_t* idx_host, void* stream) {
+    if (!h || !slab_host || slab_bytes <= 0 || !imgs || !probs_host || !idx_host || n <= 0) return B2P_E_ARG;
+    if (h->classes <= 0) { set_error(h, "program has no classifier output"); return B2P_E_ARG; }
+    if (n > h->max_batch) { set_error(h, "n=%d exceeds max_batch=%d", n, h->max_batch); return B2P_E_LIMIT; }
+    if (k <= 0 || k > B2P_MAX_TOPK) { set_error(h, "k=%d out of range", k); return B2P_E_LIMIT; }
+    B2P_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (slab_bytes > h->slab_cap) {
+        // grow-only device slab; first call (or a larger batch) pays for the allocation
+        B2P_CUDA(h, cudaStreamSynchronize(st));
+        if (h->slab_dev) cudaFree(h->slab_dev);
+        h->slab_dev = nullptr;
+        h->slab_cap = 0;
+        const int64_t cap = ((slab_bytes + (1 << 20) - 1) >> 20) << 20;
+        if (cudaMalloc(&h->slab_dev, static_cast<size_t>(cap)) != cudaSuccess) {
+            set_error(h, "cudaMalloc(%lld) for the image slab failed", (long long)cap);
+            return B2P_E_NOMEM;
+        }
+        h->slab_cap = cap;
+    }
+    B2P_CUDA(h, cudaEventRecord(h->ev[0], st));
+    B2P_CUDA(h, cudaMemcpyAsync(h->slab_dev, slab_host, static_cast<size_t>(slab_bytes), cudaMemcpyHostToDevice, st));
+    B2P_CUDA(h, cudaEventRecord(h->ev[1], st));
+    int rc = b2p_preprocess(h, h->slab_dev, imgs, n, h->x_dev, 0, stream);
+    if (rc != B2P_OK) return rc;
+    B2P_CUDA(h, cudaEventRecord(h->ev[2], st));
+    rc = b2p_forward(h, h->x_dev, n, h->logits_dev, stream);
+    if (rc != B2P_OK) return rc;
+    B2P_CUDA(h, cudaEventRecord(h->ev[3], st));
+    rc = b2p_softmax_topk(h, h->logits_dev, n, h->classes, k, h->probs_dev, h->idx_dev, stream);
+    if (rc != B2P_OK) return rc;
+    B2P_CUDA(h, cudaEventRecord(h->ev[4], st));
+    B2P_CUDA(h, cudaMemcpyAsync(probs_host, h->probs_dev, sizeof(float) * static_cast<size_t>(n) * k,
+                                cudaMemcpyDeviceToHost, st));
+    B2P_CUDA(h, cudaMemcpyAsync(idx_host, h->idx_dev, sizeof(int32_t) * static_cast<size_t>(n) * k,
+                                cudaMemcpyDeviceToHost, st));
+    B2P_CUDA(h, cudaEventRecord(h->ev[5], st));
+    h->stats.calls += 1;
+    return B2P_OK;
+}
+
+const float* b2p_last_logits(b2p_handle* h) { return h ? h->logits_dev : nullptr; }
+
+}  // extern "C"
+

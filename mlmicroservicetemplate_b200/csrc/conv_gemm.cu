@@ -1,0 +1,519 @@
+// K2 core: persistent, warp-specialised implicit-GEMM convolution / linear layer on the
+// 5th-generation tensor cores.
+//
+//   D[M, N] = A[M, K] * W[N, K]^T  (+ bias[N]) (+ residual[M, N]) (ReLU)
+//
+//   M = output pixels (n * out_h * out_w, NHWC order),  N = output channels,
+//   K = kh * kw * in_c (tap-major, channel fastest — the packed weight layout).
+//
+// A tiles come straight from the NHWC activation tensor: a 2-D tiled TMA box for 1x1/stride-1
+// convs and linear layers, TMA *im2col* mode for everything else (3x3, strided 1x1, the
+// space-to-depth stem), so no im2col matrix is ever materialised.  W tiles are 2-D tiled TMA.
+// Both land in shared memory in the K-major swizzled layout tcgen05.mma consumes; the
+// accumulator lives in TMEM (two stages, so the epilogue of tile i overlaps the MMAs of tile
+// i+1), and four epilogue warps drain it with tcgen05.ld, add the folded-BN bias and the residual,
+// apply ReLU and store bf16 NHWC (or fp32 logits).
+//
+// Warp roles (192 threads):  warp 0 = TMA producer (one elected lane), warp 1 = TMEM owner +
+// MMA issuer (one elected lane), warps 2..5 = epilogue (TMEM lane quadrant = warp_idx % 4).
+//
+// Oracle-side equivalent: nn.Conv2d + BatchNorm2d(eval) + ReLU as wired in
+// SP/torchvision/models/resnet.py:89-105,143-163 (BN folded on the host, see weights.py).
+#include <cstdio>
+#include <cstring>
+#include <cudaTypedefs.h>
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace b2p {
+
+namespace {
+
+constexpr int BLOCK_M = 128;
+constexpr int UMMA_K = 16;           // bf16: 32 bytes of K per tcgen05.mma
+constexpr int NUM_THREADS = 192;
+constexpr int ACC_STAGES = 2;
+constexpr int SMEM_BUDGET = 200 * 1024;
+
+struct GemmArgs {
+    int m_rows;       // valid output rows
+    int m_tiles;
+    int n_tiles;
+    int n_real;       // valid output columns
+    int taps_h, taps_w, k_chunks;
+    int out_h, out_w;
+    int stride, pad_lo;
+    int ldc;
+    int relu;
+    const float* bias;
+    const void* residual;
+    void* out;
+};
+
+template <int BLOCK_N, int BLOCK_K>
+struct Cfg {
+    static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
+    static constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int STAGES_RAW = SMEM_BUDGET / STAGE_BYTES;
+    static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+    static constexpr int SWIZZLE_BYTES = BLOCK_K * 2;          // 128 or 32
+    static constexpr int TMEM_COLS = ACC_STAGES * BLOCK_N;     // 128 / 256 / 512
+    static constexpr int BAR_BYTES = (2 * STAGES + 2 * ACC_STAGES) * 8 + 16;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // + alignment slack
+    static_assert(BLOCK_K == 64 || BLOCK_K == 16, "BLOCK_K must give a 128B or 32B swizzle row");
+    static_assert(TMEM_COLS == 128 || TMEM_COLS == 256 || TMEM_COLS == 512, "TMEM power of two");
+    static_assert(A_BYTES % 1024 == 0 && B_BYTES % 1024 == 0, "stage bases stay 1024B aligned");
+};
+
+template <int BLOCK_N, int BLOCK_K, bool IM2COL, bool OUT_F32>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
+                 const __grid_constant__ CUtensorMap tmap_b, const GemmArgs args) {
+    using C = Cfg<BLOCK_N, BLOCK_K>;
+    constexpr int STAGES = C::STAGES;
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                               ~static_cast<uintptr_t>(1023));
+    uint8_t* smem_a = smem;
+    uint8_t* smem_b = smem + STAGES * C::A_BYTES;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE_BYTES);
+    uint64_t* empty_bar = full_bar + STAGES;
+    uint64_t* tmem_full_bar = empty_bar + STAGES;
+    uint64_t* tmem_empty_bar = tmem_full_bar + ACC_STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + ACC_STAGES);
+
+    const int warp_idx = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+    const int total_tiles = args.m_tiles * args.n_tiles;
+    const int num_kb = args.taps_h * args.taps_w * args.k_chunks;
+
+    if (warp_idx == 0) {
+        if (elect_one()) {
+            tma_prefetch_desc(&tmap_a);
+            tma_prefetch_desc(&tmap_b);
+        }
+    } else if (warp_idx == 1) {
+        if (elect_one()) {
+            for (int i = 0; i < STAGES; ++i) {
+                mbar_init(&full_bar[i], 1);
+                mbar_init(&empty_bar[i], 1);
+            }
+            for (int i = 0; i < ACC_STAGES; ++i) {
+                mbar_init(&tmem_full_bar[i], 1);
+                mbar_init(&tmem_empty_bar[i], 4);   // one arrive per epilogue warp
+            }
+            fence_mbar_init();
+        }
+        __syncwarp();
+        tmem_alloc(tmem_slot, C::TMEM_COLS);
+        tmem_relinquish();
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp_idx == 0) {
+        // ===================================================================== TMA producer
+        if (elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            const int pq = args.out_h * args.out_w;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const int m_blk = tile / args.n_tiles;
+                const int n_blk = tile - m_blk * args.n_tiles;
+                const int m0 = m_blk * BLOCK_M;
+                int img = 0, base_w = 0, base_h = 0;
+                if (IM2COL) {
+                    img = m0 / pq;
+                    const int rem = m0 - img * pq;
+                    const int op = rem / args.out_w;
+                    const int oq = rem - op * args.out_w;
+                    base_w = oq * args.stride - args.pad_lo;
+                    base_h = op * args.stride - args.pad_lo;
+                }
+                int kcol = 0;
+                for (int r = 0; r < args.taps_h; ++r) {
+                    for (int s = 0; s < args.taps_w; ++s) {
+                        for (int cc = 0; cc < args.k_chunks; ++cc, kcol += BLOCK_K) {
+                            mbar_wait(&empty_bar[stage], phase ^ 1u);
+                            mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+                            if (IM2COL) {
+                                tma_load_im2col_4d(&tmap_a, &full_bar[stage],
+                                                   smem_a + stage * C::A_BYTES, cc * BLOCK_K,
+                                                   base_w, base_h, img, static_cast<uint16_t>(s),
+                                                   static_cast<uint16_t>(r));
+                            } else {
+                                tma_load_2d(&tmap_a, &full_bar[stage], smem_a + stage * C::A_BYTES,
+                                            kcol, m0);
+                            }
+                            tma_load_2d(&tmap_b, &full_bar[stage], smem_b + stage * C::B_BYTES, kcol,
+                                        n_blk * BLOCK_N);
+                            if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp_idx == 1) {
+        // ======================================================================= MMA issuer
+        if (elect_one()) {
+            constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BLOCK_N);
+            int stage = 0;
+            uint32_t phase = 0;
+            int acc = 0;
+            uint32_t acc_phase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u);
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BLOCK_N);
+                for (int kb = 0; kb < num_kb; ++kb) {
+                    mbar_wait(&full_bar[stage], phase);
+                    tc_fence_after();
+                    const uint64_t a_desc =
+                        umma_desc_kmajor(smem_u32(smem_a + stage * C::A_BYTES), C::SWIZZLE_BYTES);
+                    const uint64_t b_desc =
+                        umma_desc_kmajor(smem_u32(smem_b + stage * C::B_BYTES), C::SWIZZLE_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
+                        // advancing K inside a swizzle row: +32 bytes = +2 in the (addr >> 4) field
+                        umma_bf16(d_tmem, a_desc + static_cast<uint64_t>(k * 2),
+                                  b_desc + static_cast<uint64_t>(k * 2), idesc,
+                                  static_cast<uint32_t>((kb | k) != 0));
+                    }
+                    umma_commit(&empty_bar[stage]);     // smem slot is free once these MMAs retire
+                    if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+                }
+                umma_commit(&tmem_full_bar[acc]);       // accumulator complete -> epilogue
+                if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1u; }
+            }
+        }
+    } else {
+        // ========================================================================= epilogue
+        const int quad = warp_idx & 3;                  // TMEM lanes [32*quad, 32*quad+32)
+        const int lane = static_cast<int>(lane_id());
+        int acc = 0;
+        uint32_t acc_phase = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            const int m_blk = tile / args.n_tiles;
+            const int n_blk = tile - m_blk * args.n_tiles;
+            const int row = m_blk * BLOCK_M + quad * 32 + lane;
+            const bool row_ok = row < args.m_rows;
+            mbar_wait(&tmem_full_bar[acc], acc_phase);
+            tc_fence_after();
+            const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) +
+                                    static_cast<uint32_t>(acc * BLOCK_N);
+#pragma unroll 1
+            for (int chunk = 0; chunk < BLOCK_N / 32; ++chunk) {
+                uint32_t v[32];
+                tmem_ld_32x32(t_addr + static_cast<uint32_t>(chunk * 32), v);
+                tmem_ld_wait();
+                const int col0 = n_blk * BLOCK_N + chunk * 32;
+                const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
+                float f[32];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float4 b = __ldg(b4 + j);
+                    f[4 * j + 0] = __uint_as_float(v[4 * j + 0]) + b.x;
+                    f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + b.y;
+                    f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + b.z;
+                    f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + b.w;
+                }
+                if (OUT_F32) {
+                    if (row_ok) {
+                        float* o = reinterpret_cast<float*>(args.out) +
+                                   static_cast<size_t>(row) * args.ldc + col0;
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            if (col0 + 4 * j + 3 < args.n_real) {
+                                float4 o4 = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+                                if (args.relu) {
+                                    o4.x = fmaxf(o4.x, 0.f); o4.y = fmaxf(o4.y, 0.f);
+                                    o4.z = fmaxf(o4.z, 0.f); o4.w = fmaxf(o4.w, 0.f);
+                                }
+                                *reinterpret_cast<float4*>(o + 4 * j) = o4;
+                            } else {
+                                for (int e = 0; e < 4; ++e) {
+                                    if (col0 + 4 * j + e < args.n_real) {
+                                        const float x = f[4 * j + e];
+                                        o[4 * j + e] = args.relu ? fmaxf(x, 0.f) : x;
+                                    }
+                                }
+                            }
+                        }
+                    }
+                } else {
+                    if (row_ok && col0 < args.n_real) {
+                        const size_t off = static_cast<size_t>(row) * args.ldc + col0;
+                        if (args.residual != nullptr) {
+                            const uint4* r4 = reinterpret_cast<const uint4*>(
+                                reinterpret_cast<const uint16_t*>(args.residual) + off);
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const uint4 r = ld_nc_v4(r4 + j);
+                                f[8 * j + 0] += bf16_lo(r.x); f[8 * j + 1] += bf16_hi(r.x);
+                                f[8 * j + 2] += bf16_lo(r.y); f[8 * j + 3] += bf16_hi(r.y);
+                                f[8 * j + 4] += bf16_lo(r.z); f[8 * j + 5] += bf16_hi(r.z);
+                                f[8 * j + 6] += bf16_lo(r.w); f[8 * j + 7] += bf16_hi(r.w);
+                            }
+                        }
+                        if (args.relu) {
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+                        }
+                        uint4* o4 = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(args.out) + off);
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            uint4 o;
+                            o.x = pack_bf16x2(f[8 * j + 0], f[8 * j + 1]);
+                            o.y = pack_bf16x2(f[8 * j + 2], f[8 * j + 3]);
+                            o.z = pack_bf16x2(f[8 * j + 4], f[8 * j + 5]);
+                            o.w = pack_bf16x2(f[8 * j + 6], f[8 * j + 7]);
+                            st_v4(o4 + j, o);
+                        }
+                    }
+                }
+            }
+            // all of this warp's TMEM reads for the stage are complete: hand it back to the MMA warp
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+            if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1u; }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp_idx == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, C::TMEM_COLS);
+    }
+}
+
+// --------------------------------------------------------------------------- host side
+
+PFN_cuTensorMapEncodeTiled_v12000 g_encode_tiled = nullptr;
+PFN_cuTensorMapEncodeIm2col_v12000 g_encode_im2col = nullptr;
+
+void set_err(char* err, size_t n, const char* msg) {
+    if (err && n) snprintf(err, n, "%s", msg);
+}
+
+template <int BLOCK_N, int BLOCK_K, bool IM2COL, bool OUT_F32>
+cudaError_t launch_variant(const GemmPlan& p, const GemmArgs& a, int grid, cudaStream_t stream) {
+    using C = Cfg<BLOCK_N, BLOCK_K>;
+    auto kern = conv_gemm_kernel<BLOCK_N, BLOCK_K, IM2COL, OUT_F32>;
+    static bool attr_set[64] = {};   // per instantiation, per device (one replica thread per device)
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (!attr_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                             C::SMEM_BYTES);
+        if (e != cudaSuccess) return e;
+        attr_set[dev] = true;
+    }
+    kern<<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(p.tmap_a, p.tmap_b, a);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+bool tma_init(char* err, size_t err_len) {
+    if (g_encode_tiled && g_encode_im2col) return true;
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess || fn == nullptr) {
+        set_err(err, err_len, "cuTensorMapEncodeTiled not available from the driver");
+        return false;
+    }
+    g_encode_tiled = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+    fn = nullptr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &fn, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess || fn == nullptr) {
+        set_err(err, err_len, "cuTensorMapEncodeIm2col not available from the driver");
+        return false;
+    }
+    g_encode_im2col = reinterpret_cast<PFN_cuTensorMapEncodeIm2col_v12000>(fn);
+    return true;
+}
+
+static bool encode_tiled_2d(CUtensorMap* m, const void* base, uint64_t inner, uint64_t rows,
+                            uint32_t box_inner, uint32_t box_rows, CUtensorMapSwizzle sw, char* err,
+                            size_t err_len) {
+    cuuint64_t dims[2] = {inner, rows};
+    cuuint64_t strides[1] = {inner * 2};
+    cuuint32_t box[2] = {box_inner, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims,
+                                strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                                CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char b[160];
+        snprintf(b, sizeof b, "cuTensorMapEncodeTiled failed (%d) inner=%llu rows=%llu box=%ux%u",
+                 static_cast<int>(r), (unsigned long long)inner, (unsigned long long)rows, box_inner,
+                 box_rows);
+        set_err(err, err_len, b);
+        return false;
+    }
+    return true;
+}
+
+bool gemm_plan_init(GemmPlan& p, const b2p_op& op, const void* weight_dev, int64_t weight_bytes,
+                    const float* bias_dev, int rows_at_capacity, int num_sms, char* err,
+                    size_t err_len) {
+    const bool linear = op.kind == B2P_OP_LINEAR;
+    p.in_h = linear ? 1 : op.in_h;
+    p.in_w = linear ? 1 : op.in_w;
+    p.in_c = op.in_c;
+    p.out_h = linear ? 1 : op.out_h;
+    p.out_w = linear ? 1 : op.out_w;
+    p.taps_h = linear ? 1 : op.kh;
+    p.taps_w = linear ? 1 : op.kw;
+    p.stride = linear ? 1 : op.stride;
+    p.pad_lo = linear ? 0 : op.pad_lo;
+    p.pad_hi = linear ? 0 : op.pad_hi;
+    p.relu = op.relu;
+    p.out_f32 = linear ? 1 : 0;
+    p.n_real = op.out_c;
+    p.ldc = op.out_c;
+    p.bias = bias_dev;
+    p.weight = weight_dev;
+    if (op.in_c % 64 == 0) {
+        p.block_k = 64;
+    } else if (op.in_c == 16) {
+        p.block_k = 16;
+    } else {
+        set_err(err, err_len, "conv/linear in_c must be a multiple of 64 (or exactly 16 for the stem)");
+        return false;
+    }
+    p.k_chunks = op.in_c / p.block_k;
+    p.im2col = !(p.taps_h == 1 && p.taps_w == 1 && p.stride == 1 && p.pad_lo == 0 && p.pad_hi == 0);
+    const int64_t k_total = static_cast<int64_t>(p.taps_h) * p.taps_w * op.in_c;
+    if (weight_bytes % (k_total * 2) != 0) {
+        set_err(err, err_len, "weight blob size is not a whole number of K-rows");
+        return false;
+    }
+    p.n_pad = static_cast<int>(weight_bytes / (k_total * 2));
+    if (p.n_pad < op.out_c || p.n_pad % 64 != 0) {
+        set_err(err, err_len, "weight rows must be >= out_c and padded to a multiple of 64");
+        return false;
+    }
+    if (!p.out_f32 && op.out_c % 64 != 0) {
+        set_err(err, err_len, "conv out_c must be a multiple of 64");
+        return false;
+    }
+    // Tile width: fewest (waves x tile width) at capacity; ties go to the wider tile, which
+    // re-reads the activation tile fewer times.
+    const int m_tiles = (rows_at_capacity + BLOCK_M - 1) / BLOCK_M;
+    int best = 0;
+    long best_cost = 0;
+    const int cands[3] = {256, 128, 64};
+    for (int bn : cands) {
+        if (p.n_pad % bn != 0) continue;
+        if (p.block_k == 16 && bn != 64) continue;
+        if (p.out_f32 && bn != 128) continue;
+        const long tiles = static_cast<long>(m_tiles) * (p.n_pad / bn);
+        const long waves = (tiles + num_sms - 1) / num_sms;
+        const long cost = waves * (bn + 32);     // +32: fixed per-tile overhead in "column" units
+        if (best == 0 || cost < best_cost) { best = bn; best_cost = cost; }
+    }
+    if (best == 0) {
+        set_err(err, err_len, "no tile width fits this layer");
+        return false;
+    }
+    p.block_n = best;
+    const CUtensorMapSwizzle sw = p.block_k == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_32B;
+    return encode_tiled_2d(&p.tmap_b, weight_dev, static_cast<uint64_t>(k_total),
+                           static_cast<uint64_t>(p.n_pad), static_cast<uint32_t>(p.block_k),
+                           static_cast<uint32_t>(p.block_n), sw, err, err_len);
+}
+
+bool gemm_plan_set_src(GemmPlan& p, const void* src, int batch_cap, char* err, size_t err_len) {
+    const CUtensorMapSwizzle sw = p.block_k == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_32B;
+    if (!p.im2col) {
+        const uint64_t rows = static_cast<uint64_t>(batch_cap) * p.in_h * p.in_w;
+        return encode_tiled_2d(&p.tmap_a, src, static_cast<uint64_t>(p.in_c), rows,
+                               static_cast<uint32_t>(p.block_k), BLOCK_M, sw, err, err_len);
+    }
+    // NHWC seen by TMA as {C, W, H, N}.  The corners bound where the *base* pixel of a filter
+    // window may sit: lower = -pad_lo, upper = pad_hi - (filter - 1).
+    cuuint64_t dims[4] = {static_cast<cuuint64_t>(p.in_c), static_cast<cuuint64_t>(p.in_w),
+                          static_cast<cuuint64_t>(p.in_h), static_cast<cuuint64_t>(batch_cap)};
+    cuuint64_t strides[3] = {static_cast<cuuint64_t>(p.in_c) * 2,
+                             static_cast<cuuint64_t>(p.in_c) * 2 * p.in_w,
+                             static_cast<cuuint64_t>(p.in_c) * 2 * p.in_w * p.in_h};
+    int lower[2] = {-p.pad_lo, -p.pad_lo};
+    int upper[2] = {p.pad_hi - (p.taps_w - 1), p.pad_hi - (p.taps_h - 1)};
+    cuuint32_t estr[4] = {1, static_cast<cuuint32_t>(p.stride), static_cast<cuuint32_t>(p.stride), 1};
+    CUresult r = g_encode_im2col(&p.tmap_a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(src),
+                                 dims, strides, lower, upper, static_cast<cuuint32_t>(p.block_k),
+                                 BLOCK_M, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                                 CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        char b[200];
+        snprintf(b, sizeof b,
+                 "cuTensorMapEncodeIm2col failed (%d) c=%d w=%d h=%d n=%d k=%dx%d stride=%d pad=%d/%d",
+                 static_cast<int>(r), p.in_c, p.in_w, p.in_h, batch_cap, p.taps_h, p.taps_w, p.stride,
+                 p.pad_lo, p.pad_hi);
+        set_err(err, err_len, b);
+        return false;
+    }
+    // Small-tensor erratum handled the same way CUTLASS does for drivers <= 13.1: clear bit 21 of
+    // the descriptor's second word when the tensor is under 128 KiB.
+    int drv = 0;
+    cudaDriverGetVersion(&drv);
+    const uint64_t bytes = static_cast<uint64_t>(batch_cap) * p.in_h * p.in_w * p.in_c * 2;
+    if (drv <= 13010 && bytes < 131072) {
+        reinterpret_cast<uint64_t*>(&p.tmap_a)[1] &= ~(1ull << 21);
+    }
+    return true;
+}
+
+cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, const void* residual, void* out,
+                             int num_sms, cudaStream_t stream) {
+    GemmArgs a;
+    a.m_rows = m_rows;
+    a.m_tiles = (m_rows + BLOCK_M - 1) / BLOCK_M;
+    a.n_tiles = p.n_pad / p.block_n;
+    a.n_real = p.n_real;
+    a.taps_h = p.taps_h;
+    a.taps_w = p.taps_w;
+    a.k_chunks = p.k_chunks;
+    a.out_h = p.out_h;
+    a.out_w = p.out_w;
+    a.stride = p.stride;
+    a.pad_lo = p.pad_lo;
+    a.ldc = p.ldc;
+    a.relu = p.relu;
+    a.bias = p.bias;
+    a.residual = residual;
+    a.out = out;
+    const int total = a.m_tiles * a.n_tiles;
+    if (total <= 0) return cudaSuccess;
+    const int grid = total < num_sms ? total : num_sms;
+#define B2P_LAUNCH(BN, BK, IM, F32) return launch_variant<BN, BK, IM, F32>(p, a, grid, stream)
+    if (p.block_k == 16) {
+        if (p.block_n == 64 && p.im2col && !p.out_f32) B2P_LAUNCH(64, 16, true, false);
+        return cudaErrorInvalidConfiguration;
+    }
+    if (p.out_f32) {
+        if (p.block_n == 128 && !p.im2col) B2P_LAUNCH(128, 64, false, true);
+        return cudaErrorInvalidConfiguration;
+    }
+    if (p.im2col) {
+        if (p.block_n == 64) B2P_LAUNCH(64, 64, true, false);
+        if (p.block_n == 128) B2P_LAUNCH(128, 64, true, false);
+        if (p.block_n == 256) B2P_LAUNCH(256, 64, true, false);
+    } else {
+        if (p.block_n == 64) B2P_LAUNCH(64, 64, false, false);
+        if (p.block_n == 128) B2P_LAUNCH(128, 64, false, false);
+        if (p.block_n == 256) B2P_LAUNCH(256, 64, false, false);
+    }
+#undef B2P_LAUNCH
+    return cudaErrorInvalidConfiguration;
+}
+
+}  // namespace b2p

@@ -1,0 +1,65 @@
+// Internal C++ interface between the C-ABI layer (api.cu) and the kernel files.
+#pragma once
+#include <cstdint>
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include "../../include/b200predict.h"
+
+namespace b2p {
+
+// ------------------------------------------------------------------ conv / GEMM (tcgen05)
+struct GemmPlan {
+    CUtensorMap tmap_a;   // activations: 2-D tiled [rows, K] or 4-D im2col over NHWC
+    CUtensorMap tmap_b;   // weights [out_c_pad, K] bf16, K-major
+    int block_n = 0;      // 64 / 128 / 256
+    int block_k = 64;     // 64 (128-byte swizzle) or 16 (32-byte swizzle, the stem)
+    int im2col = 0;       // A operand through TMA im2col mode
+    int out_f32 = 0;      // fp32 [M, ldc] output (LINEAR) instead of bf16 NHWC
+    int taps_h = 1, taps_w = 1, k_chunks = 1;
+    int in_h = 0, in_w = 0, in_c = 0;
+    int out_h = 0, out_w = 0;
+    int stride = 1, pad_lo = 0, pad_hi = 0;
+    int n_real = 0;       // real output channels (columns >= n_real are not stored)
+    int n_pad = 0;        // weight rows (multiple of block_n)
+    int ldc = 0;          // output row pitch in elements
+    int relu = 0;
+    const float* bias = nullptr;
+    const void* weight = nullptr;
+};
+
+// Resolves the driver's tensor-map encoders once per process. Returns false if unavailable.
+bool tma_init(char* err, size_t err_len);
+
+// Fills everything except tmap_a (which depends on the source pointer).
+bool gemm_plan_init(GemmPlan& p, const b2p_op& op, const void* weight_dev, int64_t weight_bytes,
+                    const float* bias_dev, int rows_at_capacity, int num_sms, char* err,
+                    size_t err_len);
+// (Re)encodes the A-operand tensor map for a source buffer holding `batch_cap` images.
+bool gemm_plan_set_src(GemmPlan& p, const void* src, int batch_cap, char* err, size_t err_len);
+// Launches the persistent kernel for `m_rows` output rows.
+cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, const void* residual, void* out,
+                             int num_sms, cudaStream_t stream);
+
+// ------------------------------------------------------------------ small memory-bound kernels
+cudaError_t launch_stem_pack(const void* x_nchw, void* out_nhwc16, int n, int h, int w,
+                             cudaStream_t s);
+cudaError_t launch_nchw_to_nhwc(const void* x, void* out, int n, int c, int h, int w,
+                                cudaStream_t s);
+cudaError_t launch_maxpool(const void* x, void* out, int n, int in_h, int in_w, int c, int out_h,
+                           int out_w, int k, int stride, int pad, cudaStream_t s);
+cudaError_t launch_avgpool(const void* x, void* out, int n, int hw, int c, cudaStream_t s);
+cudaError_t launch_softmax_topk(const float* logits, int n, int classes, int k, float* probs,
+                                int32_t* idx, cudaStream_t s);
+
+// ------------------------------------------------------------------ K1 preprocess
+struct PreprocessLaunch {
+    int max_taps_h = 0;   // largest horizontal tap count over the batch
+    int max_row_bytes = 0;
+    int all_identity = 0;
+};
+// `imgs_dev` is the device copy of the descriptors; `imgs_host` is used to size the launch.
+cudaError_t launch_preprocess(const uint8_t* slab, const b2p_image* imgs_dev,
+                              const b2p_image* imgs_host, int n, void* out, int out_f32,
+                              cudaStream_t s, int* launches);
+
+}  // namespace b2p

@@ -1,0 +1,242 @@
+"""Turns a torchvision classifier into the flat layer program + packed weight blobs that
+libb200predict.so executes (include/b200predict.h, `b2p_op` / `b2p_model_desc`).
+
+What init() (reference src/model/model.py:6-13) has to prepare per replica happens here on the host:
+  * eval-mode BatchNorm is folded into the preceding conv in fp32
+    (w' = w * gamma / sqrt(var + eps), b' = beta - mean * gamma / sqrt(var + eps);
+    SP/torchvision/models/resnet.py:89-105, 143-163 for where the BNs sit),
+  * conv weights are re-laid as [out_c][kh][kw][in_c] bf16 (K-major rows for tcgen05),
+  * the 7x7/s2 stem is rewritten as a 4x4/s1 conv over a 2x2 space-to-depth input with 16-channel
+    pixels so that TMA im2col can feed it,
+  * activation slots are assigned by liveness so the workspace stays small.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import List, Optional
+
+import torch
+
+from . import backend as B
+
+
+@dataclass
+class Program:
+    ops: List[B.Op] = field(default_factory=list)
+    slot_elems: List[int] = field(default_factory=lambda: [0])   # slot 0 = external input
+    blobs: List[torch.Tensor] = field(default_factory=list)     # CPU tensors, kept alive for b2p_create
+    in_elems: int = 0
+    out_elems: int = 0
+    flops_per_image: float = 0.0          # conv/linear 2*MACs only (SURVEY §8d accounting)
+    name: str = ""
+
+    # ---- slot allocator (greedy, by liveness)
+    _free: List[int] = field(default_factory=list)
+
+    def alloc(self, elems: int) -> int:
+        best = None
+        for s in self._free:
+            if self.slot_elems[s] >= elems and (best is None or self.slot_elems[s] < self.slot_elems[best]):
+                best = s
+        if best is None and self._free:
+            best = max(self._free, key=lambda s: self.slot_elems[s])
+            self.slot_elems[best] = elems
+        if best is not None:
+            self._free.remove(best)
+            return best
+        self.slot_elems.append(elems)
+        return len(self.slot_elems) - 1
+
+    def release(self, slot: int) -> None:
+        if slot > 0 and slot not in self._free:
+            self._free.append(slot)
+
+    def add_blob(self, t: torch.Tensor) -> int:
+        self.blobs.append(t.contiguous())
+        return len(self.blobs) - 1
+
+
+def _bf16(t: torch.Tensor) -> torch.Tensor:
+    return t.to(torch.bfloat16).contiguous()
+
+
+def fold_bn(conv_w: torch.Tensor, bn: Optional[torch.nn.BatchNorm2d], conv_b: Optional[torch.Tensor] = None):
+    """Returns (w', b') in fp32 with eval-mode BN folded into the conv."""
+    w = conv_w.detach().float()
+    b = conv_b.detach().float() if conv_b is not None else torch.zeros(w.shape[0])
+    if bn is None:
+        return w, b
+    inv = bn.weight.detach().float() / torch.sqrt(bn.running_var.detach().float() + bn.eps)
+    return w * inv.view(-1, 1, 1, 1), (b - bn.running_mean.detach().float()) * inv + bn.bias.detach().float()
+
+
+def pack_conv_weight(w: torch.Tensor, pad_rows_to: int = 64) -> torch.Tensor:
+    """[out_c, in_c, kh, kw] fp32 -> [out_c_pad, kh, kw, in_c] bf16."""
+    oc = w.shape[0]
+    ocp = (oc + pad_rows_to - 1) // pad_rows_to * pad_rows_to
+    p = w.permute(0, 2, 3, 1).contiguous()
+    if ocp != oc:
+        p = torch.cat([p, torch.zeros(ocp - oc, *p.shape[1:])], 0)
+    return _bf16(p)
+
+
+def pad_bias(b: torch.Tensor, rows: int) -> torch.Tensor:
+    out = torch.zeros(rows, dtype=torch.float32)
+    out[: b.numel()] = b.float()
+    return out
+
+
+def stem_s2d_weight(w: torch.Tensor) -> torch.Tensor:
+    """7x7/s2/p3 weight [oc,3,7,7] -> 4x4/s1 (pad 2 before, 1 after) weight [oc,4,4,16] over the 2x2
+    space-to-depth input whose channel order is (di*2+dj)*3 + c.  Tap (a,b), sub-pixel (di,dj) maps
+    to original tap (2a+di-1, 2b+dj-1); taps that fall outside the 7x7 window are zero."""
+    oc = w.shape[0]
+    out = torch.zeros(oc, 4, 4, 16, dtype=torch.float32)
+    for a in range(4):
+        for di in range(2):
+            r = 2 * a + di - 1
+            if not 0 <= r < 7:
+                continue
+            for b in range(4):
+                for dj in range(2):
+                    s = 2 * b + dj - 1
+                    if not 0 <= s < 7:
+                        continue
+                    for c in range(3):
+                        out[:, a, b, (di * 2 + dj) * 3 + c] = w[:, c, r, s]
+    return out
+
+
+def _mk_op(kind, src, dst, res=B.SLOT_NONE, in_hwc=(0, 0, 0), out_hwc=(0, 0, 0), k=(1, 1), stride=1, pad=(0, 0),
+           relu=0, weight=-1, bias=-1) -> B.Op:
+    return B.Op(kind, src, dst, res, in_hwc[0], in_hwc[1], in_hwc[2], out_hwc[0], out_hwc[1], out_hwc[2],
+                k[0], k[1], stride, pad[0], pad[1], relu, weight, bias, (B.C.c_int32 * 4)(0, 0, 0, 0))
+
+
+class _Builder:
+    def __init__(self, name: str):
+        self.p = Program(name=name)
+
+    def conv(self, src, hwc, w, b, stride, pad, relu, res=B.SLOT_NONE, dst=None, pad_hi=None):
+        """w: fp32 [oc, ic, kh, kw] (BN already folded); returns (dst_slot, out_hwc)."""
+        h, wd, c = hwc
+        oc, ic, kh, kw = w.shape
+        assert ic == c, (ic, c)
+        pad_hi = pad if pad_hi is None else pad_hi
+        oh = (h + pad + pad_hi - kh) // stride + 1
+        ow = (wd + pad + pad_hi - kw) // stride + 1
+        wi = self.p.add_blob(pack_conv_weight(w))
+        bi = self.p.add_blob(pad_bias(b, self.p.blobs[wi].shape[0]))
+        if dst is None:
+            dst = self.p.alloc(oh * ow * oc)
+        self.p.ops.append(_mk_op(B.OP_CONV, src, dst, res, (h, wd, c), (oh, ow, oc), (kh, kw), stride,
+                                 (pad, pad_hi), int(relu), wi, bi))
+        self.p.flops_per_image += 2.0 * oh * ow * oc * ic * kh * kw
+        return dst, (oh, ow, oc)
+
+
+def build_resnet_program(model: torch.nn.Module, name: str = "resnet") -> Program:
+    """Walks a torchvision ResNet (SP/torchvision/models/resnet.py:266-282: conv1-bn1-relu-maxpool,
+    layer1..4, avgpool, fc) and emits the program.  Works for BasicBlock and Bottleneck nets."""
+    from torchvision.models.resnet import BasicBlock, Bottleneck
+
+    model = model.eval()
+    bld = _Builder(name)
+    p = bld.p
+    p.in_elems = 3 * 224 * 224
+
+    # stem: NCHW -> s2d NHWC16 -> 4x4 conv (== 7x7/s2/p3) + folded bn1 + relu
+    s2d = p.alloc(112 * 112 * 16)
+    p.ops.append(_mk_op(B.OP_STEM_PACK, B.SLOT_INPUT, s2d, in_hwc=(224, 224, 3), out_hwc=(112, 112, 16)))
+    w, b = fold_bn(model.conv1.weight, model.bn1)
+    ws = stem_s2d_weight(w).permute(0, 3, 1, 2).contiguous()          # back to [oc, ic=16, 4, 4]
+    c1, hwc = bld.conv(s2d, (112, 112, 16), ws, b, stride=1, pad=2, pad_hi=1, relu=True)
+    # the stem's FLOPs are accounted on the original 7x7x3 window, not the zero-padded s2d one
+    p.flops_per_image += 2.0 * 112 * 112 * 64 * (147 - 256)
+    p.release(s2d)
+    # maxpool 3x3/s2/p1
+    mp = p.alloc(56 * 56 * 64)
+    p.ops.append(_mk_op(B.OP_MAXPOOL, c1, mp, in_hwc=hwc, out_hwc=(56, 56, 64), k=(3, 3), stride=2, pad=(1, 1)))
+    p.release(c1)
+    x, hwc = mp, (56, 56, 64)
+
+    for layer in (model.layer1, model.layer2, model.layer3, model.layer4):
+        for blk in layer:
+            if isinstance(blk, Bottleneck):
+                w1, b1 = fold_bn(blk.conv1.weight, blk.bn1)
+                w2, b2 = fold_bn(blk.conv2.weight, blk.bn2)
+                w3, b3 = fold_bn(blk.conv3.weight, blk.bn3)
+                t1, hwc1 = bld.conv(x, hwc, w1, b1, 1, 0, True)
+                t2, hwc2 = bld.conv(t1, hwc1, w2, b2, blk.conv2.stride[0], 1, True)
+                p.release(t1)
+                if blk.downsample is not None:
+                    wd, bd = fold_bn(blk.downsample[0].weight, blk.downsample[1])
+                    idn, _ = bld.conv(x, hwc, wd, bd, blk.downsample[0].stride[0], 0, False)
+                    p.release(x)
+                else:
+                    idn = x
+                out, hwc3 = bld.conv(t2, hwc2, w3, b3, 1, 0, True, res=idn)
+                p.release(t2)
+                p.release(idn)
+                x, hwc = out, hwc3
+            elif isinstance(blk, BasicBlock):
+                w1, b1 = fold_bn(blk.conv1.weight, blk.bn1)
+                w2, b2 = fold_bn(blk.conv2.weight, blk.bn2)
+                t1, hwc1 = bld.conv(x, hwc, w1, b1, blk.conv1.stride[0], 1, True)
+                if blk.downsample is not None:
+                    wd, bd = fold_bn(blk.downsample[0].weight, blk.downsample[1])
+                    idn, _ = bld.conv(x, hwc, wd, bd, blk.downsample[0].stride[0], 0, False)
+                    p.release(x)
+                else:
+                    idn = x
+                out, hwc2 = bld.conv(t1, hwc1, w2, b2, 1, 1, True, res=idn)
+                p.release(t1)
+                p.release(idn)
+                x, hwc = out, hwc2
+            else:
+                raise TypeError(f"unsupported block {type(blk)}")
+
+    feat = p.alloc(hwc[2])
+    p.ops.append(_mk_op(B.OP_AVGPOOL, x, feat, in_hwc=hwc, out_hwc=(1, 1, hwc[2])))
+    p.release(x)
+    fc_w = model.fc.weight.detach().float()                            # [classes, in]
+    classes, fin = fc_w.shape
+    rows = (classes + 127) // 128 * 128
+    wp = torch.zeros(rows, fin)
+    wp[:classes] = fc_w
+    wi = p.add_blob(_bf16(wp))
+    bi = p.add_blob(pad_bias(model.fc.bias.detach(), rows))
+    p.ops.append(_mk_op(B.OP_LINEAR, feat, B.SLOT_OUTPUT, in_hwc=(1, 1, fin), out_hwc=(1, 1, classes),
+                        weight=wi, bias=bi))
+    p.flops_per_image += 2.0 * classes * fin
+    p.out_elems = classes
+    return p
+
+
+def single_conv_program(w: torch.Tensor, b: torch.Tensor, hwc, stride: int, pad: int, relu: bool,
+                        with_residual: bool = False, pad_hi: Optional[int] = None) -> Program:
+    """One CONV op from the external NHWC input to the external bf16 NHWC output; with_residual adds
+    the input itself as the residual (needs matching shapes).  Used by the layer-parity tests."""
+    bld = _Builder("single_conv")
+    p = bld.p
+    h, wd, c = hwc
+    p.in_elems = h * wd * c
+    _, ohwc = bld.conv(B.SLOT_INPUT, hwc, w.float(), b.float(), stride, pad, relu,
+                       res=B.SLOT_INPUT if with_residual else B.SLOT_NONE, dst=B.SLOT_OUTPUT, pad_hi=pad_hi)
+    p.out_elems = ohwc[0] * ohwc[1] * ohwc[2]
+    return p
+
+
+def single_linear_program(w: torch.Tensor, b: torch.Tensor) -> Program:
+    p = Program(name="single_linear")
+    classes, fin = w.shape
+    rows = (classes + 127) // 128 * 128
+    wp = torch.zeros(rows, fin)
+    wp[:classes] = w.float()
+    wi = p.add_blob(_bf16(wp))
+    bi = p.add_blob(pad_bias(b, rows))
+    p.in_elems = fin
+    p.out_elems = classes
+    p.ops.append(_mk_op(B.OP_LINEAR, B.SLOT_INPUT, B.SLOT_OUTPUT, in_hwc=(1, 1, fin), out_hwc=(1, 1, classes),
+                        weight=wi, bias=bi))
+    return p

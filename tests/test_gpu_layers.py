@@ -1,0 +1,167 @@
+"""Layer parity on the GPU: every op kind of the layer program, called through the C ABI
+(b2p_create / b2p_forward), against a plain torch fp32 CPU reference of the same op fed the
+same bf16-rounded inputs and weights.  Shapes are the ResNet-18/50 shapes of SURVEY §8(d)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _bf16r(t):
+    return t.to(torch.bfloat16).float()
+
+
+def _run_conv(n, hwc, oc, k, stride, pad, relu, residual, seed, pad_hi=None, sub_batch=0):
+    from mlmicroservicetemplate_b200 import backend as B, program as P
+    g = torch.Generator().manual_seed(seed)
+    h, w, c = hwc
+    x = _bf16r(torch.randn(n, h, w, c, generator=g))
+    wt = _bf16r(torch.randn(oc, c, k, k, generator=g) / (c * k * k) ** 0.5)
+    bias = torch.randn(oc, generator=g) * 0.1
+    prog = P.single_conv_program(wt, bias, hwc, stride, pad, relu, with_residual=residual, pad_hi=pad_hi)
+    rep = B.Replica(0, prog, max_batch=n, sub_batch=sub_batch)
+    xd = x.to(torch.bfloat16).cuda()
+    ph = pad if pad_hi is None else pad_hi
+    oh = (h + pad + ph - k) // stride + 1
+    ow = (w + pad + ph - k) // stride + 1
+    out = torch.empty(n, oh, ow, oc, dtype=torch.bfloat16, device="cuda")
+    rep.forward(xd, n, out)
+    torch.cuda.synchronize()
+    xin = F.pad(x.permute(0, 3, 1, 2), (pad, ph, pad, ph))
+    ref = F.conv2d(xin, wt, bias, stride=stride)
+    if residual:
+        ref = ref + x.permute(0, 3, 1, 2)
+    if relu:
+        ref = ref.relu()
+    ref = ref.permute(0, 2, 3, 1)
+    got = out.float().cpu()
+    rep.close()
+    err = (got - ref).abs()
+    tol = 2.0 ** -7 * ref.abs() + 2e-2      # one bf16 ulp of the result + accumulation-order slack
+    bad = (err > tol).sum().item()
+    print(f"conv n={n} hwc={hwc} oc={oc} k={k} s={stride} p={pad}: max_err={err.max().item():.4g} "
+          f"max_ref={ref.abs().max().item():.4g} bad={bad}/{err.numel()}")
+    assert bad == 0, f"{bad} elements off; worst {err.max().item()}"
+
+
+CONV_CASES = [
+    # n, (h, w, c), oc, k, stride, pad, relu, residual
+    (2, (56, 56, 64), 64, 1, 1, 0, True, False),          # 1x1 tiled, BLOCK_N 64
+    (2, (56, 56, 64), 256, 1, 1, 0, False, False),        # 1x1 expand
+    (2, (56, 56, 256), 256, 1, 1, 0, True, True),         # residual + relu
+    (3, (28, 28, 512), 128, 1, 1, 0, True, False),        # K = 512 (8 k-blocks, ring wraps)
+    (2, (56, 56, 64), 64, 3, 1, 1, True, False),          # 3x3 im2col
+    (2, (56, 56, 128), 128, 3, 2, 1, True, False),        # 3x3 stride 2
+    (2, (56, 56, 256), 512, 1, 2, 0, False, False),       # 1x1 stride 2 downsample
+    (5, (7, 7, 512), 512, 3, 1, 1, True, True),           # tiny spatial, tiles span images, M tail
+    (3, (14, 14, 256), 256, 3, 1, 1, True, False),
+    (2, (14, 14, 1024), 2048, 1, 2, 0, False, False),
+]
+
+
+@pytest.mark.parametrize("case", CONV_CASES, ids=lambda c: f"n{c[0]}_{c[1][0]}x{c[1][2]}_oc{c[2]}_k{c[3]}s{c[4]}")
+def test_conv(case, cuda_device):
+    n, hwc, oc, k, stride, pad, relu, residual = case
+    _run_conv(n, hwc, oc, k, stride, pad, relu, residual, seed=hash(case) % 1000)
+
+
+def test_conv_stem_s2d_shape(cuda_device):
+    # the 4x4 / pad (2,1) / 16-channel conv the stem is rewritten into (32-byte swizzle path)
+    _run_conv(2, (112, 112, 16), 64, 4, 1, 2, True, False, seed=7, pad_hi=1)
+
+
+def test_conv_sub_batched(cuda_device):
+    # same op run in chunks of 2 images: exercises the external-source re-encode and chunk offsets
+    _run_conv(5, (28, 28, 128), 128, 3, 1, 1, True, False, seed=11, sub_batch=2)
+
+
+def test_linear(cuda_device):
+    from mlmicroservicetemplate_b200 import backend as B, program as P
+    g = torch.Generator().manual_seed(3)
+    n, fin, classes = 70, 2048, 1000
+    x = _bf16r(torch.randn(n, fin, generator=g))
+    w = _bf16r(torch.randn(classes, fin, generator=g) / fin ** 0.5)
+    b = torch.randn(classes, generator=g)
+    rep = B.Replica(0, P.single_linear_program(w, b), max_batch=n)
+    out = torch.full((n, classes), float("nan"), device="cuda")
+    rep.forward(x.to(torch.bfloat16).cuda(), n, out)
+    torch.cuda.synchronize()
+    ref = x @ w.t() + b
+    err = (out.cpu() - ref).abs().max().item()
+    print("linear max_err", err)
+    rep.close()
+    assert err < 2e-3
+
+
+def _one_op_program(kind, in_hwc, out_hwc, in_elems, k=(1, 1), stride=1, pad=(0, 0)):
+    from mlmicroservicetemplate_b200 import backend as B, program as P
+    p = P.Program(name="one_op")
+    p.in_elems = in_elems
+    p.out_elems = out_hwc[0] * out_hwc[1] * out_hwc[2]
+    p.ops.append(P._mk_op(kind, B.SLOT_INPUT, B.SLOT_OUTPUT, in_hwc=in_hwc, out_hwc=out_hwc, k=k, stride=stride, pad=pad))
+    return p
+
+
+def test_maxpool(cuda_device):
+    from mlmicroservicetemplate_b200 import backend as B
+    n = 3
+    x = torch.randn(n, 112, 112, 64).to(torch.bfloat16)
+    rep = B.Replica(0, _one_op_program(B.OP_MAXPOOL, (112, 112, 64), (56, 56, 64), 112 * 112 * 64, (3, 3), 2, (1, 1)), n)
+    out = torch.empty(n, 56, 56, 64, dtype=torch.bfloat16, device="cuda")
+    rep.forward(x.cuda(), n, out)
+    torch.cuda.synchronize()
+    ref = F.max_pool2d(x.float().permute(0, 3, 1, 2), 3, 2, 1).permute(0, 2, 3, 1)
+    rep.close()
+    assert torch.equal(out.float().cpu(), ref)
+
+
+def test_avgpool(cuda_device):
+    from mlmicroservicetemplate_b200 import backend as B
+    n = 5
+    x = torch.randn(n, 7, 7, 2048).to(torch.bfloat16)
+    rep = B.Replica(0, _one_op_program(B.OP_AVGPOOL, (7, 7, 2048), (1, 1, 2048), 49 * 2048), n)
+    out = torch.empty(n, 2048, dtype=torch.bfloat16, device="cuda")
+    rep.forward(x.cuda(), n, out)
+    torch.cuda.synchronize()
+    ref = x.float().mean(dim=(1, 2))
+    rep.close()
+    assert (out.float().cpu() - ref).abs().max().item() < 4e-3
+
+
+def test_stem_pack(cuda_device):
+    from mlmicroservicetemplate_b200 import backend as B
+    n = 2
+    x = torch.randn(n, 3, 224, 224).to(torch.bfloat16)
+    rep = B.Replica(0, _one_op_program(B.OP_STEM_PACK, (224, 224, 3), (112, 112, 16), 3 * 224 * 224), n)
+    out = torch.empty(n, 112, 112, 16, dtype=torch.bfloat16, device="cuda")
+    rep.forward(x.cuda(), n, out)
+    torch.cuda.synchronize()
+    ref = torch.zeros(n, 112, 112, 16)
+    xf = x.float()
+    for di in range(2):
+        for dj in range(2):
+            for c in range(3):
+                ref[..., (di * 2 + dj) * 3 + c] = xf[:, c, di::2, dj::2]
+    rep.close()
+    assert torch.equal(out.float().cpu(), ref)
+
+
+def test_softmax_topk(cuda_device):
+    from mlmicroservicetemplate_b200 import backend as B
+    n, classes, k = 37, 1000, 5
+    g = torch.Generator().manual_seed(5)
+    logits = torch.randn(n, classes, generator=g) * 3
+    logits[3, 10] = logits[3, 500] = 9.0      # an exact tie: lowest index must win
+    rep = B.Replica(0, _one_op_program(B.OP_AVGPOOL, (1, 1, 8), (1, 1, 8), 8), n)   # any handle will do
+    probs = torch.empty(n, k, device="cuda")
+    idx = torch.empty(n, k, dtype=torch.int32, device="cuda")
+    rep.softmax_topk(logits.cuda(), n, classes, k, probs, idx)
+    torch.cuda.synchronize()
+    ref_p, ref_i = torch.softmax(logits, 1).topk(k, dim=1)
+    rep.close()
+    assert idx[3, 0].item() == 10 and idx[3, 1].item() == 500
+    mask = torch.ones(n, dtype=torch.bool)
+    mask[3] = False
+    assert torch.equal(idx.cpu().long()[mask], ref_i[mask])
+    assert torch.allclose(probs.cpu(), ref_p, rtol=1e-5, atol=1e-8)

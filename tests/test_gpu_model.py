@@ -1,0 +1,91 @@
+"""End-to-end parity on the GPU through the C ABI: uint8 images -> b2p_predict -> logits / top-k,
+against the oracle's CPU fp32 predict path on the same seeded weights and images
+(BASELINE.json configs[1]: ResNet-18 random-init, 224^2, batch 64)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _gpu_predict(arch, images, mode, k=5, sub_batch=0):
+    from mlmicroservicetemplate_b200 import backend as B, program as P
+    from oracle import model as om
+    model = om.build_model(arch)
+    prog = P.build_resnet_program(model, arch)
+    n = len(images)
+    rep = B.Replica(0, prog, max_batch=n, sub_batch=sub_batch)
+    offs, total = [], 0
+    for im in images:
+        offs.append(total)
+        total += (im.size + 255) // 256 * 256
+    slab = np.zeros(total, np.uint8)
+    geoms = []
+    for im, o in zip(images, offs):
+        slab[o:o + im.size] = im.reshape(-1)
+        geoms.append((o, im.shape[0], im.shape[1], *om.geometry(im.shape[0], im.shape[1], mode)))
+    descs = B.make_images(geoms)
+    slab_d = torch.from_numpy(slab).cuda()
+    # chained entry point ...
+    probs = torch.empty(n, k, device="cuda")
+    idx = torch.empty(n, k, dtype=torch.int32, device="cuda")
+    rep.predict(slab_d, descs, n, k, probs, idx)
+    # ... and the three stages one by one, which also exposes the logits
+    x = torch.empty(n, 3, 224, 224, dtype=torch.bfloat16, device="cuda")
+    logits = torch.full((n, prog.out_elems), float("nan"), device="cuda")
+    probs2 = torch.empty(n, k, device="cuda")
+    idx2 = torch.empty(n, k, dtype=torch.int32, device="cuda")
+    rep.preprocess(slab_d, descs, n, x)
+    rep.forward(x, n, logits)
+    rep.softmax_topk(logits, n, prog.out_elems, k, probs2, idx2)
+    torch.cuda.synchronize()
+    assert torch.equal(probs, probs2) and torch.equal(idx, idx2), "chained and staged calls must agree bit for bit"
+    out = (logits.cpu(), probs.cpu(), idx.cpu().long())
+    rep.close()
+    return model, out
+
+
+def _report(tag, got, ref):
+    err = (got - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    top1 = (got.argmax(1) == ref.argmax(1)).float().mean().item()
+    srt = ref.sort(dim=1, descending=True).values
+    margin = (srt[:, 0] - srt[:, 1]).min().item()
+    print(f"{tag}: logits max_abs_err={err:.4g} max|logit|={scale:.4g} rel={err / scale:.3g} "
+          f"top1_agree={top1:.4f} min_fp32_margin={margin:.4g} distinct_top1={ref.argmax(1).unique().numel()}")
+    return err, scale, top1
+
+
+def test_resnet18_b64_direct(cuda_device):
+    from oracle import images, model as om
+    ims = images.synthetic_batch(1, 64, 224, 224)
+    model, (logits, probs, idx) = _gpu_predict("resnet18", ims, "direct")
+    ref_logits, ref_probs, ref_idx = om.predict_arrays(ims, mode="direct", k=5, model=model)
+    err, scale, top1 = _report("resnet18 b64", logits, ref_logits)
+    assert top1 == 1.0, "top-1 must be identical on every image"
+    assert err <= 2e-2 or err / scale <= 6e-3, "logits outside the bf16-vs-fp32 band"
+    assert torch.equal(idx[:, 0], ref_idx[:, 0])
+    assert (probs - ref_probs).abs().max().item() < 5e-3
+
+
+def test_resnet18_ragged_preset_sub_batched(cuda_device):
+    from oracle import images, model as om
+    sizes = [(256, 256), (300, 400), (480, 640), (720, 1280), (333, 517), (1080, 1920), (512, 384)]
+    ims = [images.synthetic_image(300 + i, h, w) for i, (h, w) in enumerate(sizes)]
+    model, (logits, probs, idx) = _gpu_predict("resnet18", ims, "preset", sub_batch=3)
+    ref_logits, _, ref_idx = om.predict_arrays(ims, mode="preset", k=5, model=model)
+    err, scale, top1 = _report("resnet18 ragged preset", logits, ref_logits)
+    assert top1 == 1.0
+    assert err <= 2e-2 or err / scale <= 6e-3
+
+
+def test_resnet50_b16(cuda_device):
+    from oracle import images, model as om
+    ims = images.synthetic_batch(1, 16, 224, 224)
+    model, (logits, probs, idx) = _gpu_predict("resnet50", ims, "direct")
+    ref_logits, _, ref_idx = om.predict_arrays(ims, mode="direct", k=5, model=model)
+    err, scale, top1 = _report("resnet50 b16", logits, ref_logits)
+    # random-init ResNet-50 has |logit| ~ 100: the absolute 2e-2 bar is below bf16 input quantisation
+    # (SURVEY §8c c6), so the gate is relative here and the absolute number is reported.
+    assert top1 == 1.0
+    assert err / scale <= 8e-3
