@@ -152,7 +152,7 @@ def test_softmax_topk(cuda_device):
     n, classes, k = 37, 1000, 5
     g = torch.Generator().manual_seed(5)
     logits = torch.randn(n, classes, generator=g) * 3
-    logits[3, 10] = logits[3, 500] = 9.0      # an exact tie: lowest index must win
+    logits[3, 10] = logits[3, 500] = 50.0     # an exact tie above every other logit: lowest index must win
     rep = B.Replica(0, _one_op_program(B.OP_AVGPOOL, (1, 1, 8), (1, 1, 8), 8), n)   # any handle will do
     probs = torch.empty(n, k, device="cuda")
     idx = torch.empty(n, k, dtype=torch.int32, device="cuda")
@@ -164,4 +164,5 @@ def test_softmax_topk(cuda_device):
     mask = torch.ones(n, dtype=torch.bool)
     mask[3] = False
     assert torch.equal(idx.cpu().long()[mask], ref_i[mask])
-    assert torch.allclose(probs.cpu(), ref_p, rtol=1e-5, atol=1e-8)
+    assert torch.allclose(probs.cpu()[mask], ref_p[mask], rtol=1e-5, atol=1e-8)
+    assert abs(probs[3, 0].item() - 0.5) < 1e-5 and abs(probs[3, 1].item() - 0.5) < 1e-5
