@@ -163,20 +163,18 @@ def main():
         os.execvp(sys.executable, [sys.executable, "-m", "torch.distributed.run", "--nnodes=1",
                                    f"--nproc-per-node={args.gpus}", "--master-addr", "127.0.0.1",
                                    "--master-port", "29511", os.path.abspath(__file__), *sys.argv[1:]])
-    rank = int(os.environ.get("RANK", "0"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-
     import numpy as np
     import torch
-    import torch.distributed as dist
     from mlmicroservicetemplate_b200 import backend as B, program as P
+    from mlmicroservicetemplate_b200.ranks import Ranks
     from oracle import model as om      # only to build the seeded torchvision module + cpu_baseline
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a B200: the predict path has no CPU fallback")
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local_rank)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    ranks = Ranks.from_env(backend="nccl", device=torch.device("cuda", local_rank))
+    rank = ranks.rank
 
     model = om.build_model(ARCH)
     prog = P.build_resnet_program(model, ARCH)
@@ -206,17 +204,7 @@ def main():
     probs_h = torch.empty(BATCH, TOPK, dtype=torch.float32, pin_memory=True)
     idx_h = torch.empty(BATCH, TOPK, dtype=torch.int32, pin_memory=True)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def max_over_ranks(v: float) -> float:
-        if world == 1:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+    barrier, max_over_ranks = ranks.barrier, ranks.max_over_ranks
 
     K, W = args.steps, args.warmup
 
@@ -310,8 +298,7 @@ def main():
         }
         print(json.dumps(line))
     rep.close()
-    if world > 1:
-        dist.destroy_process_group()
+    ranks.close()
     return 0
 
 

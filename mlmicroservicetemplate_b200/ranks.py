@@ -1,0 +1,62 @@
+"""One-process-per-GPU plumbing for the replica-parallel bench: rank discovery, a barrier, and the
+max-over-ranks of a device-measured time.  The predict path shards by request — whole batches go to
+independent replicas — so there is NO data-path collective; torch.distributed carries only these two
+control operations (NCCL on GPUs, gloo in the CPU tests)."""
+from __future__ import annotations
+
+import os
+from dataclasses import dataclass
+
+
+@dataclass
+class Ranks:
+    rank: int = 0
+    local_rank: int = 0
+    world: int = 1
+    backend: str = ""
+
+    @classmethod
+    def from_env(cls, backend: str = "nccl", device=None) -> "Ranks":
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+        r = cls(int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0")), world, backend)
+        if world > 1:
+            import torch.distributed as dist
+            kw = {"device_id": device} if (device is not None and backend == "nccl") else {}
+            dist.init_process_group(backend, **kw)
+        return r
+
+    def _tensor(self, v: float):
+        import torch
+        dev = "cuda" if self.backend == "nccl" else "cpu"
+        return torch.tensor([v], dtype=torch.float64, device=dev)
+
+    def barrier(self) -> None:
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier()
+        if self.backend == "nccl":
+            import torch
+            torch.cuda.synchronize()
+
+    def max_over_ranks(self, v: float) -> float:
+        if self.world == 1:
+            return float(v)
+        import torch.distributed as dist
+        t = self._tensor(v)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def job_throughput(self, units_per_rank: int, elapsed_ms: float) -> float:
+        """Whole-job units/s: every rank processed `units_per_rank`; the job took the slowest rank's time."""
+        return self.world * units_per_rank / (self.max_over_ranks(elapsed_ms) * 1e-3)
+
+    def shard(self, n_items: int):
+        """Contiguous share of n_items independent work units for this rank (no exchange afterwards)."""
+        base, extra = divmod(n_items, self.world)
+        lo = self.rank * base + min(self.rank, extra)
+        return range(lo, lo + base + (1 if self.rank < extra else 0))
+
+    def close(self) -> None:
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.destroy_process_group()

@@ -1,0 +1,123 @@
+"""Model plugin — the drop-in for CodyRichter/MLMicroserviceTemplate src/model/model.py.
+
+Same two module-level functions, same signatures, same result-dict shape:
+    init() -> None                                             (reference model.py:6-13)
+    predict(image_file: UploadFile = File(...)) -> dict        (reference model.py:16-31)
+returning {'classes': [every class name], 'result': {class_name: value}}.
+
+What changed underneath: init() builds one model replica per visible B200 through the C ABI
+(libb200predict.so) plus the micro-batching engine; predict() decodes the upload on the host with
+Pillow (exactly the reference's `Image.open(image_file.file)`, now followed by .convert('RGB')),
+enqueues the uint8 HWC pixels and blocks on a future, so concurrent callers are batched.
+`predict_async` is the awaitable twin the server uses so the event loop is never blocked.
+
+Environment knobs (defaults in brackets):
+    MODEL [resnet50]    resnet18 | resnet50 | template   (`template` = the reference's constant-dict
+                        example plugin, no GPU involved — BASELINE.json configs[0])
+    GPUS  [all]         comma-separated device indices
+    MAX_BATCH [64]  MAX_WAIT_US [2000]  TOPK [5]  SEED [0]  PREPROCESS [preset] (preset | direct)
+    SUB_BATCH [0]       images per L2-resident pass of the layer program (0 = whole batch)
+"""
+from __future__ import annotations
+
+import asyncio
+import os
+import threading
+from typing import List, Optional
+
+import numpy as np
+from fastapi import File, UploadFile
+from PIL import Image
+
+_lock = threading.Lock()
+_state = {"engine": None, "classes": None, "arch": None, "decode_pool": None}
+
+TEMPLATE_RESULT = {
+    'classes': ['isGreen', 'isRed'],
+    'result': {'isGreen': 0, 'isRed': 1},
+}
+
+
+def class_names(n: int) -> List[str]:
+    # Random-init weights have no label file; names are positional (checkpoint + labels: SURVEY §8f row 3).
+    return [f"class_{i:04d}" for i in range(n)]
+
+
+def init() -> None:
+    """Runs once at start-up (reference src/server/main.py:77-84 calls it on a pool thread)."""
+    with _lock:
+        if _state["engine"] is not None or _state["arch"] == "template":
+            return
+        arch = os.getenv("MODEL", "resnet50")
+        _state["arch"] = arch
+        if arch == "template":
+            return
+        from concurrent.futures import ThreadPoolExecutor
+        from ...runtime import build_gpu_engine
+        gpus = os.getenv("GPUS")
+        devs = [int(g) for g in gpus.split(",")] if gpus else None
+        engine, n_classes = build_gpu_engine(
+            arch=arch, gpus=devs, max_batch=int(os.getenv("MAX_BATCH", "64")),
+            max_wait_us=int(os.getenv("MAX_WAIT_US", "2000")), topk=int(os.getenv("TOPK", "5")),
+            mode=os.getenv("PREPROCESS", "preset"), seed=int(os.getenv("SEED", "0")),
+            sub_batch=int(os.getenv("SUB_BATCH", "0")))
+        _state["engine"] = engine
+        _state["classes"] = class_names(n_classes)
+        _state["decode_pool"] = ThreadPoolExecutor(max_workers=int(os.getenv("DECODE_THREADS", str(os.cpu_count() or 4))))
+
+
+def shutdown() -> None:
+    """Drains the batch queue and destroys the replicas (the server's shutdown hook calls this)."""
+    with _lock:
+        eng, _state["engine"] = _state["engine"], None
+        pool, _state["decode_pool"] = _state["decode_pool"], None
+        _state["arch"] = None
+    if eng is not None:
+        eng.close()
+    if pool is not None:
+        pool.shutdown(wait=False)
+
+
+def _decode(fileobj) -> np.ndarray:
+    """Stage D: host decode to uint8 HWC (any PIL-readable mode is converted to RGB)."""
+    image = Image.open(fileobj)
+    return np.asarray(image.convert('RGB'))
+
+
+def _to_result(probs, idx) -> dict:
+    names = _state["classes"]
+    return {
+        'classes': names,
+        'result': {names[int(i)]: float(p) for p, i in zip(probs, idx)},
+    }
+
+
+def _engine():
+    eng = _state["engine"]
+    if eng is None:
+        raise RuntimeError("model is not initialised: call init() first")
+    return eng
+
+
+def predict(image_file: UploadFile = File(...)):
+    """
+    Interface method between model and server. This signature must not be
+    changed and your model must be able to predict given a file-like object
+    with the image as an input.
+    """
+    if _state["arch"] == "template":
+        Image.open(image_file.file)              # what the reference template does (model.py:23)
+        return {'classes': list(TEMPLATE_RESULT['classes']), 'result': dict(TEMPLATE_RESULT['result'])}
+    arr = _decode(image_file.file)
+    probs, idx = _engine().submit(arr).result()
+    return _to_result(probs, idx)
+
+
+async def predict_async(image_file: UploadFile = File(...)):
+    """Awaitable twin of predict(): decode on a worker thread, await the batched result."""
+    if _state["arch"] == "template":
+        return predict(image_file)
+    loop = asyncio.get_running_loop()
+    arr = await loop.run_in_executor(_state["decode_pool"], _decode, image_file.file)
+    probs, idx = await asyncio.wrap_future(_engine().submit(arr))
+    return _to_result(probs, idx)

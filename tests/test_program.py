@@ -1,0 +1,129 @@
+"""Host-side weight packing and layer-program construction, checked on CPU by interpreting the program
+with plain torch ops (test-only interpreter) against the torchvision module it was built from."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+from mlmicroservicetemplate_b200 import backend as B, program as P
+
+
+def interpret(prog: P.Program, x_nchw: torch.Tensor) -> torch.Tensor:
+    """fp32 torch interpretation of the op list (NHWC slots) using the PACKED blobs."""
+    slots = {B.SLOT_INPUT: x_nchw}
+    out = None
+    for op in prog.ops:
+        src = slots[op.src]
+        if op.kind == B.OP_STEM_PACK:
+            n = src.shape[0]
+            y = torch.zeros(n, op.out_h, op.out_w, 16)
+            for di in range(2):
+                for dj in range(2):
+                    for c in range(3):
+                        y[..., (di * 2 + dj) * 3 + c] = src[:, c, di::2, dj::2]
+        elif op.kind == B.OP_CONV:
+            w = prog.blobs[op.weight].float()[: op.out_c]                 # [oc, kh, kw, ic]
+            b = prog.blobs[op.bias][: op.out_c]
+            xin = F.pad(src.permute(0, 3, 1, 2), (op.pad_lo, op.pad_hi, op.pad_lo, op.pad_hi))
+            y = F.conv2d(xin, w.permute(0, 3, 1, 2), b, stride=op.stride).permute(0, 2, 3, 1)
+            if op.res != B.SLOT_NONE:
+                y = y + slots[op.res]
+            if op.relu:
+                y = y.relu()
+        elif op.kind == B.OP_MAXPOOL:
+            y = F.max_pool2d(src.permute(0, 3, 1, 2), op.kh, op.stride, op.pad_lo).permute(0, 2, 3, 1)
+        elif op.kind == B.OP_AVGPOOL:
+            y = src.mean(dim=(1, 2))
+        elif op.kind == B.OP_LINEAR:
+            y = src @ prog.blobs[op.weight].float()[: op.out_c].t() + prog.blobs[op.bias][: op.out_c]
+        else:
+            raise AssertionError(op.kind)
+        assert tuple(y.shape[1:]) in ((op.out_h, op.out_w, op.out_c), (op.out_c,)), (op.kind, y.shape)
+        if op.dst == B.SLOT_OUTPUT:
+            out = y
+        else:
+            assert y[0].numel() <= prog.slot_elems[op.dst], "slot too small for what the op writes"
+            slots[op.dst] = y
+    return out
+
+
+@pytest.mark.parametrize("arch,flops", [("resnet18", 3.6281e9), ("resnet50", 8.1784e9)])
+def test_program_reproduces_the_torchvision_forward(arch, flops):
+    import torchvision
+    torch.manual_seed(0)
+    model = getattr(torchvision.models, arch)(weights=None).eval()
+    # non-trivial BN statistics so that the fold is really exercised
+    g = torch.Generator().manual_seed(1)
+    for m in model.modules():
+        if isinstance(m, torch.nn.BatchNorm2d):
+            m.running_mean.copy_(torch.randn(m.num_features, generator=g) * 0.1)
+            m.running_var.copy_(torch.rand(m.num_features, generator=g) + 0.5)
+            m.weight.data.copy_(torch.rand(m.num_features, generator=g) + 0.5)
+            m.bias.data.copy_(torch.randn(m.num_features, generator=g) * 0.1)
+    prog = P.build_resnet_program(model, arch)
+    assert abs(prog.flops_per_image - flops) / flops < 1e-4
+    x = torch.randn(2, 3, 224, 224, generator=g).to(torch.bfloat16).float()
+    with torch.no_grad():
+        ref = model(x)
+        got = interpret(prog, x)
+    # only difference: weights rounded to bf16
+    assert (got - ref).abs().max().item() < 0.02 * ref.abs().max().item()
+    assert torch.equal(got.argmax(1), ref.argmax(1))
+
+
+def test_slots_are_never_clobbered_while_live():
+    import torchvision
+    prog = P.build_resnet_program(torchvision.models.resnet50(weights=None), "resnet50")
+    last_read = {}
+    for i, op in enumerate(prog.ops):
+        for s in (op.src, op.res):
+            if s not in (B.SLOT_NONE,):
+                last_read[s] = i
+    writer = {}
+    for i, op in enumerate(prog.ops):
+        assert op.dst != op.src and (op.res == B.SLOT_NONE or op.dst != op.res), "no in-place ops"
+        writer[op.dst] = i
+    # replay: a slot written at i must not be overwritten before its readers ran
+    live_until = {}
+    for i, op in enumerate(prog.ops):
+        if op.dst in live_until:
+            assert live_until[op.dst] < i, f"op {i} overwrites slot {op.dst} still needed by op {live_until[op.dst]}"
+        nxt = [j for j, o in enumerate(prog.ops) if j > i and (o.src == op.dst or o.res == op.dst)]
+        rewrite = [j for j, o in enumerate(prog.ops) if j > i and o.dst == op.dst]
+        horizon = rewrite[0] if rewrite else len(prog.ops)
+        readers = [j for j in nxt if j <= horizon]
+        if op.dst != B.SLOT_OUTPUT:
+            assert readers, f"op {i} writes slot {op.dst} that nobody reads"
+            live_until[op.dst] = max(readers)
+    assert len(prog.slot_elems) <= 6
+
+
+def test_stem_rewrite_equals_the_7x7_conv():
+    g = torch.Generator().manual_seed(2)
+    w = torch.randn(64, 3, 7, 7, generator=g)
+    x = torch.randn(2, 3, 224, 224, generator=g)
+    ref = F.conv2d(x, w, stride=2, padding=3)
+    ws = P.stem_s2d_weight(w)                                       # [64, 4, 4, 16]
+    s2d = torch.zeros(2, 16, 112, 112)
+    for di in range(2):
+        for dj in range(2):
+            for c in range(3):
+                s2d[:, (di * 2 + dj) * 3 + c] = x[:, c, di::2, dj::2]
+    got = F.conv2d(F.pad(s2d, (2, 1, 2, 1)), ws.permute(0, 3, 1, 2))
+    assert got.shape == ref.shape and (got - ref).abs().max().item() < 1e-4
+
+
+def test_fold_bn_and_packing_layout():
+    g = torch.Generator().manual_seed(3)
+    conv = torch.nn.Conv2d(8, 16, 3, bias=False)
+    bn = torch.nn.BatchNorm2d(16).eval()
+    bn.running_mean.copy_(torch.randn(16, generator=g)); bn.running_var.copy_(torch.rand(16, generator=g) + 0.5)
+    bn.weight.data.copy_(torch.rand(16, generator=g) + 0.5); bn.bias.data.copy_(torch.randn(16, generator=g))
+    x = torch.randn(1, 8, 10, 10, generator=g)
+    w, b = P.fold_bn(conv.weight, bn)
+    with torch.no_grad():
+        assert (F.conv2d(x, w, b) - bn(conv(x))).abs().max().item() < 1e-5
+    packed = P.pack_conv_weight(w)
+    assert packed.shape == (64, 3, 3, 8) and packed.dtype == torch.bfloat16
+    assert torch.equal(packed[:16].float(), w.permute(0, 2, 3, 1).to(torch.bfloat16).float())
+    assert packed[16:].abs().sum().item() == 0
