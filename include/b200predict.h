@@ -145,6 +145,28 @@ int32_t b2p_predict_host(b2p_handle* h, const uint8_t* slab_host, int64_t slab_b
  * handle-owned, valid until the next call).  Used by the parity tests.                         */
 const float* b2p_last_logits(b2p_handle* h);
 
+/* No counterpart in the reference (it has no device code at all).  The classifier head — global
+ * average pool of feat [n, hw, c] bf16 (NHWC) followed by logits = pooled x weight^T + bias — for
+ * callers that must not allocate device memory: a process whose own pool already holds all of the
+ * GPU's memory (a library-side cudaMalloc would fail), or one that keeps the allocator off its
+ * request path because cudaMalloc/cudaFree stall the device.  It takes no handle and calls no
+ * cudaMalloc/cudaFree or any allocating routine; the pooled features live in a fixed 1 MiB array
+ * inside the library image, which every GPU that loads the library holds until exit.
+ *   weight : device, bf16 [weight_rows][c], weight_rows a multiple of 128 and >= classes (zero rows
+ *            pad the tail), c a multiple of 64;  bias : device, fp32 [weight_rows];
+ *   logits : device, fp32 [n][classes].
+ * Fails with B2P_E_LIMIT when n > B2P_HEAD_STATIC_MAX_IMAGES or c > B2P_HEAD_STATIC_MAX_CHANNELS.
+ * All calls on one device share the array and it keeps the previous call's contents (nothing in it
+ * needs to start at zero: rows [0, n) are rewritten before they are read and no other row is read);
+ * calls that overlap on the GPU race on it.  The first call on each device does a one-time set-up
+ * (symbol address, driver entry points, kernel attributes) and should come before any stream
+ * capture.  Errors are reported through b2p_last_error(NULL).                                    */
+#define B2P_HEAD_STATIC_MAX_IMAGES 256
+#define B2P_HEAD_STATIC_MAX_CHANNELS 2048
+int32_t b2p_head_static(const void* feat, int32_t n, int32_t hw, int32_t c, const void* weight,
+                        int32_t weight_rows, const float* bias, int32_t classes, float* logits,
+                        void* stream);
+
 #ifdef __cplusplus
 }
 #endif

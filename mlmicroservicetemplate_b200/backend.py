@@ -80,7 +80,12 @@ SYMBOLS = [
     ("b2p_predict", C.c_int32, [C.c_void_p, C.c_void_p, C.POINTER(Image), C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     ("b2p_predict_host", C.c_int32, [C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(Image), C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p]),
     ("b2p_last_logits", C.c_void_p, [C.c_void_p]),
+    ("b2p_head_static", C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p,
+                                    C.c_int32, C.c_void_p, C.c_void_p]),
 ]
+
+HEAD_STATIC_MAX_IMAGES = 256
+HEAD_STATIC_MAX_CHANNELS = 2048
 
 _lib: Optional[C.CDLL] = None
 
@@ -113,6 +118,16 @@ def make_images(geoms: Sequence[tuple]) -> "C.Array[Image]":
     for i, g in enumerate(geoms):
         arr[i] = Image(*[int(v) for v in g])
     return arr
+
+
+def head_static(feat, n: int, hw: int, c: int, weight, weight_rows: int, bias, classes: int, logits, stream=None) -> None:
+    """Allocation-free classifier head (average pool + linear) on the current device; see the header.
+    All tensor arguments are device tensors (or raw device addresses) owned by the caller."""
+    lib = load_library()
+    rc = lib.b2p_head_static(Replica._ptr(feat), n, hw, c, Replica._ptr(weight), weight_rows, Replica._ptr(bias),
+                             classes, Replica._ptr(logits), Replica._stream(stream))
+    if rc != 0:
+        raise B2PError(rc, (lib.b2p_last_error(None) or b"").decode())
 
 
 class Replica:

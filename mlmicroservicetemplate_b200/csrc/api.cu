@@ -193,6 +193,15 @@ int check_images(b2p_handle* h, const b2p_image* imgs, int n) {
 
 }  // namespace
 
+namespace b2p {
+void set_global_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_create_error, sizeof g_create_error, fmt, ap);
+    va_end(ap);
+}
+}  // namespace b2p
+
 extern "C" {
 
 int32_t b2p_abi_version(void) { return B2P_ABI_VERSION; }

@@ -40,6 +40,9 @@ bool gemm_plan_set_src(GemmPlan& p, const void* src, int batch_cap, char* err, s
 cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, const void* residual, void* out,
                              int num_sms, cudaStream_t stream);
 
+// Records an error that is not tied to a handle; b2p_last_error(NULL) returns it.
+void set_global_error(const char* fmt, ...);
+
 // ------------------------------------------------------------------ small memory-bound kernels
 cudaError_t launch_stem_pack(const void* x_nchw, void* out_nhwc16, int n, int h, int w,
                              cudaStream_t s);
