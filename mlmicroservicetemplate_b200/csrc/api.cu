@@ -19,6 +19,8 @@ struct OpPlan {
     GemmPlan gemm;        // valid for CONV / LINEAR
     bool is_gemm = false;
     bool src_external = false;
+    bool dst_external = false;
+    bool res_external = false;
 };
 
 }  // namespace
@@ -135,7 +137,13 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
                         }
                     }
                     const int rows = o.kind == B2P_OP_LINEAR ? nb : nb * o.out_h * o.out_w;
-                    e = gemm_plan_launch(p.gemm, rows, res, dst, h->num_sms, st);
+                    char eb2[256] = "";
+                    if ((p.dst_external && !gemm_plan_set_dst(p.gemm, dst, rows, eb2, sizeof eb2)) ||
+                        (res && p.res_external && !gemm_plan_set_res(p.gemm, res, rows, eb2, sizeof eb2))) {
+                        set_error(h, "%s", eb2);
+                        return B2P_E_CUDA;
+                    }
+                    e = gemm_plan_launch(p.gemm, rows, res != nullptr, dst, h->num_sms, st);
                     break;
                 }
                 case B2P_OP_MAXPOOL:
@@ -310,6 +318,21 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
             if (!p.src_external) {
                 if (!h->slots[o.src]) B2P_FAIL(B2P_E_ARG, "op %d reads an empty slot", i);
                 if (!gemm_plan_set_src(p.gemm, h->slots[o.src], h->chunk, eb, sizeof eb))
+                    B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
+            }
+            p.dst_external = (o.dst == B2P_SLOT_OUTPUT);
+            p.res_external = (o.res == B2P_SLOT_INPUT);
+            if (o.kind == B2P_OP_LINEAR && o.res != B2P_SLOT_NONE) B2P_FAIL(B2P_E_ARG, "op %d: LINEAR has no residual", i);
+            if (!p.dst_external) {
+                if (!h->slots[o.dst]) B2P_FAIL(B2P_E_ARG, "op %d writes an empty slot", i);
+                if (h->slot_elems[o.dst] < static_cast<int64_t>(o.out_h) * o.out_w * o.out_c && o.kind == B2P_OP_CONV)
+                    B2P_FAIL(B2P_E_ARG, "op %d: destination slot too small", i);
+                if (!gemm_plan_set_dst(p.gemm, h->slots[o.dst], rows_cap, eb, sizeof eb))
+                    B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
+            }
+            if (o.res != B2P_SLOT_NONE && !p.res_external) {
+                if (!h->slots[o.res]) B2P_FAIL(B2P_E_ARG, "op %d adds an empty slot", i);
+                if (!gemm_plan_set_res(p.gemm, h->slots[o.res], rows_cap, eb, sizeof eb))
                     B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
             }
         } else if ((o.kind == B2P_OP_MAXPOOL || o.kind == B2P_OP_AVGPOOL) && o.in_c % 8 != 0) {

@@ -31,9 +31,13 @@ namespace {
 
 constexpr int BLOCK_M = 128;
 constexpr int UMMA_K = 16;           // bf16: 32 bytes of K per tcgen05.mma
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_THREADS = 224;     // 7 warps: TMA, MMA, residual loader, 4 x epilogue
+constexpr int EPI_THREADS = 128;
 constexpr int ACC_STAGES = 2;
-constexpr int SMEM_BUDGET = 200 * 1024;
+constexpr int SMEM_LIMIT = 227 * 1024;
+constexpr int OUT_CHUNK_BYTES = BLOCK_M * 64 * 2;   // one 128 x 64 bf16 staging tile (128B swizzle)
+constexpr int OUT_BUFS = 2;
+constexpr int RES_STAGES = 2;
 
 struct GemmArgs {
     int m_rows;       // valid output rows
@@ -46,43 +50,53 @@ struct GemmArgs {
     int ldc;
     int relu;
     const float* bias;
-    const void* residual;
-    void* out;
+    void* out;        // only used by the fp32 (linear) epilogue
 };
 
-template <int BLOCK_N, int BLOCK_K>
+template <int BLOCK_N, int BLOCK_K, bool OUT_F32, bool HAS_RES>
 struct Cfg {
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
     static constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int STAGES_RAW = SMEM_BUDGET / STAGE_BYTES;
+    static constexpr int OUT_BYTES = OUT_F32 ? 0 : OUT_BUFS * OUT_CHUNK_BYTES;
+    static constexpr int RES_BYTES = HAS_RES ? RES_STAGES * OUT_CHUNK_BYTES : 0;
+    static constexpr int BAR_BYTES = 256;
+    static constexpr int FIXED = 1024 /*alignment slack*/ + BAR_BYTES + OUT_BYTES + RES_BYTES;
+    static constexpr int STAGES_RAW = (SMEM_LIMIT - FIXED) / STAGE_BYTES;
     static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
     static constexpr int SWIZZLE_BYTES = BLOCK_K * 2;          // 128 or 32
     static constexpr int TMEM_COLS = ACC_STAGES * BLOCK_N;     // 128 / 256 / 512
-    static constexpr int BAR_BYTES = (2 * STAGES + 2 * ACC_STAGES) * 8 + 16;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + BAR_BYTES + 1024;  // + alignment slack
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + FIXED;
     static_assert(BLOCK_K == 64 || BLOCK_K == 16, "BLOCK_K must give a 128B or 32B swizzle row");
     static_assert(TMEM_COLS == 128 || TMEM_COLS == 256 || TMEM_COLS == 512, "TMEM power of two");
     static_assert(A_BYTES % 1024 == 0 && B_BYTES % 1024 == 0, "stage bases stay 1024B aligned");
+    static_assert(STAGES >= 3, "pipeline too shallow");
+    static_assert((2 * STAGES + 2 * ACC_STAGES + 2 * RES_STAGES) * 8 + 8 <= BAR_BYTES, "barrier area");
 };
 
-template <int BLOCK_N, int BLOCK_K, bool IM2COL, bool OUT_F32>
+template <int BLOCK_N, int BLOCK_K, bool IM2COL, bool OUT_F32, bool HAS_RES>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
-                 const __grid_constant__ CUtensorMap tmap_b, const GemmArgs args) {
-    using C = Cfg<BLOCK_N, BLOCK_K>;
+conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                 const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
+                 const GemmArgs args) {
+    using C = Cfg<BLOCK_N, BLOCK_K, OUT_F32, HAS_RES>;
     constexpr int STAGES = C::STAGES;
+    static_assert(!(OUT_F32 && HAS_RES), "the fp32 epilogue has no residual input");
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
     uint8_t* smem_a = smem;
-    uint8_t* smem_b = smem + STAGES * C::A_BYTES;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * C::STAGE_BYTES);
+    uint8_t* smem_b = smem_a + STAGES * C::A_BYTES;
+    uint8_t* smem_out = smem_b + STAGES * C::B_BYTES;          // OUT_BUFS x 16 KB, 1024B aligned
+    uint8_t* smem_res = smem_out + C::OUT_BYTES;               // RES_STAGES x 16 KB
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_res + C::RES_BYTES);
     uint64_t* empty_bar = full_bar + STAGES;
     uint64_t* tmem_full_bar = empty_bar + STAGES;
     uint64_t* tmem_empty_bar = tmem_full_bar + ACC_STAGES;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_empty_bar + ACC_STAGES);
+    uint64_t* res_full_bar = tmem_empty_bar + ACC_STAGES;
+    uint64_t* res_empty_bar = res_full_bar + RES_STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_empty_bar + RES_STAGES);
 
     const int warp_idx = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
     const int total_tiles = args.m_tiles * args.n_tiles;
@@ -92,6 +106,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
         if (elect_one()) {
             tma_prefetch_desc(&tmap_a);
             tma_prefetch_desc(&tmap_b);
+            if (!OUT_F32) tma_prefetch_desc(&tmap_out);
+            if (HAS_RES) tma_prefetch_desc(&tmap_res);
         }
     } else if (warp_idx == 1) {
         if (elect_one()) {
@@ -102,6 +118,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
             for (int i = 0; i < ACC_STAGES; ++i) {
                 mbar_init(&tmem_full_bar[i], 1);
                 mbar_init(&tmem_empty_bar[i], 4);   // one arrive per epilogue warp
+            }
+            for (int i = 0; i < RES_STAGES; ++i) {
+                mbar_init(&res_full_bar[i], 1);
+                mbar_init(&res_empty_bar[i], 4);
             }
             fence_mbar_init();
         }
@@ -140,13 +160,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
                             mbar_wait(&empty_bar[stage], phase ^ 1u);
                             mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
                             if (IM2COL) {
-                                tma_load_im2col_4d(&tmap_a, &full_bar[stage],
-                                                   smem_a + stage * C::A_BYTES, cc * BLOCK_K,
-                                                   base_w, base_h, img, static_cast<uint16_t>(s),
+                                tma_load_im2col_4d(&tmap_a, &full_bar[stage], smem_a + stage * C::A_BYTES,
+                                                   cc * BLOCK_K, base_w, base_h, img, static_cast<uint16_t>(s),
                                                    static_cast<uint16_t>(r));
                             } else {
-                                tma_load_2d(&tmap_a, &full_bar[stage], smem_a + stage * C::A_BYTES,
-                                            kcol, m0);
+                                tma_load_2d(&tmap_a, &full_bar[stage], smem_a + stage * C::A_BYTES, kcol, m0);
                             }
                             tma_load_2d(&tmap_b, &full_bar[stage], smem_b + stage * C::B_BYTES, kcol,
                                         n_blk * BLOCK_N);
@@ -171,16 +189,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 for (int kb = 0; kb < num_kb; ++kb) {
                     mbar_wait(&full_bar[stage], phase);
                     tc_fence_after();
-                    const uint64_t a_desc =
-                        umma_desc_kmajor(smem_u32(smem_a + stage * C::A_BYTES), C::SWIZZLE_BYTES);
-                    const uint64_t b_desc =
-                        umma_desc_kmajor(smem_u32(smem_b + stage * C::B_BYTES), C::SWIZZLE_BYTES);
+                    const uint64_t a_desc = umma_desc_kmajor(smem_u32(smem_a + stage * C::A_BYTES), C::SWIZZLE_BYTES);
+                    const uint64_t b_desc = umma_desc_kmajor(smem_u32(smem_b + stage * C::B_BYTES), C::SWIZZLE_BYTES);
 #pragma unroll
                     for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
                         // advancing K inside a swizzle row: +32 bytes = +2 in the (addr >> 4) field
-                        umma_bf16(d_tmem, a_desc + static_cast<uint64_t>(k * 2),
-                                  b_desc + static_cast<uint64_t>(k * 2), idesc,
-                                  static_cast<uint32_t>((kb | k) != 0));
+                        umma_bf16(d_tmem, a_desc + static_cast<uint64_t>(k * 2), b_desc + static_cast<uint64_t>(k * 2),
+                                  idesc, static_cast<uint32_t>((kb | k) != 0));
                     }
                     umma_commit(&empty_bar[stage]);     // smem slot is free once these MMAs retire
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
@@ -189,69 +204,93 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
                 if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1u; }
             }
         }
+    } else if (warp_idx == 2) {
+        // ================================================================== residual loader
+        if (HAS_RES && elect_one()) {
+            int rs = 0;
+            uint32_t rphase = 0;
+            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+                const int m_blk = tile / args.n_tiles;
+                const int n_blk = tile - m_blk * args.n_tiles;
+                for (int c64 = 0; c64 < BLOCK_N / 64; ++c64) {
+                    mbar_wait(&res_empty_bar[rs], rphase ^ 1u);
+                    mbar_arrive_expect_tx(&res_full_bar[rs], OUT_CHUNK_BYTES);
+                    tma_load_2d(&tmap_res, &res_full_bar[rs], smem_res + rs * OUT_CHUNK_BYTES,
+                                n_blk * BLOCK_N + c64 * 64, m_blk * BLOCK_M);
+                    if (++rs == RES_STAGES) { rs = 0; rphase ^= 1u; }
+                }
+            }
+        }
     } else {
         // ========================================================================= epilogue
         const int quad = warp_idx & 3;                  // TMEM lanes [32*quad, 32*quad+32)
         const int lane = static_cast<int>(lane_id());
+        const int row_in_tile = quad * 32 + lane;
+        const bool store_leader = (warp_idx == 3) && (lane == 0);
         int acc = 0;
         uint32_t acc_phase = 0;
+        int rs = 0;
+        uint32_t rphase = 0;
+        int ob = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
             const int m_blk = tile / args.n_tiles;
             const int n_blk = tile - m_blk * args.n_tiles;
-            const int row = m_blk * BLOCK_M + quad * 32 + lane;
-            const bool row_ok = row < args.m_rows;
             mbar_wait(&tmem_full_bar[acc], acc_phase);
             tc_fence_after();
             const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) +
                                     static_cast<uint32_t>(acc * BLOCK_N);
+            if (OUT_F32) {
+                // ---- fp32 logits: direct, column-masked stores (tiny: n x 1000)
+                const int row = m_blk * BLOCK_M + row_in_tile;
+                const bool row_ok = row < args.m_rows;
 #pragma unroll 1
-            for (int chunk = 0; chunk < BLOCK_N / 32; ++chunk) {
-                uint32_t v[32];
-                tmem_ld_32x32(t_addr + static_cast<uint32_t>(chunk * 32), v);
-                tmem_ld_wait();
-                const int col0 = n_blk * BLOCK_N + chunk * 32;
-                const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0);
-                float f[32];
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const float4 b = __ldg(b4 + j);
-                    f[4 * j + 0] = __uint_as_float(v[4 * j + 0]) + b.x;
-                    f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + b.y;
-                    f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + b.z;
-                    f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + b.w;
-                }
-                if (OUT_F32) {
+                for (int chunk = 0; chunk < BLOCK_N / 32; ++chunk) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(t_addr + static_cast<uint32_t>(chunk * 32), v);
+                    tmem_ld_wait();
+                    const int col0 = n_blk * BLOCK_N + chunk * 32;
                     if (row_ok) {
-                        float* o = reinterpret_cast<float*>(args.out) +
-                                   static_cast<size_t>(row) * args.ldc + col0;
+                        float* o = reinterpret_cast<float*>(args.out) + static_cast<size_t>(row) * args.ldc + col0;
 #pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            if (col0 + 4 * j + 3 < args.n_real) {
-                                float4 o4 = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
-                                if (args.relu) {
-                                    o4.x = fmaxf(o4.x, 0.f); o4.y = fmaxf(o4.y, 0.f);
-                                    o4.z = fmaxf(o4.z, 0.f); o4.w = fmaxf(o4.w, 0.f);
-                                }
-                                *reinterpret_cast<float4*>(o + 4 * j) = o4;
-                            } else {
-                                for (int e = 0; e < 4; ++e) {
-                                    if (col0 + 4 * j + e < args.n_real) {
-                                        const float x = f[4 * j + e];
-                                        o[4 * j + e] = args.relu ? fmaxf(x, 0.f) : x;
-                                    }
-                                }
+                        for (int j = 0; j < 32; ++j) {
+                            if (col0 + j < args.n_real) {
+                                const float x = __uint_as_float(v[j]) + __ldg(args.bias + col0 + j);
+                                o[j] = args.relu ? fmaxf(x, 0.f) : x;
                             }
                         }
                     }
-                } else {
-                    if (row_ok && col0 < args.n_real) {
-                        const size_t off = static_cast<size_t>(row) * args.ldc + col0;
-                        if (args.residual != nullptr) {
-                            const uint4* r4 = reinterpret_cast<const uint4*>(
-                                reinterpret_cast<const uint16_t*>(args.residual) + off);
+                }
+            } else {
+                // ---- bf16 NHWC: TMEM -> regs -> (+bias, +residual, ReLU) -> swizzled smem -> TMA store
+#pragma unroll 1
+                for (int c64 = 0; c64 < BLOCK_N / 64; ++c64) {
+                    const int col0 = n_blk * BLOCK_N + c64 * 64;
+                    uint32_t res_base = 0;
+                    if (HAS_RES) {
+                        mbar_wait(&res_full_bar[rs], rphase);
+                        res_base = smem_u32(smem_res + rs * OUT_CHUNK_BYTES) + static_cast<uint32_t>(row_in_tile * 128);
+                    }
+                    uint4 packed[8];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        uint32_t v[32];
+                        tmem_ld_32x32(t_addr + static_cast<uint32_t>(c64 * 64 + h * 32), v);
+                        tmem_ld_wait();
+                        const float4* b4 = reinterpret_cast<const float4*>(args.bias + col0 + h * 32);
+                        float f[32];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 b = __ldg(b4 + j);
+                            f[4 * j + 0] = __uint_as_float(v[4 * j + 0]) + b.x;
+                            f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + b.y;
+                            f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + b.z;
+                            f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + b.w;
+                        }
+                        if (HAS_RES) {
 #pragma unroll
                             for (int j = 0; j < 4; ++j) {
-                                const uint4 r = ld_nc_v4(r4 + j);
+                                const int chunk16 = (h * 4 + j) ^ (row_in_tile & 7);     // 128B swizzle
+                                const uint4 r = ld_shared_v4(res_base + static_cast<uint32_t>(chunk16 * 16));
                                 f[8 * j + 0] += bf16_lo(r.x); f[8 * j + 1] += bf16_hi(r.x);
                                 f[8 * j + 2] += bf16_lo(r.y); f[8 * j + 3] += bf16_hi(r.y);
                                 f[8 * j + 4] += bf16_lo(r.z); f[8 * j + 5] += bf16_hi(r.z);
@@ -262,25 +301,51 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a,
 #pragma unroll
                             for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
                         }
-                        uint4* o4 = reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(args.out) + off);
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
-                            uint4 o;
-                            o.x = pack_bf16x2(f[8 * j + 0], f[8 * j + 1]);
-                            o.y = pack_bf16x2(f[8 * j + 2], f[8 * j + 3]);
-                            o.z = pack_bf16x2(f[8 * j + 4], f[8 * j + 5]);
-                            o.w = pack_bf16x2(f[8 * j + 6], f[8 * j + 7]);
-                            st_v4(o4 + j, o);
+                            packed[h * 4 + j].x = pack_bf16x2(f[8 * j + 0], f[8 * j + 1]);
+                            packed[h * 4 + j].y = pack_bf16x2(f[8 * j + 2], f[8 * j + 3]);
+                            packed[h * 4 + j].z = pack_bf16x2(f[8 * j + 4], f[8 * j + 5]);
+                            packed[h * 4 + j].w = pack_bf16x2(f[8 * j + 6], f[8 * j + 7]);
                         }
                     }
+                    if (HAS_RES) {
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&res_empty_bar[rs]);
+                        if (++rs == RES_STAGES) { rs = 0; rphase ^= 1u; }
+                    }
+                    if (c64 == BLOCK_N / 64 - 1) {
+                        // last TMEM read of this tile is done: hand the accumulator back before storing
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+                    }
+                    // staging buffer `ob` was handed to the TMA engine two chunks ago: make sure it has been read
+                    if (store_leader) tma_store_wait_read<OUT_BUFS - 1>();
+                    named_bar_sync(1, EPI_THREADS);
+                    const uint32_t o_base = smem_u32(smem_out + ob * OUT_CHUNK_BYTES) + static_cast<uint32_t>(row_in_tile * 128);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        const int chunk16 = j ^ (row_in_tile & 7);
+                        st_shared_v4(o_base + static_cast<uint32_t>(chunk16 * 16), packed[j]);
+                    }
+                    fence_proxy_async_smem();
+                    named_bar_sync(1, EPI_THREADS);
+                    if (store_leader) {
+                        tma_store_2d(&tmap_out, smem_out + ob * OUT_CHUNK_BYTES, col0, m_blk * BLOCK_M);
+                        tma_store_commit();
+                    }
+                    ob ^= 1;
                 }
             }
-            // all of this warp's TMEM reads for the stage are complete: hand it back to the MMA warp
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+            if (OUT_F32) {
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+            }
             if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1u; }
         }
+        if (!OUT_F32 && store_leader) tma_store_wait_all<0>();
     }
 
     tc_fence_before();
@@ -300,10 +365,10 @@ void set_err(char* err, size_t n, const char* msg) {
     if (err && n) snprintf(err, n, "%s", msg);
 }
 
-template <int BLOCK_N, int BLOCK_K, bool IM2COL, bool OUT_F32>
+template <int BLOCK_N, int BLOCK_K, bool IM2COL, bool OUT_F32, bool HAS_RES>
 cudaError_t launch_variant(const GemmPlan& p, const GemmArgs& a, int grid, cudaStream_t stream) {
-    using C = Cfg<BLOCK_N, BLOCK_K>;
-    auto kern = conv_gemm_kernel<BLOCK_N, BLOCK_K, IM2COL, OUT_F32>;
+    using C = Cfg<BLOCK_N, BLOCK_K, OUT_F32, HAS_RES>;
+    auto kern = conv_gemm_kernel<BLOCK_N, BLOCK_K, IM2COL, OUT_F32, HAS_RES>;
     static bool attr_set[64] = {};   // per instantiation, per device (one replica thread per device)
     int dev = 0;
     cudaGetDevice(&dev);
@@ -314,7 +379,7 @@ cudaError_t launch_variant(const GemmPlan& p, const GemmArgs& a, int grid, cudaS
         if (e != cudaSuccess) return e;
         attr_set[dev] = true;
     }
-    kern<<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(p.tmap_a, p.tmap_b, a);
+    kern<<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(p.tmap_a, p.tmap_b, p.tmap_out, p.tmap_res, a);
     return cudaGetLastError();
 }
 
@@ -472,8 +537,19 @@ bool gemm_plan_set_src(GemmPlan& p, const void* src, int batch_cap, char* err, s
     return true;
 }
 
-cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, const void* residual, void* out,
-                             int num_sms, cudaStream_t stream) {
+bool gemm_plan_set_dst(GemmPlan& p, const void* dst, int rows, char* err, size_t err_len) {
+    if (p.out_f32) return true;     // the fp32 epilogue stores directly
+    return encode_tiled_2d(&p.tmap_out, dst, static_cast<uint64_t>(p.ldc), static_cast<uint64_t>(rows), 64, BLOCK_M,
+                           CU_TENSOR_MAP_SWIZZLE_128B, err, err_len);
+}
+
+bool gemm_plan_set_res(GemmPlan& p, const void* res, int rows, char* err, size_t err_len) {
+    return encode_tiled_2d(&p.tmap_res, res, static_cast<uint64_t>(p.ldc), static_cast<uint64_t>(rows), 64, BLOCK_M,
+                           CU_TENSOR_MAP_SWIZZLE_128B, err, err_len);
+}
+
+cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, bool has_res, void* out_f32, int num_sms,
+                             cudaStream_t stream) {
     GemmArgs a;
     a.m_rows = m_rows;
     a.m_tiles = (m_rows + BLOCK_M - 1) / BLOCK_M;
@@ -489,29 +565,30 @@ cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, const void* residual
     a.ldc = p.ldc;
     a.relu = p.relu;
     a.bias = p.bias;
-    a.residual = residual;
-    a.out = out;
+    a.out = out_f32;
     const int total = a.m_tiles * a.n_tiles;
     if (total <= 0) return cudaSuccess;
     const int grid = total < num_sms ? total : num_sms;
-#define B2P_LAUNCH(BN, BK, IM, F32) return launch_variant<BN, BK, IM, F32>(p, a, grid, stream)
+#define B2P_LAUNCH(BN, BK, IM, F32, RES) return launch_variant<BN, BK, IM, F32, RES>(p, a, grid, stream)
     if (p.block_k == 16) {
-        if (p.block_n == 64 && p.im2col && !p.out_f32) B2P_LAUNCH(64, 16, true, false);
+        if (p.block_n == 64 && p.im2col && !p.out_f32 && !has_res) B2P_LAUNCH(64, 16, true, false, false);
         return cudaErrorInvalidConfiguration;
     }
     if (p.out_f32) {
-        if (p.block_n == 128 && !p.im2col) B2P_LAUNCH(128, 64, false, true);
+        if (p.block_n == 128 && !p.im2col && !has_res) B2P_LAUNCH(128, 64, false, true, false);
         return cudaErrorInvalidConfiguration;
     }
-    if (p.im2col) {
-        if (p.block_n == 64) B2P_LAUNCH(64, 64, true, false);
-        if (p.block_n == 128) B2P_LAUNCH(128, 64, true, false);
-        if (p.block_n == 256) B2P_LAUNCH(256, 64, true, false);
-    } else {
-        if (p.block_n == 64) B2P_LAUNCH(64, 64, false, false);
-        if (p.block_n == 128) B2P_LAUNCH(128, 64, false, false);
-        if (p.block_n == 256) B2P_LAUNCH(256, 64, false, false);
+#define B2P_PICK(BN)                                                   \
+    if (p.block_n == BN) {                                             \
+        if (p.im2col && has_res) B2P_LAUNCH(BN, 64, true, false, true); \
+        if (p.im2col) B2P_LAUNCH(BN, 64, true, false, false);          \
+        if (has_res) B2P_LAUNCH(BN, 64, false, false, true);           \
+        B2P_LAUNCH(BN, 64, false, false, false);                       \
     }
+    B2P_PICK(64)
+    B2P_PICK(128)
+    B2P_PICK(256)
+#undef B2P_PICK
 #undef B2P_LAUNCH
     return cudaErrorInvalidConfiguration;
 }

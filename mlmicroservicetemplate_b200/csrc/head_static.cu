@@ -129,7 +129,7 @@ extern "C" int32_t b2p_head_static(const void* feat, int32_t n, int32_t hw, int3
         b2p::set_global_error("b2p_head_static: %s", eb);
         return B2P_E_CUDA;
     }
-    e = b2p::gemm_plan_launch(plan, n, nullptr, logits, s->num_sms, st);
+    e = b2p::gemm_plan_launch(plan, n, false, logits, s->num_sms, st);
     if (e != cudaSuccess) {
         b2p::set_global_error("b2p_head_static: GEMM launch failed: %s", cudaGetErrorString(e));
         return B2P_E_CUDA;

@@ -11,6 +11,8 @@ namespace b2p {
 struct GemmPlan {
     CUtensorMap tmap_a;   // activations: 2-D tiled [rows, K] or 4-D im2col over NHWC
     CUtensorMap tmap_b;   // weights [out_c_pad, K] bf16, K-major
+    CUtensorMap tmap_out; // bf16 output [rows, out_c], 128 x 64 store boxes (unused by the fp32 epilogue)
+    CUtensorMap tmap_res; // bf16 residual [rows, out_c], same boxes (only when the op has a residual)
     int block_n = 0;      // 64 / 128 / 256
     int block_k = 64;     // 64 (128-byte swizzle) or 16 (32-byte swizzle, the stem)
     int im2col = 0;       // A operand through TMA im2col mode
@@ -36,9 +38,13 @@ bool gemm_plan_init(GemmPlan& p, const b2p_op& op, const void* weight_dev, int64
                     size_t err_len);
 // (Re)encodes the A-operand tensor map for a source buffer holding `batch_cap` images.
 bool gemm_plan_set_src(GemmPlan& p, const void* src, int batch_cap, char* err, size_t err_len);
-// Launches the persistent kernel for `m_rows` output rows.
-cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, const void* residual, void* out,
-                             int num_sms, cudaStream_t stream);
+// (Re)encode the output / residual tensor maps for buffers with `rows` rows of out_c bf16 each.
+// TMA clips stores beyond `rows`, so `rows` must not exceed what the buffer really holds.
+bool gemm_plan_set_dst(GemmPlan& p, const void* dst, int rows, char* err, size_t err_len);
+bool gemm_plan_set_res(GemmPlan& p, const void* res, int rows, char* err, size_t err_len);
+// Launches the persistent kernel for `m_rows` output rows.  `out_f32` is only read by LINEAR plans.
+cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, bool has_res, void* out_f32, int num_sms,
+                             cudaStream_t stream);
 
 // Records an error that is not tied to a handle; b2p_last_error(NULL) returns it.
 void set_global_error(const char* fmt, ...);
