@@ -51,7 +51,10 @@ enum b2p_op_kind {
     B2P_OP_MAXPOOL = 3,    /* kh x kw / stride / pad_lo max pool, NHWC bf16                          */
     B2P_OP_AVGPOOL = 4,    /* global average pool NHWC bf16 -> [n, c] bf16                           */
     B2P_OP_STEM_PACK = 5,  /* NCHW bf16 [n,3,H,W] -> 2x2 space-to-depth NHWC [n,H/2,W/2,16] bf16    */
-    B2P_OP_NCHW_TO_NHWC = 6 /* NCHW bf16 [n,c,H,W] -> NHWC bf16 (test helper, c % 8 == 0)            */
+    B2P_OP_NCHW_TO_NHWC = 6,/* NCHW bf16 [n,c,H,W] -> NHWC bf16 (test helper, c % 8 == 0)            */
+    B2P_OP_STEM_CONV = 7   /* ResNet stem on the s2d image [n,112,112,16]: 4x4 conv (pad 2/1) + bias +
+                              ReLU -> [n,112,112,64]; with reserved[0] = 1 the 3x3/s2/p1 max pool is
+                              fused and the output is [n,56,56,64]. Weight blob as for OP_CONV.       */
 };
 
 typedef struct b2p_op {

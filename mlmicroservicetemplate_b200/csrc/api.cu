@@ -17,6 +17,8 @@ char g_create_error[512] = "";
 struct OpPlan {
     b2p_op op;
     GemmPlan gemm;        // valid for CONV / LINEAR
+    StemPlan stem;        // valid for STEM_CONV
+    void* stem_image = nullptr;
     bool is_gemm = false;
     bool src_external = false;
     bool dst_external = false;
@@ -95,7 +97,7 @@ int validate_desc(const b2p_model_desc* d) {
     if (d->sub_batch < 0) return B2P_E_ARG;
     for (int i = 0; i < d->n_ops; ++i) {
         const b2p_op& o = d->ops[i];
-        if (o.kind < B2P_OP_CONV || o.kind > B2P_OP_NCHW_TO_NHWC) return B2P_E_ARG;
+        if (o.kind < B2P_OP_CONV || o.kind > B2P_OP_STEM_CONV) return B2P_E_ARG;
         auto ok_slot = [&](int s, bool allow_none) {
             if (s == B2P_SLOT_NONE) return allow_none;
             if (s == B2P_SLOT_OUTPUT) return true;
@@ -104,7 +106,7 @@ int validate_desc(const b2p_model_desc* d) {
         if (!ok_slot(o.src, false) || o.src == B2P_SLOT_OUTPUT) return B2P_E_ARG;
         if (!ok_slot(o.dst, false) || o.dst == B2P_SLOT_INPUT) return B2P_E_ARG;
         if (!ok_slot(o.res, true) || o.res == B2P_SLOT_OUTPUT) return B2P_E_ARG;
-        if (o.kind == B2P_OP_CONV || o.kind == B2P_OP_LINEAR) {
+        if (o.kind == B2P_OP_CONV || o.kind == B2P_OP_LINEAR || o.kind == B2P_OP_STEM_CONV) {
             if (o.weight < 0 || o.weight >= d->n_blobs || o.bias < 0 || o.bias >= d->n_blobs) return B2P_E_ARG;
         }
     }
@@ -144,6 +146,19 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
                         return B2P_E_CUDA;
                     }
                     e = gemm_plan_launch(p.gemm, rows, res != nullptr, dst, h->num_sms, st);
+                    break;
+                }
+                case B2P_OP_STEM_CONV: {
+                    if (o.dst == B2P_SLOT_OUTPUT)
+                        dst = static_cast<uint8_t*>(dst) + static_cast<size_t>(off) * h->out_elems * 2;
+                    if (o.src == B2P_SLOT_INPUT || o.dst == B2P_SLOT_OUTPUT) {
+                        char eb[256] = "";
+                        if (!stem_plan_init(p.stem, src, dst, nb, o.reserved[0], eb, sizeof eb)) {
+                            set_error(h, "%s", eb);
+                            return B2P_E_CUDA;
+                        }
+                    }
+                    e = stem_plan_launch(p.stem, nb, o.relu, h->num_sms, st);
                     break;
                 }
                 case B2P_OP_MAXPOOL:
@@ -224,6 +239,7 @@ int32_t b2p_destroy(b2p_handle* h) {
     if (!h) return B2P_OK;
     cudaSetDevice(h->device);
     cudaDeviceSynchronize();
+    for (OpPlan& op : h->ops) if (op.stem_image) cudaFree(op.stem_image);
     for (void* p : h->slots) if (p) cudaFree(p);
     for (void* p : h->blobs) if (p) cudaFree(p);
     if (h->slab_dev) cudaFree(h->slab_dev);
@@ -333,6 +349,23 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
             if (o.res != B2P_SLOT_NONE && !p.res_external) {
                 if (!h->slots[o.res]) B2P_FAIL(B2P_E_ARG, "op %d adds an empty slot", i);
                 if (!gemm_plan_set_res(p.gemm, h->slots[o.res], rows_cap, eb, sizeof eb))
+                    B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
+            }
+        } else if (o.kind == B2P_OP_STEM_CONV) {
+            if (o.in_h != 112 || o.in_w != 112 || o.in_c != 16 || o.out_c != 64 || o.kh != 4 || o.kw != 4 ||
+                h->blob_bytes[o.weight] != 64 * 16 * 16 * 2 || h->blob_bytes[o.bias] < 64 * 4)
+                B2P_FAIL(B2P_E_ARG, "op %d: STEM_CONV expects the 112x112x16 s2d stem with a [64][4][4][16] weight", i);
+            std::vector<uint16_t> image(64 * 16 * 16);
+            stem_pack_weight_image(static_cast<const uint16_t*>(desc->blob_ptrs[o.weight]), image.data());
+            if (cudaMalloc(&p.stem_image, image.size() * 2) != cudaSuccess ||
+                cudaMemcpy(p.stem_image, image.data(), image.size() * 2, cudaMemcpyHostToDevice) != cudaSuccess)
+                B2P_FAIL(B2P_E_NOMEM, "op %d: stem weight image upload failed", i);
+            p.stem.w_image = static_cast<const uint8_t*>(p.stem_image);
+            p.stem.bias = static_cast<const float*>(h->blobs[o.bias]);
+            p.stem.pool = o.reserved[0];
+            if (o.src != B2P_SLOT_INPUT && o.dst != B2P_SLOT_OUTPUT) {
+                if (!h->slots[o.src] || !h->slots[o.dst]) B2P_FAIL(B2P_E_ARG, "op %d uses an empty slot", i);
+                if (!stem_plan_init(p.stem, h->slots[o.src], h->slots[o.dst], h->chunk, o.reserved[0], eb, sizeof eb))
                     B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
             }
         } else if ((o.kind == B2P_OP_MAXPOOL || o.kind == B2P_OP_AVGPOOL) && o.in_c % 8 != 0) {

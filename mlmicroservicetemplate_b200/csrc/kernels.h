@@ -46,6 +46,19 @@ bool gemm_plan_set_res(GemmPlan& p, const void* res, int rows, char* err, size_t
 cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, bool has_res, void* out_f32, int num_sms,
                              cudaStream_t stream);
 
+// ------------------------------------------------------------------ dedicated stem (+ max pool) kernel
+struct StemPlan {
+    CUtensorMap tmap_in;    // s2d input [n,112,112,16] bf16, 4-D tiled, 8-channel boxes
+    CUtensorMap tmap_out;   // [rows, 64] bf16: one conv row (112) or one pooled row (56) per store
+    const uint8_t* w_image = nullptr;   // 32 KB shared-memory image of the weights (device)
+    const float* bias = nullptr;
+    int pool = 0;
+};
+// Re-lays the packed stem weight [64][4][4][16] into the [tap][k half][out ch][8] shared-memory image.
+void stem_pack_weight_image(const uint16_t* w_packed, uint16_t* image);
+bool stem_plan_init(StemPlan& p, const void* src_s2d, void* dst, int batch_cap, int pool, char* err, size_t err_len);
+cudaError_t stem_plan_launch(const StemPlan& p, int n, int relu, int num_sms, cudaStream_t stream);
+
 // Records an error that is not tied to a handle; b2p_last_error(NULL) returns it.
 void set_global_error(const char* fmt, ...);
 

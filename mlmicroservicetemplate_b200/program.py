@@ -108,9 +108,9 @@ def stem_s2d_weight(w: torch.Tensor) -> torch.Tensor:
 
 
 def _mk_op(kind, src, dst, res=B.SLOT_NONE, in_hwc=(0, 0, 0), out_hwc=(0, 0, 0), k=(1, 1), stride=1, pad=(0, 0),
-           relu=0, weight=-1, bias=-1) -> B.Op:
+           relu=0, weight=-1, bias=-1, flag0=0) -> B.Op:
     return B.Op(kind, src, dst, res, in_hwc[0], in_hwc[1], in_hwc[2], out_hwc[0], out_hwc[1], out_hwc[2],
-                k[0], k[1], stride, pad[0], pad[1], relu, weight, bias, (B.C.c_int32 * 4)(0, 0, 0, 0))
+                k[0], k[1], stride, pad[0], pad[1], relu, weight, bias, (B.C.c_int32 * 4)(flag0, 0, 0, 0))
 
 
 class _Builder:
@@ -135,7 +135,7 @@ class _Builder:
         return dst, (oh, ow, oc)
 
 
-def build_resnet_program(model: torch.nn.Module, name: str = "resnet") -> Program:
+def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_stem: bool = True) -> Program:
     """Walks a torchvision ResNet (SP/torchvision/models/resnet.py:266-282: conv1-bn1-relu-maxpool,
     layer1..4, avgpool, fc) and emits the program.  Works for BasicBlock and Bottleneck nets."""
     from torchvision.models.resnet import BasicBlock, Bottleneck
@@ -150,14 +150,27 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet") -> Progra
     p.ops.append(_mk_op(B.OP_STEM_PACK, B.SLOT_INPUT, s2d, in_hwc=(224, 224, 3), out_hwc=(112, 112, 16)))
     w, b = fold_bn(model.conv1.weight, model.bn1)
     ws = stem_s2d_weight(w).permute(0, 3, 1, 2).contiguous()          # back to [oc, ic=16, 4, 4]
-    c1, hwc = bld.conv(s2d, (112, 112, 16), ws, b, stride=1, pad=2, pad_hi=1, relu=True)
-    # the stem's FLOPs are accounted on the original 7x7x3 window, not the zero-padded s2d one
-    p.flops_per_image += 2.0 * 112 * 112 * 64 * (147 - 256)
-    p.release(s2d)
-    # maxpool 3x3/s2/p1
-    mp = p.alloc(56 * 56 * 64)
-    p.ops.append(_mk_op(B.OP_MAXPOOL, c1, mp, in_hwc=hwc, out_hwc=(56, 56, 64), k=(3, 3), stride=2, pad=(1, 1)))
-    p.release(c1)
+    mpool = model.maxpool
+    can_fuse = (fused_stem and tuple(model.conv1.kernel_size) == (7, 7) and model.conv1.out_channels == 64
+                and mpool.kernel_size == 3 and mpool.stride == 2 and mpool.padding == 1)
+    if can_fuse:
+        # dedicated stem kernel: conv + bias + ReLU + 3x3/s2 max pool in one pass, [n,56,56,64] out
+        wi = p.add_blob(pack_conv_weight(ws))
+        bi = p.add_blob(pad_bias(b, 64))
+        mp = p.alloc(56 * 56 * 64)
+        p.ops.append(_mk_op(B.OP_STEM_CONV, s2d, mp, in_hwc=(112, 112, 16), out_hwc=(56, 56, 64), k=(4, 4), stride=1,
+                            pad=(2, 1), relu=1, weight=wi, bias=bi, flag0=1))
+        p.flops_per_image += 2.0 * 112 * 112 * 64 * 147
+        p.release(s2d)
+    else:
+        c1, hwc = bld.conv(s2d, (112, 112, 16), ws, b, stride=1, pad=2, pad_hi=1, relu=True)
+        # the stem's FLOPs are accounted on the original 7x7x3 window, not the zero-padded s2d one
+        p.flops_per_image += 2.0 * 112 * 112 * 64 * (147 - 256)
+        p.release(s2d)
+        # maxpool 3x3/s2/p1
+        mp = p.alloc(56 * 56 * 64)
+        p.ops.append(_mk_op(B.OP_MAXPOOL, c1, mp, in_hwc=hwc, out_hwc=(56, 56, 64), k=(3, 3), stride=2, pad=(1, 1)))
+        p.release(c1)
     x, hwc = mp, (56, 56, 64)
 
     for layer in (model.layer1, model.layer2, model.layer3, model.layer4):
@@ -224,6 +237,19 @@ def single_conv_program(w: torch.Tensor, b: torch.Tensor, hwc, stride: int, pad:
     _, ohwc = bld.conv(B.SLOT_INPUT, hwc, w.float(), b.float(), stride, pad, relu,
                        res=B.SLOT_INPUT if with_residual else B.SLOT_NONE, dst=B.SLOT_OUTPUT, pad_hi=pad_hi)
     p.out_elems = ohwc[0] * ohwc[1] * ohwc[2]
+    return p
+
+
+def single_stem_program(w4: torch.Tensor, b: torch.Tensor, pool: bool) -> Program:
+    """One STEM_CONV op (external s2d NHWC16 input -> external output); w4 is [64, 16, 4, 4] fp32."""
+    p = Program(name="single_stem")
+    p.in_elems = 112 * 112 * 16
+    wi = p.add_blob(pack_conv_weight(w4.float()))
+    bi = p.add_blob(pad_bias(b, 64))
+    side = 56 if pool else 112
+    p.out_elems = side * side * 64
+    p.ops.append(_mk_op(B.OP_STEM_CONV, B.SLOT_INPUT, B.SLOT_OUTPUT, in_hwc=(112, 112, 16), out_hwc=(side, side, 64),
+                        k=(4, 4), stride=1, pad=(2, 1), relu=1, weight=wi, bias=bi, flag0=int(pool)))
     return p
 
 

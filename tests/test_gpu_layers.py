@@ -71,6 +71,33 @@ def test_conv_stem_s2d_shape(cuda_device):
     _run_conv(2, (112, 112, 16), 64, 4, 1, 2, True, False, seed=7, pad_hi=1)
 
 
+@pytest.mark.parametrize("pool", [False, True], ids=["conv", "conv+maxpool"])
+@pytest.mark.parametrize("n", [1, 3])
+def test_stem_dedicated_kernel(pool, n, cuda_device):
+    """OP_STEM_CONV: 4x4/pad(2,1) conv over the s2d image + bias + ReLU (+ fused 3x3/s2/p1 max pool)."""
+    from mlmicroservicetemplate_b200 import backend as B, program as P
+    g = torch.Generator().manual_seed(31 + n)
+    x = _bf16r(torch.randn(n, 112, 112, 16, generator=g))
+    w = _bf16r(torch.randn(64, 16, 4, 4, generator=g) / 16.0)
+    b = torch.randn(64, generator=g) * 0.1
+    rep = B.Replica(0, P.single_stem_program(w, b, pool), max_batch=n)
+    side = 56 if pool else 112
+    out = torch.full((n, side, side, 64), float("nan"), dtype=torch.bfloat16, device="cuda")
+    rep.forward(x.to(torch.bfloat16).cuda(), n, out)
+    torch.cuda.synchronize()
+    ref = F.conv2d(F.pad(x.permute(0, 3, 1, 2), (2, 1, 2, 1)), w, b).relu()
+    if pool:
+        ref = F.max_pool2d(ref, 3, 2, 1)
+    ref = ref.permute(0, 2, 3, 1)
+    got = out.float().cpu()
+    rep.close()
+    err = (got - ref).abs()
+    bad = (err > 2.0 ** -7 * ref.abs() + 2e-2).sum().item()
+    print(f"stem pool={pool} n={n}: max_err={err.max().item():.4g} max_ref={ref.abs().max().item():.4g} bad={bad}/{err.numel()}")
+    assert not torch.isnan(got).any()
+    assert bad == 0
+
+
 def test_conv_sub_batched(cuda_device):
     # same op run in chunks of 2 images: exercises the external-source re-encode and chunk offsets
     _run_conv(5, (28, 28, 128), 128, 3, 1, 1, True, False, seed=11, sub_batch=2)

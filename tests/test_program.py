@@ -30,6 +30,13 @@ def interpret(prog: P.Program, x_nchw: torch.Tensor) -> torch.Tensor:
                 y = y + slots[op.res]
             if op.relu:
                 y = y.relu()
+        elif op.kind == B.OP_STEM_CONV:
+            w = prog.blobs[op.weight].float()[: op.out_c]
+            b = prog.blobs[op.bias][: op.out_c]
+            y = F.conv2d(F.pad(src.permute(0, 3, 1, 2), (2, 1, 2, 1)), w.permute(0, 3, 1, 2), b).relu()
+            if op.reserved[0]:
+                y = F.max_pool2d(y, 3, 2, 1)
+            y = y.permute(0, 2, 3, 1)
         elif op.kind == B.OP_MAXPOOL:
             y = F.max_pool2d(src.permute(0, 3, 1, 2), op.kh, op.stride, op.pad_lo).permute(0, 2, 3, 1)
         elif op.kind == B.OP_AVGPOOL:
