@@ -40,8 +40,15 @@ struct b2p_handle {
     std::vector<void*> blobs;            // device copies of the weight blobs
     std::vector<int64_t> blob_bytes;
     // predict-chain staging (handle-owned)
-    uint8_t* slab_dev = nullptr;
-    int64_t slab_cap = 0;
+    // predict_host input staging: two device slabs filled on a private copy stream, so the H2D copy
+    // of call i+1 overlaps the kernels of call i (which run on the caller's stream)
+    uint8_t* slab_dev[2] = {nullptr, nullptr};
+    int64_t slab_cap[2] = {0, 0};
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copied[2] = {};      // H2D into slab i finished (copy stream)
+    cudaEvent_t ev_consumed[2] = {};    // K1 finished reading slab i (caller's stream)
+    bool slab_used[2] = {false, false};
+    int slab_idx = 0;
     // descriptor staging: a ring of pinned + device slots so that back-to-back asynchronous calls
     // never overwrite a descriptor block whose host->device copy is still queued
     static constexpr int RING = 8;
@@ -55,7 +62,7 @@ struct b2p_handle {
     float* logits_dev = nullptr;         // [max_batch, out_elems]
     float* probs_dev = nullptr;
     int32_t* idx_dev = nullptr;
-    cudaEvent_t ev[6] = {};
+    cudaEvent_t ev[7] = {};   // copy begin/end (copy stream), K1 begin, K1/K2/K3 end, D2H end (caller's stream)
     bool ev_valid = false;
     b2p_stats stats = {};
     char err[512] = "";
@@ -242,7 +249,12 @@ int32_t b2p_destroy(b2p_handle* h) {
     for (OpPlan& op : h->ops) if (op.stem_image) cudaFree(op.stem_image);
     for (void* p : h->slots) if (p) cudaFree(p);
     for (void* p : h->blobs) if (p) cudaFree(p);
-    if (h->slab_dev) cudaFree(h->slab_dev);
+    for (int i = 0; i < 2; ++i) {
+        if (h->slab_dev[i]) cudaFree(h->slab_dev[i]);
+        if (h->ev_copied[i]) cudaEventDestroy(h->ev_copied[i]);
+        if (h->ev_consumed[i]) cudaEventDestroy(h->ev_consumed[i]);
+    }
+    if (h->copy_stream) cudaStreamDestroy(h->copy_stream);
     for (int r = 0; r < b2p_handle::RING; ++r) {
         if (h->imgs_dev[r]) cudaFree(h->imgs_dev[r]);
         if (h->imgs_pinned[r]) cudaFreeHost(h->imgs_pinned[r]);
@@ -388,6 +400,12 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
         B2P_FAIL(B2P_E_NOMEM, "staging allocation failed");
     for (auto& e : h->ev)
         if (cudaEventCreate(&e) != cudaSuccess) B2P_FAIL(B2P_E_CUDA, "cudaEventCreate failed");
+    if (cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess)
+        B2P_FAIL(B2P_E_CUDA, "copy stream creation failed");
+    for (int i = 0; i < 2; ++i)
+        if (cudaEventCreateWithFlags(&h->ev_copied[i], cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&h->ev_consumed[i], cudaEventDisableTiming) != cudaSuccess)
+            B2P_FAIL(B2P_E_CUDA, "cudaEventCreate failed");
     h->ev_valid = true;
     if (cudaDeviceSynchronize() != cudaSuccess) B2P_FAIL(B2P_E_CUDA, "device sync after create failed");
 #undef B2P_FAIL
@@ -401,8 +419,10 @@ int32_t b2p_stats_get(b2p_handle* h, b2p_stats* out) {
     if (!h || !out) return B2P_E_ARG;
     if (h->ev_valid && h->stats.calls > 0) {
         float ms[5];
+        const int from[5] = {0, 2, 3, 4, 5};
         bool ok = true;
-        for (int i = 0; i < 5 && ok; ++i) ok = cudaEventElapsedTime(&ms[i], h->ev[i], h->ev[i + 1]) == cudaSuccess;
+        for (int i = 0; i < 5 && ok; ++i)
+            ok = cudaEventElapsedTime(&ms[i], h->ev[from[i]], h->ev[from[i] + 1]) == cudaSuccess;
         if (ok) {
             h->stats.ms_h2d = ms[0];
             h->stats.ms_preprocess = ms[1];
@@ -468,36 +488,48 @@ int32_t b2p_predict_host(b2p_handle* h, const uint8_t* slab_host, int64_t slab_b
     if (k <= 0 || k > B2P_MAX_TOPK) { set_error(h, "k=%d out of range", k); return B2P_E_LIMIT; }
     B2P_CUDA(h, cudaSetDevice(h->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    if (slab_bytes > h->slab_cap) {
-        // grow-only device slab; first call (or a larger batch) pays for the allocation
+    const int si = h->slab_idx;
+    h->slab_idx ^= 1;
+    if (slab_bytes > h->slab_cap[si]) {
+        // grow-only device slab; the first calls (or a larger batch) pay for the allocation
         B2P_CUDA(h, cudaStreamSynchronize(st));
-        if (h->slab_dev) cudaFree(h->slab_dev);
-        h->slab_dev = nullptr;
-        h->slab_cap = 0;
+        B2P_CUDA(h, cudaStreamSynchronize(h->copy_stream));
+        if (h->slab_dev[si]) cudaFree(h->slab_dev[si]);
+        h->slab_dev[si] = nullptr;
+        h->slab_cap[si] = 0;
+        h->slab_used[si] = false;
         const int64_t cap = ((slab_bytes + (1 << 20) - 1) >> 20) << 20;
-        if (cudaMalloc(&h->slab_dev, static_cast<size_t>(cap)) != cudaSuccess) {
+        if (cudaMalloc(&h->slab_dev[si], static_cast<size_t>(cap)) != cudaSuccess) {
             set_error(h, "cudaMalloc(%lld) for the image slab failed", (long long)cap);
             return B2P_E_NOMEM;
         }
-        h->slab_cap = cap;
+        h->slab_cap[si] = cap;
     }
-    B2P_CUDA(h, cudaEventRecord(h->ev[0], st));
-    B2P_CUDA(h, cudaMemcpyAsync(h->slab_dev, slab_host, static_cast<size_t>(slab_bytes), cudaMemcpyHostToDevice, st));
-    B2P_CUDA(h, cudaEventRecord(h->ev[1], st));
-    int rc = b2p_preprocess(h, h->slab_dev, imgs, n, h->x_dev, 0, stream);
-    if (rc != B2P_OK) return rc;
+    // copy stream: wait until the kernels of two calls ago have consumed this slab, then copy
+    if (h->slab_used[si]) B2P_CUDA(h, cudaStreamWaitEvent(h->copy_stream, h->ev_consumed[si], 0));
+    B2P_CUDA(h, cudaEventRecord(h->ev[0], h->copy_stream));
+    B2P_CUDA(h, cudaMemcpyAsync(h->slab_dev[si], slab_host, static_cast<size_t>(slab_bytes), cudaMemcpyHostToDevice,
+                                h->copy_stream));
+    B2P_CUDA(h, cudaEventRecord(h->ev[1], h->copy_stream));
+    B2P_CUDA(h, cudaEventRecord(h->ev_copied[si], h->copy_stream));
+    B2P_CUDA(h, cudaStreamWaitEvent(st, h->ev_copied[si], 0));
     B2P_CUDA(h, cudaEventRecord(h->ev[2], st));
-    rc = b2p_forward(h, h->x_dev, n, h->logits_dev, stream);
+    int rc = b2p_preprocess(h, h->slab_dev[si], imgs, n, h->x_dev, 0, stream);
     if (rc != B2P_OK) return rc;
     B2P_CUDA(h, cudaEventRecord(h->ev[3], st));
-    rc = b2p_softmax_topk(h, h->logits_dev, n, h->classes, k, h->probs_dev, h->idx_dev, stream);
+    B2P_CUDA(h, cudaEventRecord(h->ev_consumed[si], st));
+    h->slab_used[si] = true;
+    rc = b2p_forward(h, h->x_dev, n, h->logits_dev, stream);
     if (rc != B2P_OK) return rc;
     B2P_CUDA(h, cudaEventRecord(h->ev[4], st));
+    rc = b2p_softmax_topk(h, h->logits_dev, n, h->classes, k, h->probs_dev, h->idx_dev, stream);
+    if (rc != B2P_OK) return rc;
+    B2P_CUDA(h, cudaEventRecord(h->ev[5], st));
     B2P_CUDA(h, cudaMemcpyAsync(probs_host, h->probs_dev, sizeof(float) * static_cast<size_t>(n) * k,
                                 cudaMemcpyDeviceToHost, st));
     B2P_CUDA(h, cudaMemcpyAsync(idx_host, h->idx_dev, sizeof(int32_t) * static_cast<size_t>(n) * k,
                                 cudaMemcpyDeviceToHost, st));
-    B2P_CUDA(h, cudaEventRecord(h->ev[5], st));
+    B2P_CUDA(h, cudaEventRecord(h->ev[6], st));
     h->stats.calls += 1;
     return B2P_OK;
 }

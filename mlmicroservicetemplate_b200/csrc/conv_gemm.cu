@@ -129,10 +129,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         tmem_alloc(tmem_slot, C::TMEM_COLS);
         tmem_relinquish();
     }
+    pdl_launch_dependents();      // the next kernel may start its own prologue
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();                   // predecessors done: activations readable, output buffers writable
 
     if (warp_idx == 0) {
         // ===================================================================== TMA producer
@@ -379,8 +381,8 @@ cudaError_t launch_variant(const GemmPlan& p, const GemmArgs& a, int grid, cudaS
         if (e != cudaSuccess) return e;
         attr_set[dev] = true;
     }
-    kern<<<grid, NUM_THREADS, C::SMEM_BYTES, stream>>>(p.tmap_a, p.tmap_b, p.tmap_out, p.tmap_res, a);
-    return cudaGetLastError();
+    return launch_pdl(kern, dim3(grid), dim3(NUM_THREADS), C::SMEM_BYTES, stream, p.tmap_a, p.tmap_b, p.tmap_out,
+                      p.tmap_res, a);
 }
 
 }  // namespace

@@ -7,6 +7,25 @@
 
 namespace b2p {
 
+// Launch with programmatic stream serialization: the kernel may become resident while its
+// predecessor in the stream is still draining.  Every kernel launched through this helper MUST
+// execute griddepcontrol.wait (ptx.cuh: pdl_wait) before it touches global memory.
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                              Args&&... args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(args)...);
+}
+
 // ------------------------------------------------------------------ conv / GEMM (tcgen05)
 struct GemmPlan {
     CUtensorMap tmap_a;   // activations: 2-D tiled [rows, K] or 4-D im2col over NHWC

@@ -15,6 +15,8 @@ namespace {
 // into a 4x4/s1 conv with 16-channel pixels that TMA im2col can fetch (32 B per pixel).
 __global__ void stem_pack_kernel(const uint16_t* __restrict__ x, uint4* __restrict__ out, int n, int h,
                                  int w) {
+    pdl_launch_dependents();
+    pdl_wait();
     const int oh = h >> 1, ow = w >> 1;
     const long total = static_cast<long>(n) * oh * ow;
     for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
@@ -77,6 +79,8 @@ __global__ void nchw_to_nhwc_kernel(const uint16_t* __restrict__ x, uint16_t* __
 // nn.MaxPool2d's implicit -inf padding does (SP/torchvision/models/resnet.py:200).
 __global__ void maxpool_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int n, int in_h,
                                int in_w, int c8, int out_h, int out_w, int k, int stride, int pad) {
+    pdl_launch_dependents();
+    pdl_wait();
     const long total = static_cast<long>(n) * out_h * out_w * c8;
     for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<long>(gridDim.x) * blockDim.x) {
@@ -113,6 +117,8 @@ __global__ void maxpool_kernel(const uint4* __restrict__ x, uint4* __restrict__ 
 // [n, hw, c] bf16 -> [n, c] bf16, fp32 accumulation (AdaptiveAvgPool2d((1,1)), resnet.py:205).
 __global__ void avgpool_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int n, int hw,
                                int c8) {
+    pdl_launch_dependents();
+    pdl_wait();
     const long total = static_cast<long>(n) * c8;
     for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
          i += static_cast<long>(gridDim.x) * blockDim.x) {
@@ -200,9 +206,8 @@ inline int grid_for(long total, int block, int cap = 148 * 16) {
 
 cudaError_t launch_stem_pack(const void* x, void* out, int n, int h, int w, cudaStream_t s) {
     const long total = static_cast<long>(n) * (h / 2) * (w / 2);
-    stem_pack_kernel<<<grid_for(total, 256), 256, 0, s>>>(static_cast<const uint16_t*>(x),
-                                                          static_cast<uint4*>(out), n, h, w);
-    return cudaGetLastError();
+    return launch_pdl(stem_pack_kernel, dim3(grid_for(total, 256)), dim3(256), 0, s, static_cast<const uint16_t*>(x),
+                      static_cast<uint4*>(out), n, h, w);
 }
 
 cudaError_t launch_nchw_to_nhwc(const void* x, void* out, int n, int c, int h, int w, cudaStream_t s) {
@@ -216,17 +221,14 @@ cudaError_t launch_nchw_to_nhwc(const void* x, void* out, int n, int c, int h, i
 cudaError_t launch_maxpool(const void* x, void* out, int n, int in_h, int in_w, int c, int out_h,
                            int out_w, int k, int stride, int pad, cudaStream_t s) {
     const long total = static_cast<long>(n) * out_h * out_w * (c / 8);
-    maxpool_kernel<<<grid_for(total, 256), 256, 0, s>>>(static_cast<const uint4*>(x),
-                                                        static_cast<uint4*>(out), n, in_h, in_w, c / 8,
-                                                        out_h, out_w, k, stride, pad);
-    return cudaGetLastError();
+    return launch_pdl(maxpool_kernel, dim3(grid_for(total, 256)), dim3(256), 0, s, static_cast<const uint4*>(x),
+                      static_cast<uint4*>(out), n, in_h, in_w, c / 8, out_h, out_w, k, stride, pad);
 }
 
 cudaError_t launch_avgpool(const void* x, void* out, int n, int hw, int c, cudaStream_t s) {
     const long total = static_cast<long>(n) * (c / 8);
-    avgpool_kernel<<<grid_for(total, 128), 128, 0, s>>>(static_cast<const uint4*>(x),
-                                                        static_cast<uint4*>(out), n, hw, c / 8);
-    return cudaGetLastError();
+    return launch_pdl(avgpool_kernel, dim3(grid_for(total, 128)), dim3(128), 0, s, static_cast<const uint4*>(x),
+                      static_cast<uint4*>(out), n, hw, c / 8);
 }
 
 cudaError_t launch_softmax_topk(const float* logits, int n, int classes, int k, float* probs,

@@ -116,6 +116,11 @@ __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
     return r;
 }
 
+// Programmatic dependent launch: let the next kernel in the stream start its prologue early /
+// wait until every kernel this one depends on has completed and flushed its memory.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
 // ----------------------------------------------------------------- tcgen05
 __device__ __forceinline__ void tmem_alloc(uint32_t* dst_smem, uint32_t ncols) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(

@@ -126,10 +126,12 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
         tmem_alloc(tmem_slot, C::TMEM_COLS);
         tmem_relinquish();
     }
+    pdl_launch_dependents();
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
 
     if (warp_idx == 0) {
         // ===================================================================== TMA producer
@@ -364,8 +366,8 @@ cudaError_t stem_plan_launch(const StemPlan& p, int n, int relu, int num_sms, cu
             if (e != cudaSuccess) return e;
             attr_set[dev][1] = true;
         }
-        stem_kernel<true><<<grid, STEM_THREADS, StemCfg<true>::SMEM_BYTES, stream>>>(p.tmap_in, p.tmap_out, p.w_image,
-                                                                                     p.bias, n, relu);
+        return launch_pdl(stem_kernel<true>, dim3(grid), dim3(STEM_THREADS), StemCfg<true>::SMEM_BYTES, stream, p.tmap_in,
+                          p.tmap_out, p.w_image, p.bias, n, relu);
     } else {
         if (!attr_set[dev][0]) {
             cudaError_t e = cudaFuncSetAttribute(stem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -373,8 +375,8 @@ cudaError_t stem_plan_launch(const StemPlan& p, int n, int relu, int num_sms, cu
             if (e != cudaSuccess) return e;
             attr_set[dev][0] = true;
         }
-        stem_kernel<false><<<grid, STEM_THREADS, StemCfg<false>::SMEM_BYTES, stream>>>(p.tmap_in, p.tmap_out, p.w_image,
-                                                                                      p.bias, n, relu);
+        return launch_pdl(stem_kernel<false>, dim3(grid), dim3(STEM_THREADS), StemCfg<false>::SMEM_BYTES, stream, p.tmap_in,
+                          p.tmap_out, p.w_image, p.bias, n, relu);
     }
     return cudaGetLastError();
 }
