@@ -1,0 +1,92 @@
+"""The whole stack on a GPU: HTTP POST /predict (multipart JPEG/PNG) -> decode thread -> micro-batch
+queue -> b2p_predict_host on the replica -> result dict, against the oracle's predict() on the very
+same encoded bytes (reference contract src/model/model.py:16-31 + src/server/main.py:119-140)."""
+import io
+import os
+import threading
+import time
+from types import SimpleNamespace
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def _encoded(seed, h, w, fmt):
+    from PIL import Image
+    from oracle import images
+    buf = io.BytesIO()
+    Image.fromarray(images.synthetic_image(seed, h, w)).save(buf, format=fmt, **({"quality": 90} if fmt == "JPEG" else {}))
+    return buf.getvalue()
+
+
+@pytest.fixture()
+def live_server(monkeypatch, cuda_device):
+    for k, v in dict(MODEL="resnet18", REGISTER="0", MAX_BATCH="16", MAX_WAIT_US="20000", TOPK="5",
+                     PREPROCESS="preset", GPUS="0", SEED="0").items():
+        monkeypatch.setenv(k, v)
+    import concurrent.futures as cf
+    from fastapi.testclient import TestClient
+    from mlmicroservicetemplate_b200.src.model import model as plugin
+    from mlmicroservicetemplate_b200.src.server import dependency, main
+    plugin.shutdown()
+    dependency.pool = cf.ThreadPoolExecutor(4)
+    main.dep.pool = dependency.pool
+    main._init_submitted = False
+    dependency.model_settings.ready_to_predict = False
+    with TestClient(main.app, raise_server_exceptions=False) as c:
+        t0 = time.time()
+        while not dependency.model_settings.ready_to_predict and time.time() - t0 < 120:
+            time.sleep(0.05)
+        assert dependency.model_settings.ready_to_predict, "init() did not finish"
+        yield c, plugin
+    plugin.shutdown()
+
+
+def test_concurrent_predict_matches_the_oracle(live_server):
+    client, plugin = live_server
+    from oracle import model as om
+    om.init(arch="resnet18", topk=5, mode="preset")
+    sizes = [(224, 224), (256, 256), (300, 400), (480, 640), (333, 517), (720, 1280)]
+    payloads = [_encoded(500 + i, *sizes[i % len(sizes)], "JPEG" if i % 3 else "PNG") for i in range(48)]
+    want = [om.predict(SimpleNamespace(file=io.BytesIO(b))) for b in payloads]
+
+    got, lat = [None] * len(payloads), [0.0] * len(payloads)
+    def post(i):
+        t0 = time.perf_counter()
+        got[i] = client.post("/predict", files={"image_file": (f"{i}.img", payloads[i], "application/octet-stream")})
+        lat[i] = time.perf_counter() - t0
+    threads = [threading.Thread(target=post, args=(i,)) for i in range(len(payloads))]
+    [t.start() for t in threads]
+    [t.join() for t in threads]
+
+    for i, (r, w) in enumerate(zip(got, want)):
+        assert r.status_code == 200, r.text
+        body = r.json()
+        assert body["status"] == "success" and body["result"]["classes"] == w["classes"]
+        res = body["result"]["result"]
+        top_got = max(res, key=res.get)
+        top_want = max(w["result"], key=w["result"].get)
+        assert top_got == top_want, f"request {i}: top-1 {top_got} != oracle {top_want}"
+        assert abs(res[top_got] - w["result"][top_want]) < 5e-3
+    sizes_seen = plugin._state["engine"].batch_sizes
+    assert sum(sizes_seen) == len(payloads) and max(sizes_seen) > 1, "concurrent requests must share GPU batches"
+    lat.sort()
+    print(f"/predict x{len(payloads)} concurrent: batches {sizes_seen}, p50 {1e3 * lat[len(lat) // 2]:.1f} ms, "
+          f"p99 {1e3 * lat[-1]:.1f} ms")
+
+
+def test_blocking_predict_and_error_paths(live_server):
+    client, plugin = live_server
+    out = plugin.predict(SimpleNamespace(file=io.BytesIO(_encoded(1, 300, 300, "PNG"))))
+    assert len(out["classes"]) == 1000 and len(out["result"]) == 5 and abs(sum(out["result"].values()) - 1.0) < 1.0
+    assert client.post("/predict", files={"image_file": ("x", b"not an image", "image/jpeg")}).status_code == 500
+    assert client.post("/predict", files={"other": ("x", b"1", "image/jpeg")}).status_code == 422
+    assert client.get("/status").json()["status"] == "success"
+    # greyscale and RGBA uploads are converted to RGB by the decode stage
+    from PIL import Image
+    for mode in ("L", "RGBA"):
+        buf = io.BytesIO()
+        Image.new(mode, (260, 300), 128).save(buf, format="PNG")
+        assert client.post("/predict", files={"image_file": ("x.png", buf.getvalue(), "image/png")}).status_code == 200
