@@ -52,9 +52,18 @@ enum b2p_op_kind {
     B2P_OP_AVGPOOL = 4,    /* global average pool NHWC bf16 -> [n, c] bf16                           */
     B2P_OP_STEM_PACK = 5,  /* NCHW bf16 [n,3,H,W] -> 2x2 space-to-depth NHWC [n,H/2,W/2,16] bf16    */
     B2P_OP_NCHW_TO_NHWC = 6,/* NCHW bf16 [n,c,H,W] -> NHWC bf16 (test helper, c % 8 == 0)            */
-    B2P_OP_STEM_CONV = 7   /* ResNet stem on the s2d image [n,112,112,16]: 4x4 conv (pad 2/1) + bias +
+    B2P_OP_STEM_CONV = 7,  /* ResNet stem on the s2d image [n,112,112,16]: 4x4 conv (pad 2/1) + bias +
                               ReLU -> [n,112,112,64]; with reserved[0] = 1 the 3x3/s2/p1 max pool is
                               fused and the output is [n,56,56,64]. Weight blob as for OP_CONV.       */
+    /* ViT (SP/torchvision/models/vision_transformer.py); a token matrix is an "image" of in_h = tokens,
+       in_w = 1, so linear layers are OP_CONV 1x1 (relu = 2 selects exact-erf GELU).                   */
+    B2P_OP_PATCHIFY = 8,   /* NCHW bf16 [n,3,224,224] -> 16x16 patches [n*196, 768] bf16 (c,ky,kx order)*/
+    B2P_OP_TOKENS = 9,     /* [cls | src[n,in_h-1,c]] + pos -> [n,in_h,c]; weight blob = pos f32 [in_h*c],
+                              bias blob = class token f32 [c]                                            */
+    B2P_OP_LAYERNORM = 10, /* per-token LayerNorm over c, eps = 1e-6; weight/bias blobs = gamma/beta f32;
+                              reserved[0] = 1: only token 0 of each image -> [n, c]                      */
+    B2P_OP_ATTENTION = 11  /* softmax(Q K^T / sqrt(64)) V per head on packed QKV [n,in_h,3c] -> [n,in_h,c];
+                              reserved[0] = number of heads (head dim 64)                                */
 };
 
 typedef struct b2p_op {
@@ -64,7 +73,7 @@ typedef struct b2p_op {
     int32_t out_h, out_w, out_c;
     int32_t kh, kw, stride;
     int32_t pad_lo, pad_hi;         /* zero padding before / after, same on both axes              */
-    int32_t relu;
+    int32_t relu;                   /* 0 none, 1 ReLU, 2 GELU (exact erf)                          */
     int32_t weight, bias;           /* blob indices: weight bf16 [out_c_pad][kh][kw][in_c], bias f32 */
     int32_t reserved[4];
 } b2p_op;

@@ -18,6 +18,7 @@ struct OpPlan {
     b2p_op op;
     GemmPlan gemm;        // valid for CONV / LINEAR
     StemPlan stem;        // valid for STEM_CONV
+    AttentionPlan att;    // valid for ATTENTION
     void* stem_image = nullptr;
     bool is_gemm = false;
     bool src_external = false;
@@ -104,7 +105,7 @@ int validate_desc(const b2p_model_desc* d) {
     if (d->sub_batch < 0) return B2P_E_ARG;
     for (int i = 0; i < d->n_ops; ++i) {
         const b2p_op& o = d->ops[i];
-        if (o.kind < B2P_OP_CONV || o.kind > B2P_OP_STEM_CONV) return B2P_E_ARG;
+        if (o.kind < B2P_OP_CONV || o.kind > B2P_OP_ATTENTION) return B2P_E_ARG;
         auto ok_slot = [&](int s, bool allow_none) {
             if (s == B2P_SLOT_NONE) return allow_none;
             if (s == B2P_SLOT_OUTPUT) return true;
@@ -113,7 +114,8 @@ int validate_desc(const b2p_model_desc* d) {
         if (!ok_slot(o.src, false) || o.src == B2P_SLOT_OUTPUT) return B2P_E_ARG;
         if (!ok_slot(o.dst, false) || o.dst == B2P_SLOT_INPUT) return B2P_E_ARG;
         if (!ok_slot(o.res, true) || o.res == B2P_SLOT_OUTPUT) return B2P_E_ARG;
-        if (o.kind == B2P_OP_CONV || o.kind == B2P_OP_LINEAR || o.kind == B2P_OP_STEM_CONV) {
+        if (o.kind == B2P_OP_CONV || o.kind == B2P_OP_LINEAR || o.kind == B2P_OP_STEM_CONV ||
+            o.kind == B2P_OP_TOKENS || o.kind == B2P_OP_LAYERNORM) {
             if (o.weight < 0 || o.weight >= d->n_blobs || o.bias < 0 || o.bias >= d->n_blobs) return B2P_E_ARG;
         }
     }
@@ -166,6 +168,36 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
                         }
                     }
                     e = stem_plan_launch(p.stem, nb, o.relu, h->num_sms, st);
+                    break;
+                }
+                case B2P_OP_PATCHIFY:
+                    e = launch_patchify(src, dst, nb, st);
+                    break;
+                case B2P_OP_TOKENS:
+                    e = launch_tokens(src, static_cast<const float*>(h->blobs[o.bias]),
+                                      static_cast<const float*>(h->blobs[o.weight]), dst, nb, o.in_h, o.in_c, st);
+                    break;
+                case B2P_OP_LAYERNORM: {
+                    const bool cls_only = o.reserved[0] != 0;
+                    if (o.dst == B2P_SLOT_OUTPUT)
+                        dst = static_cast<uint8_t*>(dst) + static_cast<size_t>(off) * h->out_elems * 2;
+                    e = launch_layernorm(src, static_cast<const float*>(h->blobs[o.weight]),
+                                         static_cast<const float*>(h->blobs[o.bias]), dst,
+                                         cls_only ? nb : static_cast<long>(nb) * o.in_h, o.in_c,
+                                         cls_only ? static_cast<long>(o.in_h) * o.in_c : o.in_c, 1e-6f, st);
+                    break;
+                }
+                case B2P_OP_ATTENTION: {
+                    if (o.dst == B2P_SLOT_OUTPUT)
+                        dst = static_cast<uint8_t*>(dst) + static_cast<size_t>(off) * h->out_elems * 2;
+                    if (o.src == B2P_SLOT_INPUT) {
+                        char eb[256] = "";
+                        if (!attention_plan_init(p.att, src, nb, o.in_h, o.in_c, o.reserved[0], eb, sizeof eb)) {
+                            set_error(h, "%s", eb);
+                            return B2P_E_CUDA;
+                        }
+                    }
+                    e = attention_plan_launch(p.att, dst, nb, st);
                     break;
                 }
                 case B2P_OP_MAXPOOL:
@@ -380,6 +412,17 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
                 if (!stem_plan_init(p.stem, h->slots[o.src], h->slots[o.dst], h->chunk, o.reserved[0], eb, sizeof eb))
                     B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
             }
+        } else if (o.kind == B2P_OP_ATTENTION) {
+            if (o.src != B2P_SLOT_INPUT) {
+                if (!h->slots[o.src]) B2P_FAIL(B2P_E_ARG, "op %d reads an empty slot", i);
+                if (!attention_plan_init(p.att, h->slots[o.src], h->chunk, o.in_h, o.in_c, o.reserved[0], eb, sizeof eb))
+                    B2P_FAIL(B2P_E_ARG, "op %d: %s", i, eb);
+            }
+        } else if (o.kind == B2P_OP_LAYERNORM || o.kind == B2P_OP_TOKENS) {
+            if (o.in_c != 768) B2P_FAIL(B2P_E_ARG, "op %d: token width must be 768", i);
+            const int64_t need_w = o.kind == B2P_OP_TOKENS ? static_cast<int64_t>(o.in_h) * o.in_c * 4 : o.in_c * 4;
+            if (h->blob_bytes[o.weight] < need_w || h->blob_bytes[o.bias] < o.in_c * 4)
+                B2P_FAIL(B2P_E_ARG, "op %d: parameter blob too small", i);
         } else if ((o.kind == B2P_OP_MAXPOOL || o.kind == B2P_OP_AVGPOOL) && o.in_c % 8 != 0) {
             B2P_FAIL(B2P_E_ARG, "op %d: pooling needs channels %% 8 == 0", i);
         }

@@ -299,9 +299,13 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                                 f[8 * j + 6] += bf16_lo(r.w); f[8 * j + 7] += bf16_hi(r.w);
                             }
                         }
-                        if (args.relu) {
+                        if (args.relu == 1) {
 #pragma unroll
                             for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
+                        } else if (args.relu == 2) {
+                            // exact GELU, nn.GELU() default: 0.5 x (1 + erf(x / sqrt(2)))
+#pragma unroll
+                            for (int j = 0; j < 32; ++j) f[j] = 0.5f * f[j] * (1.0f + erff(f[j] * 0.70710678118654752f));
                         }
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {

@@ -78,6 +78,21 @@ void stem_pack_weight_image(const uint16_t* w_packed, uint16_t* image);
 bool stem_plan_init(StemPlan& p, const void* src_s2d, void* dst, int batch_cap, int pool, char* err, size_t err_len);
 cudaError_t stem_plan_launch(const StemPlan& p, int n, int relu, int num_sms, cudaStream_t stream);
 
+// ------------------------------------------------------------------ ViT pieces (vit.cu)
+struct AttentionPlan {
+    CUtensorMap tmap_q;     // packed QKV [n*seq, 3*dim] bf16, 64 x 128 boxes (query tiles)
+    CUtensorMap tmap_kv;    // same tensor, 64 x 208 boxes (all keys / values of one head)
+    int seq = 0, dim = 0, heads = 0;
+};
+cudaError_t launch_patchify(const void* x_nchw, void* out, int n, cudaStream_t s);
+cudaError_t launch_tokens(const void* proj, const float* cls, const float* pos, void* out, int n, int seq, int dim,
+                          cudaStream_t s);
+cudaError_t launch_layernorm(const void* x, const float* gamma, const float* beta, void* out, long rows, int dim,
+                             long in_row_stride_elems, float eps, cudaStream_t s);
+bool attention_plan_init(AttentionPlan& p, const void* qkv, int batch_cap, int seq, int dim, int heads, char* err,
+                         size_t err_len);
+cudaError_t attention_plan_launch(const AttentionPlan& p, void* out, int n, cudaStream_t s);
+
 // Records an error that is not tied to a handle; b2p_last_error(NULL) returns it.
 void set_global_error(const char* fmt, ...);
 

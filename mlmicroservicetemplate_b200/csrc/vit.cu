@@ -1,0 +1,381 @@
+// K2b: the ViT-specific pieces of the classifier forward (SP/torchvision/models/vision_transformer.py):
+//   patchify   conv_proj's 16x16/s16 patches as GEMM rows (:213-215, :268-287)
+//   tokens     [class token | patch embeddings] + positional embedding (:289-301, :154-155)
+//   layernorm  nn.LayerNorm(eps=1e-6) (:96, :152), optionally only for the class-token row (:301)
+//   attention  nn.MultiheadAttention's scaled-dot-product core (:103, :111) on tcgen05:
+//              S = Q K^T and O = P V as UMMA with TMEM accumulators, softmax between them by the
+//              epilogue warps, one CTA per (image, head, 128-row query tile).
+// The linear layers around them (packed QKV, out-proj, MLP fc1+GELU, fc2) run on the generic
+// conv_gemm kernel as 1x1 convolutions over a 197x1 "image".
+#include <cfloat>
+#include <cstdio>
+#include <cudaTypedefs.h>
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace b2p {
+namespace {
+
+// ------------------------------------------------------------------------------ patchify
+// NCHW bf16 [n,3,224,224] -> [n*196, 768] bf16, column = c*256 + ky*16 + kx (the flattened conv_proj
+// weight order).  One thread moves one 16-pixel patch row (32 bytes).
+__global__ void patchify_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, int n) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const long total = static_cast<long>(n) * 3 * 224 * 14;       // (img, c, y, px)
+    for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<long>(gridDim.x) * blockDim.x) {
+        const int px = static_cast<int>(i % 14);
+        long t = i / 14;
+        const int y = static_cast<int>(t % 224);
+        t /= 224;
+        const int c = static_cast<int>(t % 3);
+        const int img = static_cast<int>(t / 3);
+        const uint4 a = __ldg(x + 2 * i), b = __ldg(x + 2 * i + 1);      // input is exactly (img,c,y,px)-ordered
+        const int py = y >> 4, ky = y & 15;
+        const size_t row = static_cast<size_t>(img) * 196 + py * 14 + px;
+        uint4* o = out + (row * 768 + c * 256 + ky * 16) / 8;
+        o[0] = a;
+        o[1] = b;
+    }
+}
+
+// ------------------------------------------------------------------------------ tokens
+// out[img][0] = cls + pos[0];  out[img][t] = proj[img][t-1] + pos[t]   (bf16 out, fp32 math)
+__global__ void tokens_kernel(const uint4* __restrict__ proj, const float* __restrict__ cls, const float* __restrict__ pos,
+                              uint4* __restrict__ out, int n, int seq, int dim) {
+    pdl_launch_dependents();
+    pdl_wait();
+    const int d8 = dim / 8;
+    const long total = static_cast<long>(n) * seq * d8;
+    for (long i = blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x; i < total;
+         i += static_cast<long>(gridDim.x) * blockDim.x) {
+        const int g = static_cast<int>(i % d8);
+        const long t2 = i / d8;
+        const int t = static_cast<int>(t2 % seq);
+        const int img = static_cast<int>(t2 / seq);
+        float v[8];
+        if (t == 0) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) v[e] = cls[g * 8 + e];
+        } else {
+            const uint4 p = __ldg(proj + (static_cast<size_t>(img) * (seq - 1) + (t - 1)) * d8 + g);
+            v[0] = bf16_lo(p.x); v[1] = bf16_hi(p.x); v[2] = bf16_lo(p.y); v[3] = bf16_hi(p.y);
+            v[4] = bf16_lo(p.z); v[5] = bf16_hi(p.z); v[6] = bf16_lo(p.w); v[7] = bf16_hi(p.w);
+        }
+        const float* pp = pos + static_cast<size_t>(t) * dim + g * 8;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] += __ldg(pp + e);
+        uint4 o;
+        o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+        o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+        out[i] = o;
+    }
+}
+
+// ------------------------------------------------------------------------------ layernorm
+// One warp per row of `dim` (<= 1024, multiple of 256) bf16 elements; statistics in fp32.
+// row_stride/rows_out let the final LN touch only the class-token row of each image.
+template <int DIM>
+__global__ void layernorm_kernel(const uint4* __restrict__ x, const float* __restrict__ gamma,
+                                 const float* __restrict__ beta, uint4* __restrict__ out, long rows, long in_row_stride8,
+                                 float eps) {
+    pdl_launch_dependents();
+    pdl_wait();
+    constexpr int PER_LANE = DIM / 256;            // uint4 (8 elements) per lane
+    const long row = (blockIdx.x * static_cast<long>(blockDim.x) + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    const uint4* xr = x + row * in_row_stride8;
+    float v[PER_LANE * 8];
+    float sum = 0.f;
+#pragma unroll
+    for (int j = 0; j < PER_LANE; ++j) {
+        const uint4 p = __ldg(xr + j * 32 + lane);
+        v[8 * j + 0] = bf16_lo(p.x); v[8 * j + 1] = bf16_hi(p.x); v[8 * j + 2] = bf16_lo(p.y); v[8 * j + 3] = bf16_hi(p.y);
+        v[8 * j + 4] = bf16_lo(p.z); v[8 * j + 5] = bf16_hi(p.z); v[8 * j + 6] = bf16_lo(p.w); v[8 * j + 7] = bf16_hi(p.w);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) sum += v[8 * j + e];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float mean = sum / DIM;
+    float sq = 0.f;
+#pragma unroll
+    for (int j = 0; j < PER_LANE * 8; ++j) { const float d = v[j] - mean; sq += d * d; }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    const float rstd = rsqrtf(sq / DIM + eps);
+    uint4* orow = out + row * (DIM / 8);
+#pragma unroll
+    for (int j = 0; j < PER_LANE; ++j) {
+        const int c0 = (j * 32 + lane) * 8;
+        float y[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) y[e] = (v[8 * j + e] - mean) * rstd * __ldg(gamma + c0 + e) + __ldg(beta + c0 + e);
+        uint4 o;
+        o.x = pack_bf16x2(y[0], y[1]); o.y = pack_bf16x2(y[2], y[3]);
+        o.z = pack_bf16x2(y[4], y[5]); o.w = pack_bf16x2(y[6], y[7]);
+        orow[j * 32 + lane] = o;
+    }
+}
+
+// ------------------------------------------------------------------------------ attention
+constexpr int ATT_THREADS = 192;
+constexpr int HD = 64;                 // head dimension
+constexpr int KV_ROWS = 208;           // keys padded to a multiple of 16 (UMMA N / K granularity), >= 197
+constexpr int Q_BYTES = 128 * 128;     // 128 queries x 64 dims bf16, 128B swizzle
+constexpr int KV_BYTES = 256 * 128;    // room for 208 key (value) rows of 128 bytes
+constexpr int P_CHUNK_BYTES = 128 * 128;
+constexpr int ATT_SMEM = 1024 + Q_BYTES + 2 * KV_BYTES + 4 * P_CHUNK_BYTES + 128;
+
+// tcgen05 instruction descriptor, bf16 x bf16 -> fp32, A K-major, B MN-major (bit 16).
+__host__ __device__ constexpr uint32_t umma_idesc_bf16_b_mn(uint32_t m, uint32_t n) {
+    return umma_idesc_bf16(m, n) | (1u << 16);
+}
+
+__global__ void __launch_bounds__(ATT_THREADS, 1)
+attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
+                 uint16_t* __restrict__ out, int seq, int dim, float scale_log2e) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    uint8_t* smem_q = smem;
+    uint8_t* smem_k = smem_q + Q_BYTES;
+    uint8_t* smem_v = smem_k + KV_BYTES;
+    uint8_t* smem_p = smem_v + KV_BYTES;
+    uint64_t* load_bar = reinterpret_cast<uint64_t*>(smem_p + 4 * P_CHUNK_BYTES);
+    uint64_t* s_bar = load_bar + 1;
+    uint64_t* p_bar = s_bar + 1;
+    uint64_t* o_bar = p_bar + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_bar + 1);
+
+    const int warp_idx = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+    const int mt = blockIdx.x, head = blockIdx.y, img = blockIdx.z;
+    const int row0 = img * seq;                    // first token row of this image in the [n*seq, 3*dim] matrix
+
+    if (warp_idx == 0) {
+        if (elect_one()) {
+            tma_prefetch_desc(&tmap_q);
+            tma_prefetch_desc(&tmap_kv);
+        }
+    } else if (warp_idx == 1) {
+        if (elect_one()) {
+            mbar_init(load_bar, 1);
+            mbar_init(s_bar, 1);
+            mbar_init(p_bar, 4);
+            mbar_init(o_bar, 1);
+            fence_mbar_init();
+        }
+        __syncwarp();
+        tmem_alloc(tmem_slot, 256);
+        tmem_relinquish();
+    }
+    pdl_launch_dependents();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+
+    if (warp_idx == 0) {
+        if (elect_one()) {
+            mbar_arrive_expect_tx(load_bar, Q_BYTES + 2 * KV_ROWS * 128);
+            tma_load_2d(&tmap_q, load_bar, smem_q, head * HD, row0 + mt * 128);
+            tma_load_2d(&tmap_kv, load_bar, smem_k, dim + head * HD, row0);
+            tma_load_2d(&tmap_kv, load_bar, smem_v, 2 * dim + head * HD, row0);
+        }
+    } else if (warp_idx == 1) {
+        if (elect_one()) {
+            // ---- S = Q K^T  (M=128, N=208, K=64)
+            mbar_wait(load_bar, 0);
+            tc_fence_after();
+            const uint64_t q_desc = umma_desc_kmajor(smem_u32(smem_q), 128);
+            const uint64_t k_desc = umma_desc_kmajor(smem_u32(smem_k), 128);
+            constexpr uint32_t idesc_s = umma_idesc_bf16(128, KV_ROWS);
+#pragma unroll
+            for (int k = 0; k < HD / 16; ++k)
+                umma_bf16(tmem_base, q_desc + static_cast<uint64_t>(2 * k), k_desc + static_cast<uint64_t>(2 * k), idesc_s,
+                          static_cast<uint32_t>(k != 0));
+            umma_commit(s_bar);
+            // ---- O = P V  (M=128, N=64, K=208): P K-major from the softmax warps, V MN-major as loaded
+            mbar_wait(p_bar, 0);
+            tc_fence_after();
+            constexpr uint32_t idesc_o = umma_idesc_bf16_b_mn(128, HD);
+            const uint32_t p_addr = smem_u32(smem_p), v_addr = smem_u32(smem_v);
+#pragma unroll
+            for (int ks = 0; ks < KV_ROWS / 16; ++ks) {
+                const uint64_t p_desc = umma_desc_kmajor(p_addr + (ks >> 2) * P_CHUNK_BYTES, 128) + static_cast<uint64_t>(2 * (ks & 3));
+                // MN-major, 128B swizzle: each K index is one 128-byte row; 8-row groups are 1024 B apart (SBO)
+                const uint64_t v_desc = umma_desc_kmajor(v_addr + ks * 2048, 128);
+                umma_bf16(tmem_base, p_desc, v_desc, idesc_o, static_cast<uint32_t>(ks != 0));
+            }
+            umma_commit(o_bar);
+        }
+    } else {
+        const int quad = warp_idx & 3;
+        const int lane = static_cast<int>(lane_id());
+        const int r = quad * 32 + lane;                         // query row inside the tile
+        const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+        mbar_wait(s_bar, 0);
+        tc_fence_after();
+        // pass 1: row maximum over the valid keys
+        float mx = -FLT_MAX;
+#pragma unroll 1
+        for (int c = 0; c < 7; ++c) {
+            uint32_t v[32];
+            tmem_ld_32x32(t_addr + c * 32, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+                if (c * 32 + j < seq) mx = fmaxf(mx, __uint_as_float(v[j]));
+        }
+        // pass 2: p = exp((s - max) * scale), unnormalised bf16 into the K-major swizzled P tiles; row sum in fp32
+        float sum = 0.f;
+        const uint32_t p_row = smem_u32(smem_p) + static_cast<uint32_t>(r * 128);
+#pragma unroll 1
+        for (int c = 0; c < 7; ++c) {
+            uint32_t v[32];
+            tmem_ld_32x32(t_addr + c * 32, v);
+            tmem_ld_wait();
+            float p[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+                const float e = exp2f((__uint_as_float(v[j]) - mx) * scale_log2e);
+                p[j] = (c * 32 + j < seq) ? e : 0.f;
+            }
+            const int chunk = c >> 1;                          // 64-key chunk
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                uint4 o;
+                o.x = pack_bf16x2(p[8 * j + 0], p[8 * j + 1]); o.y = pack_bf16x2(p[8 * j + 2], p[8 * j + 3]);
+                o.z = pack_bf16x2(p[8 * j + 4], p[8 * j + 5]); o.w = pack_bf16x2(p[8 * j + 6], p[8 * j + 7]);
+                // sum what the tensor core will actually see (the bf16-rounded values)
+                sum += bf16_lo(o.x) + bf16_hi(o.x) + bf16_lo(o.y) + bf16_hi(o.y) + bf16_lo(o.z) + bf16_hi(o.z) +
+                       bf16_lo(o.w) + bf16_hi(o.w);
+                const int piece = ((c & 1) * 4 + j) ^ (r & 7);
+                st_shared_v4(p_row + static_cast<uint32_t>(chunk * P_CHUNK_BYTES + piece * 16), o);
+            }
+        }
+        fence_proxy_async_smem();          // P must be visible to the tensor core's async proxy
+        tc_fence_before();                 // and all S reads are done before the accumulator is overwritten
+        __syncwarp();
+        if (lane == 0) mbar_arrive(p_bar);
+        // ---- O epilogue
+        mbar_wait(o_bar, 0);
+        tc_fence_after();
+        const float inv = 1.0f / sum;
+        const int token = mt * 128 + r;
+        uint4 packed[8];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            uint32_t v[32];
+            tmem_ld_32x32(t_addr + h * 32, v);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                packed[h * 4 + j].x = pack_bf16x2(__uint_as_float(v[8 * j + 0]) * inv, __uint_as_float(v[8 * j + 1]) * inv);
+                packed[h * 4 + j].y = pack_bf16x2(__uint_as_float(v[8 * j + 2]) * inv, __uint_as_float(v[8 * j + 3]) * inv);
+                packed[h * 4 + j].z = pack_bf16x2(__uint_as_float(v[8 * j + 4]) * inv, __uint_as_float(v[8 * j + 5]) * inv);
+                packed[h * 4 + j].w = pack_bf16x2(__uint_as_float(v[8 * j + 6]) * inv, __uint_as_float(v[8 * j + 7]) * inv);
+            }
+        }
+        if (token < seq) {
+            uint4* o = reinterpret_cast<uint4*>(out + (static_cast<size_t>(row0 + token) * dim + head * HD));
+#pragma unroll
+            for (int j = 0; j < 8; ++j) st_v4(o + j, packed[j]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp_idx == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 256);
+    }
+}
+
+PFN_cuTensorMapEncodeTiled_v12000 g_vit_encode = nullptr;
+
+bool vit_encode_2d(CUtensorMap* m, const void* base, uint64_t cols, uint64_t rows, uint32_t box_cols, uint32_t box_rows) {
+    if (!g_vit_encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess ||
+            qres != cudaDriverEntryPointSuccess || !fn)
+            return false;
+        g_vit_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+    }
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {cols * 2};
+    cuuint32_t box[2] = {box_cols, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    return g_vit_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+inline int grid_for(long total, int block, int cap = 148 * 16) {
+    long g = (total + block - 1) / block;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return static_cast<int>(g);
+}
+
+}  // namespace
+
+cudaError_t launch_patchify(const void* x, void* out, int n, cudaStream_t s) {
+    const long total = static_cast<long>(n) * 3 * 224 * 14;
+    return launch_pdl(patchify_kernel, dim3(grid_for(total, 256)), dim3(256), 0, s, static_cast<const uint4*>(x),
+                      static_cast<uint4*>(out), n);
+}
+
+cudaError_t launch_tokens(const void* proj, const float* cls, const float* pos, void* out, int n, int seq, int dim,
+                          cudaStream_t s) {
+    const long total = static_cast<long>(n) * seq * (dim / 8);
+    return launch_pdl(tokens_kernel, dim3(grid_for(total, 256)), dim3(256), 0, s, static_cast<const uint4*>(proj), cls, pos,
+                      static_cast<uint4*>(out), n, seq, dim);
+}
+
+cudaError_t launch_layernorm(const void* x, const float* gamma, const float* beta, void* out, long rows, int dim,
+                             long in_row_stride_elems, float eps, cudaStream_t s) {
+    if (dim != 768) return cudaErrorInvalidValue;
+    const int warps_per_block = 8;
+    const long blocks = (rows + warps_per_block - 1) / warps_per_block;
+    return launch_pdl(layernorm_kernel<768>, dim3(static_cast<unsigned>(blocks)), dim3(warps_per_block * 32), 0, s,
+                      static_cast<const uint4*>(x), gamma, beta, static_cast<uint4*>(out), rows, in_row_stride_elems / 8, eps);
+}
+
+bool attention_plan_init(AttentionPlan& p, const void* qkv, int batch_cap, int seq, int dim, int heads, char* err,
+                         size_t err_len) {
+    if (dim != heads * HD || seq > KV_ROWS - 0 || seq > 256 || seq < 1) {
+        snprintf(err, err_len, "attention supports head_dim 64 and sequence length <= %d", KV_ROWS);
+        return false;
+    }
+    p.seq = seq;
+    p.dim = dim;
+    p.heads = heads;
+    const uint64_t rows = static_cast<uint64_t>(batch_cap) * seq;
+    if (!vit_encode_2d(&p.tmap_q, qkv, 3ull * dim, rows, HD, 128) ||
+        !vit_encode_2d(&p.tmap_kv, qkv, 3ull * dim, rows, HD, KV_ROWS)) {
+        snprintf(err, err_len, "attention tensor map encoding failed");
+        return false;
+    }
+    return true;
+}
+
+cudaError_t attention_plan_launch(const AttentionPlan& p, void* out, int n, cudaStream_t s) {
+    static bool attr_set[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (!attr_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM);
+        if (e != cudaSuccess) return e;
+        attr_set[dev] = true;
+    }
+    const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(HD));
+    dim3 grid((p.seq + 127) / 128, p.heads, n);
+    return launch_pdl(attention_kernel, grid, dim3(ATT_THREADS), ATT_SMEM, s, p.tmap_q, p.tmap_kv,
+                      static_cast<uint16_t*>(out), p.seq, p.dim, scale_log2e);
+}
+
+}  // namespace b2p

@@ -226,6 +226,87 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
     return p
 
 
+def build_vit_program(model: torch.nn.Module, name: str = "vit_b_16") -> Program:
+    """Walks a torchvision VisionTransformer (SP/torchvision/models/vision_transformer.py:160-305:
+    conv_proj patchify, class token, positional embedding, encoder blocks :110-119, final LN, head).
+    Token matrices are "images" of 197 x 1 so every linear layer is a 1x1 OP_CONV on the GEMM core."""
+    model = model.eval()
+    if model.patch_size != 16 or model.image_size != 224 or model.hidden_dim != 768:
+        raise ValueError("only ViT-B/16 at 224 is supported")
+    bld = _Builder(name)
+    p = bld.p
+    p.in_elems = 3 * 224 * 224
+    seq, dim, heads = model.seq_length, model.hidden_dim, model.encoder.layers[0].num_heads
+    tok = (seq, 1, dim)
+
+    def linear(src, hwc, lin_w, lin_b, act=B.ACT_NONE, res=B.SLOT_NONE):
+        w = lin_w.detach().float()
+        return bld.conv(src, hwc, w.view(w.shape[0], w.shape[1], 1, 1), lin_b.detach().float(), 1, 0, act, res=res)
+
+    def layernorm(src, ln, cls_only=False):
+        wi = p.add_blob(ln.weight.detach().float())
+        bi = p.add_blob(ln.bias.detach().float())
+        dst = p.alloc(dim if cls_only else seq * dim)
+        p.ops.append(_mk_op(B.OP_LAYERNORM, src, dst, in_hwc=tok, out_hwc=(1, 1, dim) if cls_only else tok, weight=wi,
+                            bias=bi, flag0=int(cls_only)))
+        return dst
+
+    # patch embedding: patchify -> GEMM [n*196, 768] x W^T + b -> tokens (+cls, +pos)
+    patches = p.alloc((seq - 1) * dim)
+    p.ops.append(_mk_op(B.OP_PATCHIFY, B.SLOT_INPUT, patches, in_hwc=(224, 224, 3), out_hwc=(seq - 1, 1, dim)))
+    cw = model.conv_proj.weight.detach().float().reshape(dim, 3 * 16 * 16)
+    proj, _ = linear(patches, (seq - 1, 1, dim), cw, model.conv_proj.bias)
+    p.release(patches)
+    pos = p.add_blob(model.encoder.pos_embedding.detach().float().reshape(seq * dim))
+    cls = p.add_blob(model.class_token.detach().float().reshape(dim))
+    x = p.alloc(seq * dim)
+    p.ops.append(_mk_op(B.OP_TOKENS, proj, x, in_hwc=tok, out_hwc=tok, weight=pos, bias=cls))
+    p.release(proj)
+
+    for blk in model.encoder.layers:
+        att = blk.self_attention
+        y = layernorm(x, blk.ln_1)
+        qkv, _ = linear(y, tok, att.in_proj_weight, att.in_proj_bias)
+        p.release(y)
+        a = p.alloc(seq * dim)
+        p.ops.append(_mk_op(B.OP_ATTENTION, qkv, a, in_hwc=tok, out_hwc=tok, flag0=heads))
+        p.flops_per_image += 2.0 * 2.0 * seq * seq * (dim // heads) * heads
+        p.release(qkv)
+        x2, _ = linear(a, tok, att.out_proj.weight, att.out_proj.bias, res=x)
+        p.release(a)
+        p.release(x)
+        y = layernorm(x2, blk.ln_2)
+        h, hwc_h = linear(y, tok, blk.mlp[0].weight, blk.mlp[0].bias, act=B.ACT_GELU)
+        p.release(y)
+        x, _ = linear(h, hwc_h, blk.mlp[3].weight, blk.mlp[3].bias, res=x2)
+        p.release(h)
+        p.release(x2)
+
+    feat = layernorm(x, model.encoder.ln, cls_only=True)
+    p.release(x)
+    head = model.heads.head
+    classes, fin = head.weight.shape
+    rows = (classes + 127) // 128 * 128
+    wp = torch.zeros(rows, fin)
+    wp[:classes] = head.weight.detach().float()
+    wi = p.add_blob(_bf16(wp))
+    bi = p.add_blob(pad_bias(head.bias.detach(), rows))
+    p.ops.append(_mk_op(B.OP_LINEAR, feat, B.SLOT_OUTPUT, in_hwc=(1, 1, fin), out_hwc=(1, 1, classes), weight=wi, bias=bi))
+    p.flops_per_image += 2.0 * classes * fin
+    p.out_elems = classes
+    return p
+
+
+def build_program(model: torch.nn.Module, name: str = "") -> Program:
+    """Dispatches on the torchvision module type."""
+    cls = type(model).__name__
+    if cls == "ResNet":
+        return build_resnet_program(model, name or "resnet")
+    if cls == "VisionTransformer":
+        return build_vit_program(model, name or "vit")
+    raise TypeError(f"no layer-program builder for {cls}")
+
+
 def single_conv_program(w: torch.Tensor, b: torch.Tensor, hwc, stride: int, pad: int, relu: bool,
                         with_residual: bool = False, pad_hi: Optional[int] = None) -> Program:
     """One CONV op from the external NHWC input to the external bf16 NHWC output; with_residual adds

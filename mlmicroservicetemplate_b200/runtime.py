@@ -200,6 +200,21 @@ class Engine:
                 close()
 
 
+def seeded_model(arch: str, seed: int):
+    """Random-init torchvision classifier, fully determined by (arch, seed).  torchvision zero-initialises
+    the ViT head (SP/torchvision/models/vision_transformer.py:264-266), which would make every logit 0;
+    it is re-drawn from N(0, 0.02) with a fixed generator so that a random-init ViT has a usable output."""
+    import torch
+    import torchvision
+    torch.manual_seed(seed)
+    model = getattr(torchvision.models, arch)(weights=None).eval()
+    if arch.startswith("vit"):
+        g = torch.Generator().manual_seed(123)
+        with torch.no_grad():
+            model.heads.head.weight.normal_(0.0, 0.02, generator=g)
+    return model
+
+
 def build_gpu_engine(arch: str, gpus: Optional[Sequence[int]], max_batch: int, max_wait_us: int, topk: int,
                      mode: str, seed: int, sub_batch: int = 0, state_dict: Optional[dict] = None):
     """What init() does: random-init (seeded) torchvision model -> layer program -> one replica per GPU."""
@@ -208,11 +223,10 @@ def build_gpu_engine(arch: str, gpus: Optional[Sequence[int]], max_batch: int, m
     from . import program as P
     if not torch.cuda.is_available():
         raise RuntimeError("no CUDA device visible: the B200 predict path has no CPU fallback")
-    torch.manual_seed(seed)
-    model = getattr(torchvision.models, arch)(weights=None).eval()
+    model = seeded_model(arch, seed)
     if state_dict is not None:
         model.load_state_dict(state_dict)
-    prog = P.build_resnet_program(model, arch)
+    prog = P.build_program(model, arch)
     devs = list(gpus) if gpus else list(range(torch.cuda.device_count()))
     workers = [GpuReplicaWorker(d, prog, max_batch, topk, mode, sub_batch) for d in devs]
     return Engine(workers, max_batch=max_batch, max_wait_us=max_wait_us), prog.out_elems

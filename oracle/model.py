@@ -34,6 +34,12 @@ def build_model(arch: str = "resnet18", seed: int = SEED) -> torch.nn.Module:
     import torchvision
     torch.manual_seed(seed)
     m = getattr(torchvision.models, arch)(weights=None)
+    if arch.startswith("vit"):
+        # the stock ViT head is all zeros (SP/torchvision/models/vision_transformer.py:264-266): every logit
+        # would be exactly 0.  Re-draw it N(0, 0.02) from a fixed generator (bias stays 0) — SURVEY §8c c5.
+        g = torch.Generator().manual_seed(123)
+        with torch.no_grad():
+            m.heads.head.weight.normal_(0.0, 0.02, generator=g)
     return m.eval()
 
 
@@ -42,7 +48,8 @@ def init(arch: Optional[str] = None, topk: Optional[int] = None, mode: Optional[
     arch = arch or os.getenv("MODEL", "resnet18")
     _state["model"] = build_model(arch)
     _state["arch"] = arch
-    _state["classes"] = class_names(_state["model"].fc.out_features)
+    head = _state["model"].fc if hasattr(_state["model"], "fc") else _state["model"].heads.head
+    _state["classes"] = class_names(head.out_features)
     _state["topk"] = int(topk or os.getenv("TOPK", 5))
     _state["mode"] = mode or os.getenv("PREPROCESS", "direct")
 
