@@ -35,7 +35,9 @@ ARCH = "resnet50"
 BATCH = 256
 TOPK = 5
 IMG = 224
-FLOP_PER_IMAGE = 8.1784e9            # conv+fc 2*MACs, ResNet-50 224^2
+# conv/linear/attention-matmul 2*MACs per 224^2 image
+FLOPS = {"resnet50": 8.1784e9, "resnet18": 3.6281e9, "vit_b_16": 35.128e9}
+FLOP_PER_IMAGE = FLOPS[ARCH]
 METRIC = "predict images/sec (ResNet-50 224^2 bf16), batch 256 per B200 replica"
 POOL_SLABS = 6                       # 6 x 38.5 MB of inputs > 126 MB L2
 
@@ -144,6 +146,7 @@ def run_reference_arm(args):
 
 
 def main():
+    global ARCH, BATCH, FLOP_PER_IMAGE, METRIC
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)
@@ -151,7 +154,12 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--sub-batch", type=int, default=int(os.environ.get("B2P_SUB_BATCH", "0")))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--arch", default=ARCH, choices=sorted(FLOPS), help="non-default values give a secondary line")
+    ap.add_argument("--batch", type=int, default=BATCH)
     args = ap.parse_args()
+    if (args.arch, args.batch) != (ARCH, BATCH):
+        ARCH, BATCH, FLOP_PER_IMAGE = args.arch, args.batch, FLOPS[args.arch]
+        METRIC = f"predict images/sec ({ARCH} 224^2 bf16), batch {BATCH} per B200 replica"
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
 
     if args.impl == "reference":
@@ -177,7 +185,7 @@ def main():
     rank = ranks.rank
 
     model = om.build_model(ARCH)
-    prog = P.build_resnet_program(model, ARCH)
+    prog = P.build_program(model, ARCH)
     rep = B.Replica(local_rank, prog, max_batch=BATCH, sub_batch=args.sub_batch)
     stream = torch.cuda.Stream()
 
@@ -263,7 +271,7 @@ def main():
     peaks = load_peaks()
     achieved_tflops = FLOP_PER_IMAGE * BATCH / (k2_ms * 1e-3) / 1e12
     roofline = {
-        "kernel": "conv_gemm_kernel (all K2 conv/linear launches of one forward, 54 GEMMs)",
+        "kernel": "K2 forward: every tcgen05 launch of one forward (conv_gemm / stem / attention kernels)",
         "bound": "tensor", "achieved": achieved_tflops, "peak": peaks["bf16_tflops_sustained"], "unit": "TFLOP/s",
         "frac": achieved_tflops / peaks["bf16_tflops_sustained"],
         "frac_of_burst_peak": achieved_tflops / peaks["bf16_tflops"], "peak_burst": peaks["bf16_tflops"],
@@ -281,7 +289,7 @@ def main():
             "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": K, "warmup": W,
             "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": "resnet50_224_b256_predict", "arch": ARCH, "batch_per_gpu": BATCH,
+            "config": {"workload": f"{ARCH}_224_b{BATCH}_predict", "arch": ARCH, "batch_per_gpu": BATCH,
                        "global_batch": BATCH * world, "image": "224x224x3 uint8 HWC", "topk": TOPK,
                        "weights": "torchvision random init, seed 0, BN folded, bf16",
                        "parallelism": f"replicas x{world}, no collective", "sub_batch": args.sub_batch,
