@@ -30,6 +30,8 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# NCCL writes its banner / debug lines to stdout by default; stdout must carry exactly one JSON line.
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 
 ARCH = "resnet50"
 BATCH = 256

@@ -39,7 +39,12 @@ def main():
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--out", default="")
+    ap.add_argument("--sizes", default="", help="e.g. 320x320,1080x1920 (default: the full config-4 list)")
+    ap.add_argument("--modes", default="direct,preset")
     args = ap.parse_args()
+    global SIZES
+    if args.sizes:
+        SIZES = [tuple(int(v) for v in t.split("x")) for t in args.sizes.split(",")]
 
     import numpy as np
     import torch
@@ -67,7 +72,7 @@ def main():
             slab_np[i * stride:i * stride + per] = base[i].reshape(-1)
         n_slabs = max(2, int(300e6 // (n * stride)) + 1)          # > 126 MB L2 in total
         slabs = [torch.from_numpy(slab_np).cuda() for _ in range(n_slabs)]
-        for mode in ("direct", "preset"):
+        for mode in args.modes.split(","):
             geom = om.geometry(h, w, mode)
             descs = B.make_images([(i * stride, h, w, *geom) for i in range(n)])
             # parity on the first two images
