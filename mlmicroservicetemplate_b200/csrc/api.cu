@@ -123,9 +123,22 @@ int validate_desc(const b2p_model_desc* d) {
 }
 
 int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st) {
+    // Tile direction: a GEMM layer walks its row tiles in the direction OPPOSITE to the last op that
+    // touched its input, so it starts on the rows that are still resident in L2 (126 MB) instead of on
+    // the ones that were evicted first.  Slot -> direction of the last toucher (0 = ascending).
+    const bool alternate = getenv("B2P_NO_ALTERNATE") == nullptr;
+    std::vector<int> touch(h->slots.size() + 1, 0);
+    auto touch_of = [&](int slot) -> int& { return touch[slot >= 0 && slot < (int)h->slots.size() ? slot : h->slots.size()]; };
     for (int off = 0; off < n; off += h->chunk) {
         const int nb = (n - off) < h->chunk ? (n - off) : h->chunk;
         for (OpPlan& p : h->ops) {
+            {
+                const int dir = (p.is_gemm && alternate) ? !touch_of(p.op.src) : 0;
+                if (p.is_gemm) p.gemm.reverse = dir;
+                touch_of(p.op.src) = dir;
+                if (p.op.res != B2P_SLOT_NONE) touch_of(p.op.res) = dir;
+                touch_of(p.op.dst) = dir;
+            }
             const b2p_op& o = p.op;
             const void* src = slot_ptr(h, o.src, x, out, off);
             void* dst = slot_ptr(h, o.dst, x, out, off);

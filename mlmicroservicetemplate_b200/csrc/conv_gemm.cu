@@ -49,9 +49,26 @@ struct GemmArgs {
     int stride, pad_lo;
     int ldc;
     int relu;
+    int reverse;      // walk the tiles from the last to the first (see GemmPlan::reverse)
     const float* bias;
     void* out;        // only used by the fp32 (linear) epilogue
 };
+
+// GELU(x) = 0.5 x (1 + erf(x / sqrt 2)) with erf from Abramowitz & Stegun 7.1.26 (|error| <= 1.5e-7, far
+// below the bf16 rounding of the result): one reciprocal, one exp2, five FMAs instead of libdevice's erff.
+__device__ __forceinline__ float gelu_erf(float x) {
+    const float z = fabsf(x) * 0.70710678118654752f;
+    float t, e;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, z, 1.0f)));      // MUFU.RCP
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * z * z));   // MUFU.EX2
+    float p = fmaf(1.061405429f, t, -1.453152027f);
+    p = fmaf(p, t, 1.421413741f);
+    p = fmaf(p, t, -0.284496736f);
+    p = fmaf(p, t, 0.254829592f);
+    const float erf_abs = fmaf(-p * t, e, 1.0f);          // erf(|x| / sqrt 2)
+    const float hx = 0.5f * x;
+    return fmaf(fabsf(hx), erf_abs, hx);                  // 0.5 x (1 + sign(x) erf_abs)
+}
 
 template <int BLOCK_N, int BLOCK_K, bool OUT_F32, bool HAS_RES>
 struct Cfg {
@@ -143,8 +160,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             uint32_t phase = 0;
             const int pq = args.out_h * args.out_w;
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                const int m_blk = tile / args.n_tiles;
-                const int n_blk = tile - m_blk * args.n_tiles;
+                const int tid_ = args.reverse ? total_tiles - 1 - tile : tile;
+                const int m_blk = tid_ / args.n_tiles;
+                const int n_blk = tid_ - m_blk * args.n_tiles;
                 const int m0 = m_blk * BLOCK_M;
                 int img = 0, base_w = 0, base_h = 0;
                 if (IM2COL) {
@@ -212,8 +230,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             int rs = 0;
             uint32_t rphase = 0;
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                const int m_blk = tile / args.n_tiles;
-                const int n_blk = tile - m_blk * args.n_tiles;
+                const int tid_ = args.reverse ? total_tiles - 1 - tile : tile;
+                const int m_blk = tid_ / args.n_tiles;
+                const int n_blk = tid_ - m_blk * args.n_tiles;
                 for (int c64 = 0; c64 < BLOCK_N / 64; ++c64) {
                     mbar_wait(&res_empty_bar[rs], rphase ^ 1u);
                     mbar_arrive_expect_tx(&res_full_bar[rs], OUT_CHUNK_BYTES);
@@ -235,8 +254,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         uint32_t rphase = 0;
         int ob = 0;
         for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-            const int m_blk = tile / args.n_tiles;
-            const int n_blk = tile - m_blk * args.n_tiles;
+            const int tid_ = args.reverse ? total_tiles - 1 - tile : tile;
+            const int m_blk = tid_ / args.n_tiles;
+            const int n_blk = tid_ - m_blk * args.n_tiles;
             mbar_wait(&tmem_full_bar[acc], acc_phase);
             tc_fence_after();
             const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) +
@@ -305,7 +325,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         } else if (args.relu == 2) {
                             // exact GELU, nn.GELU() default: 0.5 x (1 + erf(x / sqrt(2)))
 #pragma unroll
-                            for (int j = 0; j < 32; ++j) f[j] = 0.5f * f[j] * (1.0f + erff(f[j] * 0.70710678118654752f));
+                            for (int j = 0; j < 32; ++j) f[j] = gelu_erf(f[j]);
                         }
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
@@ -570,6 +590,7 @@ cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, bool has_res, void* 
     a.pad_lo = p.pad_lo;
     a.ldc = p.ldc;
     a.relu = p.relu;
+    a.reverse = p.reverse;
     a.bias = p.bias;
     a.out = out_f32;
     const int total = a.m_tiles * a.n_tiles;

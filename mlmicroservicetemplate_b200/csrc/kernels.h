@@ -44,6 +44,8 @@ struct GemmPlan {
     int n_pad = 0;        // weight rows (multiple of block_n)
     int ldc = 0;          // output row pitch in elements
     int relu = 0;
+    int reverse = 0;      // process tiles last-to-first: consecutive layers alternate direction so that a layer
+                          // starts on the rows its predecessor wrote last (still resident in the 126 MB L2)
     const float* bias = nullptr;
     const void* weight = nullptr;
 };

@@ -110,9 +110,13 @@ __global__ void layernorm_kernel(const uint4* __restrict__ x, const float* __res
 #pragma unroll
     for (int j = 0; j < PER_LANE; ++j) {
         const int c0 = (j * 32 + lane) * 8;
+        const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c0)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c0 + 4));
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c0)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c0 + 4));
+        const float gg[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
         float y[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) y[e] = (v[8 * j + e] - mean) * rstd * __ldg(gamma + c0 + e) + __ldg(beta + c0 + e);
+        for (int e = 0; e < 8; ++e) y[e] = (v[8 * j + e] - mean) * rstd * gg[e] + bb[e];
         uint4 o;
         o.x = pack_bf16x2(y[0], y[1]); o.y = pack_bf16x2(y[2], y[3]);
         o.z = pack_bf16x2(y[4], y[5]); o.w = pack_bf16x2(y[6], y[7]);
@@ -127,14 +131,17 @@ constexpr int KV_ROWS = 208;           // keys padded to a multiple of 16 (UMMA 
 constexpr int Q_BYTES = 128 * 128;     // 128 queries x 64 dims bf16, 128B swizzle
 constexpr int KV_BYTES = 256 * 128;    // room for 208 key (value) rows of 128 bytes
 constexpr int P_CHUNK_BYTES = 128 * 128;
-constexpr int ATT_SMEM = 1024 + Q_BYTES + 2 * KV_BYTES + 4 * P_CHUNK_BYTES + 128;
+// P (4 chunks of 16 KB) is written only after S = QK^T has completed, when Q and K are dead: chunks 0-1
+// overlay K, chunk 2 overlays Q, chunk 3 gets its own 16 KB.  ~97 KB per CTA, so two CTAs share an SM and
+// one's softmax overlaps the other's loads and MMAs.
+constexpr int ATT_SMEM = 1024 + Q_BYTES + 2 * KV_BYTES + P_CHUNK_BYTES + 128;
 
 // tcgen05 instruction descriptor, bf16 x bf16 -> fp32, A K-major, B MN-major (bit 16).
 __host__ __device__ constexpr uint32_t umma_idesc_bf16_b_mn(uint32_t m, uint32_t n) {
     return umma_idesc_bf16(m, n) | (1u << 16);
 }
 
-__global__ void __launch_bounds__(ATT_THREADS, 1)
+__global__ void __launch_bounds__(ATT_THREADS, 2)
 attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
                  uint16_t* __restrict__ out, int seq, int dim, float scale_log2e) {
     extern __shared__ uint8_t smem_raw[];
@@ -142,8 +149,11 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     uint8_t* smem_q = smem;
     uint8_t* smem_k = smem_q + Q_BYTES;
     uint8_t* smem_v = smem_k + KV_BYTES;
-    uint8_t* smem_p = smem_v + KV_BYTES;
-    uint64_t* load_bar = reinterpret_cast<uint64_t*>(smem_p + 4 * P_CHUNK_BYTES);
+    uint8_t* smem_p3 = smem_v + KV_BYTES;
+    uint64_t* load_bar = reinterpret_cast<uint64_t*>(smem_p3 + P_CHUNK_BYTES);
+    // P chunk c (keys 64c .. 64c+63): {K, K + 16 KB, Q, own}
+    const uint32_t pk = smem_u32(smem_k), pq = smem_u32(smem_q), p3 = smem_u32(smem_p3);
+    auto p_chunk_addr = [&](int c) -> uint32_t { return c == 0 ? pk : (c == 1 ? pk + P_CHUNK_BYTES : (c == 2 ? pq : p3)); };
     uint64_t* s_bar = load_bar + 1;
     uint64_t* p_bar = s_bar + 1;
     uint64_t* o_bar = p_bar + 1;
@@ -201,10 +211,10 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             mbar_wait(p_bar, 0);
             tc_fence_after();
             constexpr uint32_t idesc_o = umma_idesc_bf16_b_mn(128, HD);
-            const uint32_t p_addr = smem_u32(smem_p), v_addr = smem_u32(smem_v);
+            const uint32_t v_addr = smem_u32(smem_v);
 #pragma unroll
             for (int ks = 0; ks < KV_ROWS / 16; ++ks) {
-                const uint64_t p_desc = umma_desc_kmajor(p_addr + (ks >> 2) * P_CHUNK_BYTES, 128) + static_cast<uint64_t>(2 * (ks & 3));
+                const uint64_t p_desc = umma_desc_kmajor(p_chunk_addr(ks >> 2), 128) + static_cast<uint64_t>(2 * (ks & 3));
                 // MN-major, 128B swizzle: each K index is one 128-byte row; 8-row groups are 1024 B apart (SBO)
                 const uint64_t v_desc = umma_desc_kmajor(v_addr + ks * 2048, 128);
                 umma_bf16(tmem_base, p_desc, v_desc, idesc_o, static_cast<uint32_t>(ks != 0));
@@ -231,7 +241,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         }
         // pass 2: p = exp((s - max) * scale), unnormalised bf16 into the K-major swizzled P tiles; row sum in fp32
         float sum = 0.f;
-        const uint32_t p_row = smem_u32(smem_p) + static_cast<uint32_t>(r * 128);
+        const uint32_t p_row = static_cast<uint32_t>(r * 128);
 #pragma unroll 1
         for (int c = 0; c < 7; ++c) {
             uint32_t v[32];
@@ -253,7 +263,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 sum += bf16_lo(o.x) + bf16_hi(o.x) + bf16_lo(o.y) + bf16_hi(o.y) + bf16_lo(o.z) + bf16_hi(o.z) +
                        bf16_lo(o.w) + bf16_hi(o.w);
                 const int piece = ((c & 1) * 4 + j) ^ (r & 7);
-                st_shared_v4(p_row + static_cast<uint32_t>(chunk * P_CHUNK_BYTES + piece * 16), o);
+                st_shared_v4(p_chunk_addr(chunk) + p_row + static_cast<uint32_t>(piece * 16), o);
             }
         }
         fence_proxy_async_smem();          // P must be visible to the tensor core's async proxy

@@ -179,15 +179,18 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
                 w1, b1 = fold_bn(blk.conv1.weight, blk.bn1)
                 w2, b2 = fold_bn(blk.conv2.weight, blk.bn2)
                 w3, b3 = fold_bn(blk.conv3.weight, blk.bn3)
-                t1, hwc1 = bld.conv(x, hwc, w1, b1, 1, 0, True)
-                t2, hwc2 = bld.conv(t1, hwc1, w2, b2, blk.conv2.stride[0], 1, True)
-                p.release(t1)
+                # the projection shortcut goes first: it and conv1 then read x back to back, and conv3 finds
+                # its main input (t2) written by the op right before it
                 if blk.downsample is not None:
                     wd, bd = fold_bn(blk.downsample[0].weight, blk.downsample[1])
                     idn, _ = bld.conv(x, hwc, wd, bd, blk.downsample[0].stride[0], 0, False)
-                    p.release(x)
                 else:
                     idn = x
+                t1, hwc1 = bld.conv(x, hwc, w1, b1, 1, 0, True)
+                if blk.downsample is not None:
+                    p.release(x)
+                t2, hwc2 = bld.conv(t1, hwc1, w2, b2, blk.conv2.stride[0], 1, True)
+                p.release(t1)
                 out, hwc3 = bld.conv(t2, hwc2, w3, b3, 1, 0, True, res=idn)
                 p.release(t2)
                 p.release(idn)
