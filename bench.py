@@ -278,7 +278,11 @@ def main():
         "frac": achieved_tflops / peaks["bf16_tflops_sustained"],
         "frac_of_burst_peak": achieved_tflops / peaks["bf16_tflops"], "peak_burst": peaks["bf16_tflops"],
         "peak_source": peaks["source"] + " (sustained: kernel timed inside a long step)",
-        "flop_per_launch_group": FLOP_PER_IMAGE * BATCH, "ms": k2_ms, "traffic": None,
+        "flop_per_launch_group": FLOP_PER_IMAGE * BATCH, "ms": k2_ms,
+        # dram__bytes_read.sum + dram__bytes_write.sum over the K2 launches of one 256-image ResNet-50 step, from the
+        # ncu pass committed as profiles/r01d_launches_dram_raw_ncu.csv (bytes per launch group, like `achieved`)
+        "traffic": 11.46e9 if (ARCH, BATCH) == ("resnet50", 256) else None,
+        "traffic_source": "profiles/r01d_launches_dram_raw_ncu.csv",
     }
 
     cpu_baseline = None

@@ -61,6 +61,7 @@ struct b2p_handle {
     b2p_image* cur_imgs_dev = nullptr;
     void* x_dev = nullptr;               // [max_batch,3,224,224] bf16
     float* logits_dev = nullptr;         // [max_batch, out_elems]
+    float* norm_lut = nullptr;           // [3][256] normalisation table for K1's crop-only path
     float* probs_dev = nullptr;
     int32_t* idx_dev = nullptr;
     cudaEvent_t ev[7] = {};   // copy begin/end (copy stream), K1 begin, K1/K2/K3 end, D2H end (caller's stream)
@@ -306,6 +307,7 @@ int32_t b2p_destroy(b2p_handle* h) {
         if (h->imgs_done[r]) cudaEventDestroy(h->imgs_done[r]);
     }
     if (h->x_dev) cudaFree(h->x_dev);
+    if (h->norm_lut) cudaFree(h->norm_lut);
     if (h->logits_dev) cudaFree(h->logits_dev);
     if (h->probs_dev) cudaFree(h->probs_dev);
     if (h->idx_dev) cudaFree(h->idx_dev);
@@ -374,6 +376,7 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
         cudaMemset(h->slots[i], 0, bytes);
     }
     // op plans
+    const bool autotune = getenv("B2P_AUTOTUNE") != nullptr && h->chunk >= 16;   // opt-in: measured gain is within noise
     h->ops.resize(desc->n_ops);
     for (int i = 0; i < desc->n_ops; ++i) {
         OpPlan& p = h->ops[i];
@@ -407,6 +410,55 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
                 if (!h->slots[o.res]) B2P_FAIL(B2P_E_ARG, "op %d adds an empty slot", i);
                 if (!gemm_plan_set_res(p.gemm, h->slots[o.res], rows_cap, eb, sizeof eb))
                     B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
+            }
+            // Tile-width autotune: when every operand lives in handle-owned slots, time each legal tile
+            // width on the real shapes (contents are irrelevant) and keep the fastest.
+            if (autotune && o.kind == B2P_OP_CONV && !p.src_external && !p.dst_external && !p.res_external &&
+                p.gemm.block_k == 64) {
+                const bool has_res = o.res != B2P_SLOT_NONE;
+                float best_ms = 0.f;
+                int best_bn = 0;
+                cudaEvent_t e0, e1;
+                cudaEventCreate(&e0);
+                cudaEventCreate(&e1);
+                for (int bn : {256, 128, 64}) {
+                    GemmPlan cand;
+                    cand.force_block_n = bn;
+                    char e2[256] = "";
+                    if (!gemm_plan_init(cand, o, h->blobs[o.weight], h->blob_bytes[o.weight],
+                                        static_cast<const float*>(h->blobs[o.bias]), rows_cap, h->num_sms, e2, sizeof e2) ||
+                        !gemm_plan_set_src(cand, h->slots[o.src], h->chunk, e2, sizeof e2) ||
+                        !gemm_plan_set_dst(cand, h->slots[o.dst], rows_cap, e2, sizeof e2) ||
+                        (has_res && !gemm_plan_set_res(cand, h->slots[o.res], rows_cap, e2, sizeof e2)))
+                        continue;
+                    float ms_best_of = 1e30f;
+                    bool ok = true;
+                    for (int rep = 0; rep < 4 && ok; ++rep) {
+                        cudaEventRecord(e0, 0);
+                        ok = gemm_plan_launch(cand, rows_cap, has_res, nullptr, h->num_sms, 0) == cudaSuccess;
+                        cudaEventRecord(e1, 0);
+                        ok = ok && cudaEventSynchronize(e1) == cudaSuccess;
+                        float ms = 0.f;
+                        cudaEventElapsedTime(&ms, e0, e1);
+                        if (rep > 0 && ms < ms_best_of) ms_best_of = ms;
+                    }
+                    if (ok && (best_bn == 0 || ms_best_of < best_ms)) { best_bn = bn; best_ms = ms_best_of; }
+                }
+                cudaEventDestroy(e0);
+                cudaEventDestroy(e1);
+                if (best_bn != 0 && best_bn != p.gemm.block_n) {
+                    GemmPlan tuned;
+                    tuned.force_block_n = best_bn;
+                    if (gemm_plan_init(tuned, o, h->blobs[o.weight], h->blob_bytes[o.weight],
+                                       static_cast<const float*>(h->blobs[o.bias]), rows_cap, h->num_sms, eb, sizeof eb) &&
+                        gemm_plan_set_src(tuned, h->slots[o.src], h->chunk, eb, sizeof eb) &&
+                        gemm_plan_set_dst(tuned, h->slots[o.dst], rows_cap, eb, sizeof eb) &&
+                        (!has_res || gemm_plan_set_res(tuned, h->slots[o.res], rows_cap, eb, sizeof eb)))
+                        p.gemm = tuned;
+                }
+                if (getenv("B2P_VERBOSE"))
+                    fprintf(stderr, "[b2p] op %d %dx%dx%d->%d k%d s%d res%d: tile width %d (%.1f us)\n", i, o.in_h, o.in_w,
+                            o.in_c, o.out_c, o.kh, o.stride, (int)has_res, p.gemm.block_n, best_ms * 1e3f);
             }
         } else if (o.kind == B2P_OP_STEM_CONV) {
             if (o.in_h != 112 || o.in_w != 112 || o.in_c != 16 || o.out_c != 64 || o.kh != 4 || o.kw != 4 ||
@@ -454,6 +506,8 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
         cudaMalloc(&h->probs_dev, nb * B2P_MAX_TOPK * 4) != cudaSuccess ||
         cudaMalloc(&h->idx_dev, nb * B2P_MAX_TOPK * 4) != cudaSuccess)
         B2P_FAIL(B2P_E_NOMEM, "staging allocation failed");
+    if (cudaMalloc(&h->norm_lut, 3 * 256 * sizeof(float)) != cudaSuccess || launch_norm_lut(h->norm_lut, 0) != cudaSuccess)
+        B2P_FAIL(B2P_E_NOMEM, "normalisation table set-up failed");
     for (auto& e : h->ev)
         if (cudaEventCreate(&e) != cudaSuccess) B2P_FAIL(B2P_E_CUDA, "cudaEventCreate failed");
     if (cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess)
@@ -504,7 +558,7 @@ int32_t b2p_preprocess(b2p_handle* h, const uint8_t* slab, const b2p_image* imgs
     rc = stage_images(h, imgs, n, st);
     if (rc != B2P_OK) return rc;
     int launches = 0;
-    B2P_CUDA(h, launch_preprocess(slab, h->cur_imgs_dev, imgs, n, out, out_f32, st, &launches));
+    B2P_CUDA(h, launch_preprocess(slab, h->cur_imgs_dev, imgs, n, out, out_f32, h->norm_lut, st, &launches));
     h->stats.kernel_launches += launches;
     return B2P_OK;
 }

@@ -503,6 +503,7 @@ bool gemm_plan_init(GemmPlan& p, const b2p_op& op, const void* weight_dev, int64
     long best_cost = 0;
     const int cands[3] = {256, 128, 64};
     for (int bn : cands) {
+        if (p.force_block_n && bn != p.force_block_n) continue;
         if (p.n_pad % bn != 0) continue;
         if (p.block_k == 16 && bn != 64) continue;
         if (p.out_f32 && bn != 128) continue;

@@ -33,6 +33,7 @@ struct GemmPlan {
     CUtensorMap tmap_out; // bf16 output [rows, out_c], 128 x 64 store boxes (unused by the fp32 epilogue)
     CUtensorMap tmap_res; // bf16 residual [rows, out_c], same boxes (only when the op has a residual)
     int block_n = 0;      // 64 / 128 / 256
+    int force_block_n = 0;  // set before gemm_plan_init to pin the tile width (autotuner)
     int block_k = 64;     // 64 (128-byte swizzle) or 16 (32-byte swizzle, the stem)
     int im2col = 0;       // A operand through TMA im2col mode
     int out_f32 = 0;      // fp32 [M, ldc] output (LINEAR) instead of bf16 NHWC
@@ -116,8 +117,11 @@ struct PreprocessLaunch {
     int all_identity = 0;
 };
 // `imgs_dev` is the device copy of the descriptors; `imgs_host` is used to size the launch.
+// `norm_lut` = device table [3][256] of (v/255 - mean)/std built by launch_norm_lut (may be null: the
+// crop-only fast path is then not used).
+cudaError_t launch_norm_lut(float* lut, cudaStream_t s);
 cudaError_t launch_preprocess(const uint8_t* slab, const b2p_image* imgs_dev,
                               const b2p_image* imgs_host, int n, void* out, int out_f32,
-                              cudaStream_t s, int* launches);
+                              const float* norm_lut, cudaStream_t s, int* launches);
 
 }  // namespace b2p

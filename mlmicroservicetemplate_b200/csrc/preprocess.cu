@@ -225,54 +225,65 @@ preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict_
 }
 
 // Crop-only fast path: every image of the batch already has the resized size (res == source), so
-// the resize passes are the identity and each output value depends on one source byte.  A 3 x 256
-// table of normalised values (same IEEE divisions as the general kernel, hence bit-identical) is
-// built per CTA; the body is a coalesced copy: 16-byte loads of the row window, 4-byte bf16x2
-// (or 8-byte float2) planar stores.
-constexpr int ID_ROWS = 8;
-constexpr int ID_ROW_BYTES = OUT * 3;          // 672 source bytes per output row
-constexpr int ID_ROW_PITCH = 704;              // smem pitch: 672 + 16 alignment shift, rounded to 16
+// the resize passes are the identity and each output value depends on one source byte.  The
+// normalisation is a 3 x 256 table (built once per handle with the same IEEE divisions as the general
+// kernel, hence bit-identical).  One thread = 8 consecutive pixels of one row: 24 source bytes fetched
+// as seven aligned 32-bit words + funnel shifts (any byte alignment), three 16-byte planar stores.
+__global__ void norm_lut_kernel(float* __restrict__ lut) {
+    const int v = threadIdx.x;                       // 256 threads
+    const float mean[3] = {0.485f, 0.456f, 0.406f};
+    const float stdv[3] = {0.229f, 0.224f, 0.225f};
+#pragma unroll
+    for (int c = 0; c < 3; ++c)
+        lut[c * 256 + v] = __fdiv_rn(__fsub_rn(__fdiv_rn(static_cast<float>(v), 255.0f), mean[c]), stdv[c]);
+}
 
 template <bool OUT_F32>
-__global__ void __launch_bounds__(THREADS)
-preprocess_identity_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict__ imgs, void* __restrict__ out) {
-    __shared__ float lut[3][256];
-    __shared__ __align__(16) uint8_t rows[ID_ROWS][ID_ROW_PITCH];
-    const b2p_image im = imgs[blockIdx.y];
-    const int oy0 = blockIdx.x * ID_ROWS;
-    const int tid = threadIdx.x;
-    {
-        const float mean[3] = {0.485f, 0.456f, 0.406f};
-        const float stdv[3] = {0.229f, 0.224f, 0.225f};
-#pragma unroll
-        for (int c = 0; c < 3; ++c)
-            lut[c][tid] = __fdiv_rn(__fsub_rn(__fdiv_rn(static_cast<float>(tid), 255.0f), mean[c]), stdv[c]);
-    }
-    const uint8_t* src = slab + im.offset + (static_cast<size_t>(im.top + oy0) * im.w + im.left) * 3;
-    const size_t row_stride = static_cast<size_t>(im.w) * 3;
-    int shift[ID_ROWS];
-#pragma unroll
-    for (int r = 0; r < ID_ROWS; ++r) {
-        const uint8_t* g = src + r * row_stride;
-        shift[r] = static_cast<int>(reinterpret_cast<uintptr_t>(g) & 15u);
-        stage_row(&rows[r][0], g, ID_ROW_BYTES);
-    }
-    cp_async_commit();
-    cp_async_wait_all();
+__global__ void __launch_bounds__(256)
+preprocess_identity_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict__ imgs, void* __restrict__ out,
+                           const float* __restrict__ lut_g, int n) {
+    __shared__ float lut[3 * 256];
+    for (int i = threadIdx.x; i < 3 * 256; i += 256) lut[i] = __ldg(lut_g + i);
     __syncthreads();
-    // items: (row r, channel c, pixel pair i) -> consecutive threads write consecutive 4-byte words
-    for (int item = tid; item < ID_ROWS * 3 * (OUT / 2); item += THREADS) {
-        const int i = item % (OUT / 2);
-        const int rc = item / (OUT / 2);
-        const int c = rc % 3, r = rc / 3;
-        int sh = 0;
+    const long t = blockIdx.x * 256L + threadIdx.x;
+    constexpr int GROUPS = OUT / 8;                  // 28 groups of 8 pixels per row
+    if (t >= static_cast<long>(n) * OUT * GROUPS) return;
+    const int g = static_cast<int>(t % GROUPS);
+    const int row = static_cast<int>((t / GROUPS) % OUT);
+    const int img = static_cast<int>(t / (GROUPS * OUT));
+    const b2p_image im = imgs[img];
+    const uint8_t* src = slab + im.offset + (static_cast<size_t>(im.top + row) * im.w + im.left + 8 * g) * 3;
+    const uint32_t sh = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(src) & 3u) * 8u;
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(src) & ~static_cast<uintptr_t>(3));
+    uint32_t raw[7];
 #pragma unroll
-        for (int k = 0; k < ID_ROWS; ++k) sh = (k == r) ? shift[k] : sh;
-        const uint8_t* px = &rows[r][sh + i * 6 + c];
-        const float a = lut[c][px[0]], b = lut[c][px[3]];
-        const size_t o = ((static_cast<size_t>(blockIdx.y) * 3 + c) * OUT + (oy0 + r)) * OUT + 2 * i;
-        if (OUT_F32) *reinterpret_cast<float2*>(reinterpret_cast<float*>(out) + o) = make_float2(a, b);
-        else *reinterpret_cast<uint32_t*>(reinterpret_cast<uint16_t*>(out) + o) = pack_bf16x2(a, b);
+    for (int k = 0; k < 6; ++k) raw[k] = __ldg(w + k);
+    raw[6] = sh ? __ldg(w + 6) : 0u;                 // only touched when the 24 bytes straddle a 7th word
+    uint32_t b[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) b[k] = __funnelshift_r(raw[k], raw[k + 1], sh);
+    // b[] now holds the 24 bytes r0 g0 b0 r1 g1 b1 ... little-endian
+    float v[3][8];
+#pragma unroll
+    for (int px = 0; px < 8; ++px)
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const int byte = px * 3 + c;
+            v[c][px] = lut[c * 256 + ((b[byte >> 2] >> ((byte & 3) * 8)) & 0xFFu)];
+        }
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+        const size_t o = ((static_cast<size_t>(img) * 3 + c) * OUT + row) * OUT + 8 * g;
+        if (OUT_F32) {
+            float4* o4 = reinterpret_cast<float4*>(reinterpret_cast<float*>(out) + o);
+            o4[0] = make_float4(v[c][0], v[c][1], v[c][2], v[c][3]);
+            o4[1] = make_float4(v[c][4], v[c][5], v[c][6], v[c][7]);
+        } else {
+            uint4 q;
+            q.x = pack_bf16x2(v[c][0], v[c][1]); q.y = pack_bf16x2(v[c][2], v[c][3]);
+            q.z = pack_bf16x2(v[c][4], v[c][5]); q.w = pack_bf16x2(v[c][6], v[c][7]);
+            *reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(out) + o) = q;
+        }
     }
 }
 
@@ -284,8 +295,13 @@ inline int host_max_taps(int in_size, int out_size) {
 
 }  // namespace
 
+cudaError_t launch_norm_lut(float* lut, cudaStream_t s) {
+    norm_lut_kernel<<<1, 256, 0, s>>>(lut);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_preprocess(const uint8_t* slab, const b2p_image* imgs_dev, const b2p_image* imgs_host,
-                              int n, void* out, int out_f32, cudaStream_t s, int* launches) {
+                              int n, void* out, int out_f32, const float* norm_lut, cudaStream_t s, int* launches) {
     if (n <= 0) return cudaSuccess;
     int wh_taps = 1, wv_taps = 1, max_w = 1;
     for (int i = 0; i < n; ++i) {
@@ -298,10 +314,11 @@ cudaError_t launch_preprocess(const uint8_t* slab, const b2p_image* imgs_dev, co
     bool all_identity = true;
     for (int i = 0; i < n; ++i)
         all_identity = all_identity && imgs_host[i].h == imgs_host[i].res_h && imgs_host[i].w == imgs_host[i].res_w;
-    if (all_identity) {
-        dim3 grid(OUT / ID_ROWS, n);
-        if (out_f32) preprocess_identity_kernel<true><<<grid, THREADS, 0, s>>>(slab, imgs_dev, out);
-        else preprocess_identity_kernel<false><<<grid, THREADS, 0, s>>>(slab, imgs_dev, out);
+    if (all_identity && norm_lut != nullptr) {
+        const long threads = static_cast<long>(n) * OUT * (OUT / 8);
+        const unsigned grid = static_cast<unsigned>((threads + 255) / 256);
+        if (out_f32) preprocess_identity_kernel<true><<<grid, 256, 0, s>>>(slab, imgs_dev, out, norm_lut, n);
+        else preprocess_identity_kernel<false><<<grid, 256, 0, s>>>(slab, imgs_dev, out, norm_lut, n);
         if (launches) *launches += 1;
         return cudaGetLastError();
     }

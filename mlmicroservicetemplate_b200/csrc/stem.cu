@@ -209,19 +209,21 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 float f[32];
+                // issue the TMEM loads of all conv rows first, wait once (the loads overlap each other)
+                uint32_t v[ROWS][32];
+#pragma unroll
+                for (int ri = 0; ri < ROWS; ++ri) tmem_ld_32x32(t_addr + static_cast<uint32_t>(ri * OUT_C + h * 32), v[ri]);
+                tmem_ld_wait();
 #pragma unroll
                 for (int ri = 0; ri < ROWS; ++ri) {
-                    uint32_t v[32];
-                    tmem_ld_32x32(t_addr + static_cast<uint32_t>(ri * OUT_C + h * 32), v);
-                    tmem_ld_wait();
                     // conv row 2t-1 does not exist for t == 0: the pool window ignores it (implicit -inf pad)
                     const bool valid = !POOL || ri > 0 || t > 0;
                     if (ri == 0) {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) f[j] = valid ? __uint_as_float(v[j]) : -3.0e38f;
+                        for (int j = 0; j < 32; ++j) f[j] = valid ? __uint_as_float(v[0][j]) : -3.0e38f;
                     } else {
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], __uint_as_float(v[j]));
+                        for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], __uint_as_float(v[ri][j]));
                     }
                 }
                 const float4* b4 = reinterpret_cast<const float4*>(bias + h * 32);

@@ -89,3 +89,59 @@ def test_resnet50_b16(cuda_device):
     # (SURVEY §8c c6), so the gate is relative here and the absolute number is reported.
     assert top1 == 1.0
     assert err / scale <= 8e-3
+
+
+def test_resnet50_b256_properties(cuda_device):
+    """BASELINE.json's full size (ResNet-50, batch 256) through size-independent properties: the batch
+    result is bit-identical to the same images run in four chunks of 64, to a second run (determinism),
+    and a permuted batch gives the permuted logits (no cross-image coupling anywhere in the path)."""
+    from mlmicroservicetemplate_b200 import backend as B, program as P
+    from oracle import images, model as om
+    model = om.build_model("resnet50")
+    prog = P.build_program(model, "resnet50")
+    n = 256
+    base = images.synthetic_batch(7, 32, 224, 224)
+    g = torch.Generator().manual_seed(77)
+    x = torch.stack([torch.from_numpy(base[i % 32].astype(np.float32)).permute(2, 0, 1) / 255.0 for i in range(n)])
+    x = (x + 0.05 * torch.randn(x.shape, generator=g)).to(torch.bfloat16).cuda()
+    rep = B.Replica(0, prog, max_batch=n)
+
+    def run(inp, m):
+        out = torch.full((m, 1000), float("nan"), device="cuda")
+        rep.forward(inp, m, out)
+        torch.cuda.synchronize()
+        return out
+
+    full = run(x, n)
+    assert not torch.isnan(full).any()
+    assert torch.equal(full, run(x, n)), "two runs of the same batch must be bit-identical"
+    chunks = torch.cat([run(x[i:i + 64].contiguous(), 64) for i in range(0, n, 64)])
+    assert torch.equal(full, chunks), "batch 256 must equal 4 x batch 64 bit for bit"
+    perm = torch.randperm(n, generator=g).cuda()
+    assert torch.equal(run(x[perm].contiguous(), n), full[perm]), "permuting the batch must permute the logits"
+    # anchor the full-size run to the oracle on a slice the CPU finishes in seconds
+    ref = om.forward_logits(x[:8].float().cpu(), model)
+    err = (full[:8].cpu() - ref).abs().max().item()
+    assert err / ref.abs().max().item() <= 8e-3
+    rep.close()
+
+
+def test_replicas_on_different_gpus_agree_bit_for_bit(cuda_device):
+    """SURVEY §8e determinism check: the same batch through the replica on any GPU gives identical logits."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs at least two GPUs")
+    from mlmicroservicetemplate_b200 import backend as B, program as P
+    from oracle import model as om
+    prog = P.build_program(om.build_model("resnet18"), "resnet18")
+    x = torch.randn(16, 3, 224, 224, generator=torch.Generator().manual_seed(5)).to(torch.bfloat16)
+    outs = []
+    for dev in range(torch.cuda.device_count()):
+        with torch.cuda.device(dev):
+            rep = B.Replica(dev, prog, max_batch=16)
+            out = torch.empty(16, 1000, device=f"cuda:{dev}")
+            rep.forward(x.to(f"cuda:{dev}"), 16, out)
+            torch.cuda.synchronize(dev)
+            outs.append(out.cpu())
+            rep.close()
+    torch.cuda.set_device(0)
+    assert all(torch.equal(outs[0], o) for o in outs[1:])

@@ -28,8 +28,10 @@ def interpret(prog: P.Program, x_nchw: torch.Tensor) -> torch.Tensor:
             y = F.conv2d(xin, w.permute(0, 3, 1, 2), b, stride=op.stride).permute(0, 2, 3, 1)
             if op.res != B.SLOT_NONE:
                 y = y + slots[op.res]
-            if op.relu:
+            if op.relu == 1:
                 y = y.relu()
+            elif op.relu == 2:
+                y = F.gelu(y)
         elif op.kind == B.OP_STEM_CONV:
             w = prog.blobs[op.weight].float()[: op.out_c]
             b = prog.blobs[op.bias][: op.out_c]
@@ -37,6 +39,20 @@ def interpret(prog: P.Program, x_nchw: torch.Tensor) -> torch.Tensor:
             if op.reserved[0]:
                 y = F.max_pool2d(y, 3, 2, 1)
             y = y.permute(0, 2, 3, 1)
+        elif op.kind == B.OP_PATCHIFY:
+            y = F.unfold(src, kernel_size=16, stride=16).transpose(1, 2).unsqueeze(2)        # [n,196,1,768]
+        elif op.kind == B.OP_TOKENS:
+            n = src.shape[0]
+            pos = prog.blobs[op.weight].view(1, op.in_h, op.in_c)
+            cls = prog.blobs[op.bias].view(1, 1, op.in_c).expand(n, 1, op.in_c)
+            y = (torch.cat([cls, src.view(n, op.in_h - 1, op.in_c)], 1) + pos).unsqueeze(2)
+        elif op.kind == B.OP_LAYERNORM:
+            y = F.layer_norm(src.squeeze(2), (op.in_c,), prog.blobs[op.weight], prog.blobs[op.bias], eps=1e-6)
+            y = y[:, 0] if op.reserved[0] else y.unsqueeze(2)
+        elif op.kind == B.OP_ATTENTION:
+            n, heads = src.shape[0], op.reserved[0]
+            q, k, v = [t.view(n, op.in_h, heads, op.in_c // heads).transpose(1, 2) for t in src.squeeze(2).split(op.in_c, dim=2)]
+            y = F.scaled_dot_product_attention(q, k, v).transpose(1, 2).reshape(n, op.in_h, 1, op.in_c)
         elif op.kind == B.OP_MAXPOOL:
             y = F.max_pool2d(src.permute(0, 3, 1, 2), op.kh, op.stride, op.pad_lo).permute(0, 2, 3, 1)
         elif op.kind == B.OP_AVGPOOL:
@@ -45,7 +61,7 @@ def interpret(prog: P.Program, x_nchw: torch.Tensor) -> torch.Tensor:
             y = src @ prog.blobs[op.weight].float()[: op.out_c].t() + prog.blobs[op.bias][: op.out_c]
         else:
             raise AssertionError(op.kind)
-        assert tuple(y.shape[1:]) in ((op.out_h, op.out_w, op.out_c), (op.out_c,)), (op.kind, y.shape)
+        assert tuple(y.shape[1:]) in ((op.out_h, op.out_w, op.out_c), (op.out_c,)), (op.kind, tuple(y.shape))
         if op.dst == B.SLOT_OUTPUT:
             out = y
         else:
@@ -78,9 +94,24 @@ def test_program_reproduces_the_torchvision_forward(arch, flops):
     assert torch.equal(got.argmax(1), ref.argmax(1))
 
 
-def test_slots_are_never_clobbered_while_live():
-    import torchvision
-    prog = P.build_resnet_program(torchvision.models.resnet50(weights=None), "resnet50")
+def test_vit_program_reproduces_the_torchvision_forward():
+    from mlmicroservicetemplate_b200.runtime import seeded_model
+    model = seeded_model("vit_b_16", 0)
+    prog = P.build_program(model, "vit_b_16")
+    assert abs(prog.flops_per_image - 35.128e9) / 35.128e9 < 5e-3
+    g = torch.Generator().manual_seed(4)
+    x = torch.randn(2, 3, 224, 224, generator=g).to(torch.bfloat16).float()
+    with torch.no_grad():
+        ref = model(x)
+        got = interpret(prog, x)
+    assert ref.abs().max().item() > 0.5, "the re-initialised head must give non-trivial logits"
+    assert (got - ref).abs().max().item() < 0.03 * ref.abs().max().item()
+
+
+@pytest.mark.parametrize("arch", ["resnet50", "vit_b_16"])
+def test_slots_are_never_clobbered_while_live(arch):
+    from mlmicroservicetemplate_b200.runtime import seeded_model
+    prog = P.build_program(seeded_model(arch, 0), arch)
     last_read = {}
     for i, op in enumerate(prog.ops):
         for s in (op.src, op.res):
