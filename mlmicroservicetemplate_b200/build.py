@@ -30,6 +30,9 @@ NVCC_FLAGS = [
 ]
 
 
+PER_FILE_FLAGS = {}
+
+
 def _nvcc() -> str:
     cand = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(cand):
@@ -57,7 +60,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
     for src in SOURCES:
         obj = obj_dir / (src.replace(".cu", ".o"))
         objs.append(str(obj))
-        cmd = [nvcc, *NVCC_FLAGS, "-c", str(CSRC / src), "-o", str(obj)]
+        cmd = [nvcc, *NVCC_FLAGS, *PER_FILE_FLAGS.get(src, []), "-c", str(CSRC / src), "-o", str(obj)]
         procs.append((src, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     log = []
     failed = False

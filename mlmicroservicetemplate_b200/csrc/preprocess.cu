@@ -32,6 +32,8 @@ namespace {
 constexpr int OUT = B2P_OUT_HW;      // 224
 constexpr int BAND = 8;              // output rows per CTA
 constexpr int THREADS = 256;         // 224 compute lanes + 32 that only help copying
+constexpr int RING = 2;              // raw source rows in flight per CTA (deeper rings were measured: no gain,
+                                     // the kernel is issue-bound, and they cost occupancy on wide images)
 
 __device__ __forceinline__ float tri_filter(float x) {
     x = fabsf(x);
@@ -76,6 +78,8 @@ __device__ __forceinline__ void cp_async_16(void* dst_smem, const void* src) {
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait_pending() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // Copies `nbytes` from global `g` into shared `buf + (g & 15)` so that 16-byte vectors line up.
 __device__ __forceinline__ void stage_row(uint8_t* buf, const uint8_t* g, int nbytes) {
@@ -90,21 +94,60 @@ __device__ __forceinline__ void stage_row(uint8_t* buf, const uint8_t* g, int nb
     for (int i = tail0 + threadIdx.x; i < nbytes; i += THREADS) dst[i] = __ldg(g + i);
 }
 
+// Packed fp32x2 arithmetic (sm_100): one instruction rounds two independent IEEE fp32 results exactly as
+// the scalar instruction would, so the per-channel bit-exact contract is untouched while the
+// multiply/add count per tap halves.  A pixel is kept as two pairs: (R, G) and (B, unused).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float& lo, float& hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) {
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+// a + b with ONE rounding, written as fma(a, one, b) with `one` = (1.0f, 1.0f) coming from a kernel
+// argument.  A plain add.rn.f32x2 is not usable here: ptxas 12.9 contracts mul.rn.f32x2 + add.rn.f32x2
+// into a single FFMA2 (it never does that for the scalar .rn forms, and --fmad=false does not stop it),
+// which would turn torch's un-fused taps into fused ones.  A product feeding an FMA's *multiplicand*
+// cannot be contracted, and a*1 is exact, so this is the same IEEE result as the add.
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b, f32x2 one) {
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(one), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+__device__ __forceinline__ void lds_pixel(uint32_t addr, f32x2& rg, f32x2& bx) {
+    asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(rg), "=l"(bx) : "r"(addr));
+}
+
 template <bool OUT_F32>
 __global__ void __launch_bounds__(THREADS)
 preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict__ imgs, void* __restrict__ out,
-                  int wh_taps, int wv_taps, int rowbuf_bytes) {
+                  int wh_taps, int wv_taps, int rowbuf_bytes, int frow_bytes, float one_f) {
     extern __shared__ __align__(16) uint8_t smem[];
+    const f32x2 one = pack2(one_f, one_f);
     float* wh = reinterpret_cast<float*>(smem);                       // [wh_taps][OUT]
     float* wv = wh + wh_taps * OUT;                                   // [BAND][wv_taps]
     int* vmeta = reinterpret_cast<int*>(wv + BAND * wv_taps);         // ymin[BAND], ysize[BAND]
-    uint8_t* rowbuf = reinterpret_cast<uint8_t*>(vmeta + 2 * BAND);   // 2 x rowbuf_bytes (16B aligned)
+    uint8_t* rowbuf = reinterpret_cast<uint8_t*>(vmeta + 2 * BAND);   // RING x rowbuf_bytes raw uint8 rows (16B aligned)
+    float4* frow = reinterpret_cast<float4*>(rowbuf + RING * rowbuf_bytes);   // the current row as fp32 (R,G,B,0) pixels
 
     const b2p_image im = imgs[blockIdx.y];
     const int band0 = blockIdx.x * BAND;
     const int tid = threadIdx.x;
     const uint8_t* src = slab + im.offset;
     const int row_bytes = im.w * 3;
+    (void)frow_bytes;
 
     // ---- horizontal weights for this thread's output column, transposed into smem
     int xmin = 0, xsize = 0;
@@ -142,44 +185,60 @@ preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict_
     const int iy0 = vmeta[0];
     const int iy1 = vmeta[BAND - 1] + vmeta[2 * BAND - 1];   // ranges are monotone in the output row
 
-    float acc[BAND][3];
+    f32x2 acc_rg[BAND], acc_b[BAND];
 #pragma unroll
-    for (int r = 0; r < BAND; ++r) acc[r][0] = acc[r][1] = acc[r][2] = 0.f;
+    for (int r = 0; r < BAND; ++r) acc_rg[r] = acc_b[r] = 0ull;
 
     const int hmain = xsize > 0 ? ((xsize - 1) >> 2) << 2 : 0;   // taps 1..hmain: mul then add
+    const uint32_t frow_base = smem_u32(frow) + static_cast<uint32_t>(xmin) * 16u;
 
-    if (iy0 < iy1) stage_row(rowbuf, src + static_cast<size_t>(iy0) * row_bytes, row_bytes);
-    cp_async_commit();
+    // raw rows stream through a ring of RING buffers: a row is requested RING iterations before it is
+    // consumed, so the ~1 us global-memory latency is overlapped instead of paid once per row
+#pragma unroll
+    for (int k = 0; k < RING; ++k) {
+        if (iy0 + k < iy1) stage_row(rowbuf + k * rowbuf_bytes, src + static_cast<size_t>(iy0 + k) * row_bytes, row_bytes);
+        cp_async_commit();
+    }
 
     for (int iy = iy0; iy < iy1; ++iy) {
-        cp_async_wait_all();
-        __syncthreads();
-        const int cur = (iy - iy0) & 1;
-        if (iy + 1 < iy1)
-            stage_row(rowbuf + (cur ^ 1) * rowbuf_bytes, src + static_cast<size_t>(iy + 1) * row_bytes,
-                      row_bytes);
+        cp_async_wait_pending<RING - 1>();
+        __syncthreads();                     // raw row iy landed; everyone is done reading frow (row iy-1)
+        const int cur = (iy - iy0) % RING;
+        {   // uint8 -> fp32 once per source sample (exact), all 256 threads
+            const uint8_t* g = src + static_cast<size_t>(iy) * row_bytes;
+            const uint8_t* raw = rowbuf + cur * rowbuf_bytes + (reinterpret_cast<uintptr_t>(g) & 15u);
+            for (int px = tid; px < im.w; px += THREADS)
+                frow[px] = make_float4(static_cast<float>(raw[3 * px]), static_cast<float>(raw[3 * px + 1]),
+                                       static_cast<float>(raw[3 * px + 2]), 0.f);
+        }
+        __syncthreads();                     // frow complete, raw buffer `cur` free again
+        if (iy + RING < iy1)
+            stage_row(rowbuf + cur * rowbuf_bytes, src + static_cast<size_t>(iy + RING) * row_bytes, row_bytes);
         cp_async_commit();
 
         if (tid < OUT) {
-            const uint8_t* g = src + static_cast<size_t>(iy) * row_bytes;
-            const uint8_t* s = rowbuf + cur * rowbuf_bytes + (reinterpret_cast<uintptr_t>(g) & 15u) + xmin * 3;
-            // horizontal pass, 3 channels
+            // horizontal pass: t = x0*w0; taps 1..hmain un-fused; the rest fused (torch's loop shape)
             float w = wh[tid];
-            float h0 = __fmul_rn(static_cast<float>(s[0]), w);
-            float h1 = __fmul_rn(static_cast<float>(s[1]), w);
-            float h2 = __fmul_rn(static_cast<float>(s[2]), w);
+            f32x2 w2 = pack2(w, w), prg, pb;
+            lds_pixel(frow_base, prg, pb);
+            f32x2 hrg = mul2(prg, w2), hb = mul2(pb, w2);
             int j = 1;
-            for (; j <= hmain; ++j) {
-                w = wh[j * OUT + tid];
-                h0 = __fadd_rn(h0, __fmul_rn(static_cast<float>(s[3 * j + 0]), w));
-                h1 = __fadd_rn(h1, __fmul_rn(static_cast<float>(s[3 * j + 1]), w));
-                h2 = __fadd_rn(h2, __fmul_rn(static_cast<float>(s[3 * j + 2]), w));
+            for (; j <= hmain; j += 4) {        // hmain is a multiple of 4: the un-fused taps come in fours
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    w = wh[(j + u) * OUT + tid];
+                    w2 = pack2(w, w);
+                    lds_pixel(frow_base + static_cast<uint32_t>(j + u) * 16u, prg, pb);
+                    hrg = add2(mul2(prg, w2), hrg, one);
+                    hb = add2(mul2(pb, w2), hb, one);
+                }
             }
             for (; j < xsize; ++j) {
                 w = wh[j * OUT + tid];
-                h0 = __fmaf_rn(static_cast<float>(s[3 * j + 0]), w, h0);
-                h1 = __fmaf_rn(static_cast<float>(s[3 * j + 1]), w, h1);
-                h2 = __fmaf_rn(static_cast<float>(s[3 * j + 2]), w, h2);
+                w2 = pack2(w, w);
+                lds_pixel(frow_base + static_cast<uint32_t>(j) * 16u, prg, pb);
+                hrg = fma2(prg, w2, hrg);
+                hb = fma2(pb, w2, hb);
             }
             // vertical pass: this source row is tap t of every band row whose range contains it
 #pragma unroll
@@ -188,19 +247,17 @@ preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict_
                 const int ys = vmeta[BAND + r];
                 if (t >= 0 && t < ys) {
                     const float vw = wv[r * wv_taps + t];
+                    const f32x2 vw2 = pack2(vw, vw);
                     const int vmain = ((ys - 1) >> 2) << 2;
                     if (t == 0) {
-                        acc[r][0] = __fmul_rn(h0, vw);
-                        acc[r][1] = __fmul_rn(h1, vw);
-                        acc[r][2] = __fmul_rn(h2, vw);
+                        acc_rg[r] = mul2(hrg, vw2);
+                        acc_b[r] = mul2(hb, vw2);
                     } else if (t <= vmain) {
-                        acc[r][0] = __fadd_rn(acc[r][0], __fmul_rn(h0, vw));
-                        acc[r][1] = __fadd_rn(acc[r][1], __fmul_rn(h1, vw));
-                        acc[r][2] = __fadd_rn(acc[r][2], __fmul_rn(h2, vw));
+                        acc_rg[r] = add2(mul2(hrg, vw2), acc_rg[r], one);
+                        acc_b[r] = add2(mul2(hb, vw2), acc_b[r], one);
                     } else {
-                        acc[r][0] = __fmaf_rn(h0, vw, acc[r][0]);
-                        acc[r][1] = __fmaf_rn(h1, vw, acc[r][1]);
-                        acc[r][2] = __fmaf_rn(h2, vw, acc[r][2]);
+                        acc_rg[r] = fma2(hrg, vw2, acc_rg[r]);
+                        acc_b[r] = fma2(hb, vw2, acc_b[r]);
                     }
                 }
             }
@@ -213,9 +270,12 @@ preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict_
 #pragma unroll
         for (int r = 0; r < BAND; ++r) {
             const int oy = band0 + r;
+            float a[3], unused;
+            unpack2(acc_rg[r], a[0], a[1]);
+            unpack2(acc_b[r], a[2], unused);
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
-                const float v = __fdiv_rn(__fsub_rn(__fdiv_rn(acc[r][c], 255.0f), mean[c]), stdv[c]);
+                const float v = __fdiv_rn(__fsub_rn(__fdiv_rn(a[c], 255.0f), mean[c]), stdv[c]);
                 const size_t o = ((static_cast<size_t>(blockIdx.y) * 3 + c) * OUT + oy) * OUT + tid;
                 if (OUT_F32) reinterpret_cast<float*>(out)[o] = v;
                 else reinterpret_cast<__nv_bfloat16*>(out)[o] = __float2bfloat16_rn(v);
@@ -323,8 +383,9 @@ cudaError_t launch_preprocess(const uint8_t* slab, const b2p_image* imgs_dev, co
         return cudaGetLastError();
     }
     const int rowbuf_bytes = ((max_w * 3 + 15) / 16) * 16 + 32;
+    const int frow_bytes = max_w * 16 + 16;
     const size_t smem = static_cast<size_t>(wh_taps) * OUT * 4 + static_cast<size_t>(BAND) * wv_taps * 4 +
-                        2 * BAND * 4 + 2 * static_cast<size_t>(rowbuf_bytes);
+                        2 * BAND * 4 + RING * static_cast<size_t>(rowbuf_bytes) + frow_bytes;
     if (smem > 200 * 1024) return cudaErrorInvalidValue;
     dim3 grid(OUT / BAND, n);
     cudaError_t e;
@@ -332,12 +393,12 @@ cudaError_t launch_preprocess(const uint8_t* slab, const b2p_image* imgs_dev, co
         e = cudaFuncSetAttribute(preprocess_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  static_cast<int>(smem));
         if (e != cudaSuccess) return e;
-        preprocess_kernel<true><<<grid, THREADS, smem, s>>>(slab, imgs_dev, out, wh_taps, wv_taps, rowbuf_bytes);
+        preprocess_kernel<true><<<grid, THREADS, smem, s>>>(slab, imgs_dev, out, wh_taps, wv_taps, rowbuf_bytes, frow_bytes, 1.0f);
     } else {
         e = cudaFuncSetAttribute(preprocess_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  static_cast<int>(smem));
         if (e != cudaSuccess) return e;
-        preprocess_kernel<false><<<grid, THREADS, smem, s>>>(slab, imgs_dev, out, wh_taps, wv_taps, rowbuf_bytes);
+        preprocess_kernel<false><<<grid, THREADS, smem, s>>>(slab, imgs_dev, out, wh_taps, wv_taps, rowbuf_bytes, frow_bytes, 1.0f);
     }
     if (launches) *launches += 1;
     return cudaGetLastError();
