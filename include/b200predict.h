@@ -62,8 +62,12 @@ enum b2p_op_kind {
                               bias blob = class token f32 [c]                                            */
     B2P_OP_LAYERNORM = 10, /* per-token LayerNorm over c, eps = 1e-6; weight/bias blobs = gamma/beta f32;
                               reserved[0] = 1: only token 0 of each image -> [n, c]                      */
-    B2P_OP_ATTENTION = 11  /* softmax(Q K^T / sqrt(64)) V per head on packed QKV [n,in_h,3c] -> [n,in_h,c];
+    B2P_OP_ATTENTION = 11, /* softmax(Q K^T / sqrt(64)) V per head on packed QKV [n,in_h,3c] -> [n,in_h,c];
                               reserved[0] = number of heads (head dim 64)                                */
+    B2P_OP_CONV_PAIR = 12  /* two chained 1x1/s1 convs in one kernel (a bottleneck's conv3 and the next block's
+                              conv1): dst = relu(conv(src) + bias + res) as OP_CONV, and additionally
+                              slot reserved[0] = relu(conv(dst) + bias2) with weight blob reserved[1] and bias blob
+                              reserved[2], reserved[3] = its output channels (64, 128 or 256)                 */
 };
 
 typedef struct b2p_op {

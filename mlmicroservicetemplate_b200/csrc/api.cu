@@ -19,6 +19,7 @@ struct OpPlan {
     GemmPlan gemm;        // valid for CONV / LINEAR
     StemPlan stem;        // valid for STEM_CONV
     AttentionPlan att;    // valid for ATTENTION
+    PairPlan pair;        // valid for CONV_PAIR
     void* stem_image = nullptr;
     bool is_gemm = false;
     bool src_external = false;
@@ -106,7 +107,7 @@ int validate_desc(const b2p_model_desc* d) {
     if (d->sub_batch < 0) return B2P_E_ARG;
     for (int i = 0; i < d->n_ops; ++i) {
         const b2p_op& o = d->ops[i];
-        if (o.kind < B2P_OP_CONV || o.kind > B2P_OP_ATTENTION) return B2P_E_ARG;
+        if (o.kind < B2P_OP_CONV || o.kind > B2P_OP_CONV_PAIR) return B2P_E_ARG;
         auto ok_slot = [&](int s, bool allow_none) {
             if (s == B2P_SLOT_NONE) return allow_none;
             if (s == B2P_SLOT_OUTPUT) return true;
@@ -115,8 +116,14 @@ int validate_desc(const b2p_model_desc* d) {
         if (!ok_slot(o.src, false) || o.src == B2P_SLOT_OUTPUT) return B2P_E_ARG;
         if (!ok_slot(o.dst, false) || o.dst == B2P_SLOT_INPUT) return B2P_E_ARG;
         if (!ok_slot(o.res, true) || o.res == B2P_SLOT_OUTPUT) return B2P_E_ARG;
+        if (o.kind == B2P_OP_CONV_PAIR) {
+            if (o.reserved[0] <= 0 || o.reserved[0] >= d->n_slots || o.reserved[1] < 0 || o.reserved[1] >= d->n_blobs ||
+                o.reserved[2] < 0 || o.reserved[2] >= d->n_blobs || o.res == B2P_SLOT_NONE || o.src == B2P_SLOT_INPUT ||
+                o.dst == B2P_SLOT_OUTPUT || o.res == B2P_SLOT_INPUT)
+                return B2P_E_ARG;
+        }
         if (o.kind == B2P_OP_CONV || o.kind == B2P_OP_LINEAR || o.kind == B2P_OP_STEM_CONV ||
-            o.kind == B2P_OP_TOKENS || o.kind == B2P_OP_LAYERNORM) {
+            o.kind == B2P_OP_TOKENS || o.kind == B2P_OP_LAYERNORM || o.kind == B2P_OP_CONV_PAIR) {
             if (o.weight < 0 || o.weight >= d->n_blobs || o.bias < 0 || o.bias >= d->n_blobs) return B2P_E_ARG;
         }
     }
@@ -133,12 +140,16 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
     for (int off = 0; off < n; off += h->chunk) {
         const int nb = (n - off) < h->chunk ? (n - off) : h->chunk;
         for (OpPlan& p : h->ops) {
+            int op_dir = 0;
             {
-                const int dir = (p.is_gemm && alternate) ? !touch_of(p.op.src) : 0;
+                const bool directed = p.is_gemm || p.op.kind == B2P_OP_CONV_PAIR;
+                const int dir = (directed && alternate) ? !touch_of(p.op.src) : 0;
                 if (p.is_gemm) p.gemm.reverse = dir;
+                op_dir = dir;
                 touch_of(p.op.src) = dir;
                 if (p.op.res != B2P_SLOT_NONE) touch_of(p.op.res) = dir;
                 touch_of(p.op.dst) = dir;
+                if (p.op.kind == B2P_OP_CONV_PAIR) touch_of(p.op.reserved[0]) = dir;
             }
             const b2p_op& o = p.op;
             const void* src = slot_ptr(h, o.src, x, out, off);
@@ -184,6 +195,9 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
                     e = stem_plan_launch(p.stem, nb, o.relu, h->num_sms, st);
                     break;
                 }
+                case B2P_OP_CONV_PAIR:
+                    e = pair_plan_launch(p.pair, nb * o.out_h * o.out_w, op_dir, h->num_sms, st);
+                    break;
                 case B2P_OP_PATCHIFY:
                     e = launch_patchify(src, dst, nb, st);
                     break;
@@ -477,6 +491,24 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
                 if (!stem_plan_init(p.stem, h->slots[o.src], h->slots[o.dst], h->chunk, o.reserved[0], eb, sizeof eb))
                     B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
             }
+        } else if (o.kind == B2P_OP_CONV_PAIR) {
+            const int n2 = o.reserved[3];
+            const int64_t rows_cap = static_cast<int64_t>(h->chunk) * o.out_h * o.out_w;
+            if (o.kh != 1 || o.kw != 1 || o.stride != 1 || o.pad_lo != 0 || !pair_plan_supported(o.in_c, o.out_c, n2) ||
+                h->blob_bytes[o.weight] != static_cast<int64_t>(o.out_c) * o.in_c * 2 ||
+                h->blob_bytes[o.reserved[1]] != static_cast<int64_t>(n2) * o.out_c * 2 ||
+                h->blob_bytes[o.bias] < o.out_c * 4 || h->blob_bytes[o.reserved[2]] < n2 * 4)
+                B2P_FAIL(B2P_E_ARG, "op %d: malformed CONV_PAIR", i);
+            void* s_src = h->slots[o.src]; void* s_res = h->slots[o.res]; void* s_dst = h->slots[o.dst];
+            void* s_dst2 = h->slots[o.reserved[0]];
+            if (!s_src || !s_res || !s_dst || !s_dst2) B2P_FAIL(B2P_E_ARG, "op %d uses an empty slot", i);
+            if (h->slot_elems[o.dst] < static_cast<int64_t>(o.out_h) * o.out_w * o.out_c ||
+                h->slot_elems[o.reserved[0]] < static_cast<int64_t>(o.out_h) * o.out_w * n2)
+                B2P_FAIL(B2P_E_ARG, "op %d: destination slot too small", i);
+            if (!pair_plan_init(p.pair, o.in_c, o.out_c, n2, h->blobs[o.weight], static_cast<const float*>(h->blobs[o.bias]),
+                                h->blobs[o.reserved[1]], static_cast<const float*>(h->blobs[o.reserved[2]]), eb, sizeof eb) ||
+                !pair_plan_set_buffers(p.pair, s_src, s_res, s_dst, s_dst2, static_cast<int>(rows_cap), eb, sizeof eb))
+                B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
         } else if (o.kind == B2P_OP_ATTENTION) {
             if (o.src != B2P_SLOT_INPUT) {
                 if (!h->slots[o.src]) B2P_FAIL(B2P_E_ARG, "op %d reads an empty slot", i);

@@ -1,0 +1,439 @@
+// K2 fusion: a bottleneck block's last 1x1 conv (conv3 + folded BN + residual + ReLU) together with the
+// NEXT block's first 1x1 conv (conv1 + folded BN + ReLU), as one persistent tcgen05 kernel
+// (SP/torchvision/models/resnet.py:143-163: out = relu(bn3(conv3(t2)) + identity); t1' = relu(bn1'(conv1'(out)))).
+//
+//   out1[M, N1] = relu(A[M, K1] * W3[N1, K1]^T + b3 + res[M, N1])          (written: it is the next identity)
+//   out2[M, N2] = relu(out1[M, N1] * W1[N2, N1]^T + b1)                     (never re-reads out1 from HBM)
+//
+// Un-fused, conv1' re-reads the block output from HBM (411 MB per 256 images at 56x56x256); here the
+// epilogue's bf16 staging tiles - already [128 rows x 64 channels] in the 128-byte-swizzled K-major form
+// a tcgen05.mma A operand needs - feed a second accumulator directly, so that read disappears together
+// with one kernel launch per block.
+//
+// One CTA owns a 128-row tile across ALL N1 columns (sub-tiles of 128 columns, two 64-column chunks
+// each).  TMEM: two 128-column accumulators for GEMM1 (double buffered) + N2 columns for GEMM2.
+// Warps: 0 = TMA producer (A, W3), 1 = TMEM owner + MMA issuer (both GEMMs), 2 = loader for the
+// residual chunks and W1 tiles, 3 = idle, 4..7 = epilogue.
+#include <cstdio>
+#include <cudaTypedefs.h>
+#include "kernels.h"
+#include "ptx.cuh"
+
+namespace b2p {
+namespace {
+
+constexpr int BM = 128;
+constexpr int BN1 = 128;                 // GEMM1 sub-tile width
+constexpr int TILE16K = 128 * 64 * 2;    // one 128 x 64 bf16 tile, 128B swizzle
+constexpr int G1_STAGES = 2;
+constexpr int G1_STAGE_BYTES = 2 * TILE16K;      // A (128 x 64) + W3 (128 x 64)
+constexpr int STG_BUFS = 3;              // staging tiles that double as GEMM2 A operands
+constexpr int RES_BUFS = 2;
+constexpr int W2_BUFS = 3;               // W1 units of (<=128 rows) x 64 columns
+constexpr int PAIR_THREADS = 256;
+constexpr int PAIR_SMEM = 1024 + G1_STAGES * G1_STAGE_BYTES + (STG_BUFS + 1 + RES_BUFS + W2_BUFS) * TILE16K + 512;
+
+struct PairArgs {
+    int m_rows, m_tiles;
+    int k1_blocks;        // K1 / 64
+    int n1_tiles;         // N1 / 128
+    int reverse;
+    const float* bias1;   // [N1]
+    const float* bias2;   // [N2]
+};
+
+template <int N2>
+__global__ void __launch_bounds__(PAIR_THREADS, 1)
+conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w3,
+                 const __grid_constant__ CUtensorMap tmap_res, const __grid_constant__ CUtensorMap tmap_out1,
+                 const __grid_constant__ CUtensorMap tmap_w1, const __grid_constant__ CUtensorMap tmap_out2,
+                 const PairArgs args) {
+    constexpr int W2_UNITS = (N2 + 127) / 128;          // W1 tiles per 64-column chunk (1 or 2)
+    constexpr int W2_ROWS = N2 < 128 ? N2 : 128;        // rows per W1 tile
+    constexpr int W2_UNIT_BYTES = W2_ROWS * 128;
+    constexpr int TMEM_COLS = 512;
+    constexpr uint32_t ACC2_COL = 2 * BN1;              // GEMM2 accumulator starts after the two GEMM1 stages
+
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    uint8_t* smem_g1 = smem;                                           // G1_STAGES x (A | W3)
+    uint8_t* smem_stg = smem_g1 + G1_STAGES * G1_STAGE_BYTES;          // STG_BUFS staging / A2 tiles
+    uint8_t* smem_stg2 = smem_stg + STG_BUFS * TILE16K;                // staging for out2
+    uint8_t* smem_res = smem_stg2 + TILE16K;
+    uint8_t* smem_w2 = smem_res + RES_BUFS * TILE16K;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_w2 + W2_BUFS * TILE16K);
+    uint64_t* full_bar = bars;                          // [G1_STAGES]
+    uint64_t* empty_bar = full_bar + G1_STAGES;
+    uint64_t* acc1_full = empty_bar + G1_STAGES;        // [2]
+    uint64_t* acc1_empty = acc1_full + 2;
+    uint64_t* res_full = acc1_empty + 2;                // [RES_BUFS]
+    uint64_t* res_empty = res_full + RES_BUFS;
+    uint64_t* w2_full = res_empty + RES_BUFS;           // [W2_BUFS]
+    uint64_t* w2_empty = w2_full + W2_BUFS;
+    uint64_t* a2_full = w2_empty + W2_BUFS;             // [STG_BUFS] epilogue -> MMA: chunk staged
+    uint64_t* a2_free = a2_full + STG_BUFS;             // [STG_BUFS] MMA -> epilogue: GEMM2 finished reading
+    uint64_t* acc2_full = a2_free + STG_BUFS;           // [1]
+    uint64_t* acc2_empty = acc2_full + 1;               // [1]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc2_empty + 1);
+
+    const int warp_idx = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+
+    if (warp_idx == 0) {
+        if (elect_one()) {
+            tma_prefetch_desc(&tmap_a); tma_prefetch_desc(&tmap_w3); tma_prefetch_desc(&tmap_res);
+            tma_prefetch_desc(&tmap_out1); tma_prefetch_desc(&tmap_w1); tma_prefetch_desc(&tmap_out2);
+        }
+    } else if (warp_idx == 1) {
+        if (elect_one()) {
+            for (int i = 0; i < G1_STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+            for (int i = 0; i < 2; ++i) { mbar_init(&acc1_full[i], 1); mbar_init(&acc1_empty[i], 4); }
+            for (int i = 0; i < RES_BUFS; ++i) { mbar_init(&res_full[i], 1); mbar_init(&res_empty[i], 4); }
+            for (int i = 0; i < W2_BUFS; ++i) { mbar_init(&w2_full[i], 1); mbar_init(&w2_empty[i], 1); }
+            for (int i = 0; i < STG_BUFS; ++i) { mbar_init(&a2_full[i], 1); mbar_init(&a2_free[i], 1); }
+            mbar_init(acc2_full, 1);
+            mbar_init(acc2_empty, 4);
+            fence_mbar_init();
+        }
+        __syncwarp();
+        tmem_alloc(tmem_slot, TMEM_COLS);
+        tmem_relinquish();
+    }
+    pdl_launch_dependents();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+
+    const int chunks_per_tile = args.n1_tiles * 2;
+
+    if (warp_idx == 0) {
+        // ================================================================ TMA producer: A and W3 tiles
+        if (elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int t = blockIdx.x; t < args.m_tiles; t += gridDim.x) {
+                const int m0 = (args.reverse ? args.m_tiles - 1 - t : t) * BM;
+                for (int nt = 0; nt < args.n1_tiles; ++nt) {
+                    for (int kb = 0; kb < args.k1_blocks; ++kb) {
+                        mbar_wait(&empty_bar[stage], phase ^ 1u);
+                        mbar_arrive_expect_tx(&full_bar[stage], G1_STAGE_BYTES);
+                        uint8_t* dst = smem_g1 + stage * G1_STAGE_BYTES;
+                        tma_load_2d(&tmap_a, &full_bar[stage], dst, kb * 64, m0);
+                        tma_load_2d(&tmap_w3, &full_bar[stage], dst + TILE16K, kb * 64, nt * BN1);
+                        if (++stage == G1_STAGES) { stage = 0; phase ^= 1u; }
+                    }
+                }
+            }
+        }
+    } else if (warp_idx == 1) {
+        // ================================================================ MMA issuer (GEMM1 and GEMM2)
+        if (elect_one()) {
+            constexpr uint32_t idesc1 = umma_idesc_bf16(BM, BN1);
+            constexpr uint32_t idesc2 = umma_idesc_bf16(BM, W2_ROWS);
+            int stage = 0;
+            uint32_t phase = 0;
+            int slot = 0;
+            uint32_t slot_phase = 0;
+            int sb = 0;                 // staging buffer of the next chunk GEMM2 consumes
+            uint32_t sb_phase = 0;
+            int wb = 0;                 // W1 unit ring position
+            uint32_t wb_phase = 0;
+            uint32_t acc2_phase = 0;
+
+            auto gemm2_subtile = [&](int nt) {
+                for (int c = 0; c < 2; ++c) {
+                    const int q = nt * 2 + c;
+                    if (q == 0) {
+                        mbar_wait(acc2_empty, acc2_phase ^ 1u);     // epilogue2 of the previous tile drained acc2
+                        acc2_phase ^= 1u;
+                    }
+                    mbar_wait(&a2_full[sb], sb_phase);
+                    tc_fence_after();
+                    const uint64_t a_desc = umma_desc_kmajor(smem_u32(smem_stg + sb * TILE16K), 128);
+#pragma unroll
+                    for (int u = 0; u < W2_UNITS; ++u) {
+                        mbar_wait(&w2_full[wb], wb_phase);
+                        tc_fence_after();
+                        const uint64_t b_desc = umma_desc_kmajor(smem_u32(smem_w2 + wb * TILE16K), 128);
+                        const uint32_t d = tmem_base + ACC2_COL + static_cast<uint32_t>(u * 128);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            umma_bf16(d, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k), idesc2,
+                                      static_cast<uint32_t>((q | k) != 0));
+                        umma_commit(&w2_empty[wb]);
+                        if (++wb == W2_BUFS) { wb = 0; wb_phase ^= 1u; }
+                    }
+                    umma_commit(&a2_free[sb]);
+                    if (++sb == STG_BUFS) { sb = 0; sb_phase ^= 1u; }
+                }
+            };
+
+            for (int t = blockIdx.x; t < args.m_tiles; t += gridDim.x) {
+                for (int nt = 0; nt < args.n1_tiles; ++nt) {
+                    mbar_wait(&acc1_empty[slot], slot_phase ^ 1u);
+                    tc_fence_after();
+                    const uint32_t d1 = tmem_base + static_cast<uint32_t>(slot * BN1);
+                    for (int kb = 0; kb < args.k1_blocks; ++kb) {
+                        mbar_wait(&full_bar[stage], phase);
+                        tc_fence_after();
+                        const uint32_t base = smem_u32(smem_g1 + stage * G1_STAGE_BYTES);
+                        const uint64_t a_desc = umma_desc_kmajor(base, 128);
+                        const uint64_t b_desc = umma_desc_kmajor(base + TILE16K, 128);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            umma_bf16(d1, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k), idesc1,
+                                      static_cast<uint32_t>((kb | k) != 0));
+                        umma_commit(&empty_bar[stage]);
+                        if (++stage == G1_STAGES) { stage = 0; phase ^= 1u; }
+                    }
+                    umma_commit(&acc1_full[slot]);
+                    if (++slot == 2) { slot = 0; slot_phase ^= 1u; }
+                    if (nt >= 1) gemm2_subtile(nt - 1);       // consume the chunks the epilogue produced meanwhile
+                }
+                gemm2_subtile(args.n1_tiles - 1);
+                umma_commit(acc2_full);
+            }
+        }
+    } else if (warp_idx == 2) {
+        // ================================================================ loader: residual chunks + W1 tiles
+        if (elect_one()) {
+            int rb = 0;
+            uint32_t rb_phase = 0;
+            int wb = 0;
+            uint32_t wb_phase = 0;
+            for (int t = blockIdx.x; t < args.m_tiles; t += gridDim.x) {
+                const int m0 = (args.reverse ? args.m_tiles - 1 - t : t) * BM;
+                for (int q = 0; q < chunks_per_tile; ++q) {
+                    mbar_wait(&res_empty[rb], rb_phase ^ 1u);
+                    mbar_arrive_expect_tx(&res_full[rb], TILE16K);
+                    tma_load_2d(&tmap_res, &res_full[rb], smem_res + rb * TILE16K, q * 64, m0);
+                    if (++rb == RES_BUFS) { rb = 0; rb_phase ^= 1u; }
+                    for (int u = 0; u < W2_UNITS; ++u) {
+                        mbar_wait(&w2_empty[wb], wb_phase ^ 1u);
+                        mbar_arrive_expect_tx(&w2_full[wb], W2_UNIT_BYTES);
+                        tma_load_2d(&tmap_w1, &w2_full[wb], smem_w2 + wb * TILE16K, q * 64, u * 128);
+                        if (++wb == W2_BUFS) { wb = 0; wb_phase ^= 1u; }
+                    }
+                }
+            }
+        }
+    } else if (warp_idx >= 4) {
+        // ================================================================ epilogue
+        const int quad = warp_idx & 3;
+        const int lane = static_cast<int>(lane_id());
+        const int row = quad * 32 + lane;
+        const uint32_t swz = static_cast<uint32_t>(row & 7);
+        const bool leader = (warp_idx == 4) && (lane == 0);
+        const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+        int slot = 0;
+        uint32_t slot_phase = 0;
+        int rb = 0;
+        uint32_t rb_phase = 0;
+        int sb = 0;
+        uint32_t sb_phase = 0;          // phase of a2_free[sb] for the NEXT reuse of buffer sb
+        uint32_t acc2_phase = 0;
+        for (int t = blockIdx.x; t < args.m_tiles; t += gridDim.x) {
+            const int m0 = (args.reverse ? args.m_tiles - 1 - t : t) * BM;
+            for (int nt = 0; nt < args.n1_tiles; ++nt) {
+                mbar_wait(&acc1_full[slot], slot_phase);
+                tc_fence_after();
+#pragma unroll 1
+                for (int c = 0; c < 2; ++c) {
+                    const int col0 = nt * BN1 + c * 64;
+                    mbar_wait(&res_full[rb], rb_phase);
+                    const uint32_t res_row = smem_u32(smem_res + rb * TILE16K) + static_cast<uint32_t>(row * 128);
+                    uint4 packed[8];
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        uint32_t v[32];
+                        tmem_ld_32x32(lane_addr + static_cast<uint32_t>(slot * BN1 + c * 64 + h * 32), v);
+                        tmem_ld_wait();
+                        const float4* b4 = reinterpret_cast<const float4*>(args.bias1 + col0 + h * 32);
+                        float f[32];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 b = __ldg(b4 + j);
+                            f[4 * j + 0] = __uint_as_float(v[4 * j + 0]) + b.x;
+                            f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + b.y;
+                            f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + b.z;
+                            f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + b.w;
+                        }
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            const uint4 r = ld_shared_v4(res_row + ((static_cast<uint32_t>(h * 4 + j) ^ swz) << 4));
+                            f[8 * j + 0] += bf16_lo(r.x); f[8 * j + 1] += bf16_hi(r.x);
+                            f[8 * j + 2] += bf16_lo(r.y); f[8 * j + 3] += bf16_hi(r.y);
+                            f[8 * j + 4] += bf16_lo(r.z); f[8 * j + 5] += bf16_hi(r.z);
+                            f[8 * j + 6] += bf16_lo(r.w); f[8 * j + 7] += bf16_hi(r.w);
+                        }
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) {
+                            packed[h * 4 + j].x = pack_bf16x2(fmaxf(f[8 * j + 0], 0.f), fmaxf(f[8 * j + 1], 0.f));
+                            packed[h * 4 + j].y = pack_bf16x2(fmaxf(f[8 * j + 2], 0.f), fmaxf(f[8 * j + 3], 0.f));
+                            packed[h * 4 + j].z = pack_bf16x2(fmaxf(f[8 * j + 4], 0.f), fmaxf(f[8 * j + 5], 0.f));
+                            packed[h * 4 + j].w = pack_bf16x2(fmaxf(f[8 * j + 6], 0.f), fmaxf(f[8 * j + 7], 0.f));
+                        }
+                    }
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&res_empty[rb]);
+                    if (++rb == RES_BUFS) { rb = 0; rb_phase ^= 1u; }
+                    if (c == 1) {
+                        tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) mbar_arrive(&acc1_empty[slot]);
+                    }
+                    // staging buffer sb: GEMM2 must have finished reading its previous contents (a2_free) and the
+                    // TMA store issued STG_BUFS chunks ago must have read it (leader's bulk-group wait)
+                    mbar_wait(&a2_free[sb], sb_phase ^ 1u);
+                    if (leader) tma_store_wait_read<STG_BUFS - 1>();
+                    named_bar_sync(1, 128);
+                    const uint32_t o_row = smem_u32(smem_stg + sb * TILE16K) + static_cast<uint32_t>(row * 128);
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) st_shared_v4(o_row + ((static_cast<uint32_t>(j) ^ swz) << 4), packed[j]);
+                    fence_proxy_async_smem();
+                    named_bar_sync(1, 128);
+                    if (leader) {
+                        tma_store_2d(&tmap_out1, smem_stg + sb * TILE16K, col0, m0);
+                        tma_store_commit();
+                        mbar_arrive(&a2_full[sb]);          // the tile is also GEMM2's A operand now
+                    }
+                    if (++sb == STG_BUFS) { sb = 0; sb_phase ^= 1u; }
+                }
+                if (++slot == 2) { slot = 0; slot_phase ^= 1u; }
+            }
+            // ---- second epilogue: out2 = relu(acc2 + bias2)
+            mbar_wait(acc2_full, acc2_phase);
+            acc2_phase ^= 1u;
+            tc_fence_after();
+#pragma unroll 1
+            for (int c2 = 0; c2 < N2 / 64; ++c2) {
+                uint4 packed[8];
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(lane_addr + ACC2_COL + static_cast<uint32_t>(c2 * 64 + h * 32), v);
+                    tmem_ld_wait();
+                    const float4* b4 = reinterpret_cast<const float4*>(args.bias2 + c2 * 64 + h * 32);
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) {
+                        const float4 ba = __ldg(b4 + 2 * j), bb = __ldg(b4 + 2 * j + 1);
+                        packed[h * 4 + j].x = pack_bf16x2(fmaxf(__uint_as_float(v[8 * j + 0]) + ba.x, 0.f), fmaxf(__uint_as_float(v[8 * j + 1]) + ba.y, 0.f));
+                        packed[h * 4 + j].y = pack_bf16x2(fmaxf(__uint_as_float(v[8 * j + 2]) + ba.z, 0.f), fmaxf(__uint_as_float(v[8 * j + 3]) + ba.w, 0.f));
+                        packed[h * 4 + j].z = pack_bf16x2(fmaxf(__uint_as_float(v[8 * j + 4]) + bb.x, 0.f), fmaxf(__uint_as_float(v[8 * j + 5]) + bb.y, 0.f));
+                        packed[h * 4 + j].w = pack_bf16x2(fmaxf(__uint_as_float(v[8 * j + 6]) + bb.z, 0.f), fmaxf(__uint_as_float(v[8 * j + 7]) + bb.w, 0.f));
+                    }
+                }
+                if (c2 == N2 / 64 - 1) {
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(acc2_empty);
+                }
+                if (leader) tma_store_wait_read<0>();      // smem_stg2 is single-buffered
+                named_bar_sync(1, 128);
+                const uint32_t o_row = smem_u32(smem_stg2) + static_cast<uint32_t>(row * 128);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) st_shared_v4(o_row + ((static_cast<uint32_t>(j) ^ swz) << 4), packed[j]);
+                fence_proxy_async_smem();
+                named_bar_sync(1, 128);
+                if (leader) {
+                    tma_store_2d(&tmap_out2, smem_stg2, c2 * 64, m0);
+                    tma_store_commit();
+                }
+            }
+        }
+        if (leader) tma_store_wait_all<0>();
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp_idx == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, TMEM_COLS);
+    }
+}
+
+PFN_cuTensorMapEncodeTiled_v12000 g_pair_encode = nullptr;
+
+bool pair_encode(CUtensorMap* m, const void* base, uint64_t cols, uint64_t rows, uint32_t box_cols, uint32_t box_rows) {
+    if (!g_pair_encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess ||
+            qres != cudaDriverEntryPointSuccess || !fn)
+            return false;
+        g_pair_encode = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(fn);
+    }
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {cols * 2};
+    cuuint32_t box[2] = {box_cols, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    return g_pair_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int N2>
+cudaError_t launch_pair(const PairPlan& p, const PairArgs& a, int grid, cudaStream_t s) {
+    static bool attr_set[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (!attr_set[dev]) {
+        cudaError_t e = cudaFuncSetAttribute(conv_pair_kernel<N2>, cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM);
+        if (e != cudaSuccess) return e;
+        attr_set[dev] = true;
+    }
+    return launch_pdl(conv_pair_kernel<N2>, dim3(grid), dim3(PAIR_THREADS), PAIR_SMEM, s, p.tmap_a, p.tmap_w3, p.tmap_res,
+                      p.tmap_out1, p.tmap_w1, p.tmap_out2, a);
+}
+
+}  // namespace
+
+bool pair_plan_supported(int k1, int n1, int n2) {
+    return k1 % 64 == 0 && n1 % 128 == 0 && n1 >= 128 && (n2 == 64 || n2 == 128 || n2 == 256);
+}
+
+bool pair_plan_init(PairPlan& p, int k1, int n1, int n2, const void* w3, const float* b3, const void* w1, const float* b1,
+                    char* err, size_t err_len) {
+    if (!pair_plan_supported(k1, n1, n2)) {
+        snprintf(err, err_len, "conv pair needs K1 %% 64 == 0, N1 %% 128 == 0 and N2 in {64,128,256} (got %d, %d, %d)", k1, n1, n2);
+        return false;
+    }
+    p.k1 = k1; p.n1 = n1; p.n2 = n2; p.bias1 = b3; p.bias2 = b1;
+    const uint32_t w1_rows = n2 < 128 ? n2 : 128;
+    if (!pair_encode(&p.tmap_w3, w3, k1, n1, 64, 128) || !pair_encode(&p.tmap_w1, w1, n1, n2, 64, w1_rows)) {
+        snprintf(err, err_len, "conv pair weight tensor maps failed");
+        return false;
+    }
+    return true;
+}
+
+bool pair_plan_set_buffers(PairPlan& p, const void* a, const void* res, void* out1, void* out2, int rows, char* err,
+                           size_t err_len) {
+    if (!pair_encode(&p.tmap_a, a, p.k1, rows, 64, 128) || !pair_encode(&p.tmap_res, res, p.n1, rows, 64, 128) ||
+        !pair_encode(&p.tmap_out1, out1, p.n1, rows, 64, 128) || !pair_encode(&p.tmap_out2, out2, p.n2, rows, 64, 128)) {
+        snprintf(err, err_len, "conv pair activation tensor maps failed");
+        return false;
+    }
+    return true;
+}
+
+cudaError_t pair_plan_launch(const PairPlan& p, int m_rows, int reverse, int num_sms, cudaStream_t s) {
+    PairArgs a;
+    a.m_rows = m_rows;
+    a.m_tiles = (m_rows + BM - 1) / BM;
+    a.k1_blocks = p.k1 / 64;
+    a.n1_tiles = p.n1 / BN1;
+    a.reverse = reverse;
+    a.bias1 = p.bias1;
+    a.bias2 = p.bias2;
+    if (a.m_tiles <= 0) return cudaSuccess;
+    const int grid = a.m_tiles < num_sms ? a.m_tiles : num_sms;
+    if (p.n2 == 64) return launch_pair<64>(p, a, grid, s);
+    if (p.n2 == 128) return launch_pair<128>(p, a, grid, s);
+    if (p.n2 == 256) return launch_pair<256>(p, a, grid, s);
+    return cudaErrorInvalidConfiguration;
+}
+
+}  // namespace b2p

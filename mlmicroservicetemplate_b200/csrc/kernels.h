@@ -81,6 +81,20 @@ void stem_pack_weight_image(const uint16_t* w_packed, uint16_t* image);
 bool stem_plan_init(StemPlan& p, const void* src_s2d, void* dst, int batch_cap, int pool, char* err, size_t err_len);
 cudaError_t stem_plan_launch(const StemPlan& p, int n, int relu, int num_sms, cudaStream_t stream);
 
+// ------------------------------------------------------------------ fused conv3(+res+ReLU) -> next conv1(+ReLU)
+struct PairPlan {
+    CUtensorMap tmap_a, tmap_w3, tmap_res, tmap_out1, tmap_w1, tmap_out2;
+    int k1 = 0, n1 = 0, n2 = 0;
+    const float* bias1 = nullptr;
+    const float* bias2 = nullptr;
+};
+bool pair_plan_supported(int k1, int n1, int n2);
+bool pair_plan_init(PairPlan& p, int k1, int n1, int n2, const void* w3, const float* b3, const void* w1, const float* b1,
+                    char* err, size_t err_len);
+bool pair_plan_set_buffers(PairPlan& p, const void* a, const void* res, void* out1, void* out2, int rows, char* err,
+                           size_t err_len);
+cudaError_t pair_plan_launch(const PairPlan& p, int m_rows, int reverse, int num_sms, cudaStream_t s);
+
 // ------------------------------------------------------------------ ViT pieces (vit.cu)
 struct AttentionPlan {
     CUtensorMap tmap_q;     // packed QKV [n*seq, 3*dim] bf16, 64 x 128 boxes (query tiles)

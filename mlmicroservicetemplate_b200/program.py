@@ -108,9 +108,10 @@ def stem_s2d_weight(w: torch.Tensor) -> torch.Tensor:
 
 
 def _mk_op(kind, src, dst, res=B.SLOT_NONE, in_hwc=(0, 0, 0), out_hwc=(0, 0, 0), k=(1, 1), stride=1, pad=(0, 0),
-           relu=0, weight=-1, bias=-1, flag0=0) -> B.Op:
+           relu=0, weight=-1, bias=-1, flag0=0, reserved=None) -> B.Op:
+    r = reserved if reserved is not None else (flag0, 0, 0, 0)
     return B.Op(kind, src, dst, res, in_hwc[0], in_hwc[1], in_hwc[2], out_hwc[0], out_hwc[1], out_hwc[2],
-                k[0], k[1], stride, pad[0], pad[1], relu, weight, bias, (B.C.c_int32 * 4)(flag0, 0, 0, 0))
+                k[0], k[1], stride, pad[0], pad[1], relu, weight, bias, (B.C.c_int32 * 4)(*[int(v) for v in r]))
 
 
 class _Builder:
@@ -135,7 +136,8 @@ class _Builder:
         return dst, (oh, ow, oc)
 
 
-def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_stem: bool = True) -> Program:
+def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_stem: bool = True,
+                         fuse_pairs: bool = True) -> Program:
     """Walks a torchvision ResNet (SP/torchvision/models/resnet.py:266-282: conv1-bn1-relu-maxpool,
     layer1..4, avgpool, fc) and emits the program.  Works for BasicBlock and Bottleneck nets."""
     from torchvision.models.resnet import BasicBlock, Bottleneck
@@ -173,8 +175,10 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
         p.release(c1)
     x, hwc = mp, (56, 56, 64)
 
-    for layer in (model.layer1, model.layer2, model.layer3, model.layer4):
-        for blk in layer:
+    blocks = [blk for layer in (model.layer1, model.layer2, model.layer3, model.layer4) for blk in layer]
+    carry = None          # (t1 slot, hwc1) when the previous block's CONV_PAIR already computed this block's conv1
+    for bi_, blk in enumerate(blocks):
+        if True:
             if isinstance(blk, Bottleneck):
                 w1, b1 = fold_bn(blk.conv1.weight, blk.bn1)
                 w2, b2 = fold_bn(blk.conv2.weight, blk.bn2)
@@ -186,12 +190,38 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
                     idn, _ = bld.conv(x, hwc, wd, bd, blk.downsample[0].stride[0], 0, False)
                 else:
                     idn = x
-                t1, hwc1 = bld.conv(x, hwc, w1, b1, 1, 0, True)
+                if carry is not None:
+                    t1, hwc1 = carry
+                    carry = None
+                else:
+                    t1, hwc1 = bld.conv(x, hwc, w1, b1, 1, 0, True)
                 if blk.downsample is not None:
                     p.release(x)
                 t2, hwc2 = bld.conv(t1, hwc1, w2, b2, blk.conv2.stride[0], 1, True)
                 p.release(t1)
-                out, hwc3 = bld.conv(t2, hwc2, w3, b3, 1, 0, True, res=idn)
+                # conv3 (+ residual + ReLU): fused with the NEXT block's conv1 when that is a plain 1x1/s1 conv
+                nxt = blocks[bi_ + 1] if bi_ + 1 < len(blocks) else None
+                n1 = w3.shape[0]
+                can_pair = (fuse_pairs and isinstance(nxt, Bottleneck) and nxt.conv1.kernel_size == (1, 1)
+                            and nxt.conv1.stride == (1, 1) and nxt.conv1.out_channels in (64, 128, 256)
+                            and n1 % 128 == 0 and w3.shape[1] % 64 == 0 and tuple(blk.conv3.kernel_size) == (1, 1))
+                if can_pair:
+                    wn, bn_ = fold_bn(nxt.conv1.weight, nxt.bn1)
+                    n2 = wn.shape[0]
+                    oh, ow = hwc2[0], hwc2[1]
+                    wi = p.add_blob(pack_conv_weight(w3))
+                    bi = p.add_blob(pad_bias(b3, n1))
+                    wi2 = p.add_blob(pack_conv_weight(wn))
+                    bi2 = p.add_blob(pad_bias(bn_, n2))
+                    out = p.alloc(oh * ow * n1)
+                    t1n = p.alloc(oh * ow * n2)
+                    p.ops.append(_mk_op(B.OP_CONV_PAIR, t2, out, idn, hwc2, (oh, ow, n1), (1, 1), 1, (0, 0), 1, wi, bi,
+                                        reserved=(t1n, wi2, bi2, n2)))
+                    p.flops_per_image += 2.0 * oh * ow * n1 * w3.shape[1] + 2.0 * oh * ow * n2 * n1
+                    hwc3 = (oh, ow, n1)
+                    carry = (t1n, (oh, ow, n2))
+                else:
+                    out, hwc3 = bld.conv(t2, hwc2, w3, b3, 1, 0, True, res=idn)
                 p.release(t2)
                 p.release(idn)
                 x, hwc = out, hwc3

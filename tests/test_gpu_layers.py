@@ -98,6 +98,59 @@ def test_stem_dedicated_kernel(pool, n, cuda_device):
     assert bad == 0
 
 
+@pytest.mark.parametrize("k1,n2,hw,n", [(64, 64, 56, 2), (128, 128, 28, 3), (256, 256, 14, 5), (64, 128, 56, 1)])
+def test_conv_pair_fused(k1, n2, hw, n, cuda_device):
+    """OP_CONV_PAIR (conv3 + residual + ReLU -> next conv1 + ReLU in one kernel) against the two convs in torch.
+    Both outputs are exported through an identity 1x1 conv (exact in bf16) because a program has one output."""
+    from mlmicroservicetemplate_b200 import backend as B, program as P
+    g = torch.Generator().manual_seed(k1 + n2 + hw)
+    n1 = 4 * k1
+    t2 = _bf16r(torch.randn(n, hw, hw, k1, generator=g))
+    w_id = _bf16r(torch.randn(n1, k1, 1, 1, generator=g) / k1 ** 0.5)          # makes the "identity" tensor from t2
+    w3 = _bf16r(torch.randn(n1, k1, 1, 1, generator=g) / k1 ** 0.5)
+    b3 = torch.randn(n1, generator=g) * 0.1
+    w1 = _bf16r(torch.randn(n2, n1, 1, 1, generator=g) / n1 ** 0.5)
+    b1 = torch.randn(n2, generator=g) * 0.1
+
+    def build(export_second):
+        bld = P._Builder("pair")
+        p = bld.p
+        p.in_elems = hw * hw * k1
+        idn, _ = bld.conv(B.SLOT_INPUT, (hw, hw, k1), w_id, torch.zeros(n1), 1, 0, False)
+        t2s, _ = bld.conv(B.SLOT_INPUT, (hw, hw, k1), torch.eye(k1).view(k1, k1, 1, 1), torch.zeros(k1), 1, 0, False)
+        wi, bi = p.add_blob(P.pack_conv_weight(w3)), p.add_blob(P.pad_bias(b3, n1))
+        wi2, bi2 = p.add_blob(P.pack_conv_weight(w1)), p.add_blob(P.pad_bias(b1, n2))
+        out1, out2 = p.alloc(hw * hw * n1), p.alloc(hw * hw * n2)
+        p.ops.append(P._mk_op(B.OP_CONV_PAIR, t2s, out1, idn, (hw, hw, k1), (hw, hw, n1), (1, 1), 1, (0, 0), 1, wi, bi,
+                              reserved=(out2, wi2, bi2, n2)))
+        c = n2 if export_second else n1
+        bld.conv(out2 if export_second else out1, (hw, hw, c), torch.eye(c).view(c, c, 1, 1), torch.zeros(c), 1, 0, False,
+                 dst=B.SLOT_OUTPUT)
+        p.out_elems = hw * hw * c
+        return p
+
+    x = t2.to(torch.bfloat16).cuda()
+    outs = []
+    for second in (False, True):
+        rep = B.Replica(0, build(second), max_batch=n)
+        c = n2 if second else n1
+        out = torch.full((n, hw, hw, c), float("nan"), dtype=torch.bfloat16, device="cuda")
+        rep.forward(x, n, out)
+        torch.cuda.synchronize()
+        outs.append(out.float().cpu())
+        rep.close()
+    xin = t2.permute(0, 3, 1, 2)
+    idn = _bf16r(F.conv2d(xin, w_id))
+    ref1 = (F.conv2d(xin, w3, b3) + idn).relu()
+    ref2 = F.conv2d(_bf16r(ref1), w1, b1).relu().permute(0, 2, 3, 1)
+    ref1 = ref1.permute(0, 2, 3, 1)
+    e1, e2 = (outs[0] - ref1).abs(), (outs[1] - ref2).abs()
+    print(f"pair k1={k1} n2={n2}: out1 max_err={e1.max().item():.4g} out2 max_err={e2.max().item():.4g}")
+    assert not torch.isnan(outs[0]).any() and not torch.isnan(outs[1]).any()
+    assert (e1 > 2.0 ** -7 * ref1.abs() + 2e-2).sum().item() == 0
+    assert (e2 > 2.0 ** -6 * ref2.abs() + 3e-2).sum().item() == 0      # second conv sees a bf16-rounded input
+
+
 def test_conv_sub_batched(cuda_device):
     # same op run in chunks of 2 images: exercises the external-source re-encode and chunk offsets
     _run_conv(5, (28, 28, 128), 128, 3, 1, 1, True, False, seed=11, sub_batch=2)

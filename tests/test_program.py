@@ -32,6 +32,16 @@ def interpret(prog: P.Program, x_nchw: torch.Tensor) -> torch.Tensor:
                 y = y.relu()
             elif op.relu == 2:
                 y = F.gelu(y)
+        elif op.kind == B.OP_CONV_PAIR:
+            w = prog.blobs[op.weight].float()[: op.out_c]
+            b = prog.blobs[op.bias][: op.out_c]
+            y = (F.conv2d(src.permute(0, 3, 1, 2), w.permute(0, 3, 1, 2), b).permute(0, 2, 3, 1) + slots[op.res]).relu()
+            dst2, wi2, bi2, n2 = op.reserved[0], op.reserved[1], op.reserved[2], op.reserved[3]
+            w2 = prog.blobs[wi2].float()[:n2]
+            # the fused kernel feeds the second conv the bf16-rounded first result (as the un-fused path would)
+            y2 = F.conv2d(y.permute(0, 3, 1, 2), w2.permute(0, 3, 1, 2), prog.blobs[bi2][:n2]).relu().permute(0, 2, 3, 1)
+            assert y2[0].numel() <= prog.slot_elems[dst2]
+            slots[dst2] = y2
         elif op.kind == B.OP_STEM_CONV:
             w = prog.blobs[op.weight].float()[: op.out_c]
             b = prog.blobs[op.bias][: op.out_c]
@@ -117,22 +127,26 @@ def test_slots_are_never_clobbered_while_live(arch):
         for s in (op.src, op.res):
             if s not in (B.SLOT_NONE,):
                 last_read[s] = i
+    def dsts(o):
+        return [o.dst] + ([o.reserved[0]] if o.kind == B.OP_CONV_PAIR else [])
     writer = {}
     for i, op in enumerate(prog.ops):
-        assert op.dst != op.src and (op.res == B.SLOT_NONE or op.dst != op.res), "no in-place ops"
-        writer[op.dst] = i
+        for d_ in dsts(op):
+            assert d_ != op.src and (op.res == B.SLOT_NONE or d_ != op.res), "no in-place ops"
+            writer[d_] = i
     # replay: a slot written at i must not be overwritten before its readers ran
     live_until = {}
     for i, op in enumerate(prog.ops):
-        if op.dst in live_until:
-            assert live_until[op.dst] < i, f"op {i} overwrites slot {op.dst} still needed by op {live_until[op.dst]}"
-        nxt = [j for j, o in enumerate(prog.ops) if j > i and (o.src == op.dst or o.res == op.dst)]
-        rewrite = [j for j, o in enumerate(prog.ops) if j > i and o.dst == op.dst]
-        horizon = rewrite[0] if rewrite else len(prog.ops)
-        readers = [j for j in nxt if j <= horizon]
-        if op.dst != B.SLOT_OUTPUT:
-            assert readers, f"op {i} writes slot {op.dst} that nobody reads"
-            live_until[op.dst] = max(readers)
+        for d_ in dsts(op):
+            if d_ in live_until:
+                assert live_until[d_] < i, f"op {i} overwrites slot {d_} still needed by op {live_until[d_]}"
+            nxt = [j for j, o in enumerate(prog.ops) if j > i and (o.src == d_ or o.res == d_)]
+            rewrite = [j for j, o in enumerate(prog.ops) if j > i and d_ in dsts(o)]
+            horizon = rewrite[0] if rewrite else len(prog.ops)
+            readers = [j for j in nxt if j <= horizon]
+            if d_ != B.SLOT_OUTPUT:
+                assert readers, f"op {i} writes slot {d_} that nobody reads"
+                live_until[d_] = max(readers)
     assert len(prog.slot_elems) <= 6
 
 
