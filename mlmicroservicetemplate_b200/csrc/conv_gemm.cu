@@ -31,8 +31,8 @@ namespace {
 
 constexpr int BLOCK_M = 128;
 constexpr int UMMA_K = 16;           // bf16: 32 bytes of K per tcgen05.mma
-constexpr int NUM_THREADS = 224;     // 7 warps: TMA, MMA, residual loader, 4 x epilogue
-constexpr int EPI_THREADS = 128;
+constexpr int NUM_THREADS = 352;     // 11 warps: TMA, MMA, residual loader, 2 epilogue groups x 4 warps
+constexpr int EPI_THREADS = 128;     // per epilogue group
 constexpr int ACC_STAGES = 2;
 constexpr int SMEM_LIMIT = 227 * 1024;
 constexpr int OUT_CHUNK_BYTES = BLOCK_M * 64 * 2;   // one 128 x 64 bf16 staging tile (128B swizzle)
@@ -134,7 +134,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             }
             for (int i = 0; i < ACC_STAGES; ++i) {
                 mbar_init(&tmem_full_bar[i], 1);
-                mbar_init(&tmem_empty_bar[i], 4);   // one arrive per epilogue warp
+                mbar_init(&tmem_empty_bar[i], 8);   // one arrive per epilogue warp (two groups of four)
             }
             for (int i = 0; i < RES_STAGES; ++i) {
                 mbar_init(&res_full_bar[i], 1);
@@ -244,16 +244,24 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
     } else {
         // ========================================================================= epilogue
+        // Two groups of four warps drain the accumulator: the 64-column chunks are numbered globally
+        // (tile after tile) and group g takes the chunks with sequence number % 2 == g.  That number is
+        // also the residual ring stage (RES_STAGES == 2) and the staging buffer, so each group owns one
+        // of each and the two never wait on one another.
+        static_assert(RES_STAGES == 2 && OUT_BUFS == 2, "epilogue groups own one residual stage and one staging buffer each");
         const int quad = warp_idx & 3;                  // TMEM lanes [32*quad, 32*quad+32)
+        const int group = (warp_idx - 3) >> 2;          // 0 or 1
         const int lane = static_cast<int>(lane_id());
         const int row_in_tile = quad * 32 + lane;
-        const bool store_leader = (warp_idx == 3) && (lane == 0);
+        const bool store_leader = ((warp_idx - 3) & 3) == 0 && (lane == 0);
+        const uint32_t bar_id = 1u + static_cast<uint32_t>(group);
         int acc = 0;
         uint32_t acc_phase = 0;
-        int rs = 0;
+        const int rs = group;
         uint32_t rphase = 0;
-        int ob = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int ob = group;
+        uint32_t seq = 0;                               // global chunk sequence number at the start of the tile
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, seq += BLOCK_N / 64) {
             const int tid_ = args.reverse ? total_tiles - 1 - tile : tile;
             const int m_blk = tid_ / args.n_tiles;
             const int n_blk = tid_ - m_blk * args.n_tiles;
@@ -261,8 +269,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             tc_fence_after();
             const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) +
                                     static_cast<uint32_t>(acc * BLOCK_N);
-            if (OUT_F32) {
-                // ---- fp32 logits: direct, column-masked stores (tiny: n x 1000)
+            if (OUT_F32 && group == 0) {
+                // ---- fp32 logits: direct, column-masked stores (tiny: n x 1000), first group only
                 const int row = m_blk * BLOCK_M + row_in_tile;
                 const bool row_ok = row < args.m_rows;
 #pragma unroll 1
@@ -282,10 +290,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         }
                     }
                 }
-            } else {
+            } else if (!OUT_F32) {
                 // ---- bf16 NHWC: TMEM -> regs -> (+bias, +residual, ReLU) -> swizzled smem -> TMA store
 #pragma unroll 1
                 for (int c64 = 0; c64 < BLOCK_N / 64; ++c64) {
+                    if (((seq + static_cast<uint32_t>(c64)) & 1u) != static_cast<uint32_t>(group)) continue;
                     const int col0 = n_blk * BLOCK_N + c64 * 64;
                     uint32_t res_base = 0;
                     if (HAS_RES) {
@@ -338,17 +347,11 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     if (HAS_RES) {
                         __syncwarp();
                         if (lane == 0) mbar_arrive(&res_empty_bar[rs]);
-                        if (++rs == RES_STAGES) { rs = 0; rphase ^= 1u; }
+                        rphase ^= 1u;
                     }
-                    if (c64 == BLOCK_N / 64 - 1) {
-                        // last TMEM read of this tile is done: hand the accumulator back before storing
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
-                    }
-                    // staging buffer `ob` was handed to the TMA engine two chunks ago: make sure it has been read
-                    if (store_leader) tma_store_wait_read<OUT_BUFS - 1>();
-                    named_bar_sync(1, EPI_THREADS);
+                    // this group's staging buffer was handed to the TMA engine one chunk ago: it must have been read
+                    if (store_leader) tma_store_wait_read<0>();
+                    named_bar_sync(bar_id, EPI_THREADS);
                     const uint32_t o_base = smem_u32(smem_out + ob * OUT_CHUNK_BYTES) + static_cast<uint32_t>(row_in_tile * 128);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
@@ -356,19 +359,18 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                         st_shared_v4(o_base + static_cast<uint32_t>(chunk16 * 16), packed[j]);
                     }
                     fence_proxy_async_smem();
-                    named_bar_sync(1, EPI_THREADS);
+                    named_bar_sync(bar_id, EPI_THREADS);
                     if (store_leader) {
                         tma_store_2d(&tmap_out, smem_out + ob * OUT_CHUNK_BYTES, col0, m_blk * BLOCK_M);
                         tma_store_commit();
                     }
-                    ob ^= 1;
                 }
             }
-            if (OUT_F32) {
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
-            }
+            // every TMEM read this warp makes for the tile has been issued and waited for (the packed values
+            // of its last chunk are in registers / shared memory): hand the accumulator back
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
             if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1u; }
         }
         if (!OUT_F32 && store_leader) tma_store_wait_all<0>();
