@@ -12,7 +12,7 @@ from pathlib import Path
 from typing import Optional, Sequence
 
 PKG = Path(__file__).resolve().parent
-LIB_PATH = PKG / "lib" / "libb200predict.so"
+LIB_PATH = Path(os.environ.get("B2P_LIB", PKG / "lib" / "libb200predict.so"))   # B2P_LIB: A/B-test another build
 
 ABI_VERSION = 1
 SLOT_INPUT, SLOT_OUTPUT, SLOT_NONE = 0, -2, -1

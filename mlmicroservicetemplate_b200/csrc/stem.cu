@@ -32,7 +32,7 @@ constexpr int OUT_C = 64;
 constexpr int PATCH_W = 120;            // 2 pad + 112 + 1 pad, rounded up to a multiple of 8
 constexpr int TAPS = 16;
 constexpr int W_IMAGE_BYTES = TAPS * 2 * OUT_C * 16;   // [tap][k half][out ch][8 x bf16] = 32 KB
-constexpr int STEM_THREADS = 192;
+constexpr int STEM_THREADS = 320;      // TMA, MMA, 2 epilogue groups x 4 warps (group g drains TMEM stage g)
 constexpr int STEM_STAGES = 4;
 
 template <bool POOL>
@@ -43,11 +43,11 @@ struct StemCfg {
     static constexpr int STAGE_BYTES = 2 * PLANE_BYTES;
     static constexpr int ACC_COLS = POOL ? 256 : 64;            // TMEM columns per accumulator set (3 x 64 -> 256)
     static constexpr int TMEM_COLS = 2 * ACC_COLS;              // double buffered: 512 / 128
-    static constexpr int COLBUF_BYTES = POOL ? 128 * 128 : 0;   // conv columns x 64 ch bf16, swizzled
-    static constexpr int OUTBUF_BYTES = 128 * 128;              // staging for the TMA store
+    static constexpr int COLBUF_BYTES = POOL ? 128 * 128 : 0;   // conv columns x 64 ch bf16, swizzled (per group)
+    static constexpr int OUTBUF_BYTES = 128 * 128;              // staging for the TMA store (per group)
     static constexpr int OUT_ROWS = POOL ? 56 : 112;            // rows of the store box
     static constexpr int SMEM_BYTES = 1024 + W_IMAGE_BYTES + STEM_STAGES * STAGE_BYTES + 512 /*overrun slack*/ +
-                                      COLBUF_BYTES + OUTBUF_BYTES + 256 + 1024 /*second alignment*/;
+                                      2 * (COLBUF_BYTES + OUTBUF_BYTES) + 256 + 1024 /*second alignment*/;
 };
 
 __device__ __forceinline__ void tma_load_4d(const CUtensorMap* m, uint64_t* bar, void* dst, int32_t c0, int32_t c1,
@@ -92,8 +92,8 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
     uint8_t* smem_patch = smem_w + W_IMAGE_BYTES;                       // STAGES x 2 planes
     uint8_t* smem_col = smem_patch + STEM_STAGES * C::STAGE_BYTES + 512;
     smem_col = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_col) + 1023) & ~static_cast<uintptr_t>(1023));
-    uint8_t* smem_out = smem_col + C::COLBUF_BYTES;                     // 1024B aligned (COLBUF is 16 KB or 0)
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_out + C::OUTBUF_BYTES);
+    uint8_t* smem_out = smem_col + 2 * C::COLBUF_BYTES;                 // 1024B aligned (COLBUF is 16 KB or 0)
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_out + 2 * C::OUTBUF_BYTES);
     uint64_t* empty_bar = full_bar + STEM_STAGES;
     uint64_t* tmem_full_bar = empty_bar + STEM_STAGES;
     uint64_t* tmem_empty_bar = tmem_full_bar + 2;
@@ -194,11 +194,19 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
         const int quad = warp_idx & 3;
         const int lane = static_cast<int>(lane_id());
         const int q = quad * 32 + lane;                       // conv output column handled by this thread
-        const bool leader = (warp_idx == 2) && (lane == 0);
+        // two groups of four warps: group g handles every second tile of this CTA, i.e. TMEM stage g, with
+        // its own column / staging buffers and named barrier, so one group's pooling overlaps the other's
+        const int group = (warp_idx - 2) >> 2;
+        const bool leader = ((warp_idx - 2) & 3) == 0 && (lane == 0);
+        const uint32_t bar_id = 1u + static_cast<uint32_t>(group);
+        smem_col += group * C::COLBUF_BYTES;
+        smem_out += group * C::OUTBUF_BYTES;
         const uint32_t swz = static_cast<uint32_t>(q & 7);
-        int acc = 0;
+        const int acc = group;
         uint32_t acc_phase = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        int tile_iter = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tile_iter) {
+            if ((tile_iter & 1) != group) continue;
             const int img = tile / tiles_per_img;
             const int t = tile - img * tiles_per_img;
             mbar_wait(&tmem_full_bar[acc], acc_phase);
@@ -248,17 +256,17 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
-            if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+            acc_phase ^= 1u;
 
             // the previous tile's TMA store must have finished reading the staging buffer
             if (leader) tma_store_wait_read<0>();
-            named_bar_sync(1, 128);
+            named_bar_sync(bar_id, 128);
             if (POOL) {
                 // conv columns -> shared (swizzled 16B chunks), then the horizontal 3-tap max
                 const uint32_t c_base = smem_u32(smem_col) + static_cast<uint32_t>(q * 128);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) st_shared_v4(c_base + ((static_cast<uint32_t>(j) ^ swz) << 4), packed[j]);
-                named_bar_sync(1, 128);
+                named_bar_sync(bar_id, 128);
                 const uint32_t col0 = smem_u32(smem_col), out0 = smem_u32(smem_out);
                 for (int item = q; item < 56 * 8; item += 128) {
                     const int i = item >> 3, c = item & 7;          // pooled column, 8-channel chunk
@@ -280,7 +288,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
                 for (int j = 0; j < 8; ++j) st_shared_v4(o_base + ((static_cast<uint32_t>(j) ^ swz) << 4), packed[j]);
             }
             fence_proxy_async_smem();
-            named_bar_sync(1, 128);
+            named_bar_sync(bar_id, 128);
             if (leader) {
                 const int out_row0 = (img * tiles_per_img + t) * C::OUT_ROWS;
                 tma_store_2d(&tmap_out, smem_out, 0, out_row0);
