@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define B2P_ABI_VERSION 1
+#define B2P_ABI_VERSION 2
 
 /* error codes */
 #define B2P_OK 0
@@ -80,6 +80,12 @@ typedef struct b2p_op {
     int32_t relu;                   /* 0 none, 1 ReLU, 2 GELU (exact erf)                          */
     int32_t weight, bias;           /* blob indices: weight bf16 [out_c_pad][kh][kw][in_c], bias f32 */
     int32_t reserved[4];
+    /* Optional second GEMM source for OP_CONV / OP_CONV_PAIR (src2 = B2P_SLOT_NONE when unused): the op also
+       adds a 1x1 / stride src2_stride conv of slot src2 (src2_c channels, out_h*stride x out_w*stride pixels)
+       into the same accumulator - a bottleneck's projection shortcut folded into its conv3, K = in_c + src2_c.
+       The weight blob then holds [out_c_pad][kh*kw*in_c + src2_c] and the bias blob the sum of both biases.  */
+    int32_t src2, src2_c, src2_stride;
+    int32_t reserved2;
 } b2p_op;
 
 typedef struct b2p_model_desc {

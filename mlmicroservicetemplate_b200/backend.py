@@ -14,7 +14,7 @@ from typing import Optional, Sequence
 PKG = Path(__file__).resolve().parent
 LIB_PATH = Path(os.environ.get("B2P_LIB", PKG / "lib" / "libb200predict.so"))   # B2P_LIB: A/B-test another build
 
-ABI_VERSION = 1
+ABI_VERSION = 2
 SLOT_INPUT, SLOT_OUTPUT, SLOT_NONE = 0, -2, -1
 OP_CONV, OP_LINEAR, OP_MAXPOOL, OP_AVGPOOL, OP_STEM_PACK, OP_NCHW_TO_NHWC, OP_STEM_CONV = 1, 2, 3, 4, 5, 6, 7
 OP_PATCHIFY, OP_TOKENS, OP_LAYERNORM, OP_ATTENTION, OP_CONV_PAIR = 8, 9, 10, 11, 12
@@ -40,6 +40,7 @@ class Op(C.Structure):
         ("kh", C.c_int32), ("kw", C.c_int32), ("stride", C.c_int32),
         ("pad_lo", C.c_int32), ("pad_hi", C.c_int32), ("relu", C.c_int32),
         ("weight", C.c_int32), ("bias", C.c_int32), ("reserved", C.c_int32 * 4),
+        ("src2", C.c_int32), ("src2_c", C.c_int32), ("src2_stride", C.c_int32), ("reserved2", C.c_int32),
     ]
 
 

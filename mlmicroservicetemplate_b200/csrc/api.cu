@@ -116,6 +116,8 @@ int validate_desc(const b2p_model_desc* d) {
         if (!ok_slot(o.src, false) || o.src == B2P_SLOT_OUTPUT) return B2P_E_ARG;
         if (!ok_slot(o.dst, false) || o.dst == B2P_SLOT_INPUT) return B2P_E_ARG;
         if (!ok_slot(o.res, true) || o.res == B2P_SLOT_OUTPUT) return B2P_E_ARG;
+        if (o.src2_c > 0 && (o.src2 <= 0 || o.src2 >= d->n_slots || (o.kind != B2P_OP_CONV && o.kind != B2P_OP_CONV_PAIR)))
+            return B2P_E_ARG;
         if (o.kind == B2P_OP_CONV_PAIR) {
             if (o.reserved[0] <= 0 || o.reserved[0] >= d->n_slots || o.reserved[1] < 0 || o.reserved[1] >= d->n_blobs ||
                 o.reserved[2] < 0 || o.reserved[2] >= d->n_blobs || o.res == B2P_SLOT_NONE || o.src == B2P_SLOT_INPUT ||
@@ -148,6 +150,7 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
                 op_dir = dir;
                 touch_of(p.op.src) = dir;
                 if (p.op.res != B2P_SLOT_NONE) touch_of(p.op.res) = dir;
+                if (p.op.src2_c > 0) touch_of(p.op.src2) = dir;
                 touch_of(p.op.dst) = dir;
                 if (p.op.kind == B2P_OP_CONV_PAIR) touch_of(p.op.reserved[0]) = dir;
             }
@@ -410,6 +413,11 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
                 if (!gemm_plan_set_src(p.gemm, h->slots[o.src], h->chunk, eb, sizeof eb))
                     B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
             }
+            if (p.gemm.src2_c > 0) {
+                if (!h->slots[o.src2]) B2P_FAIL(B2P_E_ARG, "op %d reads an empty second source", i);
+                if (!gemm_plan_set_src2(p.gemm, h->slots[o.src2], h->chunk, eb, sizeof eb))
+                    B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
+            }
             p.dst_external = (o.dst == B2P_SLOT_OUTPUT);
             p.res_external = (o.res == B2P_SLOT_INPUT);
             if (o.kind == B2P_OP_LINEAR && o.res != B2P_SLOT_NONE) B2P_FAIL(B2P_E_ARG, "op %d: LINEAR has no residual", i);
@@ -442,6 +450,7 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
                     if (!gemm_plan_init(cand, o, h->blobs[o.weight], h->blob_bytes[o.weight],
                                         static_cast<const float*>(h->blobs[o.bias]), rows_cap, h->num_sms, e2, sizeof e2) ||
                         !gemm_plan_set_src(cand, h->slots[o.src], h->chunk, e2, sizeof e2) ||
+                        (cand.src2_c > 0 && !gemm_plan_set_src2(cand, h->slots[o.src2], h->chunk, e2, sizeof e2)) ||
                         !gemm_plan_set_dst(cand, h->slots[o.dst], rows_cap, e2, sizeof e2) ||
                         (has_res && !gemm_plan_set_res(cand, h->slots[o.res], rows_cap, e2, sizeof e2)))
                         continue;
@@ -466,6 +475,7 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
                     if (gemm_plan_init(tuned, o, h->blobs[o.weight], h->blob_bytes[o.weight],
                                        static_cast<const float*>(h->blobs[o.bias]), rows_cap, h->num_sms, eb, sizeof eb) &&
                         gemm_plan_set_src(tuned, h->slots[o.src], h->chunk, eb, sizeof eb) &&
+                        (tuned.src2_c == 0 || gemm_plan_set_src2(tuned, h->slots[o.src2], h->chunk, eb, sizeof eb)) &&
                         gemm_plan_set_dst(tuned, h->slots[o.dst], rows_cap, eb, sizeof eb) &&
                         (!has_res || gemm_plan_set_res(tuned, h->slots[o.res], rows_cap, eb, sizeof eb)))
                         p.gemm = tuned;

@@ -121,6 +121,7 @@ extern "C" int32_t b2p_head_static(const void* feat, int32_t n, int32_t hw, int3
     op.kind = B2P_OP_LINEAR;
     op.in_c = c;
     op.out_c = classes;
+    op.src2 = B2P_SLOT_NONE;
     b2p::GemmPlan plan;
     char eb[256] = "";
     if (!b2p::gemm_plan_init(plan, op, weight, static_cast<int64_t>(weight_rows) * c * 2, bias, n, s->num_sms, eb,

@@ -32,6 +32,8 @@ struct GemmPlan {
     CUtensorMap tmap_b;   // weights [out_c_pad, K] bf16, K-major
     CUtensorMap tmap_out; // bf16 output [rows, out_c], 128 x 64 store boxes (unused by the fp32 epilogue)
     CUtensorMap tmap_res; // bf16 residual [rows, out_c], same boxes (only when the op has a residual)
+    CUtensorMap tmap_a2;  // optional second A source (projection shortcut input), im2col 1x1 / src2_stride
+    int src2_c = 0, src2_stride = 1;
     int block_n = 0;      // 64 / 128 / 256
     int force_block_n = 0;  // set before gemm_plan_init to pin the tile width (autotuner)
     int block_k = 64;     // 64 (128-byte swizzle) or 16 (32-byte swizzle, the stem)
@@ -62,6 +64,7 @@ bool gemm_plan_init(GemmPlan& p, const b2p_op& op, const void* weight_dev, int64
 bool gemm_plan_set_src(GemmPlan& p, const void* src, int batch_cap, char* err, size_t err_len);
 // (Re)encode the output / residual tensor maps for buffers with `rows` rows of out_c bf16 each.
 // TMA clips stores beyond `rows`, so `rows` must not exceed what the buffer really holds.
+bool gemm_plan_set_src2(GemmPlan& p, const void* src2, int batch_cap, char* err, size_t err_len);
 bool gemm_plan_set_dst(GemmPlan& p, const void* dst, int rows, char* err, size_t err_len);
 bool gemm_plan_set_res(GemmPlan& p, const void* res, int rows, char* err, size_t err_len);
 // Launches the persistent kernel for `m_rows` output rows.  `out_f32` is only read by LINEAR plans.

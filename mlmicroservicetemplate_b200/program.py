@@ -108,36 +108,51 @@ def stem_s2d_weight(w: torch.Tensor) -> torch.Tensor:
 
 
 def _mk_op(kind, src, dst, res=B.SLOT_NONE, in_hwc=(0, 0, 0), out_hwc=(0, 0, 0), k=(1, 1), stride=1, pad=(0, 0),
-           relu=0, weight=-1, bias=-1, flag0=0, reserved=None) -> B.Op:
+           relu=0, weight=-1, bias=-1, flag0=0, reserved=None, src2=B.SLOT_NONE, src2_c=0, src2_stride=1) -> B.Op:
     r = reserved if reserved is not None else (flag0, 0, 0, 0)
     return B.Op(kind, src, dst, res, in_hwc[0], in_hwc[1], in_hwc[2], out_hwc[0], out_hwc[1], out_hwc[2],
-                k[0], k[1], stride, pad[0], pad[1], relu, weight, bias, (B.C.c_int32 * 4)(*[int(v) for v in r]))
+                k[0], k[1], stride, pad[0], pad[1], relu, weight, bias, (B.C.c_int32 * 4)(*[int(v) for v in r]),
+                src2, src2_c, src2_stride, 0)
 
 
 class _Builder:
     def __init__(self, name: str):
         self.p = Program(name=name)
 
-    def conv(self, src, hwc, w, b, stride, pad, relu, res=B.SLOT_NONE, dst=None, pad_hi=None):
-        """w: fp32 [oc, ic, kh, kw] (BN already folded); returns (dst_slot, out_hwc)."""
+    def conv(self, src, hwc, w, b, stride, pad, relu, res=B.SLOT_NONE, dst=None, pad_hi=None, second=None):
+        """w: fp32 [oc, ic, kh, kw] (BN already folded); returns (dst_slot, out_hwc).
+        second = (slot, w2 [oc, c2, 1, 1], b2, stride2): a 1x1/stride2 conv of another slot accumulated into the
+        same output (the projection shortcut), packed as extra K columns after the main weight."""
         h, wd, c = hwc
         oc, ic, kh, kw = w.shape
         assert ic == c, (ic, c)
         pad_hi = pad if pad_hi is None else pad_hi
         oh = (h + pad + pad_hi - kh) // stride + 1
         ow = (wd + pad + pad_hi - kw) // stride + 1
-        wi = self.p.add_blob(pack_conv_weight(w))
-        bi = self.p.add_blob(pad_bias(b, self.p.blobs[wi].shape[0]))
+        packed = pack_conv_weight(w)
+        src2, c2, stride2 = B.SLOT_NONE, 0, 1
+        if second is not None:
+            src2, w2, b2, stride2 = second
+            c2 = w2.shape[1]
+            assert w2.shape[0] == oc and tuple(w2.shape[2:]) == (1, 1) and c2 % 64 == 0
+            ocp = packed.shape[0]
+            w2p = torch.zeros(ocp, c2)
+            w2p[:oc] = w2.float().view(oc, c2)
+            packed = torch.cat([packed.view(ocp, -1), _bf16(w2p)], dim=1).contiguous()
+            b = b + b2
+            self.p.flops_per_image += 2.0 * oh * ow * oc * c2
+        wi = self.p.add_blob(packed)
+        bi = self.p.add_blob(pad_bias(b, packed.shape[0]))
         if dst is None:
             dst = self.p.alloc(oh * ow * oc)
         self.p.ops.append(_mk_op(B.OP_CONV, src, dst, res, (h, wd, c), (oh, ow, oc), (kh, kw), stride,
-                                 (pad, pad_hi), int(relu), wi, bi))
+                                 (pad, pad_hi), int(relu), wi, bi, src2=src2, src2_c=c2, src2_stride=stride2))
         self.p.flops_per_image += 2.0 * oh * ow * oc * ic * kh * kw
         return dst, (oh, ow, oc)
 
 
 def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_stem: bool = True,
-                         fuse_pairs: bool = True) -> Program:
+                         fuse_pairs: bool = True, fold_shortcut: bool = True) -> Program:
     """Walks a torchvision ResNet (SP/torchvision/models/resnet.py:266-282: conv1-bn1-relu-maxpool,
     layer1..4, avgpool, fc) and emits the program.  Works for BasicBlock and Bottleneck nets."""
     from torchvision.models.resnet import BasicBlock, Bottleneck
@@ -183,11 +198,17 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
                 w1, b1 = fold_bn(blk.conv1.weight, blk.bn1)
                 w2, b2 = fold_bn(blk.conv2.weight, blk.bn2)
                 w3, b3 = fold_bn(blk.conv3.weight, blk.bn3)
-                # the projection shortcut goes first: it and conv1 then read x back to back, and conv3 finds
-                # its main input (t2) written by the op right before it
+                # The projection shortcut (1x1/stride-s conv of x) is not a layer of its own: it is accumulated into
+                # conv3's accumulator as extra K columns read from x (out = relu(W3 t2 + Wd x + b3 + bd)), so the
+                # "identity" tensor of a downsampling block is never written to or read from HBM.
+                shortcut = None
                 if blk.downsample is not None:
                     wd, bd = fold_bn(blk.downsample[0].weight, blk.downsample[1])
-                    idn, _ = bld.conv(x, hwc, wd, bd, blk.downsample[0].stride[0], 0, False)
+                    if fold_shortcut and wd.shape[1] % 64 == 0 and tuple(blk.downsample[0].kernel_size) == (1, 1):
+                        shortcut = (x, wd, bd, blk.downsample[0].stride[0])
+                        idn = B.SLOT_NONE
+                    else:
+                        idn, _ = bld.conv(x, hwc, wd, bd, blk.downsample[0].stride[0], 0, False)
                 else:
                     idn = x
                 if carry is not None:
@@ -195,14 +216,14 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
                     carry = None
                 else:
                     t1, hwc1 = bld.conv(x, hwc, w1, b1, 1, 0, True)
-                if blk.downsample is not None:
+                if blk.downsample is not None and shortcut is None:
                     p.release(x)
                 t2, hwc2 = bld.conv(t1, hwc1, w2, b2, blk.conv2.stride[0], 1, True)
                 p.release(t1)
                 # conv3 (+ residual + ReLU): fused with the NEXT block's conv1 when that is a plain 1x1/s1 conv
                 nxt = blocks[bi_ + 1] if bi_ + 1 < len(blocks) else None
                 n1 = w3.shape[0]
-                can_pair = (fuse_pairs and isinstance(nxt, Bottleneck) and nxt.conv1.kernel_size == (1, 1)
+                can_pair = (fuse_pairs and shortcut is None and isinstance(nxt, Bottleneck) and nxt.conv1.kernel_size == (1, 1)
                             and nxt.conv1.stride == (1, 1) and nxt.conv1.out_channels in (64, 128)
                             and n1 % 128 == 0 and w3.shape[1] in (64, 128) and tuple(blk.conv3.kernel_size) == (1, 1))
                 # (wider pairs - K1 >= 256 or N2 = 256, i.e. ResNet-50's stage 3 - were measured slower than the two
@@ -222,10 +243,14 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
                     p.flops_per_image += 2.0 * oh * ow * n1 * w3.shape[1] + 2.0 * oh * ow * n2 * n1
                     hwc3 = (oh, ow, n1)
                     carry = (t1n, (oh, ow, n2))
+                elif shortcut is not None:
+                    out, hwc3 = bld.conv(t2, hwc2, w3, b3, 1, 0, True, second=shortcut)
+                    p.release(x)
                 else:
                     out, hwc3 = bld.conv(t2, hwc2, w3, b3, 1, 0, True, res=idn)
                 p.release(t2)
-                p.release(idn)
+                if idn != B.SLOT_NONE:
+                    p.release(idn)
                 x, hwc = out, hwc3
             elif isinstance(blk, BasicBlock):
                 w1, b1 = fold_bn(blk.conv1.weight, blk.bn1)

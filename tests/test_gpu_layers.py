@@ -151,6 +151,38 @@ def test_conv_pair_fused(k1, n2, hw, n, cuda_device):
     assert (e2 > 2.0 ** -6 * ref2.abs() + 3e-2).sum().item() == 0      # second conv sees a bf16-rounded input
 
 
+@pytest.mark.parametrize("c_main,c_sc,oc,hw_out,stride2,n", [(64, 64, 256, 56, 1, 2), (128, 256, 512, 28, 2, 3), (512, 1024, 2048, 7, 2, 5)])
+def test_conv_with_folded_shortcut(c_main, c_sc, oc, hw_out, stride2, n, cuda_device):
+    """OP_CONV with a second GEMM source: out = relu(W3 t2 + Wd x(strided) + b): the projection shortcut as extra K."""
+    from mlmicroservicetemplate_b200 import backend as B, program as P
+    g = torch.Generator().manual_seed(c_main + c_sc)
+    hw_in = hw_out * stride2
+    x = _bf16r(torch.randn(n, hw_in, hw_in, c_sc, generator=g))                  # external input = the block input
+    w_t2 = _bf16r(torch.randn(c_main, c_sc, 1, 1, generator=g) / c_sc ** 0.5)    # makes t2 (at output resolution) from x
+    w3 = _bf16r(torch.randn(oc, c_main, 1, 1, generator=g) / c_main ** 0.5)
+    wd = _bf16r(torch.randn(oc, c_sc, 1, 1, generator=g) / c_sc ** 0.5)
+    b3, bd = torch.randn(oc, generator=g) * 0.1, torch.randn(oc, generator=g) * 0.1
+    bld = P._Builder("dual")
+    p = bld.p
+    p.in_elems = hw_in * hw_in * c_sc
+    # the second source must live in a slot: copy x through an identity conv, and derive t2 from it
+    xs, _ = bld.conv(B.SLOT_INPUT, (hw_in, hw_in, c_sc), torch.eye(c_sc).view(c_sc, c_sc, 1, 1), torch.zeros(c_sc), 1, 0, False)
+    t2, hwc2 = bld.conv(xs, (hw_in, hw_in, c_sc), w_t2, torch.zeros(c_main), stride2, 0, False)
+    bld.conv(t2, hwc2, w3, b3, 1, 0, True, second=(xs, wd, bd, stride2), dst=B.SLOT_OUTPUT)
+    p.out_elems = hw_out * hw_out * oc
+    rep = B.Replica(0, p, max_batch=n)
+    out = torch.full((n, hw_out, hw_out, oc), float("nan"), dtype=torch.bfloat16, device="cuda")
+    rep.forward(x.to(torch.bfloat16).cuda(), n, out)
+    torch.cuda.synchronize()
+    rep.close()
+    xin = x.permute(0, 3, 1, 2)
+    t2_ref = _bf16r(F.conv2d(xin, w_t2, stride=stride2))
+    ref = (F.conv2d(t2_ref, w3, b3) + F.conv2d(xin, wd, bd, stride=stride2)).relu().permute(0, 2, 3, 1)
+    err = (out.float().cpu() - ref).abs()
+    print(f"dual-source conv {c_main}+{c_sc}->{oc} s{stride2}: max_err={err.max().item():.4g}")
+    assert (err > 2.0 ** -7 * ref.abs() + 2e-2).sum().item() == 0
+
+
 def test_conv_sub_batched(cuda_device):
     # same op run in chunks of 2 images: exercises the external-source re-encode and chunk offsets
     _run_conv(5, (28, 28, 128), 128, 3, 1, 1, True, False, seed=11, sub_batch=2)

@@ -25,7 +25,14 @@ def interpret(prog: P.Program, x_nchw: torch.Tensor) -> torch.Tensor:
             w = prog.blobs[op.weight].float()[: op.out_c]                 # [oc, kh, kw, ic]
             b = prog.blobs[op.bias][: op.out_c]
             xin = F.pad(src.permute(0, 3, 1, 2), (op.pad_lo, op.pad_hi, op.pad_lo, op.pad_hi))
+            if op.src2_c > 0:      # weight rows are [kh*kw*in_c | src2_c]
+                k1 = op.kh * op.kw * op.in_c
+                wflat = w.reshape(op.out_c, -1)
+                w, w_sc = wflat[:, :k1].reshape(op.out_c, op.kh, op.kw, op.in_c), wflat[:, k1:]
             y = F.conv2d(xin, w.permute(0, 3, 1, 2), b, stride=op.stride).permute(0, 2, 3, 1)
+            if op.src2_c > 0:
+                x2 = slots[op.src2].permute(0, 3, 1, 2)
+                y = y + F.conv2d(x2, w_sc.reshape(op.out_c, op.src2_c, 1, 1), stride=op.src2_stride).permute(0, 2, 3, 1)
             if op.res != B.SLOT_NONE:
                 y = y + slots[op.res]
             if op.relu == 1:
@@ -124,7 +131,7 @@ def test_slots_are_never_clobbered_while_live(arch):
     prog = P.build_program(seeded_model(arch, 0), arch)
     last_read = {}
     for i, op in enumerate(prog.ops):
-        for s in (op.src, op.res):
+        for s in (op.src, op.res, op.src2 if op.src2_c > 0 else B.SLOT_NONE):
             if s not in (B.SLOT_NONE,):
                 last_read[s] = i
     def dsts(o):
@@ -140,7 +147,7 @@ def test_slots_are_never_clobbered_while_live(arch):
         for d_ in dsts(op):
             if d_ in live_until:
                 assert live_until[d_] < i, f"op {i} overwrites slot {d_} still needed by op {live_until[d_]}"
-            nxt = [j for j, o in enumerate(prog.ops) if j > i and (o.src == d_ or o.res == d_)]
+            nxt = [j for j, o in enumerate(prog.ops) if j > i and (o.src == d_ or o.res == d_ or (o.src2_c > 0 and o.src2 == d_))]
             rewrite = [j for j, o in enumerate(prog.ops) if j > i and d_ in dsts(o)]
             horizon = rewrite[0] if rewrite else len(prog.ops)
             readers = [j for j in nxt if j <= horizon]
