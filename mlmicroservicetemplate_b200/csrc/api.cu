@@ -120,8 +120,8 @@ int validate_desc(const b2p_model_desc* d) {
             return B2P_E_ARG;
         if (o.kind == B2P_OP_CONV_PAIR) {
             if (o.reserved[0] <= 0 || o.reserved[0] >= d->n_slots || o.reserved[1] < 0 || o.reserved[1] >= d->n_blobs ||
-                o.reserved[2] < 0 || o.reserved[2] >= d->n_blobs || o.res == B2P_SLOT_NONE || o.src == B2P_SLOT_INPUT ||
-                o.dst == B2P_SLOT_OUTPUT || o.res == B2P_SLOT_INPUT)
+                o.reserved[2] < 0 || o.reserved[2] >= d->n_blobs || o.src == B2P_SLOT_INPUT ||
+                o.dst == B2P_SLOT_OUTPUT || o.res == B2P_SLOT_INPUT || (o.res == B2P_SLOT_NONE && o.src2_c <= 0))
                 return B2P_E_ARG;
         }
         if (o.kind == B2P_OP_CONV || o.kind == B2P_OP_LINEAR || o.kind == B2P_OP_STEM_CONV ||
@@ -504,19 +504,24 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
         } else if (o.kind == B2P_OP_CONV_PAIR) {
             const int n2 = o.reserved[3];
             const int64_t rows_cap = static_cast<int64_t>(h->chunk) * o.out_h * o.out_w;
+            const int k2 = o.src2_c > 0 ? o.src2_c : 0;
             if (o.kh != 1 || o.kw != 1 || o.stride != 1 || o.pad_lo != 0 || !pair_plan_supported(o.in_c, o.out_c, n2) ||
-                h->blob_bytes[o.weight] != static_cast<int64_t>(o.out_c) * o.in_c * 2 ||
+                h->blob_bytes[o.weight] != static_cast<int64_t>(o.out_c) * (o.in_c + k2) * 2 ||
                 h->blob_bytes[o.reserved[1]] != static_cast<int64_t>(n2) * o.out_c * 2 ||
                 h->blob_bytes[o.bias] < o.out_c * 4 || h->blob_bytes[o.reserved[2]] < n2 * 4)
                 B2P_FAIL(B2P_E_ARG, "op %d: malformed CONV_PAIR", i);
-            void* s_src = h->slots[o.src]; void* s_res = h->slots[o.res]; void* s_dst = h->slots[o.dst];
+            void* s_src = h->slots[o.src]; void* s_dst = h->slots[o.dst];
+            void* s_res = o.res == B2P_SLOT_NONE ? nullptr : h->slots[o.res];
             void* s_dst2 = h->slots[o.reserved[0]];
-            if (!s_src || !s_res || !s_dst || !s_dst2) B2P_FAIL(B2P_E_ARG, "op %d uses an empty slot", i);
+            void* s_src2 = k2 > 0 ? h->slots[o.src2] : nullptr;
+            if (!s_src || (o.res != B2P_SLOT_NONE && !s_res) || !s_dst || !s_dst2 || (k2 > 0 && !s_src2))
+                B2P_FAIL(B2P_E_ARG, "op %d uses an empty slot", i);
             if (h->slot_elems[o.dst] < static_cast<int64_t>(o.out_h) * o.out_w * o.out_c ||
                 h->slot_elems[o.reserved[0]] < static_cast<int64_t>(o.out_h) * o.out_w * n2)
                 B2P_FAIL(B2P_E_ARG, "op %d: destination slot too small", i);
-            if (!pair_plan_init(p.pair, o.in_c, o.out_c, n2, h->blobs[o.weight], static_cast<const float*>(h->blobs[o.bias]),
+            if (!pair_plan_init(p.pair, o.in_c, k2, o.out_c, n2, h->blobs[o.weight], static_cast<const float*>(h->blobs[o.bias]),
                                 h->blobs[o.reserved[1]], static_cast<const float*>(h->blobs[o.reserved[2]]), eb, sizeof eb) ||
+                !pair_plan_set_src2(p.pair, s_src2, h->chunk, o.out_h, o.out_w, o.src2_stride > 0 ? o.src2_stride : 1, eb, sizeof eb) ||
                 !pair_plan_set_buffers(p.pair, s_src, s_res, s_dst, s_dst2, static_cast<int>(rows_cap), eb, sizeof eb))
                 B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
         } else if (o.kind == B2P_OP_ATTENTION) {

@@ -223,7 +223,7 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
                 # conv3 (+ residual + ReLU): fused with the NEXT block's conv1 when that is a plain 1x1/s1 conv
                 nxt = blocks[bi_ + 1] if bi_ + 1 < len(blocks) else None
                 n1 = w3.shape[0]
-                can_pair = (fuse_pairs and shortcut is None and isinstance(nxt, Bottleneck) and nxt.conv1.kernel_size == (1, 1)
+                can_pair = (fuse_pairs and isinstance(nxt, Bottleneck) and nxt.conv1.kernel_size == (1, 1)
                             and nxt.conv1.stride == (1, 1) and nxt.conv1.out_channels in (64, 128)
                             and n1 % 128 == 0 and w3.shape[1] in (64, 128) and tuple(blk.conv3.kernel_size) == (1, 1))
                 # (wider pairs - K1 >= 256 or N2 = 256, i.e. ResNet-50's stage 3 - were measured slower than the two
@@ -232,14 +232,23 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
                     wn, bn_ = fold_bn(nxt.conv1.weight, nxt.bn1)
                     n2 = wn.shape[0]
                     oh, ow = hwc2[0], hwc2[1]
-                    wi = p.add_blob(pack_conv_weight(w3))
-                    bi = p.add_blob(pad_bias(b3, n1))
+                    w3p, b3p, sc_kw = pack_conv_weight(w3).view(n1, -1), b3, {}
+                    if shortcut is not None:      # [W3 | Wd] along K, biases summed
+                        sx, swd, sbd, sstride = shortcut
+                        w3p = torch.cat([w3p, _bf16(swd.float().view(n1, -1))], dim=1).contiguous()
+                        b3p = b3 + sbd
+                        sc_kw = dict(src2=sx, src2_c=swd.shape[1], src2_stride=sstride)
+                        p.flops_per_image += 2.0 * oh * ow * n1 * swd.shape[1]
+                    wi = p.add_blob(w3p)
+                    bi = p.add_blob(pad_bias(b3p, n1))
                     wi2 = p.add_blob(pack_conv_weight(wn))
                     bi2 = p.add_blob(pad_bias(bn_, n2))
                     out = p.alloc(oh * ow * n1)
                     t1n = p.alloc(oh * ow * n2)
                     p.ops.append(_mk_op(B.OP_CONV_PAIR, t2, out, idn, hwc2, (oh, ow, n1), (1, 1), 1, (0, 0), 1, wi, bi,
-                                        reserved=(t1n, wi2, bi2, n2)))
+                                        reserved=(t1n, wi2, bi2, n2), **sc_kw))
+                    if shortcut is not None:
+                        p.release(x)
                     p.flops_per_image += 2.0 * oh * ow * n1 * w3.shape[1] + 2.0 * oh * ow * n2 * n1
                     hwc3 = (oh, ow, n1)
                     carry = (t1n, (oh, ow, n2))

@@ -40,9 +40,15 @@ def interpret(prog: P.Program, x_nchw: torch.Tensor) -> torch.Tensor:
             elif op.relu == 2:
                 y = F.gelu(y)
         elif op.kind == B.OP_CONV_PAIR:
-            w = prog.blobs[op.weight].float()[: op.out_c]
+            wflat = prog.blobs[op.weight].float()[: op.out_c].reshape(op.out_c, -1)
             b = prog.blobs[op.bias][: op.out_c]
-            y = (F.conv2d(src.permute(0, 3, 1, 2), w.permute(0, 3, 1, 2), b).permute(0, 2, 3, 1) + slots[op.res]).relu()
+            y = F.conv2d(src.permute(0, 3, 1, 2), wflat[:, : op.in_c].reshape(op.out_c, op.in_c, 1, 1), b).permute(0, 2, 3, 1)
+            if op.src2_c > 0:
+                y = y + F.conv2d(slots[op.src2].permute(0, 3, 1, 2), wflat[:, op.in_c:].reshape(op.out_c, op.src2_c, 1, 1),
+                                 stride=op.src2_stride).permute(0, 2, 3, 1)
+            if op.res != B.SLOT_NONE:
+                y = y + slots[op.res]
+            y = y.relu()
             dst2, wi2, bi2, n2 = op.reserved[0], op.reserved[1], op.reserved[2], op.reserved[3]
             w2 = prog.blobs[wi2].float()[:n2]
             # the fused kernel feeds the second conv the bf16-rounded first result (as the un-fused path would)
