@@ -20,6 +20,9 @@ struct OpPlan {
     StemPlan stem;        // valid for STEM_CONV
     AttentionPlan att;    // valid for ATTENTION
     PairPlan pair;        // valid for CONV_PAIR
+    Conv3x3Plan c3;       // valid for CONV ops taken by the patch-resident 3x3 kernel
+    bool use_c3 = false;
+    void* c3_image = nullptr;
     void* stem_image = nullptr;
     bool is_gemm = false;
     bool src_external = false;
@@ -163,6 +166,19 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
             switch (o.kind) {
                 case B2P_OP_CONV:
                 case B2P_OP_LINEAR: {
+                    if (p.use_c3) {
+                        if (o.dst == B2P_SLOT_OUTPUT)
+                            dst = static_cast<uint8_t*>(dst) + static_cast<size_t>(off) * h->out_elems * 2;
+                        if (p.src_external || p.dst_external || p.res_external) {
+                            char eb[256] = "";
+                            if (!conv3x3_c64_plan_set(p.c3, src, dst, res, nb, eb, sizeof eb)) {
+                                set_error(h, "%s", eb);
+                                return B2P_E_CUDA;
+                            }
+                        }
+                        e = conv3x3_c64_launch(p.c3, nb, o.relu, op_dir, h->num_sms, st);
+                        break;
+                    }
                     if (o.dst == B2P_SLOT_OUTPUT) {
                         const size_t esz = o.kind == B2P_OP_LINEAR ? 4 : 2;
                         dst = static_cast<uint8_t*>(dst) + static_cast<size_t>(off) * h->out_elems * esz;
@@ -309,7 +325,10 @@ int32_t b2p_destroy(b2p_handle* h) {
     if (!h) return B2P_OK;
     cudaSetDevice(h->device);
     cudaDeviceSynchronize();
-    for (OpPlan& op : h->ops) if (op.stem_image) cudaFree(op.stem_image);
+    for (OpPlan& op : h->ops) {
+        if (op.stem_image) cudaFree(op.stem_image);
+        if (op.c3_image) cudaFree(op.c3_image);
+    }
     for (void* p : h->slots) if (p) cudaFree(p);
     for (void* p : h->blobs) if (p) cudaFree(p);
     for (int i = 0; i < 2; ++i) {
@@ -412,6 +431,20 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
                 if (!h->slots[o.src]) B2P_FAIL(B2P_E_ARG, "op %d reads an empty slot", i);
                 if (!gemm_plan_set_src(p.gemm, h->slots[o.src], h->chunk, eb, sizeof eb))
                     B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
+            }
+            if (conv3x3_c64_supported(o) && h->blob_bytes[o.weight] == 64 * 9 * 64 * 2 && getenv("B2P_NO_C3") == nullptr) {
+                // 56x56x64 3x3: patch-resident kernel instead of the nine-fold im2col re-read
+                p.c3.weight = h->blobs[o.weight];
+                p.c3.bias = static_cast<const float*>(h->blobs[o.bias]);
+                p.use_c3 = true;
+                const bool ext = (o.src == B2P_SLOT_INPUT) || (o.dst == B2P_SLOT_OUTPUT) || (o.res == B2P_SLOT_INPUT);
+                if (!ext) {
+                    const void* r_ = o.res == B2P_SLOT_NONE ? nullptr : h->slots[o.res];
+                    if (!h->slots[o.src] || !h->slots[o.dst] || (o.res != B2P_SLOT_NONE && !r_))
+                        B2P_FAIL(B2P_E_ARG, "op %d uses an empty slot", i);
+                    if (!conv3x3_c64_plan_set(p.c3, h->slots[o.src], h->slots[o.dst], r_, h->chunk, eb, sizeof eb))
+                        B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
+                }
             }
             if (p.gemm.src2_c > 0) {
                 if (!h->slots[o.src2]) B2P_FAIL(B2P_E_ARG, "op %d reads an empty second source", i);

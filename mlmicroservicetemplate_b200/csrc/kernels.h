@@ -84,6 +84,19 @@ void stem_pack_weight_image(const uint16_t* w_packed, uint16_t* image);
 bool stem_plan_init(StemPlan& p, const void* src_s2d, void* dst, int batch_cap, int pool, char* err, size_t err_len);
 cudaError_t stem_plan_launch(const StemPlan& p, int n, int relu, int num_sms, cudaStream_t stream);
 
+// ------------------------------------------------------------------ patch-resident 3x3 conv, 56x56x64 -> 64
+struct Conv3x3Plan {
+    CUtensorMap tmap_in, tmap_out, tmap_res, tmap_w;
+    const void* weight = nullptr;        // packed [64][3][3][64] bf16 (device); nine 64x64 tiles stay in smem
+    const float* bias = nullptr;
+    int has_res = 0;
+};
+bool conv3x3_c64_supported(const b2p_op& o);
+void conv3x3_c64_pack_weights(const uint16_t* w_packed, uint16_t* image);
+bool conv3x3_c64_plan_set(Conv3x3Plan& p, const void* src, void* dst, const void* res, int batch_cap, char* err,
+                          size_t err_len);
+cudaError_t conv3x3_c64_launch(const Conv3x3Plan& p, int n, int relu, int reverse, int num_sms, cudaStream_t s);
+
 // ------------------------------------------------------------------ fused conv3(+res+ReLU) -> next conv1(+ReLU)
 struct PairPlan {
     CUtensorMap tmap_a, tmap_w3, tmap_res, tmap_out1, tmap_w1, tmap_out2, tmap_a2;

@@ -51,7 +51,10 @@ CONV_CASES = [
     (2, (56, 56, 64), 256, 1, 1, 0, False, False),        # 1x1 expand
     (2, (56, 56, 256), 256, 1, 1, 0, True, True),         # residual + relu
     (3, (28, 28, 512), 128, 1, 1, 0, True, False),        # K = 512 (8 k-blocks, ring wraps)
-    (2, (56, 56, 64), 64, 3, 1, 1, True, False),          # 3x3 im2col
+    (2, (56, 56, 64), 64, 3, 1, 1, True, False),          # 3x3, 56x56x64: patch-resident kernel
+    (3, (56, 56, 64), 64, 3, 1, 1, True, True),           # same + residual (ResNet-18 BasicBlock conv2)
+    (1, (56, 56, 64), 64, 3, 1, 1, False, False),
+    (2, (28, 28, 64), 64, 3, 1, 1, True, False),          # 3x3 generic im2col path
     (2, (56, 56, 128), 128, 3, 2, 1, True, False),        # 3x3 stride 2
     (2, (56, 56, 256), 512, 1, 2, 0, False, False),       # 1x1 stride 2 downsample
     (5, (7, 7, 512), 512, 3, 1, 1, True, True),           # tiny spatial, tiles span images, M tail
