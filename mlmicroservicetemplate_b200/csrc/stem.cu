@@ -6,13 +6,12 @@
 // Why a dedicated kernel: with 32-byte pixels the generic TMA-im2col path issues sixteen 4 KB loads
 // per 128-pixel tile and is latency bound (measured 580 us per 256 images, 14 % of a forward).
 // Here a tile is one full output row (112 pixels; the fused variant: the three conv rows one pooled
-// row needs).  The input patch for the whole tile - (rows+3) x 120 pixels - is fetched ONCE by two
-// tiled-TMA loads, one per 8-channel half, so that each half is a dense [pixel][16 B] plane in shared
-// memory.  In that form every filter tap (a, b) is just a different START ADDRESS into the same
-// planes: the no-swizzle K-major UMMA layout wants 8 consecutive rows 16 B apart (consecutive
-// pixels), 8-row groups 128 B apart (SBO) and the two K halves one plane apart (LBO).  Sixteen
-// K=16 MMAs per conv row accumulate the 4x4 window in TMEM; the 32 KB of weights sit in shared
-// memory for the lifetime of the CTA.
+// row needs).  The input patch for the whole tile - (rows+3) x 120 pixels of 32 bytes - is fetched ONCE by
+// one tiled-TMA load into the 32-byte-swizzled K-major layout.  Every filter tap (a, b) is then just a
+// different START ADDRESS into that patch (shifted by whole pixels): the tensor core derives the swizzle
+// from the shared-memory address bits, so row-shifted descriptors read exactly what TMA wrote.  Sixteen
+// K=16 MMAs per conv row accumulate the 4x4 window in TMEM; the 32 KB of weights (no-swizzle layout:
+// 8 x 16 B core matrices, SBO 128 B, LBO 1 KB) sit in shared memory for the lifetime of the CTA.
 //
 // Fused pooling: conv rows 2j-1, 2j, 2j+1 live in three TMEM accumulators; the epilogue takes the
 // vertical max in registers, applies bias+ReLU (both commute with max), rounds to bf16, exchanges
@@ -149,8 +148,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
                 mbar_wait(&empty_bar[stage], phase ^ 1u);
                 mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
                 uint8_t* dst = smem_patch + stage * C::STAGE_BYTES;
-                tma_load_4d(&tmap_in, &full_bar[stage], dst, 0, -2, in_row0, img);
-                tma_load_4d(&tmap_in, &full_bar[stage], dst + C::PLANE_BYTES, 8, -2, in_row0, img);
+                tma_load_4d(&tmap_in, &full_bar[stage], dst, 0, -2, in_row0, img);   // whole patch, 32B-swizzled pixels
                 if (++stage == STEM_STAGES) { stage = 0; phase ^= 1u; }
             }
         }
@@ -176,8 +174,10 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
                     for (int a = 0; a < 4; ++a) {
 #pragma unroll
                         for (int b = 0; b < 4; ++b) {
-                            const uint32_t a_addr = patch + static_cast<uint32_t>(((ri + a) * PATCH_W + b) * 16);
-                            const uint64_t a_desc = umma_desc_noswizzle(a_addr, C::PLANE_BYTES, 128);
+                            // tap (a, b) = the same patch, start address shifted by whole 32-byte pixels: the
+                            // tensor core applies the 32B swizzle from the address bits, as TMA did when writing
+                            const uint32_t a_addr = patch + static_cast<uint32_t>(((ri + a) * PATCH_W + b) * 32);
+                            const uint64_t a_desc = umma_desc_kmajor(a_addr, 32);
                             const uint64_t b_desc = umma_desc_noswizzle(w_addr + (a * 4 + b) * 2048, 1024, 128);
                             umma_bf16(d_tmem, a_desc, b_desc, idesc, static_cast<uint32_t>((a | b) != 0));
                         }
@@ -338,10 +338,10 @@ bool stem_plan_init(StemPlan& p, const void* src_s2d, void* dst, int batch_cap, 
     const int patch_rows = (pool ? 3 : 1) + 3;
     cuuint64_t dims[4] = {16, S2D_W, S2D_W, static_cast<cuuint64_t>(batch_cap)};
     cuuint64_t strides[3] = {32, 32ull * S2D_W, 32ull * S2D_W * S2D_W};
-    cuuint32_t box[4] = {8, PATCH_W, static_cast<cuuint32_t>(patch_rows), 1};
+    cuuint32_t box[4] = {16, PATCH_W, static_cast<cuuint32_t>(patch_rows), 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     CUresult r = g_stem_encode(&p.tmap_in, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(src_s2d), dims, strides,
-                               box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                               box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_32B,
                                CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
         snprintf(err, err_len, "stem input tensor map failed (%d)", static_cast<int>(r));
