@@ -22,7 +22,6 @@ struct OpPlan {
     PairPlan pair;        // valid for CONV_PAIR
     Conv3x3Plan c3;       // valid for CONV ops taken by the patch-resident 3x3 kernel
     bool use_c3 = false;
-    void* c3_image = nullptr;
     void* stem_image = nullptr;
     bool is_gemm = false;
     bool src_external = false;
@@ -327,7 +326,6 @@ int32_t b2p_destroy(b2p_handle* h) {
     cudaDeviceSynchronize();
     for (OpPlan& op : h->ops) {
         if (op.stem_image) cudaFree(op.stem_image);
-        if (op.c3_image) cudaFree(op.c3_image);
     }
     for (void* p : h->slots) if (p) cudaFree(p);
     for (void* p : h->blobs) if (p) cudaFree(p);

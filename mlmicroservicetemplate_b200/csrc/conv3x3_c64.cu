@@ -7,14 +7,14 @@
 // hit rate, 45 % L2 throughput, the MMA warp waiting on loads (profiles/r01_ncu_full_conv_gemm_summary.csv).
 // Here - exactly as in the stem kernel - a tile's input patch is fetched ONCE and every tap is a
 // different start address into it:
-//   * a tile = two output rows of one image = 2 x 56 pixels; its patch = 4 input rows x 58 pixels, held as
-//     eight [4 x 64 pixels][16 B] planes (one per 8-channel group; row pitch padded to 64 pixels), each
-//     filled by one tiled-TMA load whose out-of-range rows/columns are zero (= the conv padding);
-//   * for tap (r, s) and 16-channel K step kc the A operand starts at plane[2 kc] + (r*64 + s)*16 B in the
-//     no-swizzle K-major UMMA layout (8 pixels x 16 B core matrices, SBO 128 B, LBO = one plane);
+//   * a tile = two output rows of one image = 2 x 56 pixels; its patch = 4 input rows x 64 pixels (58 used;
+//     the pitch is padded to 64) x 128 B, written by ONE tiled-TMA load in the 128-byte-swizzled K-major
+//     layout; out-of-range rows/columns arrive as zeros (= the conv padding);
+//   * for tap (r, s) the A operand is the same patch with the descriptor start shifted by (r*64 + s) rows of
+//     128 B (the tensor core's swizzle is address-based, see desc_sw128_rowshift), four K=16 steps per tap;
 //     accumulator row m is patch pixel m: rows 0..55 are output row 2t, rows 64..119 output row 2t+1,
 //     the rest fall on the pitch padding and are dropped;
-//   * the 72 KB of weights stay in shared memory for the lifetime of the CTA;
+//   * the nine 64x64 weight tiles (72 KB) stay in shared memory for the lifetime of the CTA;
 //   * epilogue: two groups of four warps (one per TMEM stage): bias, residual (TMA-loaded), ReLU, bf16,
 //     swizzled staging, two 56-row TMA stores.
 #include <cstdio>
@@ -29,9 +29,8 @@ constexpr int HW = 56;
 constexpr int CH = 64;                       // input = output channels
 constexpr int PITCH = 64;                    // patch row pitch in pixels
 constexpr int PATCH_ROWS = 4;
-constexpr int PLANE_BYTES = PATCH_ROWS * PITCH * 16;      // 4096
-constexpr int STAGE_BYTES = 8 * PLANE_BYTES;              // 32 KB
-constexpr int W_IMAGE_BYTES = 9 * 4 * 2 * CH * 16;        // [tap][k step][k half][out ch][8 x bf16] = 73,728
+constexpr int STAGE_BYTES = PATCH_ROWS * PITCH * 128;     // one patch: 32 KB
+constexpr int W_IMAGE_BYTES = 9 * CH * 128;               // nine 64 x 64 bf16 weight tiles = 73,728
 constexpr int TILE_BYTES = 128 * 128;                     // staging / residual tile: 128 rows x 64 ch bf16
 constexpr int C3_THREADS = 320;                           // TMA, MMA, 2 epilogue groups x 4 warps
 template <bool HAS_RES>
@@ -49,21 +48,6 @@ __device__ __forceinline__ void tma_load_4d_tiled(const CUtensorMap* m, uint64_t
         "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
         : "memory");
 }
-__device__ __forceinline__ void bulk_load_1d(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                     smem_u32(dst)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
-__device__ __forceinline__ uint64_t desc_noswizzle(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-    uint64_t d = 0;
-    d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
-    d |= static_cast<uint64_t>(lbo_bytes >> 4) << 16;
-    d |= static_cast<uint64_t>(sbo_bytes >> 4) << 32;
-    d |= 1ull << 46;
-    return d;
-}
-
 // 128-byte-swizzled K-major descriptor whose start address is any whole number of 128-byte rows into the
 // patch (not 1024-byte aligned).  Measured on B200: the tensor core derives the XOR pattern from the
 // shared-memory ADDRESS bits, exactly as TMA did when it wrote the patch, so a row-shifted start address
@@ -313,15 +297,6 @@ bool c3_encode_rows(CUtensorMap* m, const void* base, uint64_t rows) {
 bool conv3x3_c64_supported(const b2p_op& o) {
     return o.kind == B2P_OP_CONV && o.kh == 3 && o.kw == 3 && o.stride == 1 && o.pad_lo == 1 && o.pad_hi == 1 &&
            o.in_h == HW && o.in_w == HW && o.in_c == CH && o.out_c == CH && o.src2_c <= 0 && (o.relu == 0 || o.relu == 1);
-}
-
-void conv3x3_c64_pack_weights(const uint16_t* w_packed /*[64][3][3][64]*/, uint16_t* image /*36864 elems*/) {
-    for (int tap = 0; tap < 9; ++tap)
-        for (int kc = 0; kc < 4; ++kc)
-            for (int h = 0; h < 2; ++h)
-                for (int n = 0; n < CH; ++n)
-                    for (int e = 0; e < 8; ++e)
-                        image[((((tap * 4 + kc) * 2 + h) * CH) + n) * 8 + e] = w_packed[(n * 9 + tap) * CH + kc * 16 + h * 8 + e];
 }
 
 bool conv3x3_c64_plan_set(Conv3x3Plan& p, const void* src, void* dst, const void* res, int batch_cap, char* err,

@@ -92,7 +92,6 @@ struct Conv3x3Plan {
     int has_res = 0;
 };
 bool conv3x3_c64_supported(const b2p_op& o);
-void conv3x3_c64_pack_weights(const uint16_t* w_packed, uint16_t* image);
 bool conv3x3_c64_plan_set(Conv3x3Plan& p, const void* src, void* dst, const void* res, int batch_cap, char* err,
                           size_t err_len);
 cudaError_t conv3x3_c64_launch(const Conv3x3Plan& p, int n, int relu, int reverse, int num_sms, cudaStream_t s);

@@ -145,3 +145,30 @@ def test_replicas_on_different_gpus_agree_bit_for_bit(cuda_device):
             rep.close()
     torch.cuda.set_device(0)
     assert all(torch.equal(outs[0], o) for o in outs[1:])
+
+
+@pytest.mark.parametrize("arch", ["resnet50", "resnet18"])
+def test_partial_batches_on_a_larger_replica(arch, cuda_device):
+    """n < max_batch and odd n: ragged last tiles in every kernel (generic GEMM, fused pair, patch 3x3, stem) while
+    the tensor maps are encoded for the replica's capacity.  Each n must match the oracle and the n=cap run."""
+    from mlmicroservicetemplate_b200 import backend as B, program as P
+    from oracle import model as om
+    model = om.build_model(arch)
+    prog = P.build_program(model, arch)
+    cap = 11
+    rep = B.Replica(0, prog, max_batch=cap)
+    g = torch.Generator().manual_seed(91)
+    x = (torch.rand(cap, 3, 224, 224, generator=g) * 2 - 1).to(torch.bfloat16)
+    xd = x.cuda()
+    ref = om.forward_logits(x.float(), model)
+    full = torch.full((cap, 1000), float("nan"), device="cuda")
+    rep.forward(xd, cap, full)
+    torch.cuda.synchronize()
+    scale = ref.abs().max().item()
+    assert (full.cpu() - ref).abs().max().item() / scale <= 8e-3
+    for n in (1, 3, 7):
+        out = torch.full((n, 1000), float("nan"), device="cuda")
+        rep.forward(xd[:n].contiguous(), n, out)
+        torch.cuda.synchronize()
+        assert torch.equal(out, full[:n]), f"n={n} differs from the first {n} rows of the full batch"
+    rep.close()
