@@ -23,7 +23,7 @@
 extern "C" {
 #endif
 
-#define B2P_ABI_VERSION 2
+#define B2P_ABI_VERSION 3
 
 /* error codes */
 #define B2P_OK 0
@@ -32,6 +32,8 @@ extern "C" {
 #define B2P_E_CUDA -3     /* a CUDA runtime/driver call failed; see b2p_last_error() */
 #define B2P_E_NOMEM -4    /* device or pinned allocation failed */
 #define B2P_E_LIMIT -5    /* a size exceeds a documented fixed maximum */
+#define B2P_E_UNSUPPORTED -6 /* well-formed input outside this path's scope (e.g. a progressive JPEG): the
+                                caller keeps it on the host decoder; nothing was launched              */
 
 typedef struct b2p_handle b2p_handle;
 
@@ -187,6 +189,48 @@ const float* b2p_last_logits(b2p_handle* h);
 #define B2P_HEAD_STATIC_MAX_CHANNELS 2048
 int32_t b2p_head_static(const void* feat, int32_t n, int32_t hw, int32_t c, const void* weight,
                         int32_t weight_rows, const float* bias, int32_t classes, float* logits,
+                        void* stream);
+
+/* ---- JPEG decode on the GPU (the step right before the path) -------------
+ * For the files it covers this produces the pixels `Image.open(image_file.file)` + `.convert('RGB')`
+ * (src/model/model.py:23; Pillow / libjpeg-turbo defaults: accurate integer IDCT, fancy chroma upsampling,
+ * fixed-point YCbCr->RGB) would: uint8 RGB, HWC, rows densely packed — bit for bit.  Scope: baseline /
+ * extended-sequential Huffman JPEG (SOF0, SOF1), 8-bit, ONE interleaved scan, greyscale or YCbCr with luma
+ * sampling 1x1 (4:4:4), 2x1 (4:2:2) or 2x2 (4:2:0), restart intervals allowed, no Adobe marker.  Everything
+ * else reports B2P_E_UNSUPPORTED and stays on the caller's host decoder.  The decoder object is independent
+ * of b2p_handle; like a handle it is bound to one device and driven by one host thread, and consecutive
+ * calls must be issued on the same stream (its workspace is reused in stream order).                     */
+typedef struct b2p_jpeg b2p_jpeg;
+
+typedef struct b2p_jpeg_info {
+    int32_t width, height;
+    int32_t components;             /* 1 = greyscale, 3 = YCbCr                                     */
+    int32_t h_samp, v_samp;         /* luma sampling factors: 1x1, 2x1 or 2x2                      */
+    int32_t restart_interval;       /* MCUs per restart interval, 0 = none                         */
+    int32_t segments;               /* independently decodable entropy-coded segments              */
+    int32_t reserved;
+    int64_t scan_bytes;             /* entropy-coded bytes                                         */
+} b2p_jpeg_info;
+
+/* Host only, no device needed: walks the markers of one file.  B2P_OK (info filled), B2P_E_UNSUPPORTED
+ * (fine for the host decoder, not for this one) or B2P_E_ARG (not a decodable JPEG); the reason is in
+ * b2p_jpeg_last_error(NULL).                                                                            */
+int32_t b2p_jpeg_inspect(const uint8_t* file, int64_t len, b2p_jpeg_info* info);
+
+int32_t b2p_jpeg_create(int32_t device, b2p_jpeg** out);
+int32_t b2p_jpeg_destroy(b2p_jpeg* d);
+const char* b2p_jpeg_last_error(const b2p_jpeg* d);   /* d may be NULL: inspect / create failures   */
+
+/* Decodes n files (HOST pointers, any memory) into the DEVICE slab: image i becomes uint8 [h][w][3] at
+ * slab + offsets[i], ready to be described by a b2p_image and handed to b2p_preprocess / b2p_predict on
+ * the same stream.  `status` (device, n x int32, may be NULL) receives per image 0 or a bit mask:
+ * 1 = the entropy-coded data ended early, 2 = an invalid Huffman code was met (pixels are then undefined,
+ * as with any corrupt file).  Headers are parsed on the calling thread; the entropy-coded bytes and the
+ * tables travel in one host->device copy; three kernels follow.  Asynchronous on `stream`.  The workspace
+ * grows (with a stream synchronisation) the first time a larger batch is seen.  Returns B2P_E_UNSUPPORTED /
+ * B2P_E_ARG without launching anything if any file is outside the scope — inspect first.                */
+int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t* lens, int32_t n,
+                        uint8_t* slab, int64_t slab_bytes, const int64_t* offsets, int32_t* status,
                         void* stream);
 
 #ifdef __cplusplus

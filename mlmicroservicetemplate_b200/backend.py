@@ -14,7 +14,7 @@ from typing import Optional, Sequence
 PKG = Path(__file__).resolve().parent
 LIB_PATH = Path(os.environ.get("B2P_LIB", PKG / "lib" / "libb200predict.so"))   # B2P_LIB: A/B-test another build
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 SLOT_INPUT, SLOT_OUTPUT, SLOT_NONE = 0, -2, -1
 OP_CONV, OP_LINEAR, OP_MAXPOOL, OP_AVGPOOL, OP_STEM_PACK, OP_NCHW_TO_NHWC, OP_STEM_CONV = 1, 2, 3, 4, 5, 6, 7
 OP_PATCHIFY, OP_TOKENS, OP_LAYERNORM, OP_ATTENTION, OP_CONV_PAIR = 8, 9, 10, 11, 12
@@ -22,7 +22,7 @@ ACT_NONE, ACT_RELU, ACT_GELU = 0, 1, 2
 OUT_HW = 224
 MAX_TOPK = 8
 
-ERRORS = {0: "OK", -1: "B2P_E_ARG", -2: "B2P_E_DEVICE", -3: "B2P_E_CUDA", -4: "B2P_E_NOMEM", -5: "B2P_E_LIMIT"}
+ERRORS = {0: "OK", -1: "B2P_E_ARG", -2: "B2P_E_DEVICE", -3: "B2P_E_CUDA", -4: "B2P_E_NOMEM", -5: "B2P_E_LIMIT", -6: "B2P_E_UNSUPPORTED"}
 
 
 class B2PError(RuntimeError):
@@ -69,6 +69,16 @@ class Stats(C.Structure):
     ]
 
 
+class JpegInfo(C.Structure):
+    _fields_ = [
+        ("width", C.c_int32), ("height", C.c_int32), ("components", C.c_int32),
+        ("h_samp", C.c_int32), ("v_samp", C.c_int32), ("restart_interval", C.c_int32),
+        ("segments", C.c_int32), ("reserved", C.c_int32), ("scan_bytes", C.c_int64),
+    ]
+
+
+E_UNSUPPORTED = -6
+
 # every symbol include/b200predict.h declares: (name, restype, argtypes)
 SYMBOLS = [
     ("b2p_abi_version", C.c_int32, []),
@@ -85,6 +95,12 @@ SYMBOLS = [
     ("b2p_last_logits", C.c_void_p, [C.c_void_p]),
     ("b2p_head_static", C.c_int32, [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_int32, C.c_void_p,
                                     C.c_int32, C.c_void_p, C.c_void_p]),
+    ("b2p_jpeg_inspect", C.c_int32, [C.c_char_p, C.c_int64, C.POINTER(JpegInfo)]),
+    ("b2p_jpeg_create", C.c_int32, [C.c_int32, C.POINTER(C.c_void_p)]),
+    ("b2p_jpeg_destroy", C.c_int32, [C.c_void_p]),
+    ("b2p_jpeg_last_error", C.c_char_p, [C.c_void_p]),
+    ("b2p_jpeg_decode", C.c_int32, [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_int64), C.c_int32, C.c_void_p,
+                                    C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p]),
 ]
 
 HEAD_STATIC_MAX_IMAGES = 256
@@ -131,6 +147,50 @@ def head_static(feat, n: int, hw: int, c: int, weight, weight_rows: int, bias, c
                              classes, Replica._ptr(logits), Replica._stream(stream))
     if rc != 0:
         raise B2PError(rc, (lib.b2p_last_error(None) or b"").decode())
+
+
+def jpeg_inspect(data: bytes) -> Optional[JpegInfo]:
+    """Header walk of one file on the host (no device needed).  Returns the geometry when the GPU decoder covers
+    the file, None when it is a fine image for the host decoder only (progressive, CMYK, not a JPEG at all ...)."""
+    lib = load_library()
+    info = JpegInfo()
+    rc = lib.b2p_jpeg_inspect(data, len(data), C.byref(info))
+    return info if rc == 0 else None
+
+
+class JpegDecoder:
+    """GPU baseline-JPEG decoder bound to one device (b2p_jpeg_* in the header).  One thread, one stream."""
+
+    def __init__(self, device: int):
+        self.lib = load_library()
+        self.device = int(device)
+        h = C.c_void_p()
+        rc = self.lib.b2p_jpeg_create(self.device, C.byref(h))
+        if rc != 0:
+            raise B2PError(rc, (self.lib.b2p_jpeg_last_error(None) or b"").decode())
+        self.h = h
+
+    def decode(self, files: Sequence[bytes], slab, slab_bytes: int, offsets: Sequence[int], status=None, stream=None) -> None:
+        """files -> uint8 HWC RGB images at slab + offsets[i] (device memory).  Asynchronous on `stream`."""
+        n = len(files)
+        arr = (C.c_char_p * max(n, 1))(*files)
+        lens = (C.c_int64 * max(n, 1))(*[len(f) for f in files])
+        offs = (C.c_int64 * max(n, 1))(*[int(o) for o in offsets])
+        rc = self.lib.b2p_jpeg_decode(self.h, arr, lens, n, Replica._ptr(slab), int(slab_bytes), offs,
+                                      Replica._ptr(status) if status is not None else None, Replica._stream(stream))
+        if rc != 0:
+            raise B2PError(rc, (self.lib.b2p_jpeg_last_error(self.h) or b"").decode())
+
+    def close(self) -> None:
+        if self.h:
+            self.lib.b2p_jpeg_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class Replica:

@@ -20,6 +20,7 @@
 // Oracle-side equivalent: nn.Conv2d + BatchNorm2d(eval) + ReLU as wired in
 // SP/torchvision/models/resnet.py:89-105,143-163 (BN folded on the host, see weights.py).
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <cudaTypedefs.h>
 #include "kernels.h"
@@ -72,10 +73,11 @@ __device__ __forceinline__ float gelu_erf(float x) {
     return fmaf(fabsf(hx), erf_abs, hx);                  // 0.5 x (1 + sign(x) erf_abs)
 }
 
-template <int BLOCK_N, int BLOCK_K, bool OUT_F32, bool HAS_RES>
+template <int BLOCK_N, int BLOCK_K, bool OUT_F32, bool HAS_RES, bool CTA2>
 struct Cfg {
     static constexpr int A_BYTES = BLOCK_M * BLOCK_K * 2;
-    static constexpr int B_BYTES = BLOCK_N * BLOCK_K * 2;
+    static constexpr int B_ROWS = CTA2 ? BLOCK_N / 2 : BLOCK_N;   // a CTA pair splits the weight rows
+    static constexpr int B_BYTES = B_ROWS * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int OUT_BYTES = OUT_F32 ? 0 : OUT_BUFS * OUT_CHUNK_BYTES;
     static constexpr int RES_BYTES = HAS_RES ? RES_STAGES * OUT_CHUNK_BYTES : 0;
@@ -93,14 +95,15 @@ struct Cfg {
     static_assert((2 * STAGES + 2 * ACC_STAGES + 2 * RES_STAGES) * 8 + 8 <= BAR_BYTES, "barrier area");
 };
 
-template <int BLOCK_N, int BLOCK_K, bool IM2COL, bool OUT_F32, bool HAS_RES>
+template <int BLOCK_N, int BLOCK_K, bool IM2COL, bool OUT_F32, bool HAS_RES, bool CTA2>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
                  const __grid_constant__ CUtensorMap tmap_a2, const GemmArgs args) {
-    using C = Cfg<BLOCK_N, BLOCK_K, OUT_F32, HAS_RES>;
+    using C = Cfg<BLOCK_N, BLOCK_K, OUT_F32, HAS_RES, CTA2>;
     constexpr int STAGES = C::STAGES;
     static_assert(!(OUT_F32 && HAS_RES), "the fp32 epilogue has no residual input");
+    static_assert(!(CTA2 && (OUT_F32 || BLOCK_K != 64 || BLOCK_N < 128)), "CTA pairs: bf16 output, 128B rows, N >= 128");
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -118,8 +121,20 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_empty_bar + RES_STAGES);
 
     const int warp_idx = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
-    const int total_tiles = args.m_tiles * args.n_tiles;
+    // CTA2: the two CTAs of a cluster own the two 128-row halves of one 256-row tile; they walk the same
+    // sequence of (row pair, column block) tiles.  An odd number of row tiles leaves one phantom half whose
+    // loads are zero-filled and whose stores are clipped by the tensor maps.
+    const uint32_t rank = CTA2 ? cluster_ctarank() : 0u;
+    const int total_tiles = (CTA2 ? (args.m_tiles + 1) / 2 : args.m_tiles) * args.n_tiles;
+    const int first_tile = CTA2 ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
+    const int tile_step = CTA2 ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
     const int num_kb = args.taps_h * args.taps_w * args.k_chunks + args.k2_chunks;
+    auto tile_coords = [&](int tile, int& m_blk, int& n_blk) {
+        const int t = args.reverse ? total_tiles - 1 - tile : tile;
+        const int mp = t / args.n_tiles;
+        n_blk = t - mp * args.n_tiles;
+        m_blk = CTA2 ? 2 * mp + static_cast<int>(rank) : mp;
+    };
 
     if (warp_idx == 0) {
         if (elect_one()) {
@@ -136,7 +151,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             }
             for (int i = 0; i < ACC_STAGES; ++i) {
                 mbar_init(&tmem_full_bar[i], 1);
-                mbar_init(&tmem_empty_bar[i], 8);   // one arrive per epilogue warp (two groups of four)
+                mbar_init(&tmem_empty_bar[i], CTA2 ? 16 : 8);   // one arrive per epilogue warp (of both CTAs)
             }
             for (int i = 0; i < RES_STAGES; ++i) {
                 mbar_init(&res_full_bar[i], 1);
@@ -145,12 +160,17 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             fence_mbar_init();
         }
         __syncwarp();
-        tmem_alloc(tmem_slot, C::TMEM_COLS);
-        tmem_relinquish();
+        if (CTA2) {
+            tmem_alloc_pair(tmem_slot, C::TMEM_COLS);
+            tmem_relinquish_pair();
+        } else {
+            tmem_alloc(tmem_slot, C::TMEM_COLS);
+            tmem_relinquish();
+        }
     }
     pdl_launch_dependents();      // the next kernel may start its own prologue
     tc_fence_before();
-    __syncthreads();
+    if (CTA2) cluster_sync_all(); else __syncthreads();     // the peer signals this CTA's barriers: both must be initialised
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait();                   // predecessors done: activations readable, output buffers writable
@@ -161,11 +181,31 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             int stage = 0;
             uint32_t phase = 0;
             const int pq = args.out_h * args.out_w;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                const int tid_ = args.reverse ? total_tiles - 1 - tile : tile;
-                const int m_blk = tid_ / args.n_tiles;
-                const int n_blk = tid_ - m_blk * args.n_tiles;
+            // CTA2: both producers credit the LEADER's full barrier; only the leader arms it (for both halves)
+            const uint32_t full0 = CTA2 ? mapa_shared(smem_u32(&full_bar[0]), 0) : 0u;
+            const bool arms = !CTA2 || rank == 0;
+            constexpr uint32_t TX_BYTES = (CTA2 ? 2u : 1u) * C::STAGE_BYTES;
+            auto load_a = [&](const CUtensorMap* map, bool im2col, int stg, int c, int w, int h, int n, int s_, int r_) {
+                uint8_t* dst = smem_a + stg * C::A_BYTES;
+                if (CTA2) {
+                    const uint32_t bar = full0 + static_cast<uint32_t>(stg * 8);
+                    if (im2col) tma_load_im2col_4d_pair(map, bar, dst, c, w, h, n, static_cast<uint16_t>(s_), static_cast<uint16_t>(r_));
+                    else tma_load_2d_pair(map, bar, dst, c, w);
+                } else {
+                    if (im2col) tma_load_im2col_4d(map, &full_bar[stg], dst, c, w, h, n, static_cast<uint16_t>(s_), static_cast<uint16_t>(r_));
+                    else tma_load_2d(map, &full_bar[stg], dst, c, w);
+                }
+            };
+            auto load_b = [&](int stg, int kcol, int nrow) {
+                uint8_t* dst = smem_b + stg * C::B_BYTES;
+                if (CTA2) tma_load_2d_pair(&tmap_b, full0 + static_cast<uint32_t>(stg * 8), dst, kcol, nrow);
+                else tma_load_2d(&tmap_b, &full_bar[stg], dst, kcol, nrow);
+            };
+            for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
+                int m_blk, n_blk;
+                tile_coords(tile, m_blk, n_blk);
                 const int m0 = m_blk * BLOCK_M;
+                const int nrow = n_blk * BLOCK_N + static_cast<int>(rank) * C::B_ROWS;
                 int img = 0, base_w = 0, base_h = 0, base_w2 = 0, base_h2 = 0;
                 if (IM2COL || args.k2_chunks > 0) {
                     img = m0 / pq;
@@ -182,16 +222,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     for (int s = 0; s < args.taps_w; ++s) {
                         for (int cc = 0; cc < args.k_chunks; ++cc, kcol += BLOCK_K) {
                             mbar_wait(&empty_bar[stage], phase ^ 1u);
-                            mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
-                            if (IM2COL) {
-                                tma_load_im2col_4d(&tmap_a, &full_bar[stage], smem_a + stage * C::A_BYTES,
-                                                   cc * BLOCK_K, base_w, base_h, img, static_cast<uint16_t>(s),
-                                                   static_cast<uint16_t>(r));
-                            } else {
-                                tma_load_2d(&tmap_a, &full_bar[stage], smem_a + stage * C::A_BYTES, kcol, m0);
-                            }
-                            tma_load_2d(&tmap_b, &full_bar[stage], smem_b + stage * C::B_BYTES, kcol,
-                                        n_blk * BLOCK_N);
+                            if (arms) mbar_arrive_expect_tx(&full_bar[stage], TX_BYTES);
+                            if (IM2COL) load_a(&tmap_a, true, stage, cc * BLOCK_K, base_w, base_h, img, s, r);
+                            else load_a(&tmap_a, false, stage, kcol, m0, 0, 0, 0, 0);
+                            load_b(stage, kcol, nrow);
                             if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                         }
                     }
@@ -199,23 +233,22 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 // second source: the projection shortcut's input pixels, K continues after the main operand
                 for (int cc = 0; cc < args.k2_chunks; ++cc, kcol += BLOCK_K) {
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
-                    mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
-                    tma_load_im2col_4d(&tmap_a2, &full_bar[stage], smem_a + stage * C::A_BYTES, cc * BLOCK_K, base_w2,
-                                       base_h2, img, 0, 0);
-                    tma_load_2d(&tmap_b, &full_bar[stage], smem_b + stage * C::B_BYTES, kcol, n_blk * BLOCK_N);
+                    if (arms) mbar_arrive_expect_tx(&full_bar[stage], TX_BYTES);
+                    load_a(&tmap_a2, true, stage, cc * BLOCK_K, base_w2, base_h2, img, 0, 0);
+                    load_b(stage, kcol, nrow);
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                 }
             }
         }
     } else if (warp_idx == 1) {
         // ======================================================================= MMA issuer
-        if (elect_one()) {
-            constexpr uint32_t idesc = umma_idesc_bf16(BLOCK_M, BLOCK_N);
+        if ((!CTA2 || rank == 0) && elect_one()) {
+            constexpr uint32_t idesc = umma_idesc_bf16(CTA2 ? 2 * BLOCK_M : BLOCK_M, BLOCK_N);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+            for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
                 mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BLOCK_N);
@@ -227,13 +260,20 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
                     for (int k = 0; k < BLOCK_K / UMMA_K; ++k) {
                         // advancing K inside a swizzle row: +32 bytes = +2 in the (addr >> 4) field
-                        umma_bf16(d_tmem, a_desc + static_cast<uint64_t>(k * 2), b_desc + static_cast<uint64_t>(k * 2),
-                                  idesc, static_cast<uint32_t>((kb | k) != 0));
+                        if (CTA2) {
+                            umma_bf16_pair(d_tmem, a_desc + static_cast<uint64_t>(k * 2), b_desc + static_cast<uint64_t>(k * 2),
+                                           idesc, static_cast<uint32_t>((kb | k) != 0));
+                        } else {
+                            umma_bf16(d_tmem, a_desc + static_cast<uint64_t>(k * 2), b_desc + static_cast<uint64_t>(k * 2),
+                                      idesc, static_cast<uint32_t>((kb | k) != 0));
+                        }
                     }
-                    umma_commit(&empty_bar[stage]);     // smem slot is free once these MMAs retire
+                    // smem slot is free once these MMAs retire (in both CTAs of a pair)
+                    if (CTA2) umma_commit_pair(&empty_bar[stage]); else umma_commit(&empty_bar[stage]);
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                 }
-                umma_commit(&tmem_full_bar[acc]);       // accumulator complete -> epilogue
+                // accumulator complete -> epilogue (of both CTAs)
+                if (CTA2) umma_commit_pair(&tmem_full_bar[acc]); else umma_commit(&tmem_full_bar[acc]);
                 if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1u; }
             }
         }
@@ -242,10 +282,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (HAS_RES && elect_one()) {
             int rs = 0;
             uint32_t rphase = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                const int tid_ = args.reverse ? total_tiles - 1 - tile : tile;
-                const int m_blk = tid_ / args.n_tiles;
-                const int n_blk = tid_ - m_blk * args.n_tiles;
+            for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
+                int m_blk, n_blk;
+                tile_coords(tile, m_blk, n_blk);
                 for (int c64 = 0; c64 < BLOCK_N / 64; ++c64) {
                     mbar_wait(&res_empty_bar[rs], rphase ^ 1u);
                     mbar_arrive_expect_tx(&res_full_bar[rs], OUT_CHUNK_BYTES);
@@ -274,10 +313,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         uint32_t rphase = 0;
         const int ob = group;
         uint32_t seq = 0;                               // global chunk sequence number at the start of the tile
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, seq += BLOCK_N / 64) {
-            const int tid_ = args.reverse ? total_tiles - 1 - tile : tile;
-            const int m_blk = tid_ / args.n_tiles;
-            const int n_blk = tid_ - m_blk * args.n_tiles;
+        const uint32_t tmem_empty0 = CTA2 ? mapa_shared(smem_u32(&tmem_empty_bar[0]), 0) : 0u;   // the leader's
+        for (int tile = first_tile; tile < total_tiles; tile += tile_step, seq += BLOCK_N / 64) {
+            int m_blk, n_blk;
+            tile_coords(tile, m_blk, n_blk);
             mbar_wait(&tmem_full_bar[acc], acc_phase);
             tc_fence_after();
             const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) +
@@ -383,17 +422,22 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             // of its last chunk are in registers / shared memory): hand the accumulator back
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
+            if (lane == 0) {
+                if (CTA2) mbar_arrive_cluster(tmem_empty0 + static_cast<uint32_t>(acc * 8));
+                else mbar_arrive(&tmem_empty_bar[acc]);
+            }
             if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1u; }
         }
         if (!OUT_F32 && store_leader) tma_store_wait_all<0>();
     }
 
     tc_fence_before();
-    __syncthreads();
+    __syncwarp();
+    // a pair must leave together: the leader's MMAs read the peer's shared memory and signal its barriers
+    if (CTA2) cluster_sync_all(); else __syncthreads();
     if (warp_idx == 1) {
         tc_fence_after();
-        tmem_dealloc(tmem_base, C::TMEM_COLS);
+        if (CTA2) tmem_dealloc_pair(tmem_base, C::TMEM_COLS); else tmem_dealloc(tmem_base, C::TMEM_COLS);
     }
 }
 
@@ -406,10 +450,10 @@ void set_err(char* err, size_t n, const char* msg) {
     if (err && n) snprintf(err, n, "%s", msg);
 }
 
-template <int BLOCK_N, int BLOCK_K, bool IM2COL, bool OUT_F32, bool HAS_RES>
+template <int BLOCK_N, int BLOCK_K, bool IM2COL, bool OUT_F32, bool HAS_RES, bool CTA2>
 cudaError_t launch_variant(const GemmPlan& p, const GemmArgs& a, int grid, cudaStream_t stream) {
-    using C = Cfg<BLOCK_N, BLOCK_K, OUT_F32, HAS_RES>;
-    auto kern = conv_gemm_kernel<BLOCK_N, BLOCK_K, IM2COL, OUT_F32, HAS_RES>;
+    using C = Cfg<BLOCK_N, BLOCK_K, OUT_F32, HAS_RES, CTA2>;
+    auto kern = conv_gemm_kernel<BLOCK_N, BLOCK_K, IM2COL, OUT_F32, HAS_RES, CTA2>;
     static bool attr_set[64] = {};   // per instantiation, per device (one replica thread per device)
     int dev = 0;
     cudaGetDevice(&dev);
@@ -420,8 +464,26 @@ cudaError_t launch_variant(const GemmPlan& p, const GemmArgs& a, int grid, cudaS
         if (e != cudaSuccess) return e;
         attr_set[dev] = true;
     }
-    return launch_pdl(kern, dim3(grid), dim3(NUM_THREADS), C::SMEM_BYTES, stream, p.tmap_a, p.tmap_b, p.tmap_out,
-                      p.tmap_res, p.tmap_a2, a);
+    if (!CTA2) {
+        return launch_pdl(kern, dim3(grid), dim3(NUM_THREADS), C::SMEM_BYTES, stream, p.tmap_a, p.tmap_b, p.tmap_out,
+                          p.tmap_res, p.tmap_a2, a);
+    }
+    // CTA pairs: a 2-wide cluster (the two SMs of a TPC) on top of the programmatic-serialization attribute
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = C::SMEM_BYTES;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = 2;
+    attr[1].val.clusterDim.y = 1;
+    attr[1].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 2;
+    return cudaLaunchKernelEx(&cfg, kern, p.tmap_a, p.tmap_b, p.tmap_out, p.tmap_res, p.tmap_a2, a);
 }
 
 }  // namespace
@@ -519,8 +581,17 @@ bool gemm_plan_init(GemmPlan& p, const b2p_op& op, const void* weight_dev, int64
     }
     // Tile width: fewest (waves x tile width) at capacity; ties go to the wider tile, which
     // re-reads the activation tile fewer times.
+    // CTA pairs (cta_group::2, 256-row MMAs) halve the weight traffic per SM.  Measured per layer on ResNet-50 b256
+    // (profiles/r01g_cta2_layers.md): 5-12 % faster for 256-wide tiles without a residual, 15-35 % SLOWER for
+    // 128-wide tiles and slightly slower with a residual stream, so that is the policy.  B2P_CTA2=all / none
+    // overrides it for A/B measurements.
+    static const char* cta2_env = getenv("B2P_CTA2");
+    const bool cta2_all = cta2_env && strcmp(cta2_env, "all") == 0;
+    const bool cta2_none = cta2_env && strcmp(cta2_env, "none") == 0;
+    const bool has_res_op = op.res != B2P_SLOT_NONE;
+    const bool cta2_ok = !cta2_none && !p.out_f32 && p.block_k == 64 && num_sms >= 2;
     const int m_tiles = (rows_at_capacity + BLOCK_M - 1) / BLOCK_M;
-    int best = 0;
+    int best = 0, best_cta2 = 0;
     long best_cost = 0;
     const int cands[3] = {256, 128, 64};
     for (int bn : cands) {
@@ -528,20 +599,24 @@ bool gemm_plan_init(GemmPlan& p, const b2p_op& op, const void* weight_dev, int64
         if (p.n_pad % bn != 0) continue;
         if (p.block_k == 16 && bn != 64) continue;
         if (p.out_f32 && bn != 128) continue;
-        const long tiles = static_cast<long>(m_tiles) * (p.n_pad / bn);
-        const long waves = (tiles + num_sms - 1) / num_sms;
+        const int pair = (cta2_ok && (cta2_all ? bn >= 128 : (bn == 256 && !has_res_op))) ? 1 : 0;
+        const long m_eff = pair ? 2L * ((m_tiles + 1) / 2) : m_tiles;
+        const long sms = pair ? (num_sms & ~1) : num_sms;
+        const long tiles = m_eff * (p.n_pad / bn);
+        const long waves = (tiles + sms - 1) / sms;
         const long cost = waves * (bn + 32);     // +32: fixed per-tile overhead in "column" units
-        if (best == 0 || cost < best_cost) { best = bn; best_cost = cost; }
+        if (best == 0 || cost < best_cost) { best = bn; best_cost = cost; best_cta2 = pair; }
     }
     if (best == 0) {
         set_err(err, err_len, "no tile width fits this layer");
         return false;
     }
     p.block_n = best;
+    p.cta2 = best_cta2;
     const CUtensorMapSwizzle sw = p.block_k == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_32B;
     return encode_tiled_2d(&p.tmap_b, weight_dev, static_cast<uint64_t>(k_total),
                            static_cast<uint64_t>(p.n_pad), static_cast<uint32_t>(p.block_k),
-                           static_cast<uint32_t>(p.block_n), sw, err, err_len);
+                           static_cast<uint32_t>(p.cta2 ? p.block_n / 2 : p.block_n), sw, err, err_len);
 }
 
 bool gemm_plan_set_src(GemmPlan& p, const void* src, int batch_cap, char* err, size_t err_len) {
@@ -640,10 +715,26 @@ cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, bool has_res, void* 
     a.reverse = p.reverse;
     a.bias = p.bias;
     a.out = out_f32;
-    const int total = a.m_tiles * a.n_tiles;
+    int total = a.m_tiles * a.n_tiles;
     if (total <= 0) return cudaSuccess;
-    const int grid = total < num_sms ? total : num_sms;
-#define B2P_LAUNCH(BN, BK, IM, F32, RES) return launch_variant<BN, BK, IM, F32, RES>(p, a, grid, stream)
+    if (p.cta2) total = 2 * ((a.m_tiles + 1) / 2) * a.n_tiles;      // CTAs, two per 256-row tile
+    const int sms = p.cta2 ? (num_sms & ~1) : num_sms;
+    const int grid = total < sms ? total : sms;
+#define B2P_LAUNCH(BN, BK, IM, F32, RES) return launch_variant<BN, BK, IM, F32, RES, false>(p, a, grid, stream)
+#define B2P_LAUNCH2(BN, IM, RES) return launch_variant<BN, 64, IM, false, RES, true>(p, a, grid, stream)
+    if (p.cta2) {
+#define B2P_PICK2(BN)                                          \
+    if (p.block_n == BN) {                                     \
+        if (p.im2col && has_res) B2P_LAUNCH2(BN, true, true);  \
+        if (p.im2col) B2P_LAUNCH2(BN, true, false);            \
+        if (has_res) B2P_LAUNCH2(BN, false, true);             \
+        B2P_LAUNCH2(BN, false, false);                         \
+    }
+        B2P_PICK2(128)
+        B2P_PICK2(256)
+#undef B2P_PICK2
+        return cudaErrorInvalidConfiguration;
+    }
     if (p.block_k == 16) {
         if (p.block_n == 64 && p.im2col && !p.out_f32 && !has_res) B2P_LAUNCH(64, 16, true, false, false);
         return cudaErrorInvalidConfiguration;
@@ -664,6 +755,7 @@ cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, bool has_res, void* 
     B2P_PICK(256)
 #undef B2P_PICK
 #undef B2P_LAUNCH
+#undef B2P_LAUNCH2
     return cudaErrorInvalidConfiguration;
 }
 

@@ -1,0 +1,836 @@
+// Baseline-JPEG decode on the GPU: the step immediately before the predict path.
+//
+// Replaces, for the files it covers, the pixels `Image.open(image_file.file)` (reference src/model/model.py:23)
+// would hand to the preprocess stage: uint8 RGB, HWC.  The arithmetic is libjpeg-turbo's default decode pipeline
+// (what Pillow runs), restated in oracle/jpeg_np.py and checked there bit-for-bit against Pillow:
+//
+//   J1 huffman_kernel   entropy decoding (T.81 F.2.2)            one thread per restart segment -> int16 blocks
+//   J2 idct_kernel      dequantise + accurate integer IDCT       one thread per 8x8 block       -> uint8 planes
+//   J3 colour_kernel    fancy chroma upsampling + YCbCr -> RGB   one thread per 4 output pixels -> uint8 HWC
+//
+// Scope: SOF0/SOF1, 8-bit, one interleaved scan, 1 or 3 components, luma 1x1 / 2x1 / 2x2 with 1x1 chroma, no Adobe
+// marker.  b2p_jpeg_inspect() says B2P_E_UNSUPPORTED for everything else and the caller keeps those files on the
+// host decoder (row D of SURVEY.md §8(a)); nothing here falls back to the CPU.
+//
+// The marker parser runs on the calling host thread (it is a few hundred bytes of header per file); everything
+// that touches pixel or coefficient data runs on the device.
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <vector>
+#include <cuda_runtime.h>
+#include "../../include/b200predict.h"
+
+namespace {
+
+// ------------------------------------------------------------------------------------------- shared layouts
+constexpr int LOOK_BITS = 9;
+
+struct HuffDev {                  // one Huffman table in decode form
+    uint16_t look[1 << LOOK_BITS];  // (code length << 8) | symbol for codes of <= 9 bits, 0 = longer
+    int32_t maxcode[18];            // largest code of length l (l = 1..16), -1 if none; [17] = sentinel
+    int32_t valoff[18];             // index of the first symbol of length l minus its smallest code
+    uint8_t vals[256];
+};
+
+struct ImageDev {
+    int32_t width, height, ncomp;
+    int32_t hs, vs;               // luma sampling factors (chroma is 1x1)
+    int32_t mcux, mcuy;
+    int32_t dc_tab[3], ac_tab[3]; // indices into the call's HuffDev array
+    int32_t blocks_w[3], blocks_h[3];
+    int64_t coef_off[3];          // int16 elements from the coefficient buffer base
+    int64_t plane_off[3];         // bytes from the plane buffer base; plane pitch = blocks_w * 8
+    int64_t out_off;              // bytes from the RGB slab base
+    int64_t block_base;           // index of this image's first block in the call-wide block numbering
+    uint16_t quant[3][64];        // natural order
+};
+
+struct SegmentDev {
+    int32_t image;
+    int32_t first_mcu, n_mcu;
+    int32_t pad;
+    int64_t begin, end;           // byte range inside the scan buffer
+};
+
+__constant__ uint8_t c_zigzag[80] = {
+    0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13,
+    6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31,
+    39, 46, 53, 60, 61, 54, 47, 55, 62, 63,
+    63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63, 63};   // guard entries for corrupt run lengths
+
+const uint8_t h_zigzag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18, 11, 4,  5,  12, 19, 26, 33, 40, 48,
+                              41, 34, 27, 20, 13, 6,  7,  14, 21, 28, 35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23,
+                              30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+
+// ------------------------------------------------------------------------------------------- J1: entropy decode
+// MSB-first bit reader over one restart segment.  A stuffed zero after 0xFF is dropped; past the end of the
+// segment the reader supplies zero bits (what libjpeg does after its "premature end of data" warning) and
+// counts them, so that the caller can tell whether any of them was actually consumed.
+struct BitReader {
+    const uint8_t* p;
+    const uint8_t* end;
+    uint64_t acc;      // the low `n` bits are valid
+    int n;
+    int pad;           // zero bits appended after the end of the segment (they are the lowest bits of acc)
+
+    __device__ __forceinline__ void refill() {
+        while (n <= 32) {
+            uint32_t b = 0;
+            if (p < end) {
+                b = *p++;
+                if (b == 0xFFu && p < end && *p == 0u) ++p;
+            } else {
+                pad += 8;
+            }
+            acc = (acc << 8) | b;
+            n += 8;
+        }
+    }
+    __device__ __forceinline__ uint32_t peek(int bits) const { return static_cast<uint32_t>(acc >> (n - bits)) & ((1u << bits) - 1u); }
+    __device__ __forceinline__ void skip(int bits) { n -= bits; }
+    __device__ __forceinline__ int overrun() const { return n < pad ? 1 : 0; }     // padding bits were consumed
+};
+
+// One Huffman symbol (jdhuff.c: HUFF_DECODE): 9-bit lookahead table, then the canonical length walk.
+__device__ __forceinline__ int huff_symbol(BitReader& br, const HuffDev* __restrict__ t, int& bad) {
+    const uint32_t e = __ldg(&t->look[br.peek(LOOK_BITS)]);
+    if (e != 0u) {
+        br.skip(static_cast<int>(e >> 8));
+        return static_cast<int>(e & 255u);
+    }
+    int len = LOOK_BITS + 1;
+    int code = static_cast<int>(br.peek(len));
+    while (len <= 16 && code > __ldg(&t->maxcode[len])) {
+        ++len;
+        code = static_cast<int>(br.peek(len));
+    }
+    if (len > 16) {
+        bad = 1;
+        br.skip(16);
+        return 0;
+    }
+    br.skip(len);
+    return __ldg(&t->vals[(code + __ldg(&t->valoff[len])) & 255]);
+}
+
+__device__ __forceinline__ int huff_extend(uint32_t v, int s) {
+    return v < (1u << (s - 1)) ? static_cast<int>(v) - (1 << s) + 1 : static_cast<int>(v);
+}
+
+// One thread per restart segment.  `lane_stride` spreads the threads out (32: one per warp, the fastest layout for
+// a few hundred independent bit streams because no two streams share a warp's instruction pointer).
+__global__ void __launch_bounds__(128)
+huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ images,
+               const SegmentDev* __restrict__ segments, const HuffDev* __restrict__ tables, int n_segments,
+               int lane_stride, int16_t* __restrict__ coef, int32_t* __restrict__ status) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t % lane_stride != 0) return;
+    const int sid = t / lane_stride;
+    if (sid >= n_segments) return;
+    const SegmentDev sg = segments[sid];
+    const ImageDev* __restrict__ im = images + sg.image;
+    const int ncomp = im->ncomp, hs = im->hs, vs = im->vs, mcux = im->mcux;
+    BitReader br;
+    br.p = scan + sg.begin;
+    br.end = scan + sg.end;
+    br.acc = 0;
+    br.n = 0;
+    br.pad = 0;
+    int bad = 0;
+    int pred[3] = {0, 0, 0};
+    int my = sg.first_mcu / mcux;
+    int mx = sg.first_mcu - my * mcux;
+    for (int m = 0; m < sg.n_mcu; ++m) {
+        for (int ci = 0; ci < ncomp; ++ci) {
+            const int ch = ci == 0 ? hs : 1, cv = ci == 0 ? vs : 1;
+            const HuffDev* __restrict__ dct = tables + im->dc_tab[ci];
+            const HuffDev* __restrict__ act = tables + im->ac_tab[ci];
+            const int bw = im->blocks_w[ci];
+            int16_t* __restrict__ cbase = coef + im->coef_off[ci];
+            for (int by = 0; by < cv; ++by) {
+                for (int bx = 0; bx < ch; ++bx) {
+                    int16_t* __restrict__ blk = cbase + (static_cast<int64_t>(my * cv + by) * bw + (mx * ch + bx)) * 64;
+                    br.refill();
+                    int s = huff_symbol(br, dct, bad);
+                    if (s) {
+                        br.refill();
+                        pred[ci] += huff_extend(br.peek(s), s);
+                        br.skip(s);
+                    }
+                    blk[0] = static_cast<int16_t>(pred[ci]);
+                    int k = 1;
+                    while (k < 64) {
+                        br.refill();
+                        const int rs = huff_symbol(br, act, bad);
+                        const int r = rs >> 4;
+                        s = rs & 15;
+                        if (s) {
+                            k += r;
+                            const int v = huff_extend(br.peek(s), s);     // <= 16 + 15 bits since the refill
+                            br.skip(s);
+                            blk[c_zigzag[k]] = static_cast<int16_t>(v);
+                            ++k;
+                        } else {
+                            if (r != 15) break;
+                            k += 16;
+                        }
+                    }
+                }
+            }
+        }
+        if (++mx == mcux) { mx = 0; ++my; }
+    }
+    const int over = br.overrun();
+    if ((over | bad) && status) atomicOr(status + sg.image, over | (bad << 1));
+}
+
+// ------------------------------------------------------------------------------------------- J2: dequantise + IDCT
+// libjpeg's accurate integer IDCT (jidctint.c: jpeg_idct_islow): 13-bit constants, columns first with 2 extra
+// fraction bits kept, then rows, then +128 through the range-limit table (index taken modulo 1024, then clamped).
+__device__ __forceinline__ void idct_1d(int x0, int x1, int x2, int x3, int x4, int x5, int x6, int x7, int (&o)[8]) {
+    int z1 = (x2 + x6) * 4433;
+    const int tmp2 = z1 + x6 * (-15137);
+    const int tmp3 = z1 + x2 * 6270;
+    const int tmp0 = (x0 + x4) << 13;
+    const int tmp1 = (x0 - x4) << 13;
+    const int tmp10 = tmp0 + tmp3, tmp13 = tmp0 - tmp3, tmp11 = tmp1 + tmp2, tmp12 = tmp1 - tmp2;
+    int t0 = x7, t1 = x5, t2 = x3, t3 = x1;
+    z1 = t0 + t3;
+    int z2 = t1 + t2, z3 = t0 + t2, z4 = t1 + t3;
+    const int z5 = (z3 + z4) * 9633;
+    t0 *= 2446;
+    t1 *= 16819;
+    t2 *= 25172;
+    t3 *= 12299;
+    z1 *= -7373;
+    z2 *= -20995;
+    z3 = z3 * (-16069) + z5;
+    z4 = z4 * (-3196) + z5;
+    t0 += z1 + z3;
+    t1 += z2 + z4;
+    t2 += z2 + z3;
+    t3 += z1 + z4;
+    o[0] = tmp10 + t3; o[7] = tmp10 - t3;
+    o[1] = tmp11 + t2; o[6] = tmp11 - t2;
+    o[2] = tmp12 + t1; o[5] = tmp12 - t1;
+    o[3] = tmp13 + t0; o[4] = tmp13 - t0;
+}
+
+__device__ __forceinline__ uint32_t range_limit(int v) {      // v = descaled IDCT output, before the +128
+    int s = v & 1023;
+    s = s < 512 ? s : s - 1024;
+    return static_cast<uint32_t>(min(max(s + 128, 0), 255));
+}
+
+// One thread per 8x8 block: grid (blocks of the largest image / 128, images).
+__global__ void __launch_bounds__(128)
+idct_kernel(const ImageDev* __restrict__ images, const int16_t* __restrict__ coef, uint8_t* __restrict__ planes) {
+    const ImageDev* __restrict__ im = images + blockIdx.y;
+    int b = blockIdx.x * blockDim.x + threadIdx.x;
+    int ci = 0;
+    for (; ci < im->ncomp; ++ci) {
+        const int nb = im->blocks_w[ci] * im->blocks_h[ci];
+        if (b < nb) break;
+        b -= nb;
+    }
+    if (ci >= im->ncomp) return;
+    const int bw = im->blocks_w[ci];
+    const int by = b / bw, bx = b - by * bw;
+    const uint4* __restrict__ src = reinterpret_cast<const uint4*>(coef + im->coef_off[ci] + static_cast<int64_t>(b) * 64);
+    const uint4* __restrict__ q4 = reinterpret_cast<const uint4*>(im->quant[ci]);
+    int x[64];
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        const uint4 c = src[r];
+        const uint4 q = __ldg(q4 + r);
+        const uint32_t cw[4] = {c.x, c.y, c.z, c.w};
+        const uint32_t qw[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            x[r * 8 + 2 * j] = static_cast<int>(static_cast<int16_t>(cw[j] & 0xFFFFu)) * static_cast<int>(qw[j] & 0xFFFFu);
+            x[r * 8 + 2 * j + 1] = static_cast<int>(static_cast<int16_t>(cw[j] >> 16)) * static_cast<int>(qw[j] >> 16);
+        }
+    }
+    // pass 1: columns
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        int o[8];
+        idct_1d(x[c], x[8 + c], x[16 + c], x[24 + c], x[32 + c], x[40 + c], x[48 + c], x[56 + c], o);
+#pragma unroll
+        for (int r = 0; r < 8; ++r) x[r * 8 + c] = (o[r] + (1 << 10)) >> 11;
+    }
+    // pass 2: rows
+    uint8_t* __restrict__ dst = planes + im->plane_off[ci] + static_cast<int64_t>(by * 8) * (bw * 8) + bx * 8;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) {
+        int o[8];
+        idct_1d(x[r * 8], x[r * 8 + 1], x[r * 8 + 2], x[r * 8 + 3], x[r * 8 + 4], x[r * 8 + 5], x[r * 8 + 6], x[r * 8 + 7], o);
+        uint32_t p[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) p[c] = range_limit((o[c] + (1 << 17)) >> 18);
+        uint2 w;
+        w.x = p[0] | (p[1] << 8) | (p[2] << 16) | (p[3] << 24);
+        w.y = p[4] | (p[5] << 8) | (p[6] << 16) | (p[7] << 24);
+        *reinterpret_cast<uint2*>(dst + static_cast<int64_t>(r) * (bw * 8)) = w;
+    }
+}
+
+// ------------------------------------------------------------------------------------------- J3: upsample + colour
+// Fancy (triangle) chroma upsampling exactly as jdsample.c does it, then jdcolor.c's fixed-point YCbCr -> RGB.
+// One thread produces four horizontally adjacent pixels: grid (ceil(W/4 * H / 256) of the largest image, images).
+__device__ __forceinline__ int clamp255(int v) { return min(max(v, 0), 255); }
+
+__device__ __forceinline__ void chroma4(const uint8_t* __restrict__ plane, int pitch, int hs, int vs, int y, int x0, int w_ds,
+                                        int h_ds, int (&out)[4]) {
+    if (hs == 1) {                                   // 4:4:4
+        const uint8_t* row = plane + static_cast<int64_t>(y) * pitch + x0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) out[j] = row[j];
+        return;
+    }
+    const int c0 = x0 >> 1;                          // x0 is a multiple of 4: chroma columns c0, c0 + 1
+    const int cm = max(c0 - 1, 0), c1 = min(c0 + 1, w_ds - 1), c2 = min(c0 + 2, w_ds - 1);
+    if (vs == 1) {                                   // 4:2:2, h2v1_fancy_upsample
+        const uint8_t* row = plane + static_cast<int64_t>(y) * pitch;
+        const int am = row[cm], a0 = row[c0], a1 = row[c1], a2 = row[c2];
+        out[0] = c0 == 0 ? a0 : (3 * a0 + am + 1) >> 2;
+        out[1] = c0 == w_ds - 1 ? a0 : (3 * a0 + a1 + 2) >> 2;
+        out[2] = (3 * a1 + a0 + 1) >> 2;
+        out[3] = c0 + 1 >= w_ds - 1 ? a1 : (3 * a1 + a2 + 2) >> 2;
+        return;
+    }
+    // 4:2:0, h2v2_fancy_upsample: blend the nearer chroma row 3:1 with the farther one (edge rows duplicated)
+    const int cy = y >> 1;
+    const int oy = (y & 1) ? min(cy + 1, h_ds - 1) : max(cy - 1, 0);
+    const uint8_t* near = plane + static_cast<int64_t>(cy) * pitch;
+    const uint8_t* far = plane + static_cast<int64_t>(oy) * pitch;
+    const int sm = 3 * near[cm] + far[cm], s0 = 3 * near[c0] + far[c0], s1 = 3 * near[c1] + far[c1],
+              s2 = 3 * near[c2] + far[c2];
+    out[0] = c0 == 0 ? (4 * s0 + 8) >> 4 : (3 * s0 + sm + 8) >> 4;
+    out[1] = c0 == w_ds - 1 ? (4 * s0 + 7) >> 4 : (3 * s0 + s1 + 7) >> 4;
+    out[2] = (3 * s1 + s0 + 8) >> 4;
+    out[3] = c0 + 1 >= w_ds - 1 ? (4 * s1 + 7) >> 4 : (3 * s1 + s2 + 7) >> 4;
+}
+
+__global__ void __launch_bounds__(256)
+colour_kernel(const ImageDev* __restrict__ images, const uint8_t* __restrict__ planes, uint8_t* __restrict__ slab) {
+    const ImageDev* __restrict__ im = images + blockIdx.y;
+    const int W = im->width, H = im->height;
+    const int quads = (W + 3) >> 2;
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= quads * H) return;
+    const int y = t / quads, x0 = (t - y * quads) * 4;
+    const int pitch_y = im->blocks_w[0] * 8;
+    const uint8_t* yrow = planes + im->plane_off[0] + static_cast<int64_t>(y) * pitch_y + x0;
+    int yy[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) yy[j] = yrow[j];       // the plane is padded to whole blocks: x0 + 3 is inside
+    uint8_t rgb[12];
+    if (im->ncomp == 1) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) rgb[3 * j] = rgb[3 * j + 1] = rgb[3 * j + 2] = static_cast<uint8_t>(yy[j]);
+    } else {
+        const int hs = im->hs, vs = im->vs;
+        const int w_ds = (W + hs - 1) / hs, h_ds = (H + vs - 1) / vs;
+        const int pitch_c = im->blocks_w[1] * 8;
+        int cb[4], cr[4];
+        chroma4(planes + im->plane_off[1], pitch_c, hs, vs, y, x0, w_ds, h_ds, cb);
+        chroma4(planes + im->plane_off[2], pitch_c, hs, vs, y, x0, w_ds, h_ds, cr);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const int b = cb[j] - 128, r = cr[j] - 128;
+            rgb[3 * j + 0] = static_cast<uint8_t>(clamp255(yy[j] + ((91881 * r + 32768) >> 16)));
+            rgb[3 * j + 1] = static_cast<uint8_t>(clamp255(yy[j] + ((-22554 * b + 32768 - 46802 * r) >> 16)));
+            rgb[3 * j + 2] = static_cast<uint8_t>(clamp255(yy[j] + ((116130 * b + 32768) >> 16)));
+        }
+    }
+    uint8_t* dst = slab + im->out_off + (static_cast<int64_t>(y) * W + x0) * 3;
+    if (x0 + 4 <= W && (reinterpret_cast<uintptr_t>(dst) & 3u) == 0) {
+        uint32_t* d4 = reinterpret_cast<uint32_t*>(dst);
+        d4[0] = rgb[0] | (rgb[1] << 8) | (rgb[2] << 16) | (static_cast<uint32_t>(rgb[3]) << 24);
+        d4[1] = rgb[4] | (rgb[5] << 8) | (rgb[6] << 16) | (static_cast<uint32_t>(rgb[7]) << 24);
+        d4[2] = rgb[8] | (rgb[9] << 8) | (rgb[10] << 16) | (static_cast<uint32_t>(rgb[11]) << 24);
+    } else {
+        const int npix = min(4, W - x0);
+        for (int j = 0; j < 3 * npix; ++j) dst[j] = rgb[j];
+    }
+}
+
+// ------------------------------------------------------------------------------------------- host: marker parser
+static_assert(offsetof(ImageDev, quant) % 16 == 0 && sizeof(ImageDev) % 16 == 0, "quant tables are read as uint4");
+static_assert(sizeof(HuffDev) % 4 == 0 && sizeof(SegmentDev) % 8 == 0, "blob sections stay aligned");
+
+struct HuffHost {
+    bool present = false;
+    uint8_t counts[16] = {};
+    uint8_t vals[256] = {};
+    int nvals = 0;
+};
+
+struct Parsed {
+    int width = 0, height = 0, ncomp = 0;
+    int ident[3] = {}, hs[3] = {}, vs[3] = {}, tq[3] = {}, td[3] = {}, ta[3] = {};
+    bool qt_present[4] = {};
+    uint16_t qt[4][64] = {};            // natural order
+    HuffHost dc[4], ac[4];
+    int restart_interval = 0;
+    int64_t scan_start = 0, scan_end = 0;
+    int mcux = 0, mcuy = 0;
+    std::vector<int64_t> seg_begin, seg_end;   // absolute byte positions in the file
+};
+
+void why(char* dst, size_t n, const char* fmt, ...) {
+    if (!dst || !n) return;
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(dst, n, fmt, ap);
+    va_end(ap);
+}
+
+// Returns B2P_OK, B2P_E_UNSUPPORTED (a fine file, but not for this decoder) or B2P_E_ARG (not a decodable JPEG).
+int parse_jpeg(const uint8_t* d, int64_t len, Parsed& P, char* msg, size_t msg_len) {
+    if (!d || len < 4 || d[0] != 0xFF || d[1] != 0xD8) { why(msg, msg_len, "not a JPEG (no SOI marker)"); return B2P_E_ARG; }
+    int64_t i = 2;
+    bool seen_sof = false;
+    for (;;) {
+        if (i + 4 > len) { why(msg, msg_len, "truncated before the scan header"); return B2P_E_ARG; }
+        if (d[i] != 0xFF) { why(msg, msg_len, "marker expected at byte %lld", (long long)i); return B2P_E_ARG; }
+        while (i + 1 < len && d[i + 1] == 0xFF) ++i;
+        if (i + 4 > len) { why(msg, msg_len, "truncated before the scan header"); return B2P_E_ARG; }
+        const int m = d[i + 1];
+        i += 2;
+        if (m == 0xD8 || (m >= 0xD0 && m <= 0xD7) || m == 0x01) continue;
+        const int64_t seg_len = (d[i] << 8) | d[i + 1];
+        if (seg_len < 2 || i + seg_len > len) { why(msg, msg_len, "truncated marker segment"); return B2P_E_ARG; }
+        const uint8_t* s = d + i + 2;
+        const int64_t n = seg_len - 2;
+        if (m == 0xDB) {
+            int64_t p = 0;
+            while (p < n) {
+                const int pq = s[p] >> 4, tq = s[p] & 15;
+                ++p;
+                if (pq != 0) { why(msg, msg_len, "16-bit quantisation table"); return B2P_E_UNSUPPORTED; }
+                if (tq > 3 || p + 64 > n) { why(msg, msg_len, "bad DQT segment"); return B2P_E_ARG; }
+                for (int k = 0; k < 64; ++k) P.qt[tq][h_zigzag[k]] = s[p + k];
+                P.qt_present[tq] = true;
+                p += 64;
+            }
+        } else if (m == 0xC0 || m == 0xC1) {
+            if (seen_sof) { why(msg, msg_len, "more than one frame header"); return B2P_E_UNSUPPORTED; }
+            seen_sof = true;
+            if (n < 6) { why(msg, msg_len, "bad SOF segment"); return B2P_E_ARG; }
+            if (s[0] != 8) { why(msg, msg_len, "sample precision %d", s[0]); return B2P_E_UNSUPPORTED; }
+            P.height = (s[1] << 8) | s[2];
+            P.width = (s[3] << 8) | s[4];
+            P.ncomp = s[5];
+            if (P.ncomp != 1 && P.ncomp != 3) { why(msg, msg_len, "%d components", P.ncomp); return B2P_E_UNSUPPORTED; }
+            if (n < 6 + 3 * P.ncomp) { why(msg, msg_len, "bad SOF segment"); return B2P_E_ARG; }
+            for (int c = 0; c < P.ncomp; ++c) {
+                P.ident[c] = s[6 + 3 * c];
+                P.hs[c] = s[7 + 3 * c] >> 4;
+                P.vs[c] = s[7 + 3 * c] & 15;
+                P.tq[c] = s[8 + 3 * c];
+                if (P.tq[c] > 3 || P.hs[c] < 1 || P.vs[c] < 1) { why(msg, msg_len, "bad component spec"); return B2P_E_ARG; }
+            }
+        } else if (m >= 0xC2 && m <= 0xCF && m != 0xC4 && m != 0xC8 && m != 0xCC) {
+            why(msg, msg_len, "progressive, lossless or arithmetic-coded frame (SOF%d)", m - 0xC0);
+            return B2P_E_UNSUPPORTED;
+        } else if (m == 0xCC) {
+            why(msg, msg_len, "arithmetic coding");
+            return B2P_E_UNSUPPORTED;
+        } else if (m == 0xC4) {
+            int64_t p = 0;
+            while (p < n) {
+                if (p + 17 > n) { why(msg, msg_len, "bad DHT segment"); return B2P_E_ARG; }
+                const int tc = s[p] >> 4, th = s[p] & 15;
+                if (tc > 1 || th > 3) { why(msg, msg_len, "bad DHT table id"); return B2P_E_ARG; }
+                HuffHost& t = tc == 0 ? P.dc[th] : P.ac[th];
+                int total = 0;
+                for (int k = 0; k < 16; ++k) { t.counts[k] = s[p + 1 + k]; total += t.counts[k]; }
+                if (total > 256 || p + 17 + total > n) { why(msg, msg_len, "bad DHT segment"); return B2P_E_ARG; }
+                memset(t.vals, 0, sizeof t.vals);
+                memcpy(t.vals, s + p + 17, total);
+                t.nvals = total;
+                t.present = true;
+                p += 17 + total;
+            }
+        } else if (m == 0xDD) {
+            if (n < 2) { why(msg, msg_len, "bad DRI segment"); return B2P_E_ARG; }
+            P.restart_interval = (s[0] << 8) | s[1];
+        } else if (m == 0xEE && n >= 5 && memcmp(s, "Adobe", 5) == 0) {
+            why(msg, msg_len, "Adobe colour-transform marker");
+            return B2P_E_UNSUPPORTED;
+        } else if (m == 0xDA) {
+            if (!seen_sof) { why(msg, msg_len, "scan header before frame header"); return B2P_E_ARG; }
+            if (n < 1 || s[0] != P.ncomp) { why(msg, msg_len, "non-interleaved or multi-scan file"); return B2P_E_UNSUPPORTED; }
+            if (n < 4 + 2 * P.ncomp) { why(msg, msg_len, "bad SOS segment"); return B2P_E_ARG; }
+            for (int c = 0; c < P.ncomp; ++c) {
+                if (s[1 + 2 * c] != P.ident[c]) { why(msg, msg_len, "scan component order"); return B2P_E_UNSUPPORTED; }
+                P.td[c] = s[2 + 2 * c] >> 4;
+                P.ta[c] = s[2 + 2 * c] & 15;
+                if (P.td[c] > 3 || P.ta[c] > 3) { why(msg, msg_len, "bad table selector"); return B2P_E_ARG; }
+            }
+            if (s[1 + 2 * P.ncomp] != 0 || s[2 + 2 * P.ncomp] != 63 || s[3 + 2 * P.ncomp] != 0) {
+                why(msg, msg_len, "spectral selection / successive approximation");
+                return B2P_E_UNSUPPORTED;
+            }
+            P.scan_start = i + seg_len;
+            break;
+        }
+        i += seg_len;
+    }
+    if (P.width < 1 || P.height < 1) { why(msg, msg_len, "empty frame"); return B2P_E_ARG; }
+    for (int c = 0; c < P.ncomp; ++c) {
+        if (!P.qt_present[P.tq[c]]) { why(msg, msg_len, "missing quantisation table"); return B2P_E_ARG; }
+        if (!P.dc[P.td[c]].present || !P.ac[P.ta[c]].present) { why(msg, msg_len, "missing Huffman table"); return B2P_E_ARG; }
+    }
+    if (P.ncomp == 1) {
+        P.hs[0] = P.vs[0] = 1;          // a single-component scan is never interleaved (T.81 A.2.2)
+    } else {
+        if (P.ident[0] == 'R' && P.ident[1] == 'G' && P.ident[2] == 'B') { why(msg, msg_len, "RGB component ids"); return B2P_E_UNSUPPORTED; }
+        const bool chroma_ok = P.hs[1] == 1 && P.vs[1] == 1 && P.hs[2] == 1 && P.vs[2] == 1;
+        const bool luma_ok = (P.hs[0] == 1 && P.vs[0] == 1) || (P.hs[0] == 2 && P.vs[0] == 1) || (P.hs[0] == 2 && P.vs[0] == 2);
+        if (!chroma_ok || !luma_ok) { why(msg, msg_len, "sampling factors %dx%d", P.hs[0], P.vs[0]); return B2P_E_UNSUPPORTED; }
+        if (P.hs[0] == 2 && (P.width + 1) / 2 <= 2) { why(msg, msg_len, "chroma narrower than 3 samples"); return B2P_E_UNSUPPORTED; }
+    }
+    P.mcux = (P.width + 8 * P.hs[0] - 1) / (8 * P.hs[0]);
+    P.mcuy = (P.height + 8 * P.vs[0] - 1) / (8 * P.vs[0]);
+    // entropy-coded data: split at RSTn, ends at the first other marker
+    int64_t seg0 = P.scan_start, j = P.scan_start;
+    for (;;) {
+        const uint8_t* f = j < len ? static_cast<const uint8_t*>(memchr(d + j, 0xFF, static_cast<size_t>(len - j))) : nullptr;
+        if (!f || f + 1 >= d + len) { why(msg, msg_len, "entropy-coded data is not terminated by a marker"); return B2P_E_ARG; }
+        j = f - d;
+        const int nx = d[j + 1];
+        if (nx == 0x00) { j += 2; continue; }
+        if (nx == 0xFF) { j += 1; continue; }
+        if (nx >= 0xD0 && nx <= 0xD7) {
+            P.seg_begin.push_back(seg0);
+            P.seg_end.push_back(j);
+            seg0 = j + 2;
+            j += 2;
+            continue;
+        }
+        break;
+    }
+    P.seg_begin.push_back(seg0);
+    P.seg_end.push_back(j);
+    P.scan_end = j;
+    const int64_t total_mcu = static_cast<int64_t>(P.mcux) * P.mcuy;
+    const int64_t expect = P.restart_interval > 0 ? (total_mcu + P.restart_interval - 1) / P.restart_interval : 1;
+    if (static_cast<int64_t>(P.seg_begin.size()) != expect) {
+        why(msg, msg_len, "%zu restart segments found, %lld expected", P.seg_begin.size(), (long long)expect);
+        return B2P_E_ARG;
+    }
+    return B2P_OK;
+}
+
+// Canonical Huffman table -> lookahead + length-walk arrays (T.81 Annex C; jdhuff.c: jpeg_make_d_derived_tbl).
+bool build_huff(const HuffHost& h, HuffDev& out) {
+    memset(&out, 0, sizeof out);
+    memcpy(out.vals, h.vals, 256);
+    int code = 0, k = 0;
+    for (int l = 1; l <= 16; ++l) {
+        const int n = h.counts[l - 1];
+        out.valoff[l] = k - code;
+        out.maxcode[l] = n ? code + n - 1 : -1;
+        if (n && code + n > (1 << l)) return false;          // over-subscribed code space
+        if (l <= LOOK_BITS) {
+            for (int c = 0; c < n; ++c) {
+                const int first = (code + c) << (LOOK_BITS - l);
+                for (int f = 0; f < (1 << (LOOK_BITS - l)); ++f)
+                    out.look[first + f] = static_cast<uint16_t>((l << 8) | h.vals[k + c]);
+            }
+        }
+        code = (code + n) << 1;
+        k += n;
+    }
+    out.maxcode[17] = 0x7FFFFFFF;
+    return true;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------- C ABI
+struct b2p_jpeg {
+    int device = -1;
+    int num_sms = 0;
+    char err[512] = "";
+    // Per-call descriptors + entropy-coded bytes travel in ONE host->device copy from a pinned blob.  Two blobs
+    // alternate so that filling the next call's blob never waits for the previous call's copy.
+    static constexpr int RING = 2;
+    uint8_t* pinned[RING] = {};
+    uint8_t* blob_dev[RING] = {};
+    int64_t blob_cap[RING] = {};
+    cudaEvent_t copied[RING] = {};
+    bool used[RING] = {};
+    int pos = 0;
+    int16_t* coef = nullptr;      // [blocks][64] int16, zeroed per call
+    int64_t coef_cap = 0;         // bytes
+    uint8_t* planes = nullptr;    // component sample planes
+    int64_t planes_cap = 0;
+};
+
+namespace {
+
+char g_jpeg_error[512] = "";
+
+void jerr(b2p_jpeg* d, const char* fmt, ...) {
+    char* dst = d ? d->err : g_jpeg_error;
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(dst, 512, fmt, ap);
+    va_end(ap);
+}
+
+#define JPEG_CUDA(d, call)                                                                            \
+    do {                                                                                              \
+        cudaError_t e__ = (call);                                                                     \
+        if (e__ != cudaSuccess) {                                                                     \
+            jerr(d, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__);     \
+            return B2P_E_CUDA;                                                                        \
+        }                                                                                             \
+    } while (0)
+
+int64_t align_up(int64_t v, int64_t a) { return (v + a - 1) / a * a; }
+
+}  // namespace
+
+extern "C" {
+
+int32_t b2p_jpeg_inspect(const uint8_t* file, int64_t len, b2p_jpeg_info* info) {
+    Parsed P;
+    const int rc = parse_jpeg(file, len, P, g_jpeg_error, sizeof g_jpeg_error);
+    if (rc != B2P_OK) return rc;
+    if (info) {
+        info->width = P.width;
+        info->height = P.height;
+        info->components = P.ncomp;
+        info->h_samp = P.hs[0];
+        info->v_samp = P.vs[0];
+        info->restart_interval = P.restart_interval;
+        info->segments = static_cast<int32_t>(P.seg_begin.size());
+        info->reserved = 0;
+        info->scan_bytes = P.scan_end - P.scan_start;
+    }
+    return B2P_OK;
+}
+
+int32_t b2p_jpeg_create(int32_t device, b2p_jpeg** out) {
+    if (!out) return B2P_E_ARG;
+    *out = nullptr;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
+        jerr(nullptr, "cudaGetDeviceProperties(%d) failed: no CUDA device (this library has no CPU path)", device);
+        return B2P_E_DEVICE;
+    }
+    if (prop.major != 10) {
+        jerr(nullptr, "device %d is sm_%d%d; libb200predict is built for sm_100a only", device, prop.major, prop.minor);
+        return B2P_E_DEVICE;
+    }
+    b2p_jpeg* d = new (std::nothrow) b2p_jpeg();
+    if (!d) return B2P_E_NOMEM;
+    d->device = device;
+    d->num_sms = prop.multiProcessorCount;
+    if (cudaSetDevice(device) != cudaSuccess) { delete d; return B2P_E_CUDA; }
+    for (int i = 0; i < b2p_jpeg::RING; ++i) {
+        if (cudaEventCreateWithFlags(&d->copied[i], cudaEventDisableTiming) != cudaSuccess) {
+            jerr(nullptr, "cudaEventCreate failed");
+            delete d;
+            return B2P_E_CUDA;
+        }
+    }
+    *out = d;
+    return B2P_OK;
+}
+
+int32_t b2p_jpeg_destroy(b2p_jpeg* d) {
+    if (!d) return B2P_OK;
+    cudaSetDevice(d->device);
+    cudaDeviceSynchronize();
+    for (int i = 0; i < b2p_jpeg::RING; ++i) {
+        if (d->pinned[i]) cudaFreeHost(d->pinned[i]);
+        if (d->blob_dev[i]) cudaFree(d->blob_dev[i]);
+        if (d->copied[i]) cudaEventDestroy(d->copied[i]);
+    }
+    if (d->coef) cudaFree(d->coef);
+    if (d->planes) cudaFree(d->planes);
+    delete d;
+    return B2P_OK;
+}
+
+const char* b2p_jpeg_last_error(const b2p_jpeg* d) { return d ? d->err : g_jpeg_error; }
+
+int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t* lens, int32_t n, uint8_t* slab,
+                        int64_t slab_bytes, const int64_t* offsets, int32_t* status, void* stream_) {
+    if (!d) return B2P_E_ARG;
+    if (!files || !lens || !slab || !offsets || n < 0) { jerr(d, "b2p_jpeg_decode: null argument"); return B2P_E_ARG; }
+    if (n == 0) return B2P_OK;
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    JPEG_CUDA(d, cudaSetDevice(d->device));
+
+    // ---- parse every header on this thread, de-duplicate the Huffman tables
+    std::vector<Parsed> P(static_cast<size_t>(n));
+    std::vector<HuffHost> uniq;
+    auto table_id = [&](const HuffHost& h) -> int {
+        for (size_t i = 0; i < uniq.size(); ++i)
+            if (uniq[i].nvals == h.nvals && memcmp(uniq[i].counts, h.counts, 16) == 0 && memcmp(uniq[i].vals, h.vals, h.nvals) == 0)
+                return static_cast<int>(i);
+        uniq.push_back(h);
+        return static_cast<int>(uniq.size() - 1);
+    };
+    std::vector<ImageDev> images(static_cast<size_t>(n));
+    int64_t n_segments = 0, scan_total = 0, coef_elems = 0, plane_bytes = 0, block_total = 0;
+    int max_blocks = 0;
+    int64_t max_quads = 0;
+    for (int i = 0; i < n; ++i) {
+        char msg[256] = "";
+        const int rc = parse_jpeg(files[i], lens[i], P[i], msg, sizeof msg);
+        if (rc != B2P_OK) { jerr(d, "file %d: %s", i, msg); return rc; }
+        const Parsed& p = P[i];
+        ImageDev& im = images[i];
+        memset(&im, 0, sizeof im);
+        im.width = p.width; im.height = p.height; im.ncomp = p.ncomp;
+        im.hs = p.hs[0]; im.vs = p.vs[0]; im.mcux = p.mcux; im.mcuy = p.mcuy;
+        im.block_base = block_total;
+        int blocks = 0;
+        for (int c = 0; c < p.ncomp; ++c) {
+            im.dc_tab[c] = table_id(p.dc[p.td[c]]);
+            im.ac_tab[c] = table_id(p.ac[p.ta[c]]);
+            im.blocks_w[c] = p.mcux * (c == 0 ? p.hs[0] : 1);
+            im.blocks_h[c] = p.mcuy * (c == 0 ? p.vs[0] : 1);
+            const int64_t nb = static_cast<int64_t>(im.blocks_w[c]) * im.blocks_h[c];
+            im.coef_off[c] = coef_elems;
+            coef_elems += nb * 64;
+            im.plane_off[c] = plane_bytes;
+            plane_bytes += align_up(nb * 64, 256);
+            blocks += static_cast<int>(nb);
+            memcpy(im.quant[c], p.qt[p.tq[c]], 128);
+        }
+        block_total += blocks;
+        if (blocks > max_blocks) max_blocks = blocks;
+        const int64_t quads = static_cast<int64_t>((p.width + 3) / 4) * p.height;
+        if (quads > max_quads) max_quads = quads;
+        im.out_off = offsets[i];
+        if (offsets[i] < 0 || offsets[i] + static_cast<int64_t>(p.width) * p.height * 3 > slab_bytes) {
+            jerr(d, "file %d: %dx%d image at offset %lld does not fit the %lld-byte slab", i, p.width, p.height,
+                 (long long)offsets[i], (long long)slab_bytes);
+            return B2P_E_ARG;
+        }
+        n_segments += static_cast<int64_t>(p.seg_begin.size());
+        scan_total += p.scan_end - p.scan_start;
+    }
+    if (n_segments > 0x7FFFFFFF / 64 || max_quads > 0x7FFFFFFFLL) { jerr(d, "batch too large"); return B2P_E_LIMIT; }
+    std::vector<HuffDev> tables(uniq.size());
+    for (size_t t = 0; t < uniq.size(); ++t) {
+        if (!build_huff(uniq[t], tables[t])) { jerr(d, "a Huffman table over-subscribes its code space"); return B2P_E_ARG; }
+    }
+
+    // ---- blob layout: images | segments | tables | scan bytes
+    const int64_t off_img = 0;
+    const int64_t off_seg = align_up(off_img + static_cast<int64_t>(n) * sizeof(ImageDev), 256);
+    const int64_t off_tab = align_up(off_seg + n_segments * static_cast<int64_t>(sizeof(SegmentDev)), 256);
+    const int64_t off_scan = align_up(off_tab + static_cast<int64_t>(tables.size() * sizeof(HuffDev)), 256);
+    const int64_t blob_bytes = align_up(off_scan + scan_total, 256);
+    const int slot = d->pos;
+    d->pos = (d->pos + 1) % b2p_jpeg::RING;
+    if (d->used[slot]) JPEG_CUDA(d, cudaEventSynchronize(d->copied[slot]));     // the copy out of this blob finished
+    if (blob_bytes > d->blob_cap[slot]) {
+        JPEG_CUDA(d, cudaStreamSynchronize(stream));
+        if (d->pinned[slot]) cudaFreeHost(d->pinned[slot]);
+        if (d->blob_dev[slot]) cudaFree(d->blob_dev[slot]);
+        d->pinned[slot] = nullptr; d->blob_dev[slot] = nullptr; d->blob_cap[slot] = 0;
+        const int64_t cap = blob_bytes + blob_bytes / 2;
+        if (cudaMallocHost(reinterpret_cast<void**>(&d->pinned[slot]), static_cast<size_t>(cap)) != cudaSuccess ||
+            cudaMalloc(reinterpret_cast<void**>(&d->blob_dev[slot]), static_cast<size_t>(cap)) != cudaSuccess) {
+            jerr(d, "could not allocate %lld bytes of staging", (long long)cap);
+            return B2P_E_NOMEM;
+        }
+        d->blob_cap[slot] = cap;
+    }
+    const int64_t coef_bytes = coef_elems * 2;
+    if (coef_bytes > d->coef_cap || plane_bytes > d->planes_cap) {
+        JPEG_CUDA(d, cudaStreamSynchronize(stream));
+        if (coef_bytes > d->coef_cap) {
+            if (d->coef) cudaFree(d->coef);
+            d->coef = nullptr; d->coef_cap = 0;
+            const int64_t cap = coef_bytes + coef_bytes / 2;
+            if (cudaMalloc(reinterpret_cast<void**>(&d->coef), static_cast<size_t>(cap)) != cudaSuccess) {
+                jerr(d, "could not allocate %lld bytes for coefficients", (long long)cap);
+                return B2P_E_NOMEM;
+            }
+            d->coef_cap = cap;
+        }
+        if (plane_bytes > d->planes_cap) {
+            if (d->planes) cudaFree(d->planes);
+            d->planes = nullptr; d->planes_cap = 0;
+            const int64_t cap = plane_bytes + plane_bytes / 2;
+            if (cudaMalloc(reinterpret_cast<void**>(&d->planes), static_cast<size_t>(cap)) != cudaSuccess) {
+                jerr(d, "could not allocate %lld bytes for sample planes", (long long)cap);
+                return B2P_E_NOMEM;
+            }
+            d->planes_cap = cap;
+        }
+    }
+
+    // ---- fill the pinned blob
+    uint8_t* blob = d->pinned[slot];
+    memcpy(blob + off_img, images.data(), static_cast<size_t>(n) * sizeof(ImageDev));
+    SegmentDev* segs = reinterpret_cast<SegmentDev*>(blob + off_seg);
+    int64_t si = 0, scan_pos = 0;
+    for (int i = 0; i < n; ++i) {
+        const Parsed& p = P[i];
+        const int64_t total_mcu = static_cast<int64_t>(p.mcux) * p.mcuy;
+        const int64_t ri = p.restart_interval > 0 ? p.restart_interval : total_mcu;
+        for (size_t s = 0; s < p.seg_begin.size(); ++s, ++si) {
+            SegmentDev& g = segs[si];
+            g.image = i;
+            g.first_mcu = static_cast<int32_t>(static_cast<int64_t>(s) * ri);
+            const int64_t left = total_mcu - g.first_mcu;
+            g.n_mcu = static_cast<int32_t>(left < ri ? left : ri);
+            g.pad = 0;
+            g.begin = scan_pos + (p.seg_begin[s] - p.scan_start);
+            g.end = scan_pos + (p.seg_end[s] - p.scan_start);
+        }
+        memcpy(blob + off_scan + scan_pos, files[i] + p.scan_start, static_cast<size_t>(p.scan_end - p.scan_start));
+        scan_pos += p.scan_end - p.scan_start;
+    }
+    memcpy(blob + off_tab, tables.data(), tables.size() * sizeof(HuffDev));
+
+    // ---- device work, all on the caller's stream
+    uint8_t* dev = d->blob_dev[slot];
+    JPEG_CUDA(d, cudaMemcpyAsync(dev, blob, static_cast<size_t>(blob_bytes), cudaMemcpyHostToDevice, stream));
+    JPEG_CUDA(d, cudaEventRecord(d->copied[slot], stream));
+    d->used[slot] = true;
+    JPEG_CUDA(d, cudaMemsetAsync(d->coef, 0, static_cast<size_t>(coef_bytes), stream));
+    if (status) JPEG_CUDA(d, cudaMemsetAsync(status, 0, static_cast<size_t>(n) * sizeof(int32_t), stream));
+    const ImageDev* images_dev = reinterpret_cast<const ImageDev*>(dev + off_img);
+    const SegmentDev* segs_dev = reinterpret_cast<const SegmentDev*>(dev + off_seg);
+    const HuffDev* tabs_dev = reinterpret_cast<const HuffDev*>(dev + off_tab);
+    {
+        // few segments: one per warp (nothing else shares the warp's instruction stream); many: pack them
+        const int lane_stride = n_segments <= static_cast<int64_t>(d->num_sms) * 48 ? 32 : 1;
+        const int threads = lane_stride == 32 ? 64 : 128;
+        const int64_t total_threads = n_segments * lane_stride;
+        const int grid = static_cast<int>((total_threads + threads - 1) / threads);
+        huffman_kernel<<<grid, threads, 0, stream>>>(dev + off_scan, images_dev, segs_dev, tabs_dev, static_cast<int>(n_segments),
+                                                     lane_stride, d->coef, status);
+        JPEG_CUDA(d, cudaGetLastError());
+    }
+    {
+        dim3 grid(static_cast<unsigned>((max_blocks + 127) / 128), static_cast<unsigned>(n));
+        idct_kernel<<<grid, 128, 0, stream>>>(images_dev, d->coef, d->planes);
+        JPEG_CUDA(d, cudaGetLastError());
+    }
+    {
+        dim3 grid(static_cast<unsigned>((max_quads + 255) / 256), static_cast<unsigned>(n));
+        colour_kernel<<<grid, 256, 0, stream>>>(images_dev, d->planes, slab);
+        JPEG_CUDA(d, cudaGetLastError());
+    }
+    return B2P_OK;
+}
+
+}  // extern "C"

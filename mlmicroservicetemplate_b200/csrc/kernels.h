@@ -36,6 +36,7 @@ struct GemmPlan {
     int src2_c = 0, src2_stride = 1;
     int block_n = 0;      // 64 / 128 / 256
     int force_block_n = 0;  // set before gemm_plan_init to pin the tile width (autotuner)
+    int cta2 = 0;         // run as CTA pairs: 256-row tiles, each CTA loads half of the weight tile (cta_group::2)
     int block_k = 64;     // 64 (128-byte swizzle) or 16 (32-byte swizzle, the stem)
     int im2col = 0;       // A operand through TMA im2col mode
     int out_f32 = 0;      // fp32 [M, ldc] output (LINEAR) instead of bf16 NHWC
