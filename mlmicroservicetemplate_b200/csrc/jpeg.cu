@@ -52,7 +52,8 @@ struct SegmentDev {
     int32_t image;
     int32_t first_mcu, n_mcu;
     int32_t pad;
-    int64_t begin, end;           // byte range inside the scan buffer
+    int64_t begin;                // byte offset of the un-stuffed segment inside the scan buffer (4-byte aligned)
+    int64_t nbits;                // its length in bits
 };
 
 __constant__ uint8_t c_zigzag[80] = {
@@ -66,32 +67,47 @@ const uint8_t h_zigzag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18
                               30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
 
 // ------------------------------------------------------------------------------------------- J1: entropy decode
-// MSB-first bit reader over one restart segment.  A stuffed zero after 0xFF is dropped; past the end of the
-// segment the reader supplies zero bits (what libjpeg does after its "premature end of data" warning) and
-// counts them, so that the caller can tell whether any of them was actually consumed.
+// A Huffman-coded segment has no index: the position of symbol i is only known once symbols 0..i-1 are decoded.
+// One CTA per restart segment breaks that chain with the self-synchronising property of Huffman streams:
+//   1. the segment's bits are cut into one chunk per thread; thread 0 starts in the true state, every other thread
+//      GUESSES (first bit of its chunk, first block of an MCU, DC position) and decodes its chunk without output,
+//      recording the state it reaches at the chunk end and the number of blocks it completed;
+//   2. every thread whose predecessor ended in a different state than the one it started from re-decodes from the
+//      predecessor's end state; repeat until no thread changes.  Thread 0 is right from the start, so after j
+//      rounds threads 0..j are provably right and the loop ends in at most blockDim rounds — in practice 2-4,
+//      because a decoder started in the wrong state falls into step with the true one within a few symbols;
+//   3. a prefix sum of the block counts gives every thread the index of its first block; it decodes its chunk once
+//      more, now writing coefficients (DC as the difference it reads);
+//   4. a prefix sum over each component's DC differences in decode order yields the DC values (T.81 F.2.1.3.1).
+// The result is exactly what a sequential decoder produces; a stream that never synchronises only costs rounds.
+//
+// The host hands over each segment un-stuffed (FF 00 -> FF), 4-byte aligned and zero padded, so a bit position is a
+// plain offset and the reader can take 32 bits at a time.
 struct BitReader {
-    const uint8_t* p;
-    const uint8_t* end;
-    uint64_t acc;      // the low `n` bits are valid
-    int n;
-    int pad;           // zero bits appended after the end of the segment (they are the lowest bits of acc)
+    const uint32_t* __restrict__ words;   // big-endian bit order inside each byte-swapped word
+    uint32_t nwords;
+    uint32_t next;                        // index of the next word to take
+    uint64_t win;                         // bit 63 = next unread bit
+    int have;                             // valid bits in win
 
-    __device__ __forceinline__ void refill() {
-        while (n <= 32) {
-            uint32_t b = 0;
-            if (p < end) {
-                b = *p++;
-                if (b == 0xFFu && p < end && *p == 0u) ++p;
-            } else {
-                pad += 8;
-            }
-            acc = (acc << 8) | b;
-            n += 8;
+    __device__ __forceinline__ uint32_t word(uint32_t i) const {
+        return i < nwords ? __byte_perm(__ldg(words + i), 0, 0x0123) : 0u;
+    }
+    __device__ __forceinline__ void seek(uint32_t bitpos) {
+        next = bitpos >> 5;
+        const int off = static_cast<int>(bitpos & 31u);
+        win = static_cast<uint64_t>(word(next++)) << (32 + off);
+        have = 32 - off;
+    }
+    __device__ __forceinline__ void refill() {           // afterwards at least 33 bits are valid
+        if (have <= 32) {
+            win |= static_cast<uint64_t>(word(next++)) << (32 - have);
+            have += 32;
         }
     }
-    __device__ __forceinline__ uint32_t peek(int bits) const { return static_cast<uint32_t>(acc >> (n - bits)) & ((1u << bits) - 1u); }
-    __device__ __forceinline__ void skip(int bits) { n -= bits; }
-    __device__ __forceinline__ int overrun() const { return n < pad ? 1 : 0; }     // padding bits were consumed
+    __device__ __forceinline__ uint32_t position() const { return next * 32u - static_cast<uint32_t>(have); }
+    __device__ __forceinline__ uint32_t peek(int bits) const { return static_cast<uint32_t>(win >> (64 - bits)); }
+    __device__ __forceinline__ void skip(int bits) { win <<= bits; have -= bits; }
 };
 
 // One Huffman symbol (jdhuff.c: HUFF_DECODE): 9-bit lookahead table, then the canonical length walk.
@@ -120,71 +136,221 @@ __device__ __forceinline__ int huff_extend(uint32_t v, int s) {
     return v < (1u << (s - 1)) ? static_cast<int>(v) - (1 << s) + 1 : static_cast<int>(v);
 }
 
-// One thread per restart segment.  `lane_stride` spreads the threads out (32: one per warp, the fastest layout for
-// a few hundred independent bit streams because no two streams share a warp's instruction pointer).
-__global__ void __launch_bounds__(128)
-huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ images,
-               const SegmentDev* __restrict__ segments, const HuffDev* __restrict__ tables, int n_segments,
-               int lane_stride, int16_t* __restrict__ coef, int32_t* __restrict__ status) {
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t % lane_stride != 0) return;
-    const int sid = t / lane_stride;
-    if (sid >= n_segments) return;
-    const SegmentDev sg = segments[sid];
-    const ImageDev* __restrict__ im = images + sg.image;
-    const int ncomp = im->ncomp, hs = im->hs, vs = im->vs, mcux = im->mcux;
+struct DecodeState {
+    uint32_t pos;     // bit position of the next symbol
+    int blk;          // block inside the MCU
+    int k;            // 0 = the DC symbol is next, else the zig-zag index of the next AC coefficient
+};
+
+struct SegmentCtx {
+    const ImageDev* __restrict__ im;
+    const HuffDev* __restrict__ tables;
+    int bpm;          // blocks per MCU
+    int luma;         // luma blocks per MCU (hs * vs)
+    int hs;
+    int first_mcu;
+    int total_blocks;
+    uint32_t nbits;
+    const uint32_t* __restrict__ words;
+    uint32_t nwords;
+};
+
+// Address of block `b` (segment-relative, decode order) in the coefficient planes.
+__device__ __forceinline__ int16_t* block_ptr(const SegmentCtx& c, int16_t* __restrict__ coef, int b, int& comp) {
+    const int mcu = c.first_mcu + b / c.bpm;
+    const int j = b - (b / c.bpm) * c.bpm;
+    const int my = mcu / c.im->mcux, mx = mcu - my * c.im->mcux;
+    int by, bx;
+    if (j < c.luma) {
+        comp = 0;
+        const int sy = j / c.hs, sx = j - sy * c.hs;
+        const int vs = c.luma / c.hs;
+        by = my * vs + sy;
+        bx = mx * c.hs + sx;
+    } else {
+        comp = j - c.luma + 1;
+        by = my;
+        bx = mx;
+    }
+    return coef + c.im->coef_off[comp] + (static_cast<int64_t>(by) * c.im->blocks_w[comp] + bx) * 64;
+}
+
+// Decodes the symbols that START in [st.pos, end_bit).  WRITE = false: only tracks the state and counts completed
+// blocks.  WRITE = true: stores coefficients for blocks first_block, first_block + 1, ... (DC as a difference) and
+// stops after the segment's last block.
+template <bool WRITE>
+__device__ __forceinline__ void decode_range(const SegmentCtx& c, DecodeState& st, uint32_t end_bit, int& blocks,
+                                             int first_block, int16_t* __restrict__ coef, int& bad, int& overrun) {
     BitReader br;
-    br.p = scan + sg.begin;
-    br.end = scan + sg.end;
-    br.acc = 0;
-    br.n = 0;
-    br.pad = 0;
-    int bad = 0;
-    int pred[3] = {0, 0, 0};
-    int my = sg.first_mcu / mcux;
-    int mx = sg.first_mcu - my * mcux;
-    for (int m = 0; m < sg.n_mcu; ++m) {
-        for (int ci = 0; ci < ncomp; ++ci) {
-            const int ch = ci == 0 ? hs : 1, cv = ci == 0 ? vs : 1;
-            const HuffDev* __restrict__ dct = tables + im->dc_tab[ci];
-            const HuffDev* __restrict__ act = tables + im->ac_tab[ci];
-            const int bw = im->blocks_w[ci];
-            int16_t* __restrict__ cbase = coef + im->coef_off[ci];
-            for (int by = 0; by < cv; ++by) {
-                for (int bx = 0; bx < ch; ++bx) {
-                    int16_t* __restrict__ blk = cbase + (static_cast<int64_t>(my * cv + by) * bw + (mx * ch + bx)) * 64;
-                    br.refill();
-                    int s = huff_symbol(br, dct, bad);
-                    if (s) {
-                        br.refill();
-                        pred[ci] += huff_extend(br.peek(s), s);
-                        br.skip(s);
-                    }
-                    blk[0] = static_cast<int16_t>(pred[ci]);
-                    int k = 1;
-                    while (k < 64) {
-                        br.refill();
-                        const int rs = huff_symbol(br, act, bad);
-                        const int r = rs >> 4;
-                        s = rs & 15;
-                        if (s) {
-                            k += r;
-                            const int v = huff_extend(br.peek(s), s);     // <= 16 + 15 bits since the refill
-                            br.skip(s);
-                            blk[c_zigzag[k]] = static_cast<int16_t>(v);
-                            ++k;
-                        } else {
-                            if (r != 15) break;
-                            k += 16;
-                        }
-                    }
-                }
+    br.words = c.words;
+    br.nwords = c.nwords;
+    br.seek(st.pos);
+    int blk = st.blk, k = st.k;
+    int done = 0;
+    int b = first_block;
+    int comp = blk < c.luma ? 0 : blk - c.luma + 1;
+    int16_t* __restrict__ out = nullptr;
+    if (WRITE) {
+        if (b >= c.total_blocks) return;
+        out = block_ptr(c, coef, b, comp);
+    }
+    const HuffDev* __restrict__ dct = c.tables + c.im->dc_tab[comp];
+    const HuffDev* __restrict__ act = c.tables + c.im->ac_tab[comp];
+    uint32_t pos = st.pos;
+    while (pos < end_bit) {
+        br.refill();
+        if (k == 0) {
+            const int s = huff_symbol(br, dct, bad) & 15;
+            if (s) {
+                if (WRITE) out[0] = static_cast<int16_t>(huff_extend(br.peek(s), s));
+                br.skip(s);
+            }
+            k = 1;
+        } else {
+            const int rs = huff_symbol(br, act, bad);
+            const int r = rs >> 4, s = rs & 15;
+            if (s) {
+                k += r;
+                if (WRITE) out[c_zigzag[k]] = static_cast<int16_t>(huff_extend(br.peek(s), s));
+                br.skip(s);
+                ++k;
+            } else {
+                k = r == 15 ? k + 16 : 64;
             }
         }
-        if (++mx == mcux) { mx = 0; ++my; }
+        pos = br.position();
+        if (k >= 64) {                       // block complete
+            k = 0;
+            ++done;
+            if (++blk == c.bpm) blk = 0;
+            comp = blk < c.luma ? 0 : blk - c.luma + 1;
+            dct = c.tables + c.im->dc_tab[comp];
+            act = c.tables + c.im->ac_tab[comp];
+            if (WRITE) {
+                if (++b >= c.total_blocks) {
+                    if (pos > c.nbits) overrun = 1;      // the last block needed bits the file does not have
+                    break;
+                }
+                out = block_ptr(c, coef, b, comp);
+            }
+        }
     }
-    const int over = br.overrun();
-    if ((over | bad) && status) atomicOr(status + sg.image, over | (bad << 1));
+    st.pos = pos;
+    st.blk = blk;
+    st.k = k;
+    blocks = done;
+}
+
+constexpr int HUFF_MAX_THREADS = 1024;
+constexpr int HUFF_MIN_CHUNK_BITS = 256;      // default; B2P_JPEG_CHUNK_BITS overrides it for experiments
+
+// Exclusive prefix sum of one int per thread over the CTA; `total` receives the sum of all.
+__device__ __forceinline__ int cta_exclusive_scan(int v, int* s_warp, int& total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
+    int inc = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int o = __shfl_up_sync(0xffffffffu, inc, d);
+        if (lane >= d) inc += o;
+    }
+    __syncthreads();                       // s_warp may still be read from a previous scan
+    if (lane == 31) s_warp[warp] = inc;
+    __syncthreads();
+    int base = 0, sum = 0;
+    for (int w = 0; w < nwarps; ++w) {
+        const int x = s_warp[w];
+        if (w < warp) base += x;
+        sum += x;
+    }
+    total = sum;
+    return base + inc - v;
+}
+
+__global__ void __launch_bounds__(HUFF_MAX_THREADS)
+huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ images,
+               const SegmentDev* __restrict__ segments, const HuffDev* __restrict__ tables,
+               int16_t* __restrict__ coef, int32_t* __restrict__ status, int min_chunk_bits) {
+    __shared__ uint32_t s_pos[HUFF_MAX_THREADS];
+    __shared__ int s_state[HUFF_MAX_THREADS];        // blk << 8 | k
+    __shared__ int s_warp[HUFF_MAX_THREADS / 32];
+    const SegmentDev sg = segments[blockIdx.x];
+    const int t = threadIdx.x, P = blockDim.x;
+    SegmentCtx c;
+    c.im = images + sg.image;
+    c.tables = tables;
+    c.hs = c.im->hs;
+    c.luma = c.im->hs * c.im->vs;
+    c.bpm = c.im->ncomp == 1 ? 1 : c.luma + 2;
+    c.first_mcu = sg.first_mcu;
+    c.total_blocks = sg.n_mcu * c.bpm;
+    c.nbits = static_cast<uint32_t>(sg.nbits);
+    c.words = reinterpret_cast<const uint32_t*>(scan + sg.begin);
+    c.nwords = (c.nbits + 31u) >> 5;
+    // one chunk per thread: a multiple of 32 bits, at least HUFF_MIN_CHUNK_BITS (trailing threads may get nothing)
+    uint32_t chunk = (c.nbits + static_cast<uint32_t>(P) - 1u) / static_cast<uint32_t>(P);
+    chunk = max((chunk + 31u) & ~31u, static_cast<uint32_t>(min_chunk_bits));
+    const uint32_t my_begin = min(static_cast<uint32_t>(t) * chunk, c.nbits);
+    const uint32_t my_end = min(my_begin + chunk, c.nbits);
+
+    // ---- 1 + 2: find every chunk's true entry state
+    DecodeState in = {my_begin, 0, 0};
+    DecodeState out = in;
+    int blocks = 0, bad = 0, overrun = 0;
+    bool dirty = true;
+    for (int round = 0; round <= P; ++round) {
+        if (dirty) {
+            out = in;
+            blocks = 0;
+            int ignore = 0;
+            decode_range<false>(c, out, my_end, blocks, 0, nullptr, ignore, ignore);
+        }
+        s_pos[t] = out.pos;
+        s_state[t] = (out.blk << 8) | out.k;
+        __syncthreads();
+        DecodeState want = in;
+        if (t > 0) {
+            want.pos = s_pos[t - 1];
+            want.blk = s_state[t - 1] >> 8;
+            want.k = s_state[t - 1] & 255;
+        }
+        dirty = want.pos != in.pos || want.blk != in.blk || want.k != in.k;
+        in = want;
+        if (!__syncthreads_or(dirty ? 1 : 0)) break;
+    }
+
+    // ---- 3: index of each thread's first block, then the decode that writes
+    int total = 0;
+    const int first_block = cta_exclusive_scan(blocks, s_warp, total);
+    if (total < c.total_blocks) overrun = 1;            // the data ran out before the last block was complete
+    {
+        DecodeState st = in;
+        int n = 0;
+        decode_range<true>(c, st, my_end, n, first_block, coef, bad, overrun);
+    }
+    if ((overrun | bad) && status) atomicOr(status + sg.image, overrun | (bad << 1));
+    __syncthreads();                                    // every coefficient of this segment is in place
+
+    // ---- 4: DC differences -> DC values, per component, in decode order
+    for (int comp = 0; comp < c.im->ncomp; ++comp) {
+        const int per_mcu = comp == 0 ? c.luma : 1;
+        const int nblk = sg.n_mcu * per_mcu;
+        const int per_thread = (nblk + P - 1) / P;
+        const int i0 = min(t * per_thread, nblk), i1 = min(i0 + per_thread, nblk);
+        auto dc_ptr = [&](int i) -> int16_t* {
+            const int m = i / per_mcu, j = i - m * per_mcu;
+            int cc;
+            return block_ptr(c, coef, m * c.bpm + (comp == 0 ? j : c.luma + comp - 1), cc);
+        };
+        int sum = 0;
+        for (int i = i0; i < i1; ++i) sum += *dc_ptr(i);
+        int all = 0;
+        int run = cta_exclusive_scan(sum, s_warp, all);
+        for (int i = i0; i < i1; ++i) {
+            int16_t* p = dc_ptr(i);
+            run += *p;
+            *p = static_cast<int16_t>(run);
+        }
+    }
 }
 
 // ------------------------------------------------------------------------------------------- J2: dequantise + IDCT
@@ -729,12 +895,12 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
         if (!build_huff(uniq[t], tables[t])) { jerr(d, "a Huffman table over-subscribes its code space"); return B2P_E_ARG; }
     }
 
-    // ---- blob layout: images | segments | tables | scan bytes
+    // ---- blob layout: images | segments | tables | un-stuffed scan bytes (each segment 4-byte aligned)
     const int64_t off_img = 0;
     const int64_t off_seg = align_up(off_img + static_cast<int64_t>(n) * sizeof(ImageDev), 256);
     const int64_t off_tab = align_up(off_seg + n_segments * static_cast<int64_t>(sizeof(SegmentDev)), 256);
     const int64_t off_scan = align_up(off_tab + static_cast<int64_t>(tables.size() * sizeof(HuffDev)), 256);
-    const int64_t blob_bytes = align_up(off_scan + scan_total, 256);
+    const int64_t blob_bytes = align_up(off_scan + scan_total + 8 * n_segments, 256);
     const int slot = d->pos;
     d->pos = (d->pos + 1) % b2p_jpeg::RING;
     if (d->used[slot]) JPEG_CUDA(d, cudaEventSynchronize(d->copied[slot]));     // the copy out of this blob finished
@@ -776,11 +942,11 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
         }
     }
 
-    // ---- fill the pinned blob
+    // ---- fill the pinned blob; the entropy-coded bytes lose their stuffing (FF 00 -> FF) on the way
     uint8_t* blob = d->pinned[slot];
     memcpy(blob + off_img, images.data(), static_cast<size_t>(n) * sizeof(ImageDev));
     SegmentDev* segs = reinterpret_cast<SegmentDev*>(blob + off_seg);
-    int64_t si = 0, scan_pos = 0;
+    int64_t si = 0, scan_pos = 0, max_seg_bits = 0;
     for (int i = 0; i < n; ++i) {
         const Parsed& p = P[i];
         const int64_t total_mcu = static_cast<int64_t>(p.mcux) * p.mcuy;
@@ -792,12 +958,27 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
             const int64_t left = total_mcu - g.first_mcu;
             g.n_mcu = static_cast<int32_t>(left < ri ? left : ri);
             g.pad = 0;
-            g.begin = scan_pos + (p.seg_begin[s] - p.scan_start);
-            g.end = scan_pos + (p.seg_end[s] - p.scan_start);
+            g.begin = scan_pos;
+            uint8_t* dst = blob + off_scan + scan_pos;
+            const uint8_t* src = files[i] + p.seg_begin[s];
+            const uint8_t* end = files[i] + p.seg_end[s];
+            int64_t w = 0;
+            while (src < end) {
+                const uint8_t* f = static_cast<const uint8_t*>(memchr(src, 0xFF, static_cast<size_t>(end - src)));
+                const int64_t run = (f ? f + 1 : end) - src;          // up to and including the FF
+                memcpy(dst + w, src, static_cast<size_t>(run));
+                w += run;
+                src += run;
+                if (f && src < end && *src == 0x00) ++src;             // the stuffed zero
+            }
+            g.nbits = w * 8;
+            if (g.nbits > max_seg_bits) max_seg_bits = g.nbits;
+            const int64_t padded = align_up(w, 4) + 4;
+            memset(dst + w, 0, static_cast<size_t>(padded - w));
+            scan_pos += padded;
         }
-        memcpy(blob + off_scan + scan_pos, files[i] + p.scan_start, static_cast<size_t>(p.scan_end - p.scan_start));
-        scan_pos += p.scan_end - p.scan_start;
     }
+    if (max_seg_bits >= 0xFFFFFF00LL) { jerr(d, "an entropy-coded segment of 512 MiB or more"); return B2P_E_LIMIT; }
     memcpy(blob + off_tab, tables.data(), tables.size() * sizeof(HuffDev));
 
     // ---- device work, all on the caller's stream
@@ -811,13 +992,17 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
     const SegmentDev* segs_dev = reinterpret_cast<const SegmentDev*>(dev + off_seg);
     const HuffDev* tabs_dev = reinterpret_cast<const HuffDev*>(dev + off_tab);
     {
-        // few segments: one per warp (nothing else shares the warp's instruction stream); many: pack them
-        const int lane_stride = n_segments <= static_cast<int64_t>(d->num_sms) * 48 ? 32 : 1;
-        const int threads = lane_stride == 32 ? 64 : 128;
-        const int64_t total_threads = n_segments * lane_stride;
-        const int grid = static_cast<int>((total_threads + threads - 1) / threads);
-        huffman_kernel<<<grid, threads, 0, stream>>>(dev + off_scan, images_dev, segs_dev, tabs_dev, static_cast<int>(n_segments),
-                                                     lane_stride, d->coef, status);
+        // one CTA per restart segment, one chunk of at least `min_chunk` bits per thread
+        static const int min_chunk = [] {
+            const char* e = getenv("B2P_JPEG_CHUNK_BITS");
+            const int v = e ? atoi(e) : HUFF_MIN_CHUNK_BITS;
+            return v >= 64 ? (v + 31) / 32 * 32 : HUFF_MIN_CHUNK_BITS;
+        }();
+        int64_t want = (max_seg_bits + min_chunk - 1) / min_chunk;
+        want = (want + 31) / 32 * 32;
+        const int threads = static_cast<int>(want < 32 ? 32 : (want > HUFF_MAX_THREADS ? HUFF_MAX_THREADS : want));
+        huffman_kernel<<<static_cast<unsigned>(n_segments), threads, 0, stream>>>(dev + off_scan, images_dev, segs_dev, tabs_dev,
+                                                                                  d->coef, status, min_chunk);
         JPEG_CUDA(d, cudaGetLastError());
     }
     {

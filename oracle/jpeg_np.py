@@ -5,7 +5,7 @@ CPU restatement of the baseline-JPEG decode that sits immediately before the pre
 the pixels come from the third-party decoder behind that call).
 
 Third-party dependency carrying the arithmetic: Pillow 12.2.0 (unpinned in the reference's requirements.txt:8) with its
-bundled libjpeg-turbo.  This file restates libjpeg-turbo's *published* default decode pipeline:
+bundled libjpeg-turbo 3.1.4.1.  This file restates libjpeg-turbo's *published* default decode pipeline:
 
   * entropy decoding            — ITU-T T.81 Annex F.2.2 (jdhuff.c: decode_mcu_slow)
   * dequantisation + IDCT       — the accurate integer IDCT "islow" (jidctint.c: jpeg_idct_islow, CONST_BITS=13,

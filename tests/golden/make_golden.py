@@ -9,6 +9,9 @@ reference from /root/reference, which does not exist on the GPU box):
 2. aa_resize_vectors.npz — torch's F.interpolate(bilinear, antialias=True) + normalise (the oracle's P0)
    on seeded synthetic images, sub-sampled, plus float64 checksums of the full tensors.
 3. resnet18_logits.npz — oracle fp32 CPU logits / top-5 of ResNet-18 (seed 0) on seeded images.
+4. jpeg_vectors.npz — small JPEG files written by Pillow (4:2:0 / 4:2:2 / 4:4:4 / greyscale, odd sizes, restart
+   intervals, optimised tables) and the pixels Pillow itself decodes from them (`Image.open(f).convert('RGB')`,
+   the reference's decoder, model.py:23), Pillow + libjpeg-turbo versions recorded.
 """
 import io
 import json
@@ -107,7 +110,35 @@ def resnet18_logits():
     print("resnet18 logits", logits.shape, float(logits.abs().max()))
 
 
+def jpeg_vectors():
+    import PIL
+    from PIL import Image, ImageFile, features
+    from oracle import images
+    ImageFile.MAXBLOCK = 1 << 24
+    cases = [(21, 16, 16, dict(quality=90)), (22, 33, 47, dict(quality=75)),
+             (23, 33, 47, dict(quality=75, subsampling=0)), (24, 41, 30, dict(quality=60, subsampling=1)),
+             (25, 48, 64, dict(quality=85, restart_marker_blocks=3)), (26, 24, 100, dict(quality=30, optimize=True)),
+             (27, 37, 53, dict(quality=95, grey=True)), (28, 64, 64, dict(quality=100, subsampling=2))]
+    out = {}
+    meta = []
+    for seed, h, w, kw in cases:
+        kw = dict(kw)
+        grey = kw.pop("grey", False)
+        arr = images.synthetic_image(seed, h, w)
+        buf = io.BytesIO()
+        Image.fromarray(arr[..., 0] if grey else arr).save(buf, "JPEG", **kw)
+        data = buf.getvalue()
+        key = f"s{seed}_{h}x{w}"
+        out[key + "_file"] = np.frombuffer(data, np.uint8)
+        out[key + "_rgb"] = np.asarray(Image.open(io.BytesIO(data)).convert("RGB"))
+        meta.append({"key": key, "h": h, "w": w, "grey": grey, "save_args": kw, "bytes": len(data)})
+    note = f"Pillow {PIL.__version__}, libjpeg-turbo {features.version('libjpeg_turbo')}"
+    np.savez_compressed(os.path.join(HERE, "jpeg_vectors.npz"), meta=json.dumps(meta), note=note, **out)
+    print("jpeg vectors:", note, [m["key"] for m in meta])
+
+
 if __name__ == "__main__":
+    jpeg_vectors()
     aa_vectors()
     resnet18_logits()
     reference_contract()

@@ -90,6 +90,18 @@ def test_mixed_batch_matches_pillow_bit_for_bit(decoder):
         assert (host[o + i.width * i.height * 3:nxt] == 0xAB).all()
 
 
+def test_committed_golden_vectors(decoder):
+    import json
+    import os
+    z = np.load(os.path.join(os.path.dirname(__file__), "golden", "jpeg_vectors.npz"))
+    meta = json.loads(str(z["meta"]))
+    files = [z[m["key"] + "_file"].tobytes() for m in meta]
+    outs, status, *_ = _decode_batch(decoder, files)
+    assert (status == 0).all()
+    for m, got in zip(meta, outs):
+        assert np.array_equal(got, z[m["key"] + "_rgb"]), m
+
+
 def test_two_calls_in_a_row_reuse_the_workspace(decoder):
     a = [_encode(_picture(96, 128, seed=s), quality=80) for s in range(4)]
     b = [_encode(_picture(64, 48, seed=10 + s), quality=95, subsampling=0) for s in range(7)]
