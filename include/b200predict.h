@@ -217,9 +217,15 @@ typedef struct b2p_jpeg_info {
  * b2p_jpeg_last_error(NULL).                                                                            */
 int32_t b2p_jpeg_inspect(const uint8_t* file, int64_t len, b2p_jpeg_info* info);
 
+typedef struct b2p_jpeg_stats {
+    float ms_copy, ms_huffman, ms_idct, ms_colour;   /* CUDA-event times of the most recent b2p_jpeg_decode  */
+    int64_t calls;
+} b2p_jpeg_stats;
+
 int32_t b2p_jpeg_create(int32_t device, b2p_jpeg** out);
 int32_t b2p_jpeg_destroy(b2p_jpeg* d);
 const char* b2p_jpeg_last_error(const b2p_jpeg* d);   /* d may be NULL: inspect / create failures   */
+int32_t b2p_jpeg_stats_get(b2p_jpeg* d, b2p_jpeg_stats* out);   /* waits for the most recent call       */
 
 /* Decodes n files (HOST pointers, any memory) into the DEVICE slab: image i becomes uint8 [h][w][3] at
  * slab + offsets[i], ready to be described by a b2p_image and handed to b2p_preprocess / b2p_predict on

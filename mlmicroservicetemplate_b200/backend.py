@@ -77,6 +77,11 @@ class JpegInfo(C.Structure):
     ]
 
 
+class JpegStats(C.Structure):
+    _fields_ = [("ms_copy", C.c_float), ("ms_huffman", C.c_float), ("ms_idct", C.c_float), ("ms_colour", C.c_float),
+                ("calls", C.c_int64)]
+
+
 E_UNSUPPORTED = -6
 
 # every symbol include/b200predict.h declares: (name, restype, argtypes)
@@ -99,6 +104,7 @@ SYMBOLS = [
     ("b2p_jpeg_create", C.c_int32, [C.c_int32, C.POINTER(C.c_void_p)]),
     ("b2p_jpeg_destroy", C.c_int32, [C.c_void_p]),
     ("b2p_jpeg_last_error", C.c_char_p, [C.c_void_p]),
+    ("b2p_jpeg_stats_get", C.c_int32, [C.c_void_p, C.POINTER(JpegStats)]),
     ("b2p_jpeg_decode", C.c_int32, [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_int64), C.c_int32, C.c_void_p,
                                     C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p]),
 ]
@@ -180,6 +186,13 @@ class JpegDecoder:
                                       Replica._ptr(status) if status is not None else None, Replica._stream(stream))
         if rc != 0:
             raise B2PError(rc, (self.lib.b2p_jpeg_last_error(self.h) or b"").decode())
+
+    def stats(self) -> JpegStats:
+        st = JpegStats()
+        rc = self.lib.b2p_jpeg_stats_get(self.h, C.byref(st))
+        if rc != 0:
+            raise B2PError(rc, "b2p_jpeg_stats_get")
+        return st
 
     def close(self) -> None:
         if self.h:

@@ -110,30 +110,20 @@ struct BitReader {
     __device__ __forceinline__ void skip(int bits) { win <<= bits; have -= bits; }
 };
 
-// One Huffman symbol (jdhuff.c: HUFF_DECODE): 9-bit lookahead table, then the canonical length walk.
-__device__ __forceinline__ int huff_symbol(BitReader& br, const HuffDev* __restrict__ t, int& bad) {
-    const uint32_t e = __ldg(&t->look[br.peek(LOOK_BITS)]);
-    if (e != 0u) {
-        br.skip(static_cast<int>(e >> 8));
-        return static_cast<int>(e & 255u);
-    }
+// The rare long code (more than LOOK_BITS bits): canonical length walk over the table in global memory
+// (jdhuff.c: jpeg_huff_decode).  Returns (length << 8) | symbol.
+__device__ __noinline__ uint32_t huff_long_code(uint64_t win, const HuffDev* __restrict__ t, int& bad) {
     int len = LOOK_BITS + 1;
-    int code = static_cast<int>(br.peek(len));
+    int code = static_cast<int>(win >> (64 - len));
     while (len <= 16 && code > __ldg(&t->maxcode[len])) {
         ++len;
-        code = static_cast<int>(br.peek(len));
+        code = static_cast<int>(win >> (64 - len));
     }
     if (len > 16) {
         bad = 1;
-        br.skip(16);
-        return 0;
+        return 16u << 8;
     }
-    br.skip(len);
-    return __ldg(&t->vals[(code + __ldg(&t->valoff[len])) & 255]);
-}
-
-__device__ __forceinline__ int huff_extend(uint32_t v, int s) {
-    return v < (1u << (s - 1)) ? static_cast<int>(v) - (1 << s) + 1 : static_cast<int>(v);
+    return (static_cast<uint32_t>(len) << 8) | __ldg(&t->vals[(code + __ldg(&t->valoff[len])) & 255]);
 }
 
 struct DecodeState {
@@ -153,6 +143,8 @@ struct SegmentCtx {
     uint32_t nbits;
     const uint32_t* __restrict__ words;
     uint32_t nwords;
+    const uint16_t* look;       // shared memory: [component][0 = DC, 1 = AC][512] lookahead entries
+    const uint8_t* zigzag;      // shared memory copy of c_zigzag (divergent indices serialise in the constant cache)
 };
 
 // Address of block `b` (segment-relative, decode order) in the coefficient planes.
@@ -194,38 +186,32 @@ __device__ __forceinline__ void decode_range(const SegmentCtx& c, DecodeState& s
         if (b >= c.total_blocks) return;
         out = block_ptr(c, coef, b, comp);
     }
-    const HuffDev* __restrict__ dct = c.tables + c.im->dc_tab[comp];
-    const HuffDev* __restrict__ act = c.tables + c.im->ac_tab[comp];
     uint32_t pos = st.pos;
+    // The 32 lanes of a warp walk 32 different pieces of the stream, so the loop body is written with selects
+    // instead of branches wherever the two sides are short: DC and AC symbols take the same path.
     while (pos < end_bit) {
         br.refill();
-        if (k == 0) {
-            const int s = huff_symbol(br, dct, bad) & 15;
-            if (s) {
-                if (WRITE) out[0] = static_cast<int16_t>(huff_extend(br.peek(s), s));
-                br.skip(s);
-            }
-            k = 1;
-        } else {
-            const int rs = huff_symbol(br, act, bad);
-            const int r = rs >> 4, s = rs & 15;
-            if (s) {
-                k += r;
-                if (WRITE) out[c_zigzag[k]] = static_cast<int16_t>(huff_extend(br.peek(s), s));
-                br.skip(s);
-                ++k;
-            } else {
-                k = r == 15 ? k + 16 : 64;
-            }
+        const bool is_dc = k == 0;
+        uint32_t e = c.look[(comp * 2 + (is_dc ? 0 : 1)) * (1 << LOOK_BITS) + br.peek(LOOK_BITS)];
+        if (e == 0u) {
+            const HuffDev* __restrict__ t = c.tables + (is_dc ? c.im->dc_tab[comp] : c.im->ac_tab[comp]);
+            e = huff_long_code(br.win, t, bad);
         }
+        br.skip(static_cast<int>(e >> 8));
+        const int s = static_cast<int>(e & 15u);
+        const int r = is_dc ? 0 : static_cast<int>((e >> 4) & 15u);
+        const uint32_t raw = static_cast<uint32_t>((br.win >> 1) >> (63 - s));          // s == 0 -> 0
+        const int v = raw < (1u << ((s - 1) & 31)) ? static_cast<int>(raw) - (1 << s) + 1 : static_cast<int>(raw);
+        br.skip(s);
+        const int kk = k + r;                                   // zig-zag position of this coefficient
+        if (WRITE && s != 0) out[c.zigzag[kk]] = static_cast<int16_t>(v);
+        k = s != 0 ? kk + 1 : (is_dc ? 1 : (r == 15 ? k + 16 : 64));
         pos = br.position();
         if (k >= 64) {                       // block complete
             k = 0;
             ++done;
             if (++blk == c.bpm) blk = 0;
             comp = blk < c.luma ? 0 : blk - c.luma + 1;
-            dct = c.tables + c.im->dc_tab[comp];
-            act = c.tables + c.im->ac_tab[comp];
             if (WRITE) {
                 if (++b >= c.total_blocks) {
                     if (pos > c.nbits) overrun = 1;      // the last block needed bits the file does not have
@@ -269,15 +255,27 @@ __device__ __forceinline__ int cta_exclusive_scan(int v, int* s_warp, int& total
 __global__ void __launch_bounds__(HUFF_MAX_THREADS)
 huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ images,
                const SegmentDev* __restrict__ segments, const HuffDev* __restrict__ tables,
-               int16_t* __restrict__ coef, int32_t* __restrict__ status, int min_chunk_bits) {
+               int16_t* __restrict__ coef, int32_t* __restrict__ status, int min_chunk_bits, int debug_rounds) {
     __shared__ uint32_t s_pos[HUFF_MAX_THREADS];
     __shared__ int s_state[HUFF_MAX_THREADS];        // blk << 8 | k
     __shared__ int s_warp[HUFF_MAX_THREADS / 32];
+    __shared__ uint16_t s_look[3 * 2 << LOOK_BITS];
+    __shared__ uint8_t s_zigzag[80];
     const SegmentDev sg = segments[blockIdx.x];
     const int t = threadIdx.x, P = blockDim.x;
     SegmentCtx c;
     c.im = images + sg.image;
     c.tables = tables;
+    c.look = s_look;
+    c.zigzag = s_zigzag;
+    for (int i = t; i < c.im->ncomp * 2 * (1 << LOOK_BITS) / 2; i += P) {       // 32-bit copies, two entries each
+        const int tab = i / (1 << (LOOK_BITS - 1));                               // component * 2 + (0 DC, 1 AC)
+        const int w = i - tab * (1 << (LOOK_BITS - 1));
+        const HuffDev* src = tables + ((tab & 1) ? c.im->ac_tab[tab >> 1] : c.im->dc_tab[tab >> 1]);
+        reinterpret_cast<uint32_t*>(s_look)[i] = __ldg(reinterpret_cast<const uint32_t*>(src->look) + w);
+    }
+    for (int i = t; i < 80; i += P) s_zigzag[i] = c_zigzag[i];
+    __syncthreads();
     c.hs = c.im->hs;
     c.luma = c.im->hs * c.im->vs;
     c.bpm = c.im->ncomp == 1 ? 1 : c.luma + 2;
@@ -297,7 +295,8 @@ huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ im
     DecodeState out = in;
     int blocks = 0, bad = 0, overrun = 0;
     bool dirty = true;
-    for (int round = 0; round <= P; ++round) {
+    int round = 0;
+    for (; round <= P; ++round) {
         if (dirty) {
             out = in;
             blocks = 0;
@@ -317,6 +316,8 @@ huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ im
         in = want;
         if (!__syncthreads_or(dirty ? 1 : 0)) break;
     }
+
+    if (debug_rounds && status && t == 0) atomicMax(status + sg.image, (round + 1) << 8);   // measurement aid only
 
     // ---- 3: index of each thread's first block, then the decode that writes
     int total = 0;
@@ -738,6 +739,9 @@ struct b2p_jpeg {
     int64_t coef_cap = 0;         // bytes
     uint8_t* planes = nullptr;    // component sample planes
     int64_t planes_cap = 0;
+    cudaEvent_t ev[5] = {};       // around the copy and each kernel of the most recent call
+    bool ev_valid = false;
+    int64_t calls = 0;
 };
 
 namespace {
@@ -809,7 +813,27 @@ int32_t b2p_jpeg_create(int32_t device, b2p_jpeg** out) {
             return B2P_E_CUDA;
         }
     }
+    for (auto& e : d->ev) {
+        if (cudaEventCreate(&e) != cudaSuccess) {
+            jerr(nullptr, "cudaEventCreate failed");
+            delete d;
+            return B2P_E_CUDA;
+        }
+    }
     *out = d;
+    return B2P_OK;
+}
+
+int32_t b2p_jpeg_stats_get(b2p_jpeg* d, b2p_jpeg_stats* out) {
+    if (!d || !out) return B2P_E_ARG;
+    memset(out, 0, sizeof *out);
+    out->calls = d->calls;
+    if (!d->ev_valid) return B2P_OK;
+    if (cudaEventSynchronize(d->ev[4]) != cudaSuccess) return B2P_E_CUDA;
+    cudaEventElapsedTime(&out->ms_copy, d->ev[0], d->ev[1]);
+    cudaEventElapsedTime(&out->ms_huffman, d->ev[1], d->ev[2]);
+    cudaEventElapsedTime(&out->ms_idct, d->ev[2], d->ev[3]);
+    cudaEventElapsedTime(&out->ms_colour, d->ev[3], d->ev[4]);
     return B2P_OK;
 }
 
@@ -822,6 +846,8 @@ int32_t b2p_jpeg_destroy(b2p_jpeg* d) {
         if (d->blob_dev[i]) cudaFree(d->blob_dev[i]);
         if (d->copied[i]) cudaEventDestroy(d->copied[i]);
     }
+    for (auto& e : d->ev)
+        if (e) cudaEventDestroy(e);
     if (d->coef) cudaFree(d->coef);
     if (d->planes) cudaFree(d->planes);
     delete d;
@@ -983,11 +1009,13 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
 
     // ---- device work, all on the caller's stream
     uint8_t* dev = d->blob_dev[slot];
+    JPEG_CUDA(d, cudaEventRecord(d->ev[0], stream));
     JPEG_CUDA(d, cudaMemcpyAsync(dev, blob, static_cast<size_t>(blob_bytes), cudaMemcpyHostToDevice, stream));
     JPEG_CUDA(d, cudaEventRecord(d->copied[slot], stream));
     d->used[slot] = true;
     JPEG_CUDA(d, cudaMemsetAsync(d->coef, 0, static_cast<size_t>(coef_bytes), stream));
     if (status) JPEG_CUDA(d, cudaMemsetAsync(status, 0, static_cast<size_t>(n) * sizeof(int32_t), stream));
+    JPEG_CUDA(d, cudaEventRecord(d->ev[1], stream));
     const ImageDev* images_dev = reinterpret_cast<const ImageDev*>(dev + off_img);
     const SegmentDev* segs_dev = reinterpret_cast<const SegmentDev*>(dev + off_seg);
     const HuffDev* tabs_dev = reinterpret_cast<const HuffDev*>(dev + off_tab);
@@ -1002,19 +1030,25 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
         want = (want + 31) / 32 * 32;
         const int threads = static_cast<int>(want < 32 ? 32 : (want > HUFF_MAX_THREADS ? HUFF_MAX_THREADS : want));
         huffman_kernel<<<static_cast<unsigned>(n_segments), threads, 0, stream>>>(dev + off_scan, images_dev, segs_dev, tabs_dev,
-                                                                                  d->coef, status, min_chunk);
+                                                                                  d->coef, status, min_chunk,
+                                                                                  getenv("B2P_JPEG_DEBUG_ROUNDS") != nullptr);
         JPEG_CUDA(d, cudaGetLastError());
+        JPEG_CUDA(d, cudaEventRecord(d->ev[2], stream));
     }
     {
         dim3 grid(static_cast<unsigned>((max_blocks + 127) / 128), static_cast<unsigned>(n));
         idct_kernel<<<grid, 128, 0, stream>>>(images_dev, d->coef, d->planes);
         JPEG_CUDA(d, cudaGetLastError());
+        JPEG_CUDA(d, cudaEventRecord(d->ev[3], stream));
     }
     {
         dim3 grid(static_cast<unsigned>((max_quads + 255) / 256), static_cast<unsigned>(n));
         colour_kernel<<<grid, 256, 0, stream>>>(images_dev, d->planes, slab);
         JPEG_CUDA(d, cudaGetLastError());
+        JPEG_CUDA(d, cudaEventRecord(d->ev[4], stream));
     }
+    d->ev_valid = true;
+    ++d->calls;
     return B2P_OK;
 }
 

@@ -7,6 +7,9 @@ a batcher thread groups requests (up to MAX_BATCH, or whatever arrived within MA
 first one) and hands whole batches round-robin to one worker thread per GPU.  A worker copies the
 batch into its pinned host slab and makes ONE call into the C ABI (b2p_predict_host): H2D copy,
 K1 preprocess, K2 forward, K3 softmax/top-k and the D2H copy of k (prob, index) pairs per image.
+Uploads that are baseline JPEGs can skip the host decoder altogether (JpegFile): their bytes are
+decoded by b2p_jpeg_decode straight into the device slab and the device-resident chain (b2p_predict)
+runs on it.
 
 The path shards by request: replicas are independent, no tensor crosses GPUs, so there is no
 collective anywhere.
@@ -48,8 +51,21 @@ def image_geometry(h: int, w: int, mode: str) -> Tuple[int, int, int, int]:
 
 
 @dataclass
+class JpegFile:
+    """An upload the GPU decoder covers (b2p_jpeg_inspect said yes): the file bytes travel to the device as they
+    are and the pixels first exist in HBM.  Everything else reaches the engine as decoded uint8 HWC pixels."""
+    data: bytes
+    height: int
+    width: int
+
+
+class CorruptImage(ValueError):
+    """The entropy-coded data of one upload was damaged (the GPU decoder's status word was non-zero)."""
+
+
+@dataclass
 class _Request:
-    image: np.ndarray
+    image: object                      # np.ndarray (uint8 HWC) or JpegFile
     future: Future
     t_enqueue: float = field(default_factory=time.perf_counter)
 
@@ -76,6 +92,25 @@ class GpuReplicaWorker:
             self.probs = torch.empty((max_batch, topk), dtype=torch.float32, pin_memory=True)
             self.idx = torch.empty((max_batch, topk), dtype=torch.int32, pin_memory=True)
         self.slab_np = self.slab.numpy()
+        # GPU JPEG decode (created on first use): decoder object, device slab, device result buffers
+        self.jpeg = None
+        self.dev_slab = None
+        self.dev_status = None
+        self.dev_probs = None
+        self.dev_idx = None
+        self.status_host = None
+
+    def _ensure_jpeg(self, nbytes: int) -> None:
+        torch = self.torch
+        if self.jpeg is None:
+            self.jpeg = self.B.JpegDecoder(self.device)
+            self.dev_status = torch.zeros(self.max_batch, dtype=torch.int32, device=f"cuda:{self.device}")
+            self.dev_probs = torch.empty((self.max_batch, self.topk), dtype=torch.float32, device=f"cuda:{self.device}")
+            self.dev_idx = torch.empty((self.max_batch, self.topk), dtype=torch.int32, device=f"cuda:{self.device}")
+            self.status_host = torch.zeros(self.max_batch, dtype=torch.int32, pin_memory=True)
+        if self.dev_slab is None or nbytes > self.dev_slab.numel():
+            self.stream.synchronize()
+            self.dev_slab = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=f"cuda:{self.device}")
 
     def _ensure_slab(self, nbytes: int) -> None:
         if nbytes > self.slab.numel():
@@ -87,24 +122,56 @@ class GpuReplicaWorker:
         n = len(images)
         if n == 0 or n > self.max_batch:
             raise ValueError(f"batch of {n} outside 1..{self.max_batch}")
-        offs, total = [], 0
+        offs, shapes, total = [], [], 0
         for im in images:
-            if im.dtype != np.uint8 or im.ndim != 3 or im.shape[2] != 3:
-                raise ValueError("images must be uint8 HWC with 3 channels")
+            if isinstance(im, JpegFile):
+                h, w = im.height, im.width
+            else:
+                if im.dtype != np.uint8 or im.ndim != 3 or im.shape[2] != 3:
+                    raise ValueError("images must be uint8 HWC with 3 channels")
+                h, w = im.shape[0], im.shape[1]
             offs.append(total)
-            total += (im.size + 255) // 256 * 256
-        self._ensure_slab(total)
-        geoms = []
-        for im, o in zip(images, offs):
-            self.slab_np[o:o + im.size] = im.reshape(-1)
-            geoms.append((o, im.shape[0], im.shape[1], *image_geometry(im.shape[0], im.shape[1], self.mode)))
+            shapes.append((h, w))
+            total += (h * w * 3 + 255) // 256 * 256
+        geoms = [(o, h, w, *image_geometry(h, w, self.mode)) for o, (h, w) in zip(offs, shapes)]
         descs = self.B.make_images(geoms)
-        with self.torch.cuda.device(self.device):
-            self.replica.predict_host(self.slab, total, descs, n, self.topk, self.probs, self.idx, stream=self.stream)
+        jpeg_items = [i for i, im in enumerate(images) if isinstance(im, JpegFile)]
+        host_items = [i for i, im in enumerate(images) if not isinstance(im, JpegFile)]
+        if host_items:
+            self._ensure_slab(total)
+            for i in host_items:
+                self.slab_np[offs[i]:offs[i] + images[i].size] = images[i].reshape(-1)
+        if not jpeg_items:
+            with self.torch.cuda.device(self.device):
+                self.replica.predict_host(self.slab, total, descs, n, self.topk, self.probs, self.idx, stream=self.stream)
+                self.stream.synchronize()
+            return self.probs[:n].numpy().copy(), self.idx[:n].numpy().copy()
+        # At least one file is decoded on the GPU: the batch slab lives in HBM.  Host-decoded images are copied
+        # into it, JPEG files are decoded into it (K-J1..J3), then the device-resident predict chain runs.
+        torch = self.torch
+        with torch.cuda.device(self.device), torch.cuda.stream(self.stream):
+            self._ensure_jpeg(total)
+            if host_items:
+                lo = min(offs[i] for i in host_items)
+                hi = max(offs[i] + shapes[i][0] * shapes[i][1] * 3 for i in host_items)
+                self.dev_slab[lo:hi].copy_(self.slab[lo:hi], non_blocking=True)
+            self.jpeg.decode([images[i].data for i in jpeg_items], self.dev_slab, self.dev_slab.numel(),
+                             [offs[i] for i in jpeg_items], status=self.dev_status, stream=self.stream)
+            self.replica.predict(self.dev_slab, descs, n, self.topk, self.dev_probs, self.dev_idx, stream=self.stream)
+            self.probs[:n].copy_(self.dev_probs[:n], non_blocking=True)
+            self.idx[:n].copy_(self.dev_idx[:n], non_blocking=True)
+            self.status_host[:len(jpeg_items)].copy_(self.dev_status[:len(jpeg_items)], non_blocking=True)
             self.stream.synchronize()
-        return self.probs[:n].numpy().copy(), self.idx[:n].numpy().copy()
+        errors = {}
+        st = self.status_host[:len(jpeg_items)].numpy()
+        for j, i in enumerate(jpeg_items):
+            if st[j]:
+                errors[i] = CorruptImage(f"JPEG entropy-coded data is damaged (decoder status {int(st[j])})")
+        return self.probs[:n].numpy().copy(), self.idx[:n].numpy().copy(), errors
 
     def close(self) -> None:
+        if self.jpeg is not None:
+            self.jpeg.close()
         self.replica.close()
 
 
@@ -130,7 +197,7 @@ class Engine:
             t.start()
 
     # ---- client side
-    def submit(self, image: np.ndarray) -> Future:
+    def submit(self, image) -> Future:
         if self._closed:
             raise RuntimeError("engine is shut down")
         fut: Future = Future()
@@ -178,9 +245,14 @@ class Engine:
             if batch is None:
                 break
             try:
-                probs, idx = worker.run_batch([r.image for r in batch])
+                out = worker.run_batch([r.image for r in batch])
+                probs, idx = out[0], out[1]
+                errors = out[2] if len(out) > 2 else {}      # per-image failures do not fail the whole batch
                 for j, r in enumerate(batch):
-                    r.future.set_result((probs[j], idx[j]))
+                    if j in errors:
+                        r.future.set_exception(errors[j])
+                    else:
+                        r.future.set_result((probs[j], idx[j]))
             except BaseException as e:          # propagate to every waiter: predict() re-raises -> HTTP 500
                 for r in batch:
                     if not r.future.done():

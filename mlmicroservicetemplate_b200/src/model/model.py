@@ -17,6 +17,9 @@ Environment knobs (defaults in brackets):
     GPUS  [all]         comma-separated device indices
     MAX_BATCH [64]  MAX_WAIT_US [2000]  TOPK [5]  SEED [0]  PREPROCESS [preset] (preset | direct)
     SUB_BATCH [0]       images per L2-resident pass of the layer program (0 = whole batch)
+    DECODE [gpu]        gpu: uploads that are baseline JPEGs (b2p_jpeg_inspect) are decoded on the GPU, bit-exact
+                        with Pillow; everything else (PNG, progressive / CMYK JPEG, ...) is decoded by Pillow
+                        as in the reference.  host: every upload goes through Pillow.
 """
 from __future__ import annotations
 
@@ -30,7 +33,7 @@ from fastapi import File, UploadFile
 from PIL import Image
 
 _lock = threading.Lock()
-_state = {"engine": None, "classes": None, "arch": None, "decode_pool": None}
+_state = {"engine": None, "classes": None, "arch": None, "decode_pool": None, "decode": "host"}
 
 TEMPLATE_RESULT = {
     'classes': ['isGreen', 'isRed'],
@@ -62,6 +65,7 @@ def init() -> None:
             mode=os.getenv("PREPROCESS", "preset"), seed=int(os.getenv("SEED", "0")),
             sub_batch=int(os.getenv("SUB_BATCH", "0")))
         _state["engine"] = engine
+        _state["decode"] = os.getenv("DECODE", "gpu")
         _state["classes"] = class_names(n_classes)
         _state["decode_pool"] = ThreadPoolExecutor(max_workers=int(os.getenv("DECODE_THREADS", str(os.cpu_count() or 4))))
 
@@ -72,14 +76,25 @@ def shutdown() -> None:
         eng, _state["engine"] = _state["engine"], None
         pool, _state["decode_pool"] = _state["decode_pool"], None
         _state["arch"] = None
+        _state["decode"] = "host"
     if eng is not None:
         eng.close()
     if pool is not None:
         pool.shutdown(wait=False)
 
 
-def _decode(fileobj) -> np.ndarray:
-    """Stage D: host decode to uint8 HWC (any PIL-readable mode is converted to RGB)."""
+def _decode(fileobj):
+    """Stage D.  With DECODE=gpu a baseline JPEG is only header-checked here and handed on as bytes (the GPU
+    decodes it); any other PIL-readable file is decoded on the host to uint8 HWC RGB, as the reference would."""
+    if _state.get("decode") == "gpu":
+        from ... import backend
+        from ...runtime import JpegFile
+        data = fileobj.read()
+        info = backend.jpeg_inspect(data)
+        if info is not None:
+            return JpegFile(data, info.height, info.width)
+        import io
+        fileobj = io.BytesIO(data)
     image = Image.open(fileobj)
     return np.asarray(image.convert('RGB'))
 

@@ -90,6 +90,17 @@ def test_mixed_batch_matches_pillow_bit_for_bit(decoder):
         assert (host[o + i.width * i.height * 3:nxt] == 0xAB).all()
 
 
+@pytest.mark.parametrize("size,kw", [((16, 16), dict(quality=50)), ((24, 40), dict(quality=95, subsampling=0)),
+                                     ((64, 64), dict(quality=90)), ((200, 300), dict(quality=92, subsampling=1))])
+def test_single_image_batches(decoder, size, kw):
+    """One file per call: the Huffman kernel then runs with the smallest CTAs (32 threads for a tiny file), so the
+    table staging and the chunking are exercised at every CTA size, not only the 1024-thread one of a mixed batch."""
+    f = _encode(_picture(*size, seed=7), **kw)
+    outs, status, *_ = _decode_batch(decoder, [f])
+    assert status[0] == 0
+    assert np.array_equal(outs[0], _pillow(f))
+
+
 def test_committed_golden_vectors(decoder):
     import json
     import os

@@ -90,3 +90,41 @@ def test_blocking_predict_and_error_paths(live_server):
         buf = io.BytesIO()
         Image.new(mode, (260, 300), 128).save(buf, format="PNG")
         assert client.post("/predict", files={"image_file": ("x.png", buf.getvalue(), "image/png")}).status_code == 200
+
+
+def test_gpu_decoded_and_host_decoded_uploads_give_identical_answers(cuda_device):
+    """DECODE=gpu must not change a single bit of the answer: the same JPEG files go through the engine once as
+    bytes (decoded by b2p_jpeg_decode into the device slab) and once as Pillow-decoded pixels (host slab + H2D)."""
+    from PIL import Image
+    from mlmicroservicetemplate_b200 import backend as B, runtime as R
+    from oracle import images
+    engine, _ = R.build_gpu_engine("resnet18", [0], max_batch=16, max_wait_us=50000, topk=5, mode="preset", seed=0)
+    try:
+        files = []
+        for i, (h, w, sub) in enumerate([(224, 224, 2), (300, 400, 2), (256, 256, 0), (480, 640, 1), (333, 517, 2),
+                                          (231, 229, 2), (720, 1280, 2), (224, 224, 0)]):
+            buf = io.BytesIO()
+            Image.fromarray(images.synthetic_image(700 + i, h, w)).save(buf, "JPEG", quality=88, subsampling=sub)
+            files.append(buf.getvalue())
+        infos = [B.jpeg_inspect(f) for f in files]
+        assert all(i is not None for i in infos)
+        as_bytes = engine.predict_many([R.JpegFile(f, i.height, i.width) for f, i in zip(files, infos)])
+        as_pixels = engine.predict_many([np.asarray(Image.open(io.BytesIO(f)).convert("RGB")) for f in files])
+        for (pa, ia), (pb, ib) in zip(as_bytes, as_pixels):
+            assert np.array_equal(ia, ib) and np.array_equal(pa, pb)
+        # a mixed batch: GPU-decoded files next to host-decoded pixels, plus one damaged file that must fail alone
+        hd_cut = files[1][:len(files[1]) // 2] + b"\xff\xd9"
+        info_cut = B.jpeg_inspect(hd_cut)
+        assert info_cut is not None
+        mixed = [R.JpegFile(files[0], infos[0].height, infos[0].width),
+                 np.asarray(Image.open(io.BytesIO(files[2])).convert("RGB")),
+                 R.JpegFile(hd_cut, info_cut.height, info_cut.width),
+                 R.JpegFile(files[4], infos[4].height, infos[4].width)]
+        futs = [engine.submit(m) for m in mixed]
+        for j, want in ((0, 0), (1, 2), (3, 4)):
+            p, i = futs[j].result(timeout=60)
+            assert np.array_equal(i, as_pixels[want][1]) and np.array_equal(p, as_pixels[want][0])
+        with pytest.raises(R.CorruptImage):
+            futs[2].result(timeout=60)
+    finally:
+        engine.close()
