@@ -128,11 +128,38 @@ def cpu_reference_run(steps: int, warmup: int, budget_s: float, sample_batch: in
             "ms_per_step": 1e3 * statistics.median(times), "steps": len(times)}
 
 
+def host_decode_run(budget_s: float = 3.0):
+    """The reference's own decoder (Pillow, src/model/model.py:23) on the 256 JPEG files of the workload, all cores."""
+    import io
+    from concurrent.futures import ThreadPoolExecutor
+    import numpy as np
+    from PIL import Image
+    files = []
+    for im in make_batch(1):
+        buf = io.BytesIO()
+        Image.fromarray(im).save(buf, "JPEG", quality=90)
+        files.append(buf.getvalue())
+    cores = os.cpu_count() or 1
+
+    def one(f):
+        return np.asarray(Image.open(io.BytesIO(f)).convert("RGB"))
+    with ThreadPoolExecutor(cores) as ex:
+        list(ex.map(one, files[:32]))
+        t0 = time.perf_counter()
+        n = 0
+        while time.perf_counter() - t0 < budget_s:
+            list(ex.map(one, files))
+            n += len(files)
+        dt = time.perf_counter() - t0
+    return {"value": n / dt, "unit": "images/s", "cores": cores, "what": "Pillow decode of the 224x224 q90 JPEG files"}
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     r = cpu_reference_run(args.steps, args.warmup, budget_s=120.0, sample_batch=32)
+    hd = host_decode_run()
     line = {
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": "images/s", "n_gpus": args.gpus,
         "steps": r["steps"], "warmup": 1, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
@@ -141,6 +168,9 @@ def run_reference_arm(args):
                    "note": "reference predict() has no arithmetic; this is its contract filled in on CPU (oracle)"},
         "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": r["value"], "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "host_decode": hd,
+        "e2e_from_jpeg": {"value": 1.0 / (1.0 / r["value"] + 1.0 / hd["value"]), "unit": "images/s",
+                          "what": "Pillow decode then the CPU predict, both on all host cores, back to back"},
         "gpu_launches": 0,
     }
     print(json.dumps(line))
@@ -261,6 +291,48 @@ def main():
     stage = rep.stats()
     checksum = float(probs_h.sum().item())          # the D2H result is really read on the host
 
+    # ---------------------------------------------------------------- end to end from JPEG FILES (`e2e_from_jpeg`)
+    # The step before the path: the batch arrives as JPEG files in host memory, is decoded on the
+    # GPU (b2p_jpeg_decode: Huffman + IDCT + upsample/colour kernels) into the device slab, then K1-K3 run on it.
+    import io as _io
+    from PIL import Image as _Image
+    files = []
+    for im in base:
+        buf = _io.BytesIO()
+        _Image.fromarray(im).save(buf, "JPEG", quality=90)
+        files.append(buf.getvalue())
+    dec = B.JpegDecoder(local_rank)
+    jslab = torch.empty(slab_bytes, dtype=torch.uint8, device="cuda")
+    jstatus = torch.zeros(BATCH, dtype=torch.int32, device="cuda")
+    joffs = [i * stride for i in range(BATCH)]
+    rotated = [files[s:] + files[:s] for s in range(POOL_SLABS)]
+
+    def step_jpeg(i):
+        dec.decode(rotated[i % POOL_SLABS], jslab, slab_bytes, joffs, status=jstatus, stream=stream)
+        rep.predict(jslab, descs, BATCH, TOPK, probs, idx, stream=stream)
+        with torch.cuda.stream(stream):
+            probs_h.copy_(probs, non_blocking=True)
+            idx_h.copy_(idx, non_blocking=True)
+
+    for i in range(W):
+        step_jpeg(i)
+    stream.synchronize()
+    ref_px = np.asarray(_Image.open(_io.BytesIO(rotated[(W - 1) % POOL_SLABS][0])).convert("RGB"))
+    jpeg_exact = bool(np.array_equal(jslab[:per_img].cpu().numpy().reshape(IMG, IMG, 3), ref_px)) and int(jstatus.abs().sum().item()) == 0
+    barrier()
+    j0, j1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    j0.record(stream)
+    for i in range(K):
+        step_jpeg(i)
+    j1.record(stream)
+    barrier()
+    jpeg_ms = max_over_ranks(j0.elapsed_time(j1))
+    jpeg_value = world * BATCH * K / (jpeg_ms * 1e-3)
+    jst = dec.stats()
+    jpeg_file_bytes = sum(len(f) for f in files)
+    jpeg_checksum = float(probs_h.sum().item())
+    dec.close()
+
     # per-batch latency (submit -> results on the host), synchronising every step
     lat = []
     for i in range(min(K, 30)):
@@ -305,6 +377,13 @@ def main():
                     "d2h_bytes_per_step": BATCH * TOPK * 8, "ms_per_step": e2e_ms / K,
                     "stages_ms_last_call": {k: stage[k] for k in ("ms_h2d", "ms_preprocess", "ms_forward", "ms_epilogue", "ms_d2h")},
                     "api": "b2p_predict_host (pinned host slab in, pinned probs/idx out)", "checksum": checksum},
+            "e2e_from_jpeg": {"value": jpeg_value, "unit": "images/s", "ms_per_step": jpeg_ms / K,
+                              "h2d_bytes_per_step": jpeg_file_bytes, "d2h_bytes_per_step": BATCH * TOPK * 8,
+                              "decode_ms_last_call": {"copy": jst.ms_copy, "huffman": jst.ms_huffman, "idct": jst.ms_idct,
+                                                      "colour": jst.ms_colour},
+                              "decoded_pixels_bit_exact_vs_pillow": jpeg_exact, "checksum": jpeg_checksum,
+                              "api": "b2p_jpeg_decode (JPEG files in host memory -> device slab) + b2p_predict + D2H",
+                              "files": f"{BATCH} x {IMG}x{IMG} quality 90 4:2:0, {jpeg_file_bytes / BATCH:.0f} B each"},
             "latency_ms": {"p50": lat[len(lat) // 2], "p99": lat[min(len(lat) - 1, int(len(lat) * 0.99))], "n": len(lat),
                            "what": "one 256-image batch, host slab -> host results, per GPU"},
             "gpu_launches": int(launches_per_run),

@@ -26,10 +26,10 @@
 namespace {
 
 // ------------------------------------------------------------------------------------------- shared layouts
-constexpr int LOOK_BITS = 9;
+constexpr int LOOK_BITS = 11;
 
 struct HuffDev {                  // one Huffman table in decode form
-    uint16_t look[1 << LOOK_BITS];  // (code length << 8) | symbol for codes of <= 9 bits, 0 = longer
+    uint16_t look[1 << LOOK_BITS];  // (code length << 8) | symbol for codes of <= LOOK_BITS bits, 0 = longer
     int32_t maxcode[18];            // largest code of length l (l = 1..16), -1 if none; [17] = sentinel
     int32_t valoff[18];             // index of the first symbol of length l minus its smallest code
     uint8_t vals[256];
@@ -188,25 +188,28 @@ __device__ __forceinline__ void decode_range(const SegmentCtx& c, DecodeState& s
     }
     uint32_t pos = st.pos;
     // The 32 lanes of a warp walk 32 different pieces of the stream, so the loop body is written with selects
-    // instead of branches wherever the two sides are short: DC and AC symbols take the same path.
+    // instead of branches wherever the two sides are short: DC and AC symbols take the same path, and the code and
+    // its extra bits leave the window in one shift.
     while (pos < end_bit) {
         br.refill();
         const bool is_dc = k == 0;
-        uint32_t e = c.look[(comp * 2 + (is_dc ? 0 : 1)) * (1 << LOOK_BITS) + br.peek(LOOK_BITS)];
+        const uint32_t hi = static_cast<uint32_t>(br.win >> 32), lo = static_cast<uint32_t>(br.win);
+        uint32_t e = c.look[(comp * 2 + (is_dc ? 0 : 1)) * (1 << LOOK_BITS) + (hi >> (32 - LOOK_BITS))];
         if (e == 0u) {
             const HuffDev* __restrict__ t = c.tables + (is_dc ? c.im->dc_tab[comp] : c.im->ac_tab[comp]);
             e = huff_long_code(br.win, t, bad);
         }
-        br.skip(static_cast<int>(e >> 8));
+        const int len = static_cast<int>(e >> 8);                  // 1..16
         const int s = static_cast<int>(e & 15u);
         const int r = is_dc ? 0 : static_cast<int>((e >> 4) & 15u);
-        const uint32_t raw = static_cast<uint32_t>((br.win >> 1) >> (63 - s));          // s == 0 -> 0
+        const uint32_t after = __funnelshift_l(lo, hi, len);       // the 32 bits that follow the code
+        const uint32_t raw = s ? after >> (32 - s) : 0u;
         const int v = raw < (1u << ((s - 1) & 31)) ? static_cast<int>(raw) - (1 << s) + 1 : static_cast<int>(raw);
-        br.skip(s);
-        const int kk = k + r;                                   // zig-zag position of this coefficient
+        br.skip(len + s);                                          // at most 31 bits
+        pos += static_cast<uint32_t>(len + s);
+        const int kk = k + r;                                      // zig-zag position of this coefficient
         if (WRITE && s != 0) out[c.zigzag[kk]] = static_cast<int16_t>(v);
         k = s != 0 ? kk + 1 : (is_dc ? 1 : (r == 15 ? k + 16 : 64));
-        pos = br.position();
         if (k >= 64) {                       // block complete
             k = 0;
             ++done;
@@ -228,7 +231,7 @@ __device__ __forceinline__ void decode_range(const SegmentCtx& c, DecodeState& s
 }
 
 constexpr int HUFF_MAX_THREADS = 1024;
-constexpr int HUFF_MIN_CHUNK_BITS = 256;      // default; B2P_JPEG_CHUNK_BITS overrides it for experiments
+constexpr int HUFF_MIN_CHUNK_BITS = 512;      // default (measured best of 256..8192); B2P_JPEG_CHUNK_BITS overrides it
 
 // Exclusive prefix sum of one int per thread over the CTA; `total` receives the sum of all.
 __device__ __forceinline__ int cta_exclusive_scan(int v, int* s_warp, int& total) {
