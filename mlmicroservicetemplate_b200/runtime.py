@@ -288,17 +288,27 @@ def seeded_model(arch: str, seed: int):
 
 
 def build_gpu_engine(arch: str, gpus: Optional[Sequence[int]], max_batch: int, max_wait_us: int, topk: int,
-                     mode: str, seed: int, sub_batch: int = 0, state_dict: Optional[dict] = None):
-    """What init() does: random-init (seeded) torchvision model -> layer program -> one replica per GPU."""
+                     mode: str, seed: int, sub_batch: int = 0, state_dict: Optional[dict] = None,
+                     packed_path: Optional[str] = None):
+    """What init() does: a packed program file, or a (seeded random-init / checkpointed) torchvision model turned
+    into a layer program, -> one replica per GPU.  Returns (engine, number of classes); the class names of a packed
+    file are left on `engine.classes`."""
     import torch
-    import torchvision
-    from . import program as P
     if not torch.cuda.is_available():
         raise RuntimeError("no CUDA device visible: the B200 predict path has no CPU fallback")
-    model = seeded_model(arch, seed)
-    if state_dict is not None:
-        model.load_state_dict(state_dict)
-    prog = P.build_program(model, arch)
+    classes = None
+    if packed_path:
+        from .packed import load_program
+        prog, classes = load_program(packed_path)
+    else:
+        import torchvision  # noqa: F401
+        from . import program as P
+        model = seeded_model(arch, seed)
+        if state_dict is not None:
+            model.load_state_dict(state_dict)
+        prog = P.build_program(model, arch)
     devs = list(gpus) if gpus else list(range(torch.cuda.device_count()))
     workers = [GpuReplicaWorker(d, prog, max_batch, topk, mode, sub_batch) for d in devs]
-    return Engine(workers, max_batch=max_batch, max_wait_us=max_wait_us), prog.out_elems
+    engine = Engine(workers, max_batch=max_batch, max_wait_us=max_wait_us)
+    engine.classes = classes
+    return engine, prog.out_elems

@@ -17,6 +17,10 @@ Environment knobs (defaults in brackets):
     GPUS  [all]         comma-separated device indices
     MAX_BATCH [64]  MAX_WAIT_US [2000]  TOPK [5]  SEED [0]  PREPROCESS [preset] (preset | direct)
     SUB_BATCH [0]       images per L2-resident pass of the layer program (0 = whole batch)
+    WEIGHTS             path of a packed program (`python -m mlmicroservicetemplate_b200.packed`): folded bf16 weights in
+                        kernel layout + class names, loaded as-is (no torchvision at start-up); MODEL is then ignored
+    CHECKPOINT          path of a torch.save'd torchvision state_dict for MODEL (default: seeded random init)
+    LABELS              text file with one class name per line (default: positional names)
     DECODE [gpu]        gpu: uploads that are baseline JPEGs (b2p_jpeg_inspect) are decoded on the GPU, bit-exact
                         with Pillow; everything else (PNG, progressive / CMYK JPEG, ...) is decoded by Pillow
                         as in the reference.  host: every upload goes through Pillow.
@@ -59,14 +63,25 @@ def init() -> None:
         from ...runtime import build_gpu_engine
         gpus = os.getenv("GPUS")
         devs = [int(g) for g in gpus.split(",")] if gpus else None
+        state_dict = None
+        if os.getenv("CHECKPOINT") and not os.getenv("WEIGHTS"):
+            import torch
+            sd = torch.load(os.environ["CHECKPOINT"], map_location="cpu", weights_only=True)
+            state_dict = sd.get("state_dict", sd) if isinstance(sd, dict) else sd
         engine, n_classes = build_gpu_engine(
             arch=arch, gpus=devs, max_batch=int(os.getenv("MAX_BATCH", "64")),
             max_wait_us=int(os.getenv("MAX_WAIT_US", "2000")), topk=int(os.getenv("TOPK", "5")),
             mode=os.getenv("PREPROCESS", "preset"), seed=int(os.getenv("SEED", "0")),
-            sub_batch=int(os.getenv("SUB_BATCH", "0")))
+            sub_batch=int(os.getenv("SUB_BATCH", "0")), state_dict=state_dict, packed_path=os.getenv("WEIGHTS"))
         _state["engine"] = engine
         _state["decode"] = os.getenv("DECODE", "gpu")
-        _state["classes"] = class_names(n_classes)
+        names = getattr(engine, "classes", None)
+        if os.getenv("LABELS"):
+            with open(os.environ["LABELS"], encoding="utf-8") as f:
+                names = [ln.rstrip("\n") for ln in f if ln.strip()]
+        if names is not None and len(names) != n_classes:
+            raise RuntimeError(f"{len(names)} class names for a model with {n_classes} outputs")
+        _state["classes"] = list(names) if names is not None else class_names(n_classes)
         _state["decode_pool"] = ThreadPoolExecutor(max_workers=int(os.getenv("DECODE_THREADS", str(os.cpu_count() or 4))))
 
 

@@ -172,3 +172,24 @@ def test_partial_batches_on_a_larger_replica(arch, cuda_device):
         torch.cuda.synchronize()
         assert torch.equal(out, full[:n]), f"n={n} differs from the first {n} rows of the full batch"
     rep.close()
+
+
+def test_replica_from_a_packed_file_is_bit_identical(tmp_path, cuda_device):
+    """init() from a .b2pw file must give the very logits init() from the module gives."""
+    from mlmicroservicetemplate_b200 import backend as B, packed, program as P
+    from mlmicroservicetemplate_b200.runtime import seeded_model
+    prog = P.build_program(seeded_model("resnet18", 0), "resnet18")
+    path = str(tmp_path / "r18.b2pw")
+    packed.save_program(prog, path)
+    loaded, _ = packed.load_program(path)
+    g = torch.Generator().manual_seed(5)
+    x = (torch.rand(6, 3, 224, 224, generator=g) * 2 - 1).to(torch.bfloat16).cuda()
+    outs = []
+    for p in (prog, loaded):
+        rep = B.Replica(0, p, max_batch=6)
+        out = torch.empty(6, 1000, device="cuda")
+        rep.forward(x, 6, out)
+        torch.cuda.synchronize()
+        outs.append(out.clone())
+        rep.close()
+    assert torch.equal(outs[0], outs[1])

@@ -128,3 +128,31 @@ def test_gpu_decoded_and_host_decoded_uploads_give_identical_answers(cuda_device
             futs[2].result(timeout=60)
     finally:
         engine.close()
+
+
+def test_plugin_init_from_packed_weights_and_labels(tmp_path, monkeypatch, cuda_device):
+    """WEIGHTS=<file.b2pw>: init() reads the packed program and its class names; predict() answers with them."""
+    from mlmicroservicetemplate_b200 import packed, program as P
+    from mlmicroservicetemplate_b200.runtime import seeded_model
+    from mlmicroservicetemplate_b200.src.model import model as plugin
+    names = [f"species-{i}" for i in range(1000)]
+    path = str(tmp_path / "r18.b2pw")
+    packed.save_program(P.build_program(seeded_model("resnet18", 0), "resnet18"), path, names)
+    for k, v in dict(MODEL="ignored-when-WEIGHTS-is-set", WEIGHTS=path, GPUS="0", MAX_BATCH="4", MAX_WAIT_US="1000",
+                     TOPK="3", PREPROCESS="preset").items():
+        monkeypatch.setenv(k, v)
+    plugin.shutdown()
+    plugin.init()
+    try:
+        out = plugin.predict(SimpleNamespace(file=io.BytesIO(_encoded(9, 256, 320, "JPEG"))))
+        assert out["classes"] == names and len(out["result"]) == 3
+        assert all(k.startswith("species-") for k in out["result"])
+        # same upload through a module-built engine: identical numbers
+        plugin.shutdown()
+        monkeypatch.delenv("WEIGHTS")
+        monkeypatch.setenv("MODEL", "resnet18")
+        plugin.init()
+        ref = plugin.predict(SimpleNamespace(file=io.BytesIO(_encoded(9, 256, 320, "JPEG"))))
+        assert sorted(out["result"].values()) == sorted(ref["result"].values())
+    finally:
+        plugin.shutdown()
