@@ -54,8 +54,8 @@ def load_peaks():
 
 
 def make_batch(seed: int):
-    from oracle import images
-    return images.synthetic_batch(seed, BATCH, IMG, IMG)
+    from mlmicroservicetemplate_b200 import synth
+    return synth.synthetic_batch(seed, BATCH, IMG, IMG)
 
 
 class ClockSampler:
@@ -207,7 +207,7 @@ def main():
     import torch
     from mlmicroservicetemplate_b200 import backend as B, program as P
     from mlmicroservicetemplate_b200.ranks import Ranks
-    from oracle import model as om      # only to build the seeded torchvision module + cpu_baseline
+    from mlmicroservicetemplate_b200.runtime import seeded_model
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a B200: the predict path has no CPU fallback")
@@ -216,7 +216,7 @@ def main():
     ranks = Ranks.from_env(backend="nccl", device=torch.device("cuda", local_rank))
     rank = ranks.rank
 
-    model = om.build_model(ARCH)
+    model = seeded_model(ARCH, 0)
     prog = P.build_program(model, ARCH)
     rep = B.Replica(local_rank, prog, max_batch=BATCH, sub_batch=args.sub_batch)
     stream = torch.cuda.Stream()

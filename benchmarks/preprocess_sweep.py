@@ -7,7 +7,7 @@ bf16, achieved HBM GB/s vs the measured peak.
 Per size and mode (direct = resize straight to 224^2; preset = resize-256 + centre-crop-224):
   bytes  = algorithmic bytes of SURVEY §8(d): n * (3*H*W [window for preset] + 301,056)
   GB/s   = bytes / CUDA-event time of b2p_preprocess on device-resident uint8 HWC input
-  parity = max |fp32 output - oracle| on two images of the batch (gate 1e-6) and bf16 ulps (gate 1)
+  parity = max |fp32 output - torch CPU| on two images of the batch (gate 1e-6) and bf16 ulps (gate 1)
 Inputs rotate over several slabs so that consecutive iterations do not re-read L2-resident data.
 """
 from __future__ import annotations
@@ -24,14 +24,39 @@ SIZES = [(320, 320), (480, 480), (640, 640), (800, 800), (1024, 1024), (1280, 12
          (480, 640), (720, 1280), (1080, 1920)]
 
 
+def _tap_window(in_size, out_size, i):
+    """(first source index, count) of the antialias triangle filter for output index i."""
+    scale = in_size / out_size
+    support = scale if scale >= 1 else 1.0
+    center = scale * (i + 0.5)
+    lo = max(int(center - support + 0.5), 0)
+    return lo, min(int(center + support + 0.5), in_size) - lo
+
+
 def preset_window_bytes(h, w):
     """Source bytes that feed the 224^2 crop in preset mode (window extent on each axis)."""
-    from oracle.preprocess_np import aa_weights, preset_geometry
+    from mlmicroservicetemplate_b200.runtime import preset_geometry
     rh, rw, top, left = preset_geometry(h, w)
-    wv, wh = aa_weights(h, rh), aa_weights(w, rw)
-    y0, y1 = wv[top][0], wv[top + 223][0] + wv[top + 223][1]
-    x0, x1 = wh[left][0], wh[left + 223][0] + wh[left + 223][1]
+    y0 = _tap_window(h, rh, top)[0]
+    y1 = sum(_tap_window(h, rh, top + 223))
+    x0 = _tap_window(w, rw, left)[0]
+    x1 = sum(_tap_window(w, rw, left + 223))
     return 3 * (y1 - y0) * (x1 - x0)
+
+
+def torch_cpu_preprocess(img, res_h, res_w, top, left):
+    """What torch's CPU path gives for stage P (fp32, antialiased bilinear, no re-quantisation): the parity figure
+    this sweep prints next to each timing.  The gating parity tests live in tests/test_gpu_preprocess.py."""
+    import numpy as np
+    import torch
+    import torch.nn.functional as F
+    x = torch.from_numpy(np.ascontiguousarray(img)).permute(2, 0, 1)[None].float()
+    if (x.shape[2], x.shape[3]) != (res_h, res_w):
+        x = F.interpolate(x, size=(res_h, res_w), mode="bilinear", align_corners=False, antialias=True)
+    x = x[:, :, top:top + 224, left:left + 224]
+    mean = torch.tensor([0.485, 0.456, 0.406]).view(1, 3, 1, 1)
+    std = torch.tensor([0.229, 0.224, 0.225]).view(1, 3, 1, 1)
+    return (x / 255.0 - mean) / std
 
 
 def main():
@@ -49,7 +74,8 @@ def main():
     import numpy as np
     import torch
     from mlmicroservicetemplate_b200 import backend as B, program as P
-    from oracle import images, model as om
+    from mlmicroservicetemplate_b200 import synth as images
+    from mlmicroservicetemplate_b200.runtime import image_geometry
 
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"hbm_gbs": 6650.0}
     peak = peaks["hbm_gbs"]
@@ -73,13 +99,13 @@ def main():
         n_slabs = max(2, int(300e6 // (n * stride)) + 1)          # > 126 MB L2 in total
         slabs = [torch.from_numpy(slab_np).cuda() for _ in range(n_slabs)]
         for mode in args.modes.split(","):
-            geom = om.geometry(h, w, mode)
+            geom = image_geometry(h, w, mode)
             descs = B.make_images([(i * stride, h, w, *geom) for i in range(n)])
             # parity on the first two images
             rep.preprocess(slabs[0], B.make_images([(i * stride, h, w, *geom) for i in range(2)]), 2, out32, out_f32=True)
             rep.preprocess(slabs[0], descs, n, out16)
             torch.cuda.synchronize()
-            ref = torch.cat([om.preprocess(base[i], *geom) for i in range(2)], 0)
+            ref = torch.cat([torch_cpu_preprocess(base[i], *geom) for i in range(2)], 0)
             err = (out32.cpu() - ref).abs().max().item()
             def key(t):
                 i16 = t.view(torch.int16).to(torch.int32)

@@ -38,7 +38,7 @@ def main():
     args = ap.parse_args()
 
     from PIL import Image
-    from oracle import images
+    from mlmicroservicetemplate_b200 import synth as images
     payloads = []
     for i in range(64):
         buf = io.BytesIO()
