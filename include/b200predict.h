@@ -196,7 +196,7 @@ int32_t b2p_head_static(const void* feat, int32_t n, int32_t hw, int32_t c, cons
  * (src/model/model.py:23; Pillow / libjpeg-turbo defaults: accurate integer IDCT, fancy chroma upsampling,
  * fixed-point YCbCr->RGB) would: uint8 RGB, HWC, rows densely packed — bit for bit.  Scope: baseline /
  * extended-sequential Huffman JPEG (SOF0, SOF1), 8-bit, ONE interleaved scan, greyscale or YCbCr with luma
- * sampling 1x1 (4:4:4), 2x1 (4:2:2) or 2x2 (4:2:0), restart intervals allowed, no Adobe marker.  Everything
+ * sampling 1x1 (4:4:4), 2x1 (4:2:2) or 2x2 (4:2:0), restart intervals allowed, no Adobe marker, at most 64 Mpixel.  Everything
  * else reports B2P_E_UNSUPPORTED and stays on the caller's host decoder.  The decoder object is independent
  * of b2p_handle; like a handle it is bound to one device and driven by one host thread, and consecutive
  * calls must be issued on the same stream (its workspace is reused in stream order).                     */

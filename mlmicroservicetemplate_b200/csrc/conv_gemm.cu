@@ -53,6 +53,8 @@ struct GemmArgs {
     int ldc;
     int relu;
     int reverse;      // walk the tiles from the last to the first (see GemmPlan::reverse)
+    int split_tiles;  // the last `split_tiles` tiles of the walk are cut into `split_ways` 64-column pieces, so that
+    int split_ways;   // a nearly empty last wave costs a fraction of a tile time instead of a whole one (0 = off)
     const float* bias;
     void* out;        // only used by the fp32 (linear) epilogue
 };
@@ -99,7 +101,8 @@ template <int BLOCK_N, int BLOCK_K, bool IM2COL, bool OUT_F32, bool HAS_RES, boo
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                  const __grid_constant__ CUtensorMap tmap_out, const __grid_constant__ CUtensorMap tmap_res,
-                 const __grid_constant__ CUtensorMap tmap_a2, const GemmArgs args) {
+                 const __grid_constant__ CUtensorMap tmap_a2, const __grid_constant__ CUtensorMap tmap_b64,
+                 const GemmArgs args) {
     using C = Cfg<BLOCK_N, BLOCK_K, OUT_F32, HAS_RES, CTA2>;
     constexpr int STAGES = C::STAGES;
     static_assert(!(OUT_F32 && HAS_RES), "the fp32 epilogue has no residual input");
@@ -129,12 +132,25 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int first_tile = CTA2 ? static_cast<int>(blockIdx.x >> 1) : static_cast<int>(blockIdx.x);
     const int tile_step = CTA2 ? static_cast<int>(gridDim.x >> 1) : static_cast<int>(gridDim.x);
     const int num_kb = args.taps_h * args.taps_w * args.k_chunks + args.k2_chunks;
-    auto tile_coords = [&](int tile, int& m_blk, int& n_blk) {
-        const int t = args.reverse ? total_tiles - 1 - tile : tile;
+    // Work items: the first `full_tiles` are whole 128 x BLOCK_N tiles; each of the remaining tiles is handed out
+    // as `split_ways` separate 64-column pieces (sub >= 0), which other CTAs pick up in the same last wave.
+    const int full_tiles = total_tiles - args.split_tiles;
+    const int total_items = full_tiles + args.split_tiles * args.split_ways;
+    auto tile_coords = [&](int item, int& m_blk, int& n_blk, int& sub) {
+        int t = item;
+        sub = -1;
+        if (item >= full_tiles) {
+            const int u = item - full_tiles;
+            const int q = u / args.split_ways;
+            t = full_tiles + q;
+            sub = u - q * args.split_ways;
+        }
+        if (args.reverse) t = total_tiles - 1 - t;
         const int mp = t / args.n_tiles;
         n_blk = t - mp * args.n_tiles;
         m_blk = CTA2 ? 2 * mp + static_cast<int>(rank) : mp;
     };
+    constexpr uint32_t SUB_B_BYTES = 64 * BLOCK_K * 2;          // weight rows of one 64-column piece
 
     if (warp_idx == 0) {
         if (elect_one()) {
@@ -185,6 +201,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             const uint32_t full0 = CTA2 ? mapa_shared(smem_u32(&full_bar[0]), 0) : 0u;
             const bool arms = !CTA2 || rank == 0;
             constexpr uint32_t TX_BYTES = (CTA2 ? 2u : 1u) * C::STAGE_BYTES;
+            constexpr uint32_t TX_BYTES_SUB = C::A_BYTES + SUB_B_BYTES;
             auto load_a = [&](const CUtensorMap* map, bool im2col, int stg, int c, int w, int h, int n, int s_, int r_) {
                 uint8_t* dst = smem_a + stg * C::A_BYTES;
                 if (CTA2) {
@@ -196,16 +213,18 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     else tma_load_2d(map, &full_bar[stg], dst, c, w);
                 }
             };
-            auto load_b = [&](int stg, int kcol, int nrow) {
+            auto load_b = [&](int stg, int kcol, int nrow, bool piece) {
                 uint8_t* dst = smem_b + stg * C::B_BYTES;
                 if (CTA2) tma_load_2d_pair(&tmap_b, full0 + static_cast<uint32_t>(stg * 8), dst, kcol, nrow);
-                else tma_load_2d(&tmap_b, &full_bar[stg], dst, kcol, nrow);
+                else tma_load_2d(piece ? &tmap_b64 : &tmap_b, &full_bar[stg], dst, kcol, nrow);
             };
-            for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
-                int m_blk, n_blk;
-                tile_coords(tile, m_blk, n_blk);
+            for (int tile = first_tile; tile < total_items; tile += tile_step) {
+                int m_blk, n_blk, sub;
+                tile_coords(tile, m_blk, n_blk, sub);
+                const bool piece = sub >= 0;
+                const uint32_t tx = piece ? TX_BYTES_SUB : TX_BYTES;
                 const int m0 = m_blk * BLOCK_M;
-                const int nrow = n_blk * BLOCK_N + static_cast<int>(rank) * C::B_ROWS;
+                const int nrow = n_blk * BLOCK_N + (piece ? sub * 64 : static_cast<int>(rank) * C::B_ROWS);
                 int img = 0, base_w = 0, base_h = 0, base_w2 = 0, base_h2 = 0;
                 if (IM2COL || args.k2_chunks > 0) {
                     img = m0 / pq;
@@ -222,10 +241,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     for (int s = 0; s < args.taps_w; ++s) {
                         for (int cc = 0; cc < args.k_chunks; ++cc, kcol += BLOCK_K) {
                             mbar_wait(&empty_bar[stage], phase ^ 1u);
-                            if (arms) mbar_arrive_expect_tx(&full_bar[stage], TX_BYTES);
+                            if (arms) mbar_arrive_expect_tx(&full_bar[stage], tx);
                             if (IM2COL) load_a(&tmap_a, true, stage, cc * BLOCK_K, base_w, base_h, img, s, r);
                             else load_a(&tmap_a, false, stage, kcol, m0, 0, 0, 0, 0);
-                            load_b(stage, kcol, nrow);
+                            load_b(stage, kcol, nrow, piece);
                             if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                         }
                     }
@@ -233,9 +252,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 // second source: the projection shortcut's input pixels, K continues after the main operand
                 for (int cc = 0; cc < args.k2_chunks; ++cc, kcol += BLOCK_K) {
                     mbar_wait(&empty_bar[stage], phase ^ 1u);
-                    if (arms) mbar_arrive_expect_tx(&full_bar[stage], TX_BYTES);
+                    if (arms) mbar_arrive_expect_tx(&full_bar[stage], tx);
                     load_a(&tmap_a2, true, stage, cc * BLOCK_K, base_w2, base_h2, img, 0, 0);
-                    load_b(stage, kcol, nrow);
+                    load_b(stage, kcol, nrow, piece);
                     if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                 }
             }
@@ -243,12 +262,14 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     } else if (warp_idx == 1) {
         // ======================================================================= MMA issuer
         if ((!CTA2 || rank == 0) && elect_one()) {
-            constexpr uint32_t idesc = umma_idesc_bf16(CTA2 ? 2 * BLOCK_M : BLOCK_M, BLOCK_N);
+            constexpr uint32_t idesc_full = umma_idesc_bf16(CTA2 ? 2 * BLOCK_M : BLOCK_M, BLOCK_N);
+            constexpr uint32_t idesc_piece = umma_idesc_bf16(BLOCK_M, 64);
             int stage = 0;
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
-            for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
+            for (int tile = first_tile; tile < total_items; tile += tile_step) {
+                const uint32_t idesc = tile >= full_tiles ? idesc_piece : idesc_full;
                 mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u);
                 tc_fence_after();
                 const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * BLOCK_N);
@@ -282,14 +303,15 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (HAS_RES && elect_one()) {
             int rs = 0;
             uint32_t rphase = 0;
-            for (int tile = first_tile; tile < total_tiles; tile += tile_step) {
-                int m_blk, n_blk;
-                tile_coords(tile, m_blk, n_blk);
-                for (int c64 = 0; c64 < BLOCK_N / 64; ++c64) {
+            for (int tile = first_tile; tile < total_items; tile += tile_step) {
+                int m_blk, n_blk, sub;
+                tile_coords(tile, m_blk, n_blk, sub);
+                const int n_chunks = sub >= 0 ? 1 : BLOCK_N / 64;
+                for (int c64 = 0; c64 < n_chunks; ++c64) {
                     mbar_wait(&res_empty_bar[rs], rphase ^ 1u);
                     mbar_arrive_expect_tx(&res_full_bar[rs], OUT_CHUNK_BYTES);
                     tma_load_2d(&tmap_res, &res_full_bar[rs], smem_res + rs * OUT_CHUNK_BYTES,
-                                n_blk * BLOCK_N + c64 * 64, m_blk * BLOCK_M);
+                                n_blk * BLOCK_N + (sub >= 0 ? sub : c64) * 64, m_blk * BLOCK_M);
                     if (++rs == RES_STAGES) { rs = 0; rphase ^= 1u; }
                 }
             }
@@ -314,9 +336,10 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int ob = group;
         uint32_t seq = 0;                               // global chunk sequence number at the start of the tile
         const uint32_t tmem_empty0 = CTA2 ? mapa_shared(smem_u32(&tmem_empty_bar[0]), 0) : 0u;   // the leader's
-        for (int tile = first_tile; tile < total_tiles; tile += tile_step, seq += BLOCK_N / 64) {
-            int m_blk, n_blk;
-            tile_coords(tile, m_blk, n_blk);
+        for (int tile = first_tile; tile < total_items; tile += tile_step) {
+            int m_blk, n_blk, sub;
+            tile_coords(tile, m_blk, n_blk, sub);
+            const int n_chunks = sub >= 0 ? 1 : BLOCK_N / 64;
             mbar_wait(&tmem_full_bar[acc], acc_phase);
             tc_fence_after();
             const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) +
@@ -345,9 +368,9 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             } else if (!OUT_F32) {
                 // ---- bf16 NHWC: TMEM -> regs -> (+bias, +residual, ReLU) -> swizzled smem -> TMA store
 #pragma unroll 1
-                for (int c64 = 0; c64 < BLOCK_N / 64; ++c64) {
+                for (int c64 = 0; c64 < n_chunks; ++c64) {
                     if (((seq + static_cast<uint32_t>(c64)) & 1u) != static_cast<uint32_t>(group)) continue;
-                    const int col0 = n_blk * BLOCK_N + c64 * 64;
+                    const int col0 = n_blk * BLOCK_N + (sub >= 0 ? sub : c64) * 64;   // a piece sits in TMEM columns 0..63
                     uint32_t res_base = 0;
                     if (HAS_RES) {
                         mbar_wait(&res_full_bar[rs], rphase);
@@ -426,6 +449,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 if (CTA2) mbar_arrive_cluster(tmem_empty0 + static_cast<uint32_t>(acc * 8));
                 else mbar_arrive(&tmem_empty_bar[acc]);
             }
+            seq += static_cast<uint32_t>(n_chunks);
             if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1u; }
         }
         if (!OUT_F32 && store_leader) tma_store_wait_all<0>();
@@ -466,7 +490,7 @@ cudaError_t launch_variant(const GemmPlan& p, const GemmArgs& a, int grid, cudaS
     }
     if (!CTA2) {
         return launch_pdl(kern, dim3(grid), dim3(NUM_THREADS), C::SMEM_BYTES, stream, p.tmap_a, p.tmap_b, p.tmap_out,
-                          p.tmap_res, p.tmap_a2, a);
+                          p.tmap_res, p.tmap_a2, p.tmap_b64, a);
     }
     // CTA pairs: a 2-wide cluster (the two SMs of a TPC) on top of the programmatic-serialization attribute
     cudaLaunchConfig_t cfg = {};
@@ -483,7 +507,7 @@ cudaError_t launch_variant(const GemmPlan& p, const GemmArgs& a, int grid, cudaS
     attr[1].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 2;
-    return cudaLaunchKernelEx(&cfg, kern, p.tmap_a, p.tmap_b, p.tmap_out, p.tmap_res, p.tmap_a2, a);
+    return cudaLaunchKernelEx(&cfg, kern, p.tmap_a, p.tmap_b, p.tmap_out, p.tmap_res, p.tmap_a2, p.tmap_b64, a);
 }
 
 }  // namespace
@@ -591,21 +615,35 @@ bool gemm_plan_init(GemmPlan& p, const b2p_op& op, const void* weight_dev, int64
     const bool has_res_op = op.res != B2P_SLOT_NONE;
     const bool cta2_ok = !cta2_none && !p.out_f32 && p.block_k == 64 && num_sms >= 2;
     const int m_tiles = (rows_at_capacity + BLOCK_M - 1) / BLOCK_M;
+    // Tail splitting is opt-in (B2P_TAIL_SPLIT=1, read per plan): A/B runs put it within the box-to-box noise on
+    // ResNet-50 / ViT-B/16 / ResNet-18 (profiles/r01i_tail_split_ab.txt) — the GEMMs here are bound by operand
+    // delivery, and a 64-column piece still loads the whole 128-row activation tile.
+    p.tail_split = getenv("B2P_TAIL_SPLIT") != nullptr && !p.out_f32 && p.block_k == 64;
     int best = 0, best_cta2 = 0;
-    long best_cost = 0;
+    double best_cost = 0;
     const int cands[3] = {256, 128, 64};
     for (int bn : cands) {
         if (p.force_block_n && bn != p.force_block_n) continue;
         if (p.n_pad % bn != 0) continue;
         if (p.block_k == 16 && bn != 64) continue;
         if (p.out_f32 && bn != 128) continue;
-        const int pair = (cta2_ok && (cta2_all ? bn >= 128 : (bn == 256 && !has_res_op))) ? 1 : 0;
-        const long m_eff = pair ? 2L * ((m_tiles + 1) / 2) : m_tiles;
-        const long sms = pair ? (num_sms & ~1) : num_sms;
-        const long tiles = m_eff * (p.n_pad / bn);
-        const long waves = (tiles + sms - 1) / sms;
-        const long cost = waves * (bn + 32);     // +32: fixed per-tile overhead in "column" units
-        if (best == 0 || cost < best_cost) { best = bn; best_cost = cost; best_cta2 = pair; }
+        const double tile_cost = bn + 32;           // +32: fixed per-tile overhead in "column" units
+        // single CTAs; a nearly empty last wave is cut into 64-column pieces (see gemm_tail_split)
+        {
+            const long tiles = static_cast<long>(m_tiles) * (p.n_pad / bn);
+            const long q = tiles / num_sms, r = tiles % num_sms;
+            // (the tail split applied at launch is deliberately not part of this choice: letting it pick wider tiles
+            // for the residual layers measured slower, profiles/r01i_tail_split_ab.txt)
+            const double cost = q * tile_cost + (r ? tile_cost : 0.0);
+            if (best == 0 || cost < best_cost) { best = bn; best_cost = cost; best_cta2 = 0; }
+        }
+        // CTA pairs: measured 7 % cheaper per tile for the layers the policy admits, no tail splitting
+        if (cta2_ok && (cta2_all ? bn >= 128 : (bn == 256 && !has_res_op))) {
+            const long pairs = num_sms / 2;
+            const long tiles = static_cast<long>((m_tiles + 1) / 2) * (p.n_pad / bn);
+            const double cost = static_cast<double>((tiles + pairs - 1) / pairs) * tile_cost;
+            if (best == 0 || cost <= best_cost) { best = bn; best_cost = cost; best_cta2 = 1; }
+        }
     }
     if (best == 0) {
         set_err(err, err_len, "no tile width fits this layer");
@@ -614,9 +652,13 @@ bool gemm_plan_init(GemmPlan& p, const b2p_op& op, const void* weight_dev, int64
     p.block_n = best;
     p.cta2 = best_cta2;
     const CUtensorMapSwizzle sw = p.block_k == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_32B;
-    return encode_tiled_2d(&p.tmap_b, weight_dev, static_cast<uint64_t>(k_total),
-                           static_cast<uint64_t>(p.n_pad), static_cast<uint32_t>(p.block_k),
-                           static_cast<uint32_t>(p.cta2 ? p.block_n / 2 : p.block_n), sw, err, err_len);
+    if (!encode_tiled_2d(&p.tmap_b, weight_dev, static_cast<uint64_t>(k_total),
+                         static_cast<uint64_t>(p.n_pad), static_cast<uint32_t>(p.block_k),
+                         static_cast<uint32_t>(p.cta2 ? p.block_n / 2 : p.block_n), sw, err, err_len))
+        return false;
+    // 64-row weight boxes for the pieces of a split last wave (also encoded when unused: the kernel takes the map)
+    return encode_tiled_2d(&p.tmap_b64, weight_dev, static_cast<uint64_t>(k_total), static_cast<uint64_t>(p.n_pad),
+                           static_cast<uint32_t>(p.block_k), 64, sw, err, err_len);
 }
 
 bool gemm_plan_set_src(GemmPlan& p, const void* src, int batch_cap, char* err, size_t err_len) {
@@ -719,6 +761,18 @@ cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, bool has_res, void* 
     if (total <= 0) return cudaSuccess;
     if (p.cta2) total = 2 * ((a.m_tiles + 1) / 2) * a.n_tiles;      // CTAs, two per 256-row tile
     const int sms = p.cta2 ? (num_sms & ~1) : num_sms;
+    a.split_tiles = 0;
+    a.split_ways = 0;
+    if (p.tail_split && !p.cta2 && p.block_n > 64 && total > sms) {
+        // gemm_tail_split: the r tiles of the last, partly filled wave become r * (block_n / 64) pieces when that
+        // makes the wave shorter (a piece costs about (64 + 32) / (block_n + 32) of a tile)
+        const int r = total % sms, s = p.block_n / 64;
+        if (r > 0 && static_cast<long>((static_cast<long>(r) * s + sms - 1) / sms) * (64 + 32) < p.block_n + 32) {
+            a.split_tiles = r;
+            a.split_ways = s;
+            total += r * (s - 1);
+        }
+    }
     const int grid = total < sms ? total : sms;
 #define B2P_LAUNCH(BN, BK, IM, F32, RES) return launch_variant<BN, BK, IM, F32, RES, false>(p, a, grid, stream)
 #define B2P_LAUNCH2(BN, IM, RES) return launch_variant<BN, 64, IM, false, RES, true>(p, a, grid, stream)

@@ -653,6 +653,12 @@ int parse_jpeg(const uint8_t* d, int64_t len, Parsed& P, char* msg, size_t msg_l
         i += seg_len;
     }
     if (P.width < 1 || P.height < 1) { why(msg, msg_len, "empty frame"); return B2P_E_ARG; }
+    // A 600-byte file may claim 65535 x 65535 pixels; the workspace for that would be ~20 GB.  Leave anything above
+    // 64 Mpixel to the host decoder and its own decompression-bomb policy.
+    if (static_cast<int64_t>(P.width) * P.height > (64LL << 20)) {
+        why(msg, msg_len, "%d x %d pixels is above the GPU decoder's 64 Mpixel limit", P.width, P.height);
+        return B2P_E_UNSUPPORTED;
+    }
     for (int c = 0; c < P.ncomp; ++c) {
         if (!P.qt_present[P.tq[c]]) { why(msg, msg_len, "missing quantisation table"); return B2P_E_ARG; }
         if (!P.dc[P.td[c]].present || !P.ac[P.ta[c]].present) { why(msg, msg_len, "missing Huffman table"); return B2P_E_ARG; }

@@ -33,6 +33,8 @@ struct GemmPlan {
     CUtensorMap tmap_out; // bf16 output [rows, out_c], 128 x 64 store boxes (unused by the fp32 epilogue)
     CUtensorMap tmap_res; // bf16 residual [rows, out_c], same boxes (only when the op has a residual)
     CUtensorMap tmap_a2;  // optional second A source (projection shortcut input), im2col 1x1 / src2_stride
+    CUtensorMap tmap_b64; // weights again with 64-row boxes: the 64-column pieces of a split last wave
+    int tail_split = 0;   // allow cutting the tiles of a nearly empty last wave into 64-column pieces
     int src2_c = 0, src2_stride = 1;
     int block_n = 0;      // 64 / 128 / 256
     int force_block_n = 0;  // set before gemm_plan_init to pin the tile width (autotuner)

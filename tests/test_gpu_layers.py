@@ -281,3 +281,15 @@ def test_softmax_topk(cuda_device):
     assert torch.equal(idx.cpu().long()[mask], ref_i[mask])
     assert torch.allclose(probs.cpu()[mask], ref_p[mask], rtol=1e-5, atol=1e-8)
     assert abs(probs[3, 0].item() - 0.5) < 1e-5 and abs(probs[3, 1].item() - 0.5) < 1e-5
+
+
+@pytest.mark.parametrize("case", [
+    (8, (56, 56, 256), 256, 1, 1, 0, True, True),         # 196 tiles of 128 x 256: 148 + 48, residual stream
+    (112, (14, 14, 256), 256, 3, 1, 1, True, False),      # 172 tiles, im2col operand
+    (5, (56, 56, 64), 256, 1, 1, 0, False, False),        # 123 tiles (< one wave): nothing to split, flag must be inert
+], ids=["1x1_res", "3x3_im2col", "single_wave"])
+def test_conv_with_tail_split(case, cuda_device, monkeypatch):
+    """B2P_TAIL_SPLIT=1: the tiles of the partly filled last wave are computed as 64-column pieces by other CTAs."""
+    monkeypatch.setenv("B2P_TAIL_SPLIT", "1")
+    n, hwc, oc, k, stride, pad, relu, residual = case
+    _run_conv(n, hwc, oc, k, stride, pad, relu, residual, seed=77)
