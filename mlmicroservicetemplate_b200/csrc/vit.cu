@@ -125,16 +125,18 @@ __global__ void layernorm_kernel(const uint4* __restrict__ x, const float* __res
 }
 
 // ------------------------------------------------------------------------------ attention
-constexpr int ATT_THREADS = 192;
+constexpr int ATT_THREADS = 320;       // warp 0 loads, warp 1 issues the MMAs, warps 2-9 = softmax / epilogue (two per TMEM lane quadrant)
 constexpr int HD = 64;                 // head dimension
 constexpr int KV_ROWS = 208;           // keys padded to a multiple of 16 (UMMA N / K granularity), >= 197
 constexpr int Q_BYTES = 128 * 128;     // 128 queries x 64 dims bf16, 128B swizzle
 constexpr int KV_BYTES = 256 * 128;    // room for 208 key (value) rows of 128 bytes
 constexpr int P_CHUNK_BYTES = 128 * 128;
 // P (4 chunks of 16 KB) is written only after S = QK^T has completed, when Q and K are dead: chunks 0-1
-// overlay K, chunk 2 overlays Q, chunk 3 gets its own 16 KB.  ~97 KB per CTA, so two CTAs share an SM and
-// one's softmax overlaps the other's loads and MMAs.
-constexpr int ATT_SMEM = 1024 + Q_BYTES + 2 * KV_BYTES + P_CHUNK_BYTES + 128;
+// overlay K, chunk 2 overlays Q, chunk 3 gets its own 16 KB.  ~99 KB per CTA, so two CTAs share an SM and
+// one's softmax overlaps the other's loads and MMAs.  The softmax is the long pole of a CTA (208 exp2 per row),
+// so eight warps share it: two per TMEM lane quadrant, each taking half of the keys.
+constexpr int ATT_XCHG_BYTES = 2 * 2 * 128 * 4;      // row max and row sum halves exchanged between the two warps of a row
+constexpr int ATT_SMEM = 1024 + Q_BYTES + 2 * KV_BYTES + P_CHUNK_BYTES + 128 + ATT_XCHG_BYTES;
 
 // tcgen05 instruction descriptor, bf16 x bf16 -> fp32, A K-major, B MN-major (bit 16).
 __host__ __device__ constexpr uint32_t umma_idesc_bf16_b_mn(uint32_t m, uint32_t n) {
@@ -158,6 +160,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     uint64_t* p_bar = s_bar + 1;
     uint64_t* o_bar = p_bar + 1;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_bar + 1);
+    float* x_max = reinterpret_cast<float*>(smem_p3 + P_CHUNK_BYTES + 128);      // [2][128]
+    float* x_sum = x_max + 2 * 128;                                               // [2][128]
 
     const int warp_idx = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
     const int mt = blockIdx.x, head = blockIdx.y, img = blockIdx.z;
@@ -172,7 +176,7 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         if (elect_one()) {
             mbar_init(load_bar, 1);
             mbar_init(s_bar, 1);
-            mbar_init(p_bar, 4);
+            mbar_init(p_bar, 8);
             mbar_init(o_bar, 1);
             fence_mbar_init();
         }
@@ -222,16 +226,21 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             umma_commit(o_bar);
         }
     } else {
+        // Two warps share every TMEM lane quadrant (a warp may only read lanes 32 * (warp_idx % 4) ...): the first
+        // set takes keys 0..127 (column chunks 0-3), the second keys 128..207 (chunks 4-6); row maxima and row
+        // sums are combined through shared memory, and the O epilogue is split the same way (dims 0-31 / 32-63).
         const int quad = warp_idx & 3;
+        const int half = (warp_idx - 2) >> 2;
         const int lane = static_cast<int>(lane_id());
         const int r = quad * 32 + lane;                         // query row inside the tile
         const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
+        const int c_lo = half ? 4 : 0, c_hi = half ? 7 : 4;
         mbar_wait(s_bar, 0);
         tc_fence_after();
-        // pass 1: row maximum over the valid keys
+        // pass 1: row maximum over the valid keys of this half, then over both halves
         float mx = -FLT_MAX;
 #pragma unroll 1
-        for (int c = 0; c < 7; ++c) {
+        for (int c = c_lo; c < c_hi; ++c) {
             uint32_t v[32];
             tmem_ld_32x32(t_addr + c * 32, v);
             tmem_ld_wait();
@@ -239,11 +248,14 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
             for (int j = 0; j < 32; ++j)
                 if (c * 32 + j < seq) mx = fmaxf(mx, __uint_as_float(v[j]));
         }
+        x_max[half * 128 + r] = mx;
+        named_bar_sync(1, 256);
+        mx = fmaxf(mx, x_max[(half ^ 1) * 128 + r]);
         // pass 2: p = exp((s - max) * scale), unnormalised bf16 into the K-major swizzled P tiles; row sum in fp32
         float sum = 0.f;
         const uint32_t p_row = static_cast<uint32_t>(r * 128);
 #pragma unroll 1
-        for (int c = 0; c < 7; ++c) {
+        for (int c = c_lo; c < c_hi; ++c) {
             uint32_t v[32];
             tmem_ld_32x32(t_addr + c * 32, v);
             tmem_ld_wait();
@@ -266,6 +278,8 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
                 st_shared_v4(p_chunk_addr(chunk) + p_row + static_cast<uint32_t>(piece * 16), o);
             }
         }
+        // (the PV MMA reads keys 0..207 only; chunk 6 wrote keys 192..223 of P chunk 3, zeros beyond `seq`)
+        x_sum[half * 128 + r] = sum;
         fence_proxy_async_smem();          // P must be visible to the tensor core's async proxy
         tc_fence_before();                 // and all S reads are done before the accumulator is overwritten
         __syncwarp();
@@ -273,26 +287,26 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
         // ---- O epilogue
         mbar_wait(o_bar, 0);
         tc_fence_after();
-        const float inv = 1.0f / sum;
+        named_bar_sync(1, 256);            // both halves of every row sum are in shared memory
+        const float inv = 1.0f / (sum + x_sum[(half ^ 1) * 128 + r]);
         const int token = mt * 128 + r;
-        uint4 packed[8];
-#pragma unroll
-        for (int h = 0; h < 2; ++h) {
+        uint4 packed[4];
+        {
             uint32_t v[32];
-            tmem_ld_32x32(t_addr + h * 32, v);
+            tmem_ld_32x32(t_addr + half * 32, v);
             tmem_ld_wait();
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-                packed[h * 4 + j].x = pack_bf16x2(__uint_as_float(v[8 * j + 0]) * inv, __uint_as_float(v[8 * j + 1]) * inv);
-                packed[h * 4 + j].y = pack_bf16x2(__uint_as_float(v[8 * j + 2]) * inv, __uint_as_float(v[8 * j + 3]) * inv);
-                packed[h * 4 + j].z = pack_bf16x2(__uint_as_float(v[8 * j + 4]) * inv, __uint_as_float(v[8 * j + 5]) * inv);
-                packed[h * 4 + j].w = pack_bf16x2(__uint_as_float(v[8 * j + 6]) * inv, __uint_as_float(v[8 * j + 7]) * inv);
+                packed[j].x = pack_bf16x2(__uint_as_float(v[8 * j + 0]) * inv, __uint_as_float(v[8 * j + 1]) * inv);
+                packed[j].y = pack_bf16x2(__uint_as_float(v[8 * j + 2]) * inv, __uint_as_float(v[8 * j + 3]) * inv);
+                packed[j].z = pack_bf16x2(__uint_as_float(v[8 * j + 4]) * inv, __uint_as_float(v[8 * j + 5]) * inv);
+                packed[j].w = pack_bf16x2(__uint_as_float(v[8 * j + 6]) * inv, __uint_as_float(v[8 * j + 7]) * inv);
             }
         }
         if (token < seq) {
-            uint4* o = reinterpret_cast<uint4*>(out + (static_cast<size_t>(row0 + token) * dim + head * HD));
+            uint4* o = reinterpret_cast<uint4*>(out + (static_cast<size_t>(row0 + token) * dim + head * HD + half * 32));
 #pragma unroll
-            for (int j = 0; j < 8; ++j) st_v4(o + j, packed[j]);
+            for (int j = 0; j < 4; ++j) st_v4(o + j, packed[j]);
         }
     }
     tc_fence_before();
