@@ -18,7 +18,13 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <array>
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <new>
+#include <thread>
 #include <vector>
 #include <cuda_runtime.h>
 #include "../../include/b200predict.h"
@@ -731,6 +737,78 @@ bool build_huff(const HuffHost& h, HuffDev& out) {
 }  // namespace
 
 // ------------------------------------------------------------------------------------------- C ABI
+// A few persistent host threads for the per-file work of b2p_jpeg_decode (marker walk, un-stuffing copy): with
+// megapixel files that work is tens of megabytes of memchr/memcpy per call and would otherwise serialise on the
+// caller's thread.  run() hands out item indices through an atomic counter; the caller takes part as well.
+class HostPool {
+public:
+    explicit HostPool(int helpers) {
+        for (int i = 0; i < helpers; ++i) threads_.emplace_back([this] { loop(); });
+    }
+    ~HostPool() {
+        {
+            std::lock_guard<std::mutex> lk(m_);
+            stop_ = true;
+        }
+        cv_.notify_all();
+        for (auto& t : threads_) t.join();
+    }
+    int helpers() const { return static_cast<int>(threads_.size()); }
+    void run(int items, const std::function<void(int)>& fn) {
+        if (items <= 0) return;
+        if (threads_.empty() || items == 1) {
+            for (int i = 0; i < items; ++i) fn(i);
+            return;
+        }
+        {
+            std::lock_guard<std::mutex> lk(m_);
+            fn_ = &fn;
+            items_ = items;
+            next_.store(0);
+            pending_ = static_cast<int>(threads_.size());
+            ++generation_;
+        }
+        cv_.notify_all();
+        work();
+        std::unique_lock<std::mutex> lk(m_);
+        done_.wait(lk, [this] { return pending_ == 0; });
+        fn_ = nullptr;
+    }
+
+private:
+    void work() {
+        for (;;) {
+            const int i = next_.fetch_add(1);
+            if (i >= items_) break;
+            (*fn_)(i);
+        }
+    }
+    void loop() {
+        uint64_t seen = 0;
+        for (;;) {
+            {
+                std::unique_lock<std::mutex> lk(m_);
+                cv_.wait(lk, [&] { return stop_ || generation_ != seen; });
+                if (stop_) return;
+                seen = generation_;
+            }
+            work();
+            {
+                std::lock_guard<std::mutex> lk(m_);
+                if (--pending_ == 0) done_.notify_one();
+            }
+        }
+    }
+    std::vector<std::thread> threads_;
+    std::mutex m_;
+    std::condition_variable cv_, done_;
+    const std::function<void(int)>* fn_ = nullptr;
+    std::atomic<int> next_{0};
+    int items_ = 0, pending_ = 0;
+    uint64_t generation_ = 0;
+    bool stop_ = false;
+};
+
 struct b2p_jpeg {
     int device = -1;
     int num_sms = 0;
@@ -748,6 +826,7 @@ struct b2p_jpeg {
     int64_t coef_cap = 0;         // bytes
     uint8_t* planes = nullptr;    // component sample planes
     int64_t planes_cap = 0;
+    HostPool* pool = nullptr;     // helper threads for the host side of decode()
     cudaEvent_t ev[5] = {};       // around the copy and each kernel of the most recent call
     bool ev_valid = false;
     int64_t calls = 0;
@@ -829,6 +908,15 @@ int32_t b2p_jpeg_create(int32_t device, b2p_jpeg** out) {
             return B2P_E_CUDA;
         }
     }
+    {
+        // helper threads: B2P_JPEG_THREADS (total, including the caller), default min(8, half the hardware threads)
+        const char* e = getenv("B2P_JPEG_THREADS");
+        int total = e ? atoi(e) : static_cast<int>(std::thread::hardware_concurrency() / 2);
+        if (total > 8 && !e) total = 8;
+        if (total < 1) total = 1;
+        if (total > 64) total = 64;
+        d->pool = new (std::nothrow) HostPool(total - 1);
+    }
     *out = d;
     return B2P_OK;
 }
@@ -859,6 +947,7 @@ int32_t b2p_jpeg_destroy(b2p_jpeg* d) {
         if (e) cudaEventDestroy(e);
     if (d->coef) cudaFree(d->coef);
     if (d->planes) cudaFree(d->planes);
+    delete d->pool;
     delete d;
     return B2P_OK;
 }
@@ -887,10 +976,18 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
     int64_t n_segments = 0, scan_total = 0, coef_elems = 0, plane_bytes = 0, block_total = 0;
     int max_blocks = 0;
     int64_t max_quads = 0;
+    {
+        std::vector<int> rcs(static_cast<size_t>(n), B2P_OK);
+        std::vector<std::array<char, 200>> msgs(static_cast<size_t>(n));
+        auto parse_one = [&](int i) {
+            msgs[i][0] = 0;
+            rcs[i] = parse_jpeg(files[i], lens[i], P[i], msgs[i].data(), msgs[i].size());
+        };
+        if (d->pool) d->pool->run(n, parse_one); else for (int i = 0; i < n; ++i) parse_one(i);
+        for (int i = 0; i < n; ++i)
+            if (rcs[i] != B2P_OK) { jerr(d, "file %d: %s", i, msgs[i].data()); return rcs[i]; }
+    }
     for (int i = 0; i < n; ++i) {
-        char msg[256] = "";
-        const int rc = parse_jpeg(files[i], lens[i], P[i], msg, sizeof msg);
-        if (rc != B2P_OK) { jerr(d, "file %d: %s", i, msg); return rc; }
         const Parsed& p = P[i];
         ImageDev& im = images[i];
         memset(&im, 0, sizeof im);
@@ -981,22 +1078,32 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
     uint8_t* blob = d->pinned[slot];
     memcpy(blob + off_img, images.data(), static_cast<size_t>(n) * sizeof(ImageDev));
     SegmentDev* segs = reinterpret_cast<SegmentDev*>(blob + off_seg);
-    int64_t si = 0, scan_pos = 0, max_seg_bits = 0;
+    // every segment gets a slot sized for its raw (still stuffed) length, so the files can be copied in parallel
+    std::vector<int64_t> first_seg(static_cast<size_t>(n) + 1, 0), first_byte(static_cast<size_t>(n) + 1, 0);
     for (int i = 0; i < n; ++i) {
+        int64_t bytes = 0;
+        for (size_t sg = 0; sg < P[i].seg_begin.size(); ++sg) bytes += align_up(P[i].seg_end[sg] - P[i].seg_begin[sg], 4) + 4;
+        first_seg[i + 1] = first_seg[i] + static_cast<int64_t>(P[i].seg_begin.size());
+        first_byte[i + 1] = first_byte[i] + bytes;
+    }
+    std::vector<int64_t> image_max_bits(static_cast<size_t>(n), 0);
+    auto fill_one = [&](int i) {
         const Parsed& p = P[i];
         const int64_t total_mcu = static_cast<int64_t>(p.mcux) * p.mcuy;
         const int64_t ri = p.restart_interval > 0 ? p.restart_interval : total_mcu;
-        for (size_t s = 0; s < p.seg_begin.size(); ++s, ++si) {
-            SegmentDev& g = segs[si];
+        int64_t scan_pos = first_byte[i], most = 0;
+        for (size_t sg = 0; sg < p.seg_begin.size(); ++sg) {
+            SegmentDev& g = segs[first_seg[i] + static_cast<int64_t>(sg)];
             g.image = i;
-            g.first_mcu = static_cast<int32_t>(static_cast<int64_t>(s) * ri);
+            g.first_mcu = static_cast<int32_t>(static_cast<int64_t>(sg) * ri);
             const int64_t left = total_mcu - g.first_mcu;
             g.n_mcu = static_cast<int32_t>(left < ri ? left : ri);
             g.pad = 0;
             g.begin = scan_pos;
             uint8_t* dst = blob + off_scan + scan_pos;
-            const uint8_t* src = files[i] + p.seg_begin[s];
-            const uint8_t* end = files[i] + p.seg_end[s];
+            const uint8_t* src = files[i] + p.seg_begin[sg];
+            const uint8_t* end = files[i] + p.seg_end[sg];
+            const int64_t slot_bytes = align_up(end - src, 4) + 4;
             int64_t w = 0;
             while (src < end) {
                 const uint8_t* f = static_cast<const uint8_t*>(memchr(src, 0xFF, static_cast<size_t>(end - src)));
@@ -1007,12 +1114,15 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
                 if (f && src < end && *src == 0x00) ++src;             // the stuffed zero
             }
             g.nbits = w * 8;
-            if (g.nbits > max_seg_bits) max_seg_bits = g.nbits;
-            const int64_t padded = align_up(w, 4) + 4;
-            memset(dst + w, 0, static_cast<size_t>(padded - w));
-            scan_pos += padded;
+            if (g.nbits > most) most = g.nbits;
+            memset(dst + w, 0, static_cast<size_t>(slot_bytes - w));
+            scan_pos += slot_bytes;
         }
-    }
+        image_max_bits[i] = most;
+    };
+    if (d->pool) d->pool->run(n, fill_one); else for (int i = 0; i < n; ++i) fill_one(i);
+    int64_t max_seg_bits = 0;
+    for (int i = 0; i < n; ++i) if (image_max_bits[i] > max_seg_bits) max_seg_bits = image_max_bits[i];
     if (max_seg_bits >= 0xFFFFFF00LL) { jerr(d, "an entropy-coded segment of 512 MiB or more"); return B2P_E_LIMIT; }
     memcpy(blob + off_tab, tables.data(), tables.size() * sizeof(HuffDev));
 
