@@ -261,6 +261,45 @@ __device__ __forceinline__ int cta_exclusive_scan(int v, int* s_warp, int& total
     return base + inc - v;
 }
 
+// ---- thread-block cluster helpers: a large segment is spread over up to 8 CTAs (8 SMs) that exchange chunk states
+// through distributed shared memory instead of living on one SM's issue slots
+__device__ __forceinline__ uint32_t cl_rank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ uint32_t cl_size() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cl_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// value of a 32-bit shared-memory variable (given by its address in THIS CTA) as CTA `rank` of the cluster holds it
+__device__ __forceinline__ uint32_t cl_load(const void* local, uint32_t rank) {
+    const uint32_t a = static_cast<uint32_t>(__cvta_generic_to_shared(local));
+    uint32_t remote, v;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(a), "r"(rank));
+    asm volatile("ld.shared::cluster.u32 %0, [%1];" : "=r"(v) : "r"(remote) : "memory");
+    return v;
+}
+
+// Exclusive prefix sum over all threads of the cluster (CTA rank major); `slot` must not be reused within a launch.
+template <bool CLUSTER>
+__device__ __forceinline__ int group_exclusive_scan(int v, int* s_warp, int* s_tot, int slot, int& total) {
+    int local_total = 0;
+    const int base_local = cta_exclusive_scan(v, s_warp, local_total);
+    if (!CLUSTER) {
+        total = local_total;
+        return base_local;
+    }
+    if (threadIdx.x == 0) s_tot[slot] = local_total;
+    cl_sync();
+    const uint32_t me = cl_rank(), n = cl_size();
+    int base = 0, sum = 0;
+    for (uint32_t r = 0; r < n; ++r) {
+        const int x = static_cast<int>(cl_load(&s_tot[slot], r));
+        if (r < me) base += x;
+        sum += x;
+    }
+    total = sum;
+    return base + base_local;
+}
+
+template <bool CLUSTER>
 __global__ void __launch_bounds__(HUFF_MAX_THREADS)
 huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ images,
                const SegmentDev* __restrict__ segments, const HuffDev* __restrict__ tables,
@@ -270,8 +309,13 @@ huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ im
     __shared__ int s_warp[HUFF_MAX_THREADS / 32];
     __shared__ uint16_t s_look[3 * 2 << LOOK_BITS];
     __shared__ uint8_t s_zigzag[80];
-    const SegmentDev sg = segments[blockIdx.x];
+    __shared__ int s_tot[4];
+    __shared__ int s_flag[2];
+    const int C = CLUSTER ? static_cast<int>(cl_size()) : 1;           // CTAs that share this segment
+    const int rank = CLUSTER ? static_cast<int>(cl_rank()) : 0;
+    const SegmentDev sg = segments[CLUSTER ? blockIdx.x / C : blockIdx.x];
     const int t = threadIdx.x, P = blockDim.x;
+    const int gt = rank * P + t, PT = C * P;                           // thread index / count over the whole segment
     SegmentCtx c;
     c.im = images + sg.image;
     c.tables = tables;
@@ -294,9 +338,9 @@ huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ im
     c.words = reinterpret_cast<const uint32_t*>(scan + sg.begin);
     c.nwords = (c.nbits + 31u) >> 5;
     // one chunk per thread: a multiple of 32 bits, at least HUFF_MIN_CHUNK_BITS (trailing threads may get nothing)
-    uint32_t chunk = (c.nbits + static_cast<uint32_t>(P) - 1u) / static_cast<uint32_t>(P);
+    uint32_t chunk = (c.nbits + static_cast<uint32_t>(PT) - 1u) / static_cast<uint32_t>(PT);
     chunk = max((chunk + 31u) & ~31u, static_cast<uint32_t>(min_chunk_bits));
-    const uint32_t my_begin = min(static_cast<uint32_t>(t) * chunk, c.nbits);
+    const uint32_t my_begin = static_cast<uint32_t>(min(static_cast<uint64_t>(gt) * chunk, static_cast<uint64_t>(c.nbits)));
     const uint32_t my_end = min(my_begin + chunk, c.nbits);
 
     // ---- 1 + 2: find every chunk's true entry state
@@ -305,7 +349,7 @@ huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ im
     int blocks = 0, bad = 0, overrun = 0;
     bool dirty = true;
     int round = 0;
-    for (; round <= P; ++round) {
+    for (; round <= PT; ++round) {
         if (dirty) {
             out = in;
             blocks = 0;
@@ -314,23 +358,36 @@ huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ im
         }
         s_pos[t] = out.pos;
         s_state[t] = (out.blk << 8) | out.k;
-        __syncthreads();
+        if (CLUSTER) cl_sync(); else __syncthreads();
         DecodeState want = in;
         if (t > 0) {
             want.pos = s_pos[t - 1];
             want.blk = s_state[t - 1] >> 8;
             want.k = s_state[t - 1] & 255;
+        } else if (CLUSTER && rank > 0) {                   // the chunk before this CTA's first one lives in the previous CTA
+            want.pos = cl_load(&s_pos[P - 1], static_cast<uint32_t>(rank - 1));
+            const int st = static_cast<int>(cl_load(&s_state[P - 1], static_cast<uint32_t>(rank - 1)));
+            want.blk = st >> 8;
+            want.k = st & 255;
         }
         dirty = want.pos != in.pos || want.blk != in.blk || want.k != in.k;
         in = want;
-        if (!__syncthreads_or(dirty ? 1 : 0)) break;
+        int any = __syncthreads_or(dirty ? 1 : 0);
+        if (CLUSTER) {
+            // (flag slots alternate: a slot is rewritten two rounds later, after every reader has passed two barriers)
+            if (t == 0) s_flag[round & 1] = any;
+            cl_sync();
+            any = 0;
+            for (int r = 0; r < C; ++r) any |= static_cast<int>(cl_load(&s_flag[round & 1], static_cast<uint32_t>(r)));
+        }
+        if (!any) break;
     }
 
-    if (debug_rounds && status && t == 0) atomicMax(status + sg.image, (round + 1) << 8);   // measurement aid only
+    if (debug_rounds && status && gt == 0) atomicMax(status + sg.image, (round + 1) << 8);   // measurement aid only
 
     // ---- 3: index of each thread's first block, then the decode that writes
     int total = 0;
-    const int first_block = cta_exclusive_scan(blocks, s_warp, total);
+    const int first_block = group_exclusive_scan<CLUSTER>(blocks, s_warp, s_tot, 0, total);
     if (total < c.total_blocks) overrun = 1;            // the data ran out before the last block was complete
     {
         DecodeState st = in;
@@ -338,14 +395,15 @@ huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ im
         decode_range<true>(c, st, my_end, n, first_block, coef, bad, overrun);
     }
     if ((overrun | bad) && status) atomicOr(status + sg.image, overrun | (bad << 1));
-    __syncthreads();                                    // every coefficient of this segment is in place
+    if (CLUSTER) cl_sync(); else __syncthreads();       // every coefficient of this segment is in place
 
     // ---- 4: DC differences -> DC values, per component, in decode order
     for (int comp = 0; comp < c.im->ncomp; ++comp) {
         const int per_mcu = comp == 0 ? c.luma : 1;
         const int nblk = sg.n_mcu * per_mcu;
-        const int per_thread = (nblk + P - 1) / P;
-        const int i0 = min(t * per_thread, nblk), i1 = min(i0 + per_thread, nblk);
+        const int per_thread = (nblk + PT - 1) / PT;
+        const int i0 = static_cast<int>(min(static_cast<int64_t>(gt) * per_thread, static_cast<int64_t>(nblk)));
+        const int i1 = min(i0 + per_thread, nblk);
         auto dc_ptr = [&](int i) -> int16_t* {
             const int m = i / per_mcu, j = i - m * per_mcu;
             int cc;
@@ -354,13 +412,14 @@ huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ im
         int sum = 0;
         for (int i = i0; i < i1; ++i) sum += *dc_ptr(i);
         int all = 0;
-        int run = cta_exclusive_scan(sum, s_warp, all);
+        int run = group_exclusive_scan<CLUSTER>(sum, s_warp, s_tot, 1 + comp, all);
         for (int i = i0; i < i1; ++i) {
             int16_t* p = dc_ptr(i);
             run += *p;
             *p = static_cast<int16_t>(run);
         }
     }
+    if (CLUSTER) cl_sync();        // nobody leaves while a neighbour may still read this CTA's shared memory
 }
 
 // ------------------------------------------------------------------------------------------- J2: dequantise + IDCT
@@ -1147,11 +1206,40 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
         }();
         int64_t want = (max_seg_bits + min_chunk - 1) / min_chunk;
         want = (want + 31) / 32 * 32;
-        const int threads = static_cast<int>(want < 32 ? 32 : (want > HUFF_MAX_THREADS ? HUFF_MAX_THREADS : want));
-        huffman_kernel<<<static_cast<unsigned>(n_segments), threads, 0, stream>>>(dev + off_scan, images_dev, segs_dev, tabs_dev,
-                                                                                  d->coef, status, min_chunk,
-                                                                                  getenv("B2P_JPEG_DEBUG_ROUNDS") != nullptr);
-        JPEG_CUDA(d, cudaGetLastError());
+        const int debug_rounds = getenv("B2P_JPEG_DEBUG_ROUNDS") != nullptr;
+        // segments that want more than one CTA's worth of threads are spread over a cluster of CTAs (other SMs):
+        // B2P_JPEG_CLUSTER caps the cluster size (1 = never; default 4: measured on 32 x 1080p files the Huffman
+        // kernel takes 2.43 / 1.39 / 1.07 / 3.1 ms with 1 / 2 / 4 / 8 CTAs per file — 1024-thread CTAs are one per SM,
+        // so 8-CTA clusters no longer fit the GPU in one wave)
+        static const int max_cluster = [] {
+            const char* e = getenv("B2P_JPEG_CLUSTER");
+            const int v = e ? atoi(e) : 4;
+            return v >= 8 ? 8 : (v >= 4 ? 4 : (v >= 2 ? 2 : 1));
+        }();
+        int cluster = 1;
+        while (cluster < max_cluster && want > static_cast<int64_t>(cluster) * HUFF_MAX_THREADS) cluster *= 2;
+        if (cluster == 1) {
+            const int threads = static_cast<int>(want < 32 ? 32 : (want > HUFF_MAX_THREADS ? HUFF_MAX_THREADS : want));
+            huffman_kernel<false><<<static_cast<unsigned>(n_segments), threads, 0, stream>>>(
+                dev + off_scan, images_dev, segs_dev, tabs_dev, d->coef, status, min_chunk, debug_rounds);
+            JPEG_CUDA(d, cudaGetLastError());
+        } else {
+            cudaLaunchConfig_t cfg = {};
+            cfg.gridDim = dim3(static_cast<unsigned>(n_segments * cluster));
+            cfg.blockDim = dim3(HUFF_MAX_THREADS);
+            cfg.stream = stream;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = static_cast<unsigned>(cluster);
+            attr[0].val.clusterDim.y = 1;
+            attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr;
+            cfg.numAttrs = 1;
+            const uint8_t* scan_dev = dev + off_scan;
+            int16_t* coef_dev = d->coef;
+            JPEG_CUDA(d, cudaLaunchKernelEx(&cfg, huffman_kernel<true>, scan_dev, images_dev, segs_dev, tabs_dev, coef_dev,
+                                            status, min_chunk, debug_rounds));
+        }
         JPEG_CUDA(d, cudaEventRecord(d->ev[2], stream));
     }
     {

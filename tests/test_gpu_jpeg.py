@@ -101,6 +101,21 @@ def test_single_image_batches(decoder, size, kw):
     assert np.array_equal(outs[0], _pillow(f))
 
 
+def test_large_files_spread_over_cta_clusters(decoder):
+    """Segments of more than 64 KB no longer fit one CTA's 1024 chunks of 512 bits: the Huffman kernel then runs as a
+    cluster of 2, 4 or 8 CTAs that exchange chunk states through distributed shared memory.  Mixed with a tiny file
+    (which gets the same cluster size, mostly idle) the pixels must still equal Pillow's."""
+    for files in ([_encode(_picture(200, 300, seed=3), quality=93, subsampling=0)],                      # ~80 KB: 2 CTAs
+                  [_encode(_picture(300, 400, seed=8), quality=93, subsampling=0)],                      # ~160 KB: 4 CTAs
+                  [_encode(_picture(768, 1024, seed=4), quality=95), _encode(_picture(24, 32, seed=5), quality=80)],
+                  [_encode(_picture(1080, 1920, seed=6), quality=92), _encode(_picture(1080, 1920, seed=7), quality=75,
+                                                                              subsampling=1)]):
+        outs, status, *_ = _decode_batch(decoder, files)
+        assert (status == 0).all(), status
+        for f, got in zip(files, outs):
+            assert len(f) > 0 and np.array_equal(got, _pillow(f)), (len(f), got.shape)
+
+
 def test_committed_golden_vectors(decoder):
     import json
     import os
