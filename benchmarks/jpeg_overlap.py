@@ -20,24 +20,28 @@ def main():
     ap.add_argument("--batch", type=int, default=256)
     ap.add_argument("--steps", type=int, default=60)
     ap.add_argument("--warmup", type=int, default=6)
+    ap.add_argument("--size", type=int, nargs=2, default=[224, 224], help="H W of the uploads (e.g. 1080 1920: photos)")
+    ap.add_argument("--distinct", type=int, default=64)
     args = ap.parse_args()
     import numpy as np
     import torch
     from PIL import Image
     from mlmicroservicetemplate_b200 import backend as B, program as P, synth
-    from mlmicroservicetemplate_b200.runtime import seeded_model
+    from mlmicroservicetemplate_b200.runtime import image_geometry, seeded_model
     torch.cuda.set_device(0)
     n, k = args.batch, 5
+    H, W = args.size
     files = []
-    for im in synth.synthetic_batch(1, min(n, 64), 224, 224):
+    for im in synth.synthetic_batch(1, min(n, args.distinct), H, W):
         buf = io.BytesIO()
         Image.fromarray(im).save(buf, "JPEG", quality=90)
         files.append(buf.getvalue())
     files = [files[i % len(files)] for i in range(n)]
     rot = [files[s:] + files[:s] for s in range(4)]
-    stride = (224 * 224 * 3 + 255) // 256 * 256
+    stride = (H * W * 3 + 255) // 256 * 256
     offs = [i * stride for i in range(n)]
-    descs = B.make_images([(o, 224, 224, 224, 224, 0, 0) for o in offs])
+    geom = image_geometry(H, W, "direct" if (H, W) == (224, 224) else "preset")
+    descs = B.make_images([(o, H, W, *geom) for o in offs])
     rep = B.Replica(0, P.build_program(seeded_model(args.arch, 0), args.arch), max_batch=n)
     dec = B.JpegDecoder(0)
     slabs = [torch.empty(n * stride, dtype=torch.uint8, device="cuda") for _ in range(2)]
@@ -92,7 +96,7 @@ def main():
     pipelined(args.warmup)
     ms_pipe = pipelined(args.steps)
     same = bool(torch.equal(ref, probs_h)) if (args.steps % 4) == 0 else None
-    print(json.dumps({"arch": args.arch, "batch": n, "serial_ms": ms_serial, "serial_images_per_s": n / ms_serial * 1e3,
+    print(json.dumps({"arch": args.arch, "batch": n, "upload": f"{H}x{W} JPEG q90 4:2:0", "serial_ms": ms_serial, "serial_images_per_s": n / ms_serial * 1e3,
                       "pipelined_ms": ms_pipe, "pipelined_images_per_s": n / ms_pipe * 1e3,
                       "same_result_as_serial": same, "file_bytes": sum(len(f) for f in files) // n}))
     dec.close()
