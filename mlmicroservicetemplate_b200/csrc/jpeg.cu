@@ -886,7 +886,10 @@ struct b2p_jpeg {
     uint8_t* planes = nullptr;    // component sample planes
     int64_t planes_cap = 0;
     HostPool* pool = nullptr;     // helper threads for the host side of decode()
-    cudaEvent_t ev[5] = {};       // around the copy and each kernel of the most recent call
+    cudaStream_t copy_stream = nullptr;   // the blob's host->device copy runs here, under the previous call's kernels
+    cudaEvent_t kernels_done[RING] = {};  // the kernels that read blob_dev[i] have finished (caller's stream)
+    cudaEvent_t ev_copy[2] = {};          // around the copy (copy stream)
+    cudaEvent_t ev[5] = {};       // around each kernel of the most recent call ([0] unused, kept for layout)
     bool ev_valid = false;
     int64_t calls = 0;
 };
@@ -954,11 +957,18 @@ int32_t b2p_jpeg_create(int32_t device, b2p_jpeg** out) {
     d->num_sms = prop.multiProcessorCount;
     if (cudaSetDevice(device) != cudaSuccess) { delete d; return B2P_E_CUDA; }
     for (int i = 0; i < b2p_jpeg::RING; ++i) {
-        if (cudaEventCreateWithFlags(&d->copied[i], cudaEventDisableTiming) != cudaSuccess) {
+        if (cudaEventCreateWithFlags(&d->copied[i], cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&d->kernels_done[i], cudaEventDisableTiming) != cudaSuccess) {
             jerr(nullptr, "cudaEventCreate failed");
             delete d;
             return B2P_E_CUDA;
         }
+    }
+    if (cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreate(&d->ev_copy[0]) != cudaSuccess || cudaEventCreate(&d->ev_copy[1]) != cudaSuccess) {
+        jerr(nullptr, "could not create the copy stream");
+        delete d;
+        return B2P_E_CUDA;
     }
     for (auto& e : d->ev) {
         if (cudaEventCreate(&e) != cudaSuccess) {
@@ -986,7 +996,7 @@ int32_t b2p_jpeg_stats_get(b2p_jpeg* d, b2p_jpeg_stats* out) {
     out->calls = d->calls;
     if (!d->ev_valid) return B2P_OK;
     if (cudaEventSynchronize(d->ev[4]) != cudaSuccess) return B2P_E_CUDA;
-    cudaEventElapsedTime(&out->ms_copy, d->ev[0], d->ev[1]);
+    cudaEventElapsedTime(&out->ms_copy, d->ev_copy[0], d->ev_copy[1]);
     cudaEventElapsedTime(&out->ms_huffman, d->ev[1], d->ev[2]);
     cudaEventElapsedTime(&out->ms_idct, d->ev[2], d->ev[3]);
     cudaEventElapsedTime(&out->ms_colour, d->ev[3], d->ev[4]);
@@ -1004,6 +1014,11 @@ int32_t b2p_jpeg_destroy(b2p_jpeg* d) {
     }
     for (auto& e : d->ev)
         if (e) cudaEventDestroy(e);
+    for (auto& e : d->ev_copy)
+        if (e) cudaEventDestroy(e);
+    for (auto& e : d->kernels_done)
+        if (e) cudaEventDestroy(e);
+    if (d->copy_stream) cudaStreamDestroy(d->copy_stream);
     if (d->coef) cudaFree(d->coef);
     if (d->planes) cudaFree(d->planes);
     delete d->pool;
@@ -1097,6 +1112,7 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
     if (d->used[slot]) JPEG_CUDA(d, cudaEventSynchronize(d->copied[slot]));     // the copy out of this blob finished
     if (blob_bytes > d->blob_cap[slot]) {
         JPEG_CUDA(d, cudaStreamSynchronize(stream));
+        JPEG_CUDA(d, cudaStreamSynchronize(d->copy_stream));
         if (d->pinned[slot]) cudaFreeHost(d->pinned[slot]);
         if (d->blob_dev[slot]) cudaFree(d->blob_dev[slot]);
         d->pinned[slot] = nullptr; d->blob_dev[slot] = nullptr; d->blob_cap[slot] = 0;
@@ -1185,14 +1201,19 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
     if (max_seg_bits >= 0xFFFFFF00LL) { jerr(d, "an entropy-coded segment of 512 MiB or more"); return B2P_E_LIMIT; }
     memcpy(blob + off_tab, tables.data(), tables.size() * sizeof(HuffDev));
 
-    // ---- device work, all on the caller's stream
+    // ---- device work.  The copy goes to a private stream so that it runs under the kernels of the previous call
+    // (two blobs alternate); it only has to wait for the kernels that last read THIS device blob.  Everything else is
+    // on the caller's stream, which waits for the copy.
     uint8_t* dev = d->blob_dev[slot];
-    JPEG_CUDA(d, cudaEventRecord(d->ev[0], stream));
-    JPEG_CUDA(d, cudaMemcpyAsync(dev, blob, static_cast<size_t>(blob_bytes), cudaMemcpyHostToDevice, stream));
-    JPEG_CUDA(d, cudaEventRecord(d->copied[slot], stream));
+    if (d->used[slot]) JPEG_CUDA(d, cudaStreamWaitEvent(d->copy_stream, d->kernels_done[slot], 0));
+    JPEG_CUDA(d, cudaEventRecord(d->ev_copy[0], d->copy_stream));
+    JPEG_CUDA(d, cudaMemcpyAsync(dev, blob, static_cast<size_t>(blob_bytes), cudaMemcpyHostToDevice, d->copy_stream));
+    JPEG_CUDA(d, cudaEventRecord(d->ev_copy[1], d->copy_stream));
+    JPEG_CUDA(d, cudaEventRecord(d->copied[slot], d->copy_stream));
     d->used[slot] = true;
     JPEG_CUDA(d, cudaMemsetAsync(d->coef, 0, static_cast<size_t>(coef_bytes), stream));
     if (status) JPEG_CUDA(d, cudaMemsetAsync(status, 0, static_cast<size_t>(n) * sizeof(int32_t), stream));
+    JPEG_CUDA(d, cudaStreamWaitEvent(stream, d->copied[slot], 0));
     JPEG_CUDA(d, cudaEventRecord(d->ev[1], stream));
     const ImageDev* images_dev = reinterpret_cast<const ImageDev*>(dev + off_img);
     const SegmentDev* segs_dev = reinterpret_cast<const SegmentDev*>(dev + off_seg);
@@ -1253,6 +1274,7 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
         colour_kernel<<<grid, 256, 0, stream>>>(images_dev, d->planes, slab);
         JPEG_CUDA(d, cudaGetLastError());
         JPEG_CUDA(d, cudaEventRecord(d->ev[4], stream));
+        JPEG_CUDA(d, cudaEventRecord(d->kernels_done[slot], stream));
     }
     d->ev_valid = true;
     ++d->calls;
