@@ -151,3 +151,27 @@ async def predict_async(image_file: UploadFile = File(...)):
     arr = await loop.run_in_executor(_state["decode_pool"], _decode, image_file.file)
     probs, idx = await asyncio.wrap_future(_engine().submit(arr))
     return _to_result(probs, idx)
+
+
+def _dumps(obj) -> bytes:
+    # exactly what starlette's JSONResponse.render does, so the bytes on the wire do not change
+    import json
+    return json.dumps(obj, ensure_ascii=False, allow_nan=False, indent=None, separators=(",", ":")).encode("utf-8")
+
+
+async def predict_async_json(image_file: UploadFile = File(...)) -> bytes:
+    """predict_async() already rendered as the JSON text of its result dict.  The 'classes' list (every class name,
+    identical in every answer) is rendered once per model instead of being walked by the framework's encoder on every
+    request — that walk was the largest per-request cost on the event loop."""
+    if _state["arch"] == "template":
+        return _dumps(predict(image_file))
+    loop = asyncio.get_running_loop()
+    arr = await loop.run_in_executor(_state["decode_pool"], _decode, image_file.file)
+    probs, idx = await asyncio.wrap_future(_engine().submit(arr))
+    names = _state["classes"]
+    cached = _state.get("classes_json")
+    if cached is None or cached[0] is not names:
+        cached = (names, _dumps(names))
+        _state["classes_json"] = cached
+    result = {names[int(i)]: float(p) for p, i in zip(probs, idx)}
+    return b'{"classes":' + cached[1] + b',"result":' + _dumps(result) + b'}'

@@ -25,7 +25,7 @@ import threading
 from dotenv import load_dotenv
 from fastapi import FastAPI, File, Request, UploadFile
 from fastapi.middleware.cors import CORSMiddleware
-from starlette.responses import JSONResponse
+from starlette.responses import JSONResponse, Response
 
 from ..model import model as plugin
 from . import dependency as dep
@@ -109,4 +109,6 @@ async def start_init_and_report_status():
 @app.post("/predict")
 async def create_prediction(image_file: UploadFile = File(...)):
     _require_ready()
-    return {"status": "success", "result": await plugin.predict_async(image_file)}
+    # same JSON text as returning {"status": "success", "result": <predict dict>}, without the per-request encoder walk
+    body = await plugin.predict_async_json(image_file)
+    return Response(content=b'{"status":"success","result":' + body + b'}', media_type="application/json")

@@ -121,6 +121,11 @@ def test_predict_route_batches_concurrent_clients(client):
         for i, r in enumerate(out):
             assert r.status_code == 200
             body = r.json()
+            # the hand-assembled body (class list rendered once per model) is byte-for-byte what the framework's own
+            # JSON response of the same dict would have been
+            from starlette.responses import JSONResponse
+            assert r.content == JSONResponse(content=body).body
+            assert r.headers["content-type"] == "application/json"
             assert body["status"] == "success" and len(body["result"]["classes"]) == 1000
             assert f"class_{i:04d}" in body["result"]["result"], "each client must get ITS image's result"
         assert sum(w.batches) == 24 and max(w.batches) > 1
