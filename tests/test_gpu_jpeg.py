@@ -167,3 +167,34 @@ def test_unsupported_files_are_refused_before_any_launch(decoder):
     assert e.value.code == B.E_UNSUPPORTED
     with pytest.raises(B.B2PError):
         decoder.decode([_encode(_picture(32, 32, seed=2), quality=80)], slab, 100, [0])     # slab too small
+
+
+def test_damaged_files_never_take_the_decoder_down(decoder):
+    """Corrupt entropy-coded data, corrupt Huffman / quantisation tables: the kernels must stay inside their buffers
+    (a stray access would poison the CUDA context and fail everything after it), flag what they can, and the next
+    clean file must still decode bit for bit."""
+    from mlmicroservicetemplate_b200 import backend as B
+    rng = np.random.default_rng(99)
+    clean = _encode(_picture(72, 88, seed=3), quality=88)
+    seeds = [clean, _encode(_picture(64, 64, seed=4), quality=70, subsampling=0, optimize=True),
+             _encode(_picture(48, 80, seed=5), quality=92, restart_marker_blocks=3), _encode(_picture(56, 56, seed=6, grey=True), quality=80)]
+    accepted = refused = flagged = 0
+    for trial in range(240):
+        data = bytearray(seeds[trial % len(seeds)])
+        lo = 2 if trial % 3 == 0 else len(data) // 3          # sometimes the tables, mostly the entropy-coded data
+        for _ in range(int(rng.integers(1, 12))):
+            data[int(rng.integers(lo, len(data) - 2))] = int(rng.integers(0, 256))
+        data = bytes(data)
+        if B.jpeg_inspect(data) is None:
+            refused += 1
+            continue
+        try:
+            outs, status, *_ = _decode_batch(decoder, [data, clean])
+        except B.B2PError as e:                               # e.g. a Huffman table that over-subscribes its code space
+            assert e.code in (-1, B.E_UNSUPPORTED), e
+            refused += 1
+            continue
+        accepted += 1
+        flagged += int(status[0] != 0)
+        assert status[1] == 0 and np.array_equal(outs[1], _pillow(clean))
+    assert accepted > 60 and flagged > 0, (accepted, refused, flagged)

@@ -97,3 +97,44 @@ def test_c_abi_header_parser_agrees_with_the_restatement():
     for m in json.loads(str(z["meta"])):
         info = B.jpeg_inspect(z[m["key"] + "_file"].tobytes())
         assert info is not None and (info.height, info.width) == (m["h"], m["w"])
+
+
+def test_header_parser_survives_damaged_files():
+    """Uploads are untrusted: whatever bytes arrive, b2p_jpeg_inspect must answer (geometry or 'not for me') and never
+    read outside the buffer.  2,400 random mutations of valid files: flipped bytes, cut tails, rewritten segment
+    lengths, spliced garbage.  (The buffer handed over is exactly as long as the file, so an over-read would hit the
+    allocator's red zone under ASan and, more to the point, the lengths it reports must stay inside the file.)"""
+    from mlmicroservicetemplate_b200 import backend as B
+    rng = np.random.default_rng(1234)
+    arr = images.synthetic_image(4, 40, 56)
+    seeds = [_encode(arr, quality=85), _encode(arr, quality=85, subsampling=0, optimize=True),
+             _encode(arr, quality=60, restart_marker_blocks=2), _encode(arr[..., 0], quality=70)]
+    answered = 0
+    for trial in range(2400):
+        data = bytearray(seeds[trial % len(seeds)])
+        kind = trial % 6
+        if kind == 0:                                   # a few random byte flips anywhere
+            for _ in range(int(rng.integers(1, 6))):
+                data[int(rng.integers(0, len(data)))] = int(rng.integers(0, 256))
+        elif kind == 1:                                 # truncation
+            data = data[:int(rng.integers(0, len(data)))]
+        elif kind == 2:                                 # flips confined to the headers
+            for _ in range(int(rng.integers(1, 8))):
+                data[int(rng.integers(0, min(len(data), 620)))] = int(rng.integers(0, 256))
+        elif kind == 3:                                 # a marker length field rewritten
+            pos = data.find(b"\xff", int(rng.integers(2, 300)))
+            if 0 <= pos < len(data) - 4:
+                data[pos + 2] = int(rng.integers(0, 256))
+                data[pos + 3] = int(rng.integers(0, 256))
+        elif kind == 4:                                 # garbage spliced in
+            at = int(rng.integers(0, len(data)))
+            data[at:at] = bytes(rng.integers(0, 256, int(rng.integers(1, 64)), dtype=np.uint8))
+        else:                                           # 0xFF bytes sprinkled over the entropy-coded data
+            for _ in range(int(rng.integers(1, 10))):
+                data[int(rng.integers(len(data) // 2, len(data)))] = 0xFF
+        info = B.jpeg_inspect(bytes(data))
+        if info is not None:
+            answered += 1
+            assert 1 <= info.width <= 65535 and 1 <= info.height <= 65535 and info.width * info.height <= 64 << 20
+            assert info.components in (1, 3) and info.segments >= 1 and 0 <= info.scan_bytes <= len(data)
+    assert answered > 100          # many mutations leave a decodable header: both outcomes are exercised
