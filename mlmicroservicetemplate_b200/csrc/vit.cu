@@ -9,6 +9,7 @@
 // conv_gemm kernel as 1x1 convolutions over a 197x1 "image".
 #include <cfloat>
 #include <cstdio>
+#include <cstdlib>
 #include <cudaTypedefs.h>
 #include "kernels.h"
 #include "ptx.cuh"
@@ -317,6 +318,252 @@ attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_consta
     }
 }
 
+// ------------------------------------------------------------------------------ attention, persistent version
+// One CTA per SM walks the (image, head, query tile) items.  Two items are in flight at any time, in two slots
+// (slot = item parity): each slot has its own Q/K/V/P shared-memory stage, its own 256 TMEM columns (S, later
+// overwritten by O) and its own group of four softmax warps, so the softmax of one item runs under the loads, the
+// MMAs and the epilogue of the other, and none of the per-CTA costs of the first version (TMEM allocation, barrier
+// set-up, cold first load) is paid per item.
+//   warp 0   TMA producer:  Q / K / V of item i into stage i % 2 as soon as PV(i - 2) has released it
+//   warp 1   MMA issuer:    S(i) = Q K^T, then O(i - 1) = P V as soon as the softmax of i - 1 has published P
+//   warps 2-5 / 6-9  softmax + O epilogue of the even / odd items
+constexpr int A2_THREADS = 320;
+constexpr int A2_STAGE_BYTES = Q_BYTES + 2 * KV_BYTES + P_CHUNK_BYTES;      // 96 KB: Q | K | V | P chunk 3
+constexpr int A2_SMEM = 1024 + 2 * A2_STAGE_BYTES + 256;
+
+__global__ void __launch_bounds__(A2_THREADS, 1)
+attention_persistent_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
+                            uint16_t* __restrict__ out, int seq, int dim, int heads, int n_items, float scale_log2e) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * A2_STAGE_BYTES);
+    uint64_t* full_bar = bars;            // [2] loads of the stage have landed
+    uint64_t* s_bar = bars + 2;           // [2] S = QK^T complete in TMEM
+    uint64_t* p_bar = bars + 4;           // [2] P written to shared memory by the four softmax warps
+    uint64_t* o_bar = bars + 6;           // [2] O = PV complete: the stage's shared memory is free again
+    uint64_t* t_bar = bars + 8;           // [2] the epilogue has read O: the slot's TMEM columns are free again
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+
+    const int warp_idx = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
+    if (warp_idx == 0) {
+        if (elect_one()) {
+            tma_prefetch_desc(&tmap_q);
+            tma_prefetch_desc(&tmap_kv);
+        }
+    } else if (warp_idx == 1) {
+        if (elect_one()) {
+            for (int b = 0; b < 2; ++b) {
+                mbar_init(&full_bar[b], 1);
+                mbar_init(&s_bar[b], 1);
+                mbar_init(&p_bar[b], 4);
+                mbar_init(&o_bar[b], 1);
+                mbar_init(&t_bar[b], 4);
+            }
+            fence_mbar_init();
+        }
+        __syncwarp();
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
+    }
+    pdl_launch_dependents();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+
+    // item -> (image, head, query tile); consecutive items share K and V (the two query tiles of a head)
+    auto item_coords = [&](int item, int& img, int& head, int& mt) {
+        mt = item & 1;
+        const int ih = item >> 1;
+        img = ih / heads;
+        head = ih - img * heads;
+    };
+    const int first = static_cast<int>(blockIdx.x), step = static_cast<int>(gridDim.x);
+
+    if (warp_idx == 0) {
+        if (elect_one()) {
+            int it = 0;
+            for (int item = first; item < n_items; item += step, ++it) {
+                const int b = it & 1;
+                if (it >= 2) mbar_wait(&o_bar[b], static_cast<uint32_t>(((it - 2) >> 1) & 1));   // PV(it - 2) done with this stage
+                int img, head, mt;
+                item_coords(item, img, head, mt);
+                const int row0 = img * seq;
+                uint8_t* st = smem + b * A2_STAGE_BYTES;
+                mbar_arrive_expect_tx(&full_bar[b], Q_BYTES + 2 * KV_ROWS * 128);
+                tma_load_2d(&tmap_q, &full_bar[b], st, head * HD, row0 + mt * 128);
+                tma_load_2d(&tmap_kv, &full_bar[b], st + Q_BYTES, dim + head * HD, row0);
+                tma_load_2d(&tmap_kv, &full_bar[b], st + Q_BYTES + KV_BYTES, 2 * dim + head * HD, row0);
+            }
+        }
+    } else if (warp_idx == 1) {
+        if (elect_one()) {
+            constexpr uint32_t idesc_s = umma_idesc_bf16(128, KV_ROWS);
+            constexpr uint32_t idesc_o = umma_idesc_bf16_b_mn(128, HD);
+            auto issue_pv = [&](int it) {
+                const int b = it & 1;
+                mbar_wait(&p_bar[b], static_cast<uint32_t>((it >> 1) & 1));
+                tc_fence_after();
+                const uint32_t st = smem_u32(smem + b * A2_STAGE_BYTES);
+                const uint32_t pk = st + Q_BYTES, pq = st, p3 = st + Q_BYTES + 2 * KV_BYTES, v_addr = st + Q_BYTES + KV_BYTES;
+                const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(b * 256);
+#pragma unroll
+                for (int ks = 0; ks < KV_ROWS / 16; ++ks) {
+                    const int c = ks >> 2;
+                    const uint32_t pa = c == 0 ? pk : (c == 1 ? pk + P_CHUNK_BYTES : (c == 2 ? pq : p3));
+                    const uint64_t p_desc = umma_desc_kmajor(pa, 128) + static_cast<uint64_t>(2 * (ks & 3));
+                    const uint64_t v_desc = umma_desc_kmajor(v_addr + ks * 2048, 128);
+                    umma_bf16(d_tmem, p_desc, v_desc, idesc_o, static_cast<uint32_t>(ks != 0));
+                }
+                umma_commit(&o_bar[b]);
+            };
+            int it = 0;
+            for (int item = first; item < n_items; item += step, ++it) {
+                const int b = it & 1;
+                mbar_wait(&full_bar[b], static_cast<uint32_t>((it >> 1) & 1));
+                if (it >= 2) mbar_wait(&t_bar[b], static_cast<uint32_t>(((it - 2) >> 1) & 1));   // O(it - 2) has been read
+                tc_fence_after();
+                const uint32_t st = smem_u32(smem + b * A2_STAGE_BYTES);
+                const uint64_t q_desc = umma_desc_kmajor(st, 128);
+                const uint64_t k_desc = umma_desc_kmajor(st + Q_BYTES, 128);
+                const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(b * 256);
+#pragma unroll
+                for (int k = 0; k < HD / 16; ++k)
+                    umma_bf16(d_tmem, q_desc + static_cast<uint64_t>(2 * k), k_desc + static_cast<uint64_t>(2 * k), idesc_s,
+                              static_cast<uint32_t>(k != 0));
+                umma_commit(&s_bar[b]);
+                if (it >= 1) issue_pv(it - 1);
+            }
+            if (it >= 1) issue_pv(it - 1);
+        }
+    } else {
+        // ---- softmax + O epilogue: group g = warps 2+4g .. 5+4g takes the items of parity g
+        const int g = (warp_idx - 2) >> 2;
+        const int quad = warp_idx & 3;                          // TMEM lane quadrant this warp may read
+        const int lane = static_cast<int>(lane_id());
+        const int r = quad * 32 + lane;                         // query row inside the tile
+        const uint32_t st = smem_u32(smem + g * A2_STAGE_BYTES);
+        const uint32_t pk = st + Q_BYTES, pq = st, p3 = st + Q_BYTES + 2 * KV_BYTES;
+        auto p_chunk_addr = [&](int c) -> uint32_t { return c == 0 ? pk : (c == 1 ? pk + P_CHUNK_BYTES : (c == 2 ? pq : p3)); };
+        const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(g * 256);
+        const uint32_t p_row = static_cast<uint32_t>(r * 128);
+        int it = g;
+        for (int item = first + g * step; item < n_items; item += 2 * step, it += 2) {
+            const uint32_t ph = static_cast<uint32_t>((it >> 1) & 1);
+            int img, head, mt;
+            item_coords(item, img, head, mt);
+            mbar_wait(&s_bar[g], ph);
+            tc_fence_after();
+            // The softmax is instruction-bound (ncu: 16 k warp instructions per item before this was trimmed), so every
+            // element costs as little as possible: the key mask is only applied in the one 32-column chunk that
+            // straddles `seq`, exp((s - max) * scale) is one FFMA and one MUFU.EX2, and the row sum adds the fp32
+            // values (the bf16 rounding of P is unbiased; summing the rounded values instead cost three more
+            // instructions per element for a 1e-4 relative change of the normaliser).
+            const int full_chunks = seq >> 5;                   // chunks whose 32 keys are all valid
+            // pass 1: row maximum over the valid keys
+            float mx = -FLT_MAX;
+#pragma unroll 1
+            for (int c = 0; c < 7; ++c) {
+                if (c * 32 >= seq) break;
+                uint32_t v[32];
+                tmem_ld_32x32(t_addr + c * 32, v);
+                tmem_ld_wait();
+                if (c < full_chunks) {
+                    float m0 = __uint_as_float(v[0]), m1 = __uint_as_float(v[1]), m2 = __uint_as_float(v[2]), m3 = __uint_as_float(v[3]);
+#pragma unroll
+                    for (int j = 4; j < 32; j += 4) {
+                        m0 = fmaxf(m0, __uint_as_float(v[j]));
+                        m1 = fmaxf(m1, __uint_as_float(v[j + 1]));
+                        m2 = fmaxf(m2, __uint_as_float(v[j + 2]));
+                        m3 = fmaxf(m3, __uint_as_float(v[j + 3]));
+                    }
+                    mx = fmaxf(mx, fmaxf(fmaxf(m0, m1), fmaxf(m2, m3)));
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (c * 32 + j < seq) mx = fmaxf(mx, __uint_as_float(v[j]));
+                }
+            }
+            // pass 2: p = 2^(s * scale - max * scale) as unnormalised bf16 into the K-major swizzled P tiles
+            const float neg_mxs = -mx * scale_log2e;
+            float sum0 = 0.f, sum1 = 0.f;
+#pragma unroll 1
+            for (int c = 0; c < 7; ++c) {
+                float p[32];
+                if (c * 32 < seq) {
+                    uint32_t v[32];
+                    tmem_ld_32x32(t_addr + c * 32, v);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        float e;
+                        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(fmaf(__uint_as_float(v[j]), scale_log2e, neg_mxs)));
+                        p[j] = e;
+                    }
+                    if (c >= full_chunks) {
+#pragma unroll
+                        for (int j = 0; j < 32; ++j)
+                            if (c * 32 + j >= seq) p[j] = 0.f;
+                    }
+#pragma unroll
+                    for (int j = 0; j < 32; j += 2) { sum0 += p[j]; sum1 += p[j + 1]; }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) p[j] = 0.f;
+                }
+                const int chunk = c >> 1;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    uint4 o;
+                    o.x = pack_bf16x2(p[8 * j + 0], p[8 * j + 1]); o.y = pack_bf16x2(p[8 * j + 2], p[8 * j + 3]);
+                    o.z = pack_bf16x2(p[8 * j + 4], p[8 * j + 5]); o.w = pack_bf16x2(p[8 * j + 6], p[8 * j + 7]);
+                    const int piece = ((c & 1) * 4 + j) ^ (r & 7);
+                    st_shared_v4(p_chunk_addr(chunk) + p_row + static_cast<uint32_t>(piece * 16), o);
+                }
+            }
+            const float sum = sum0 + sum1;
+            fence_proxy_async_smem();          // P must be visible to the tensor core's async proxy
+            tc_fence_before();                 // every S read is done before O overwrites the columns
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&p_bar[g]);
+            // ---- O epilogue
+            mbar_wait(&o_bar[g], ph);
+            tc_fence_after();
+            const float inv = 1.0f / sum;
+            const int token = mt * 128 + r;
+            uint4 packed[8];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                uint32_t v[32];
+                tmem_ld_32x32(t_addr + h * 32, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    packed[h * 4 + j].x = pack_bf16x2(__uint_as_float(v[8 * j + 0]) * inv, __uint_as_float(v[8 * j + 1]) * inv);
+                    packed[h * 4 + j].y = pack_bf16x2(__uint_as_float(v[8 * j + 2]) * inv, __uint_as_float(v[8 * j + 3]) * inv);
+                    packed[h * 4 + j].z = pack_bf16x2(__uint_as_float(v[8 * j + 4]) * inv, __uint_as_float(v[8 * j + 5]) * inv);
+                    packed[h * 4 + j].w = pack_bf16x2(__uint_as_float(v[8 * j + 6]) * inv, __uint_as_float(v[8 * j + 7]) * inv);
+                }
+            }
+            tc_fence_before();                 // O is in registers: the slot's TMEM columns may take S(it + 2)
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&t_bar[g]);
+            if (token < seq) {
+                uint4* o = reinterpret_cast<uint4*>(out + (static_cast<size_t>(img * seq + token) * dim + head * HD));
+#pragma unroll
+                for (int j = 0; j < 8; ++j) st_v4(o + j, packed[j]);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp_idx == 1) {
+        tc_fence_after();
+        tmem_dealloc(tmem_base, 512);
+    }
+}
+
 PFN_cuTensorMapEncodeTiled_v12000 g_vit_encode = nullptr;
 
 bool vit_encode_2d(CUtensorMap* m, const void* base, uint64_t cols, uint64_t rows, uint32_t box_cols, uint32_t box_rows) {
@@ -397,6 +644,23 @@ cudaError_t attention_plan_launch(const AttentionPlan& p, void* out, int n, cuda
         attr_set[dev] = true;
     }
     const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(HD));
+    // persistent two-slot kernel unless B2P_ATT_V1 is set (the one-item-per-CTA version, kept for A/B runs) or the
+    // sequence needs other than two query tiles
+    static const bool use_v1 = getenv("B2P_ATT_V1") != nullptr;
+    if (!use_v1 && p.seq > 128 && p.seq <= 256) {
+        static bool attr2_set[64] = {};
+        if (!attr2_set[dev]) {
+            cudaError_t e = cudaFuncSetAttribute(attention_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, A2_SMEM);
+            if (e != cudaSuccess) return e;
+            attr2_set[dev] = true;
+        }
+        int sms = 0;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        const int n_items = n * p.heads * 2;
+        const int grid2 = n_items < sms ? n_items : sms;
+        return launch_pdl(attention_persistent_kernel, dim3(grid2), dim3(A2_THREADS), A2_SMEM, s, p.tmap_q, p.tmap_kv,
+                          static_cast<uint16_t*>(out), p.seq, p.dim, p.heads, n_items, scale_log2e);
+    }
     dim3 grid((p.seq + 127) / 128, p.heads, n);
     return launch_pdl(attention_kernel, grid, dim3(ATT_THREADS), ATT_SMEM, s, p.tmap_q, p.tmap_kv,
                       static_cast<uint16_t*>(out), p.seq, p.dim, scale_log2e);
