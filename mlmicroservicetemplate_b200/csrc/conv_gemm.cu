@@ -11,14 +11,19 @@
 // space-to-depth stem), so no im2col matrix is ever materialised.  W tiles are 2-D tiled TMA.
 // Both land in shared memory in the K-major swizzled layout tcgen05.mma consumes; the
 // accumulator lives in TMEM (two stages, so the epilogue of tile i overlaps the MMAs of tile
-// i+1), and four epilogue warps drain it with tcgen05.ld, add the folded-BN bias and the residual,
-// apply ReLU and store bf16 NHWC (or fp32 logits).
+// i+1), and two groups of four epilogue warps drain it in alternating 64-column chunks with tcgen05.ld, add the
+// folded-BN bias and the residual (TMA-loaded 128 x 64 tiles), apply ReLU / GELU and hand bf16 tiles to TMA stores
+// through swizzled staging buffers (LINEAR: fp32 logits stored directly).
 //
-// Warp roles (192 threads):  warp 0 = TMA producer (one elected lane), warp 1 = TMEM owner +
-// MMA issuer (one elected lane), warps 2..5 = epilogue (TMEM lane quadrant = warp_idx % 4).
+// Warp roles (352 threads):  warp 0 = TMA producer (one elected lane), warp 1 = TMEM owner + MMA issuer (one
+// elected lane), warp 2 = residual loader, warps 3..10 = two epilogue groups (TMEM lane quadrant = warp_idx % 4).
+//
+// Variants: a second A source whose K blocks follow the main operand's (folded projection shortcut); CTA pairs
+// (CTA2: cta_group::2, 256-row MMAs, each CTA loads half of the weight tile); optional tail splitting (the tiles of
+// a partly filled last wave handed out as 64-column pieces); forward / reverse tile order for L2 reuse.
 //
 // Oracle-side equivalent: nn.Conv2d + BatchNorm2d(eval) + ReLU as wired in
-// SP/torchvision/models/resnet.py:89-105,143-163 (BN folded on the host, see weights.py).
+// SP/torchvision/models/resnet.py:89-105,143-163 (BN folded on the host, see program.py: fold_bn).
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
