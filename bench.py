@@ -352,9 +352,9 @@ def main():
         "peak_source": peaks["source"] + " (sustained: kernel timed inside a long step)",
         "flop_per_launch_group": FLOP_PER_IMAGE * BATCH, "ms": k2_ms,
         # dram__bytes_read.sum + dram__bytes_write.sum over the K2 launches of one 256-image ResNet-50 step, from the
-        # ncu pass committed as profiles/r01d_launches_dram_raw_ncu.csv (bytes per launch group, like `achieved`)
-        "traffic": 11.46e9 if (ARCH, BATCH) == ("resnet50", 256) else None,
-        "traffic_source": "profiles/r01d_launches_dram_raw_ncu.csv",
+        # ncu pass committed as profiles/r01j_launches_dram_raw_ncu.csv (bytes per launch group, like `achieved`)
+        "traffic": 8.42e9 if (ARCH, BATCH) == ("resnet50", 256) else None,
+        "traffic_source": "profiles/r01j_launches_dram_raw_ncu.csv",
     }
 
     cpu_baseline = None
