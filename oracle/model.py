@@ -98,3 +98,34 @@ def predict(image_file) -> dict:
         "classes": list(names),
         "result": {names[int(i)]: float(p) for p, i in zip(probs[0], idx[0])},
     }
+
+
+def bf16_weight_model(model: torch.nn.Module) -> torch.nn.Module:
+    """the "bf16 weights, fp32 math" oracle.  A deep copy of a torchvision ResNet whose BatchNorms are
+    folded into the preceding convolutions in fp32 (eval statistics) and whose conv / linear WEIGHTS are then rounded
+    to bf16 — the values the GPU path multiplies with — while every activation and accumulation stays fp32.  The
+    distance GPU <-> this model isolates the GPU's own rounding (bf16 activations between layers, accumulation
+    order) from the unavoidable weight/input quantisation."""
+    import copy
+    from torch.nn.utils.fusion import fuse_conv_bn_eval
+    m = copy.deepcopy(model).eval()
+
+    def fold(parent, conv_name, bn_name):
+        conv, bn = getattr(parent, conv_name), getattr(parent, bn_name)
+        setattr(parent, conv_name, fuse_conv_bn_eval(conv, bn))
+        setattr(parent, bn_name, torch.nn.Identity())
+
+    fold(m, "conv1", "bn1")
+    for layer in (m.layer1, m.layer2, m.layer3, m.layer4):
+        for blk in layer:
+            for i in (1, 2, 3):
+                if hasattr(blk, f"conv{i}"):
+                    fold(blk, f"conv{i}", f"bn{i}")
+            if blk.downsample is not None:
+                blk.downsample[0] = fuse_conv_bn_eval(blk.downsample[0], blk.downsample[1])
+                blk.downsample[1] = torch.nn.Identity()
+    with torch.no_grad():
+        for mod in m.modules():
+            if isinstance(mod, (torch.nn.Conv2d, torch.nn.Linear)):
+                mod.weight.copy_(mod.weight.to(torch.bfloat16).float())
+    return m

@@ -89,6 +89,14 @@ def test_resnet50_b16(cuda_device):
     # (SURVEY §8c c6), so the gate is relative here and the absolute number is reported.
     assert top1 == 1.0
     assert err / scale <= 8e-3
+    # c6: the same logits against the "bf16 weights, fp32 math" oracle (inputs rounded to bf16 as K1 stores them):
+    # what is left is the GPU path's own rounding of the activations between layers
+    q = om.bf16_weight_model(model)
+    xq = torch.cat([om.preprocess(im, 224, 224, 0, 0) for im in ims], 0).to(torch.bfloat16).float()
+    with torch.no_grad():
+        ref_q = q(xq)
+    err_q, scale_q, top1_q = _report("resnet50 b16 vs bf16-weight fp32-math oracle", logits, ref_q)
+    assert top1_q == 1.0 and err_q / scale_q <= 8e-3
 
 
 def test_resnet50_b256_properties(cuda_device):
