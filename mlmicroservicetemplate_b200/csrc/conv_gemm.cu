@@ -43,7 +43,7 @@ constexpr int ACC_STAGES = 2;
 constexpr int SMEM_LIMIT = 227 * 1024;
 constexpr int OUT_CHUNK_BYTES = BLOCK_M * 64 * 2;   // one 128 x 64 bf16 staging tile (128B swizzle)
 constexpr int OUT_BUFS = 2;
-constexpr int RES_STAGES = 2;
+constexpr int RES_STAGES = 4;          // residual kernels: four 16 KB tiles that are residual input AND output staging, two per group
 
 struct GemmArgs {
     int m_rows;       // valid output rows
@@ -86,7 +86,10 @@ struct Cfg {
     static constexpr int B_ROWS = CTA2 ? BLOCK_N / 2 : BLOCK_N;   // a CTA pair splits the weight rows
     static constexpr int B_BYTES = B_ROWS * BLOCK_K * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int OUT_BYTES = OUT_F32 ? 0 : OUT_BUFS * OUT_CHUNK_BYTES;
+    // without a residual: one staging tile per epilogue group.  With one: the residual tile is loaded INTO the staging
+    // tile, updated in place and stored from there, which pays for two tiles per group in the same 64 KB, so that
+    // the residual of a group's next chunk is always in flight while it works on the current one
+    static constexpr int OUT_BYTES = (OUT_F32 || HAS_RES) ? 0 : OUT_BUFS * OUT_CHUNK_BYTES;
     static constexpr int RES_BYTES = HAS_RES ? RES_STAGES * OUT_CHUNK_BYTES : 0;
     static constexpr int BAR_BYTES = 256;
     static constexpr int FIXED = 1024 /*alignment slack*/ + BAR_BYTES + OUT_BYTES + RES_BYTES;
@@ -176,7 +179,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             }
             for (int i = 0; i < RES_STAGES; ++i) {
                 mbar_init(&res_full_bar[i], 1);
-                mbar_init(&res_empty_bar[i], 4);
+                mbar_init(&res_empty_bar[i], 1);      // the group's store leader, once the TMA store has read the tile
             }
             fence_mbar_init();
         }
@@ -306,6 +309,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     } else if (warp_idx == 2) {
         // ================================================================== residual loader
         if (HAS_RES && elect_one()) {
+            // chunk q (numbered over the CTA's whole walk) belongs to group q & 1 and is that group's (q >> 1)-th
+            // chunk: tile 2 * ((q >> 1) & 1) + (q & 1), i.e. the four tiles are simply used round-robin
             int rs = 0;
             uint32_t rphase = 0;
             for (int tile = first_tile; tile < total_items; tile += tile_step) {
@@ -325,9 +330,12 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         // ========================================================================= epilogue
         // Two groups of four warps drain the accumulator: the 64-column chunks are numbered globally
         // (tile after tile) and group g takes the chunks with sequence number % 2 == g.  That number is
-        // also the residual ring stage (RES_STAGES == 2) and the staging buffer, so each group owns one
-        // of each and the two never wait on one another.
-        static_assert(RES_STAGES == 2 && OUT_BUFS == 2, "epilogue groups own one residual stage and one staging buffer each");
+        // also the staging buffer, so each group owns its buffers and the two never wait on one another.
+        // Without a residual a group has ONE staging tile.  With a residual it has TWO tiles that are residual input
+        // and output staging at once: the loader fills a tile with the residual, the group adds its accumulator in
+        // place (a thread only touches its own row) and the tile is stored from where it lies; as soon as that store
+        // has read the tile the loader may fetch the residual of the group's chunk after next into it.
+        static_assert(RES_STAGES == 4 && OUT_BUFS == 2, "two in/out tiles per group with a residual, one staging tile without");
         const int quad = warp_idx & 3;                  // TMEM lanes [32*quad, 32*quad+32)
         const int group = (warp_idx - 3) >> 2;          // 0 or 1
         const int lane = static_cast<int>(lane_id());
@@ -336,8 +344,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const uint32_t bar_id = 1u + static_cast<uint32_t>(group);
         int acc = 0;
         uint32_t acc_phase = 0;
-        const int rs = group;
-        uint32_t rphase = 0;
+        uint32_t nloc = 0;                              // this group's chunk counter (residual kernels)
         const int ob = group;
         uint32_t seq = 0;                               // global chunk sequence number at the start of the tile
         const uint32_t tmem_empty0 = CTA2 ? mapa_shared(smem_u32(&tmem_empty_bar[0]), 0) : 0u;   // the leader's
@@ -377,9 +384,16 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     if (((seq + static_cast<uint32_t>(c64)) & 1u) != static_cast<uint32_t>(group)) continue;
                     const int col0 = n_blk * BLOCK_N + (sub >= 0 ? sub : c64) * 64;   // a piece sits in TMEM columns 0..63
                     uint32_t res_base = 0;
+                    const int io = group + 2 * static_cast<int>(nloc & 1u);            // this chunk's in/out tile
                     if (HAS_RES) {
-                        mbar_wait(&res_full_bar[rs], rphase);
-                        res_base = smem_u32(smem_res + rs * OUT_CHUNK_BYTES) + static_cast<uint32_t>(row_in_tile * 128);
+                        if (store_leader && nloc > 0) {
+                            // the previous chunk's store has read its tile: hand the tile back to the loader now, so
+                            // that the residual of the NEXT chunk travels while this one is being worked on
+                            tma_store_wait_read<0>();
+                            mbar_arrive(&res_empty_bar[group + 2 * static_cast<int>((nloc - 1) & 1u)]);
+                        }
+                        mbar_wait(&res_full_bar[io], (nloc >> 1) & 1u);
+                        res_base = smem_u32(smem_res + io * OUT_CHUNK_BYTES) + static_cast<uint32_t>(row_in_tile * 128);
                     }
                     uint4 packed[8];
 #pragma unroll
@@ -424,15 +438,17 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                             packed[h * 4 + j].w = pack_bf16x2(f[8 * j + 6], f[8 * j + 7]);
                         }
                     }
+                    uint8_t* stage_tile;
                     if (HAS_RES) {
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&res_empty_bar[rs]);
-                        rphase ^= 1u;
+                        stage_tile = smem_res + io * OUT_CHUNK_BYTES;       // in place: every thread rewrites its own row
+                        ++nloc;
+                    } else {
+                        stage_tile = smem_out + ob * OUT_CHUNK_BYTES;
+                        // this group's staging buffer was handed to the TMA engine one chunk ago: it must have been read
+                        if (store_leader) tma_store_wait_read<0>();
+                        named_bar_sync(bar_id, EPI_THREADS);
                     }
-                    // this group's staging buffer was handed to the TMA engine one chunk ago: it must have been read
-                    if (store_leader) tma_store_wait_read<0>();
-                    named_bar_sync(bar_id, EPI_THREADS);
-                    const uint32_t o_base = smem_u32(smem_out + ob * OUT_CHUNK_BYTES) + static_cast<uint32_t>(row_in_tile * 128);
+                    const uint32_t o_base = smem_u32(stage_tile) + static_cast<uint32_t>(row_in_tile * 128);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) {
                         const int chunk16 = j ^ (row_in_tile & 7);
@@ -441,7 +457,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     fence_proxy_async_smem();
                     named_bar_sync(bar_id, EPI_THREADS);
                     if (store_leader) {
-                        tma_store_2d(&tmap_out, smem_out + ob * OUT_CHUNK_BYTES, col0, m_blk * BLOCK_M);
+                        tma_store_2d(&tmap_out, stage_tile, col0, m_blk * BLOCK_M);
                         tma_store_commit();
                     }
                 }
