@@ -28,7 +28,7 @@ constexpr int TILE16K = 128 * 64 * 2;    // one 128 x 64 bf16 tile, 128B swizzle
 constexpr int G1_STAGES = 2;
 constexpr int G1_STAGE_BYTES = 2 * TILE16K;      // A (128 x 64) + W3 (128 x 64)
 constexpr int STG_BUFS = 3;              // staging tiles that double as GEMM2 A operands
-constexpr int RES_BUFS = 2;
+constexpr int RES_BUFS = 3;
 constexpr int W2_BUFS = 3;               // W1 units of (<=128 rows) x 64 columns
 constexpr int PAIR_THREADS = 256;
 constexpr int PAIR_SMEM = 1024 + G1_STAGES * G1_STAGE_BYTES + (STG_BUFS + 1 + RES_BUFS + W2_BUFS) * TILE16K + 512;
@@ -218,21 +218,32 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             uint32_t rb_phase = 0;
             int wb = 0;
             uint32_t wb_phase = 0;
-            for (int t = blockIdx.x; t < args.m_tiles; t += gridDim.x) {
+            // The residual of a chunk is needed at the START of that chunk's epilogue, its W1 tile only afterwards (by
+            // the second GEMM), and both come from this one thread: so the residual loads run RES_BUFS - 1 chunks
+            // ahead of the W1 loads instead of waiting behind them.
+            const int my_tiles = (args.m_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+            const int total_chunks = my_tiles * chunks_per_tile;
+            int res_issued = 0;
+            auto issue_res = [&](int idx) {
+                const int tl = idx / chunks_per_tile, q = idx - tl * chunks_per_tile;
+                const int t = static_cast<int>(blockIdx.x) + tl * static_cast<int>(gridDim.x);
                 const int m0 = (args.reverse ? args.m_tiles - 1 - t : t) * BM;
-                for (int q = 0; q < chunks_per_tile; ++q) {
-                    if (args.has_res) {
-                        mbar_wait(&res_empty[rb], rb_phase ^ 1u);
-                        mbar_arrive_expect_tx(&res_full[rb], TILE16K);
-                        tma_load_2d(&tmap_res, &res_full[rb], smem_res + rb * TILE16K, q * 64, m0);
-                        if (++rb == RES_BUFS) { rb = 0; rb_phase ^= 1u; }
-                    }
-                    for (int u = 0; u < W2_UNITS; ++u) {
-                        mbar_wait(&w2_empty[wb], wb_phase ^ 1u);
-                        mbar_arrive_expect_tx(&w2_full[wb], W2_UNIT_BYTES);
-                        tma_load_2d(&tmap_w1, &w2_full[wb], smem_w2 + wb * TILE16K, q * 64, u * 128);
-                        if (++wb == W2_BUFS) { wb = 0; wb_phase ^= 1u; }
-                    }
+                mbar_wait(&res_empty[rb], rb_phase ^ 1u);
+                mbar_arrive_expect_tx(&res_full[rb], TILE16K);
+                tma_load_2d(&tmap_res, &res_full[rb], smem_res + rb * TILE16K, q * 64, m0);
+                if (++rb == RES_BUFS) { rb = 0; rb_phase ^= 1u; }
+            };
+            for (int c = 0; c < total_chunks; ++c) {
+                if (args.has_res) {
+                    const int ahead = c + RES_BUFS - 1 < total_chunks - 1 ? c + RES_BUFS - 1 : total_chunks - 1;
+                    while (res_issued <= ahead) issue_res(res_issued++);
+                }
+                const int q = c % chunks_per_tile;
+                for (int u = 0; u < W2_UNITS; ++u) {
+                    mbar_wait(&w2_empty[wb], wb_phase ^ 1u);
+                    mbar_arrive_expect_tx(&w2_full[wb], W2_UNIT_BYTES);
+                    tma_load_2d(&tmap_w1, &w2_full[wb], smem_w2 + wb * TILE16K, q * 64, u * 128);
+                    if (++wb == W2_BUFS) { wb = 0; wb_phase ^= 1u; }
                 }
             }
         }
