@@ -13,7 +13,7 @@
 // One CTA owns a 128-row tile across ALL N1 columns (sub-tiles of 128 columns, two 64-column chunks
 // each).  TMEM: two 128-column accumulators for GEMM1 (double buffered) + N2 columns for GEMM2.
 // Warps: 0 = TMA producer (A, W3), 1 = TMEM owner + MMA issuer (both GEMMs), 2 = loader for the
-// residual chunks and W1 tiles, 3 = idle, 4..7 = epilogue.
+// residual chunks and W1 tiles, 3 = idle, 4..7 / 8..11 = two epilogue groups (left / right 64 columns of a sub-tile).
 #include <cstdio>
 #include <cudaTypedefs.h>
 #include "kernels.h"
@@ -27,10 +27,10 @@ constexpr int BN1 = 128;                 // GEMM1 sub-tile width
 constexpr int TILE16K = 128 * 64 * 2;    // one 128 x 64 bf16 tile, 128B swizzle
 constexpr int G1_STAGES = 2;
 constexpr int G1_STAGE_BYTES = 2 * TILE16K;      // A (128 x 64) + W3 (128 x 64)
-constexpr int STG_BUFS = 3;              // staging tiles that double as GEMM2 A operands
-constexpr int RES_BUFS = 3;
+constexpr int STG_BUFS = 4;              // staging tiles that double as GEMM2 A operands: two per epilogue group
+constexpr int RES_BUFS = 2;              // one residual tile per epilogue group
 constexpr int W2_BUFS = 3;               // W1 units of (<=128 rows) x 64 columns
-constexpr int PAIR_THREADS = 256;
+constexpr int PAIR_THREADS = 384;         // TMA, MMA, loader, (idle), two epilogue groups of four warps
 constexpr int PAIR_SMEM = 1024 + G1_STAGES * G1_STAGE_BYTES + (STG_BUFS + 1 + RES_BUFS + W2_BUFS) * TILE16K + 512;
 
 struct PairArgs {
@@ -89,7 +89,7 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     } else if (warp_idx == 1) {
         if (elect_one()) {
             for (int i = 0; i < G1_STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
-            for (int i = 0; i < 2; ++i) { mbar_init(&acc1_full[i], 1); mbar_init(&acc1_empty[i], 4); }
+            for (int i = 0; i < 2; ++i) { mbar_init(&acc1_full[i], 1); mbar_init(&acc1_empty[i], 8); }
             for (int i = 0; i < RES_BUFS; ++i) { mbar_init(&res_full[i], 1); mbar_init(&res_empty[i], 4); }
             for (int i = 0; i < W2_BUFS; ++i) { mbar_init(&w2_full[i], 1); mbar_init(&w2_empty[i], 1); }
             for (int i = 0; i < STG_BUFS; ++i) { mbar_init(&a2_full[i], 1); mbar_init(&a2_free[i], 1); }
@@ -253,22 +253,26 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int lane = static_cast<int>(lane_id());
         const int row = quad * 32 + lane;
         const uint32_t swz = static_cast<uint32_t>(row & 7);
-        const bool leader = (warp_idx == 4) && (lane == 0);
+        // Two groups of four warps: group g takes the g-th 64-column chunk of every 128-column GEMM1 sub-tile (so the
+        // left and right halves of an accumulator stage are drained at the same time), owns residual tile g and the
+        // staging tiles g and g + 2; group 0 also runs the second epilogue (out2) of every tile.
+        const int group = (warp_idx - 4) >> 2;
+        const bool leader = (warp_idx == 4 + 4 * group) && (lane == 0);
+        const uint32_t bar_id = 1u + static_cast<uint32_t>(group);
         const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
         int slot = 0;
         uint32_t slot_phase = 0;
-        int rb = 0;
+        const int rb = group;
         uint32_t rb_phase = 0;
-        int sb = 0;
-        uint32_t sb_phase = 0;          // phase of a2_free[sb] for the NEXT reuse of buffer sb
+        uint32_t mloc = 0;              // this group's chunk counter: staging tile group + 2 * (mloc & 1)
         uint32_t acc2_phase = 0;
         for (int t = blockIdx.x; t < args.m_tiles; t += gridDim.x) {
             const int m0 = (args.reverse ? args.m_tiles - 1 - t : t) * BM;
             for (int nt = 0; nt < args.n1_tiles; ++nt) {
                 mbar_wait(&acc1_full[slot], slot_phase);
                 tc_fence_after();
-#pragma unroll 1
-                for (int c = 0; c < 2; ++c) {
+                {
+                    const int c = group;
                     const int col0 = nt * BN1 + c * 64;
                     if (args.has_res) mbar_wait(&res_full[rb], rb_phase);
                     const uint32_t res_row = smem_u32(smem_res + rb * TILE16K) + static_cast<uint32_t>(row * 128);
@@ -309,33 +313,33 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     if (args.has_res) {
                         __syncwarp();
                         if (lane == 0) mbar_arrive(&res_empty[rb]);
-                        if (++rb == RES_BUFS) { rb = 0; rb_phase ^= 1u; }
+                        rb_phase ^= 1u;
                     }
-                    if (c == 1) {
-                        tc_fence_before();
-                        __syncwarp();
-                        if (lane == 0) mbar_arrive(&acc1_empty[slot]);
-                    }
-                    // staging buffer sb: GEMM2 must have finished reading its previous contents (a2_free) and the
-                    // TMA store issued STG_BUFS chunks ago must have read it (leader's bulk-group wait)
-                    mbar_wait(&a2_free[sb], sb_phase ^ 1u);
-                    if (leader) tma_store_wait_read<STG_BUFS - 1>();
-                    named_bar_sync(1, 128);
+                    tc_fence_before();                     // this warp's reads of the accumulator stage are done
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&acc1_empty[slot]);
+                    // staging tile sb: GEMM2 must have finished reading its previous contents (a2_free) and this
+                    // group's TMA store of two chunks ago must have read it (at most the latest store may be pending)
+                    const int sb = group + 2 * static_cast<int>(mloc & 1u);
+                    mbar_wait(&a2_free[sb], ((mloc >> 1) & 1u) ^ 1u);
+                    if (leader) tma_store_wait_read<1>();
+                    named_bar_sync(bar_id, 128);
                     const uint32_t o_row = smem_u32(smem_stg + sb * TILE16K) + static_cast<uint32_t>(row * 128);
 #pragma unroll
                     for (int j = 0; j < 8; ++j) st_shared_v4(o_row + ((static_cast<uint32_t>(j) ^ swz) << 4), packed[j]);
                     fence_proxy_async_smem();
-                    named_bar_sync(1, 128);
+                    named_bar_sync(bar_id, 128);
                     if (leader) {
                         tma_store_2d(&tmap_out1, smem_stg + sb * TILE16K, col0, m0);
                         tma_store_commit();
                         mbar_arrive(&a2_full[sb]);          // the tile is also GEMM2's A operand now
                     }
-                    if (++sb == STG_BUFS) { sb = 0; sb_phase ^= 1u; }
+                    ++mloc;
                 }
                 if (++slot == 2) { slot = 0; slot_phase ^= 1u; }
             }
-            // ---- second epilogue: out2 = relu(acc2 + bias2)
+            // ---- second epilogue: out2 = relu(acc2 + bias2), group 0 only (group 1 is already on the next tile)
+            if (group != 0) continue;
             mbar_wait(acc2_full, acc2_phase);
             acc2_phase ^= 1u;
             tc_fence_after();
