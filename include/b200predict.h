@@ -224,7 +224,7 @@ typedef struct b2p_jpeg_stats {
 
 int32_t b2p_jpeg_create(int32_t device, b2p_jpeg** out);
 int32_t b2p_jpeg_destroy(b2p_jpeg* d);
-const char* b2p_jpeg_last_error(const b2p_jpeg* d);   /* d may be NULL: inspect / create failures   */
+const char* b2p_jpeg_last_error(const b2p_jpeg* d);   /* d may be NULL: the calling THREAD's last inspect / create failure */
 int32_t b2p_jpeg_stats_get(b2p_jpeg* d, b2p_jpeg_stats* out);   /* waits for the most recent call       */
 
 /* Decodes n files (HOST pointers, any memory) into the DEVICE slab: image i becomes uint8 [h][w][3] at

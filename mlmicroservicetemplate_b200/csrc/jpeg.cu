@@ -897,7 +897,7 @@ struct b2p_jpeg {
 
 namespace {
 
-char g_jpeg_error[512] = "";
+thread_local char g_jpeg_error[512] = "";   // per thread: inspect() is called from many request threads at once
 
 void jerr(b2p_jpeg* d, const char* fmt, ...) {
     char* dst = d ? d->err : g_jpeg_error;
