@@ -126,7 +126,19 @@ __global__ void avgpool_kernel(const uint4* __restrict__ x, uint4* __restrict__ 
         const int img = static_cast<int>(i / c8);
         float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         const uint4* p = x + static_cast<size_t>(img) * hw * c8 + cg;
-        for (int j = 0; j < hw; ++j) {
+        // seven independent loads in flight per thread (49 = 7 x 7 for ResNet), accumulated in row order
+        int j = 0;
+        for (; j + 7 <= hw; j += 7) {
+            uint4 v[7];
+#pragma unroll
+            for (int u = 0; u < 7; ++u) v[u] = __ldg(p + static_cast<size_t>(j + u) * c8);
+#pragma unroll
+            for (int u = 0; u < 7; ++u) {
+                a[0] += bf16_lo(v[u].x); a[1] += bf16_hi(v[u].x); a[2] += bf16_lo(v[u].y); a[3] += bf16_hi(v[u].y);
+                a[4] += bf16_lo(v[u].z); a[5] += bf16_hi(v[u].z); a[6] += bf16_lo(v[u].w); a[7] += bf16_hi(v[u].w);
+            }
+        }
+        for (; j < hw; ++j) {
             const uint4 v = __ldg(p + static_cast<size_t>(j) * c8);
             a[0] += bf16_lo(v.x); a[1] += bf16_hi(v.x); a[2] += bf16_lo(v.y); a[3] += bf16_hi(v.y);
             a[4] += bf16_lo(v.z); a[5] += bf16_hi(v.z); a[6] += bf16_lo(v.w); a[7] += bf16_hi(v.w);
