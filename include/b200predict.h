@@ -140,7 +140,9 @@ int32_t b2p_stats_get(b2p_handle* h, b2p_stats* out);
  * antialiased resize + crop + /255 + (x-mean)/std + HWC->NCHW.  `slab` is a DEVICE pointer to the
  * uint8 images, `imgs` a HOST array of n descriptors (copied before return).  `out` is a device
  * tensor [n,3,224,224], bf16 when out_f32 == 0, fp32 otherwise (the fp32 form exists for the
- * 1e-6 parity gate).                                                                           */
+ * 1e-6 parity gate).  Precondition (not checkable here, the slab size is unknown): every
+ * [offset, offset + h*w*3) lies inside the caller's slab.  b2p_predict_host and b2p_jpeg_decode,
+ * which are told the slab size, check it and fail with B2P_E_ARG.                              */
 int32_t b2p_preprocess(b2p_handle* h, const uint8_t* slab, const b2p_image* imgs, int32_t n,
                        void* out, int32_t out_f32, void* stream);
 

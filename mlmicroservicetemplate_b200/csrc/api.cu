@@ -12,7 +12,9 @@ using namespace b2p;
 
 namespace {
 
-char g_create_error[512] = "";
+// Error text of calls that have no handle (b2p_create, b2p_head_static): one buffer per calling THREAD, because
+// init() builds the replicas of several GPUs from several threads at once.
+thread_local char g_create_error[512] = "";
 
 struct OpPlan {
     b2p_op op;
@@ -36,6 +38,7 @@ struct b2p_handle {
     int num_sms = 0;
     int max_batch = 0;
     int chunk = 0;                       // images per pass through the program
+    bool alternate = true;               // alternate the tile direction layer by layer (B2P_NO_ALTERNATE, read at create)
     int64_t in_elems = 0, out_elems = 0;
     int classes = 0;
     std::vector<OpPlan> ops;
@@ -130,6 +133,24 @@ int validate_desc(const b2p_model_desc* d) {
             o.kind == B2P_OP_TOKENS || o.kind == B2P_OP_LAYERNORM || o.kind == B2P_OP_CONV_PAIR) {
             if (o.weight < 0 || o.weight >= d->n_blobs || o.bias < 0 || o.bias >= d->n_blobs) return B2P_E_ARG;
         }
+        // every op: the slots it touches must hold the tensors its shape fields describe (a malformed program
+        // would otherwise read or write out of bounds on the device)
+        if (o.in_h <= 0 || o.in_w <= 0 || o.in_c <= 0 || o.out_h <= 0 || o.out_w <= 0 || o.out_c <= 0) return B2P_E_ARG;
+        auto holds = [&](int s, int64_t need) {
+            if (s == B2P_SLOT_INPUT) return need <= d->in_elems_per_image;
+            if (s == B2P_SLOT_OUTPUT) return need <= d->out_elems_per_image;
+            return need <= d->slot_elems[s];
+        };
+        int64_t in_need = static_cast<int64_t>(o.in_h) * o.in_w * o.in_c;
+        int64_t out_need = static_cast<int64_t>(o.out_h) * o.out_w * o.out_c;
+        if (o.kind == B2P_OP_TOKENS) in_need = static_cast<int64_t>(o.in_h - 1) * o.in_w * o.in_c;   // the class token is added
+        if (o.kind == B2P_OP_ATTENTION) in_need *= 3;                                               // packed Q | K | V
+        if (!holds(o.src, in_need) || !holds(o.dst, out_need)) return B2P_E_ARG;
+        if (o.res != B2P_SLOT_NONE && !holds(o.res, out_need)) return B2P_E_ARG;
+        if (o.src2_c > 0) {
+            const int64_t st = o.src2_stride > 0 ? o.src2_stride : 1;
+            if (!holds(o.src2, static_cast<int64_t>(o.out_h) * st * o.out_w * st * o.src2_c)) return B2P_E_ARG;
+        }
     }
     return B2P_OK;
 }
@@ -138,7 +159,7 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
     // Tile direction: a GEMM layer walks its row tiles in the direction OPPOSITE to the last op that
     // touched its input, so it starts on the rows that are still resident in L2 (126 MB) instead of on
     // the ones that were evicted first.  Slot -> direction of the last toucher (0 = ascending).
-    const bool alternate = getenv("B2P_NO_ALTERNATE") == nullptr;
+    const bool alternate = h->alternate;
     std::vector<int> touch(h->slots.size() + 1, 0);
     auto touch_of = [&](int slot) -> int& { return touch[slot >= 0 && slot < (int)h->slots.size() ? slot : h->slots.size()]; };
     for (int off = 0; off < n; off += h->chunk) {
@@ -159,6 +180,8 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
             const b2p_op& o = p.op;
             const void* src = slot_ptr(h, o.src, x, out, off);
             void* dst = slot_ptr(h, o.dst, x, out, off);
+            if (dst && o.dst == B2P_SLOT_OUTPUT)    // chunk `off` of the caller's output (fp32 logits for LINEAR, else bf16)
+                dst = static_cast<uint8_t*>(dst) + static_cast<size_t>(off) * h->out_elems * (o.kind == B2P_OP_LINEAR ? 4 : 2);
             const void* res = o.res == B2P_SLOT_NONE ? nullptr : slot_ptr(h, o.res, x, out, off);
             if (!src || !dst) { set_error(h, "program references an unallocated slot"); return B2P_E_ARG; }
             cudaError_t e = cudaSuccess;
@@ -166,8 +189,6 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
                 case B2P_OP_CONV:
                 case B2P_OP_LINEAR: {
                     if (p.use_c3) {
-                        if (o.dst == B2P_SLOT_OUTPUT)
-                            dst = static_cast<uint8_t*>(dst) + static_cast<size_t>(off) * h->out_elems * 2;
                         if (p.src_external || p.dst_external || p.res_external) {
                             char eb[256] = "";
                             if (!conv3x3_c64_plan_set(p.c3, src, dst, res, nb, eb, sizeof eb)) {
@@ -177,10 +198,6 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
                         }
                         e = conv3x3_c64_launch(p.c3, nb, o.relu, op_dir, h->num_sms, st);
                         break;
-                    }
-                    if (o.dst == B2P_SLOT_OUTPUT) {
-                        const size_t esz = o.kind == B2P_OP_LINEAR ? 4 : 2;
-                        dst = static_cast<uint8_t*>(dst) + static_cast<size_t>(off) * h->out_elems * esz;
                     }
                     if (p.src_external) {
                         // A-operand map points into the caller's buffer: encode it for this chunk
@@ -201,8 +218,6 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
                     break;
                 }
                 case B2P_OP_STEM_CONV: {
-                    if (o.dst == B2P_SLOT_OUTPUT)
-                        dst = static_cast<uint8_t*>(dst) + static_cast<size_t>(off) * h->out_elems * 2;
                     if (o.src == B2P_SLOT_INPUT || o.dst == B2P_SLOT_OUTPUT) {
                         char eb[256] = "";
                         if (!stem_plan_init(p.stem, src, dst, nb, o.reserved[0], eb, sizeof eb)) {
@@ -225,8 +240,6 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
                     break;
                 case B2P_OP_LAYERNORM: {
                     const bool cls_only = o.reserved[0] != 0;
-                    if (o.dst == B2P_SLOT_OUTPUT)
-                        dst = static_cast<uint8_t*>(dst) + static_cast<size_t>(off) * h->out_elems * 2;
                     e = launch_layernorm(src, static_cast<const float*>(h->blobs[o.weight]),
                                          static_cast<const float*>(h->blobs[o.bias]), dst,
                                          cls_only ? nb : static_cast<long>(nb) * o.in_h, o.in_c,
@@ -234,8 +247,6 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
                     break;
                 }
                 case B2P_OP_ATTENTION: {
-                    if (o.dst == B2P_SLOT_OUTPUT)
-                        dst = static_cast<uint8_t*>(dst) + static_cast<size_t>(off) * h->out_elems * 2;
                     if (o.src == B2P_SLOT_INPUT) {
                         char eb[256] = "";
                         if (!attention_plan_init(p.att, src, nb, o.in_h, o.in_c, o.reserved[0], eb, sizeof eb)) {
@@ -380,6 +391,7 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
     h->chunk = (desc->sub_batch > 0 && desc->sub_batch < desc->max_batch) ? desc->sub_batch : desc->max_batch;
     h->in_elems = desc->in_elems_per_image;
     h->out_elems = desc->out_elems_per_image;
+    h->alternate = getenv("B2P_NO_ALTERNATE") == nullptr;
 
 #define B2P_FAIL(code, ...)                         \
     do {                                            \
@@ -674,6 +686,15 @@ int32_t b2p_predict_host(b2p_handle* h, const uint8_t* slab_host, int64_t slab_b
     if (h->classes <= 0) { set_error(h, "program has no classifier output"); return B2P_E_ARG; }
     if (n > h->max_batch) { set_error(h, "n=%d exceeds max_batch=%d", n, h->max_batch); return B2P_E_LIMIT; }
     if (k <= 0 || k > B2P_MAX_TOPK) { set_error(h, "k=%d out of range", k); return B2P_E_LIMIT; }
+    for (int i = 0; i < n; ++i) {
+        // every descriptor must lie inside the slab that is about to be copied (K1 reads h*w*3 bytes at offset)
+        if (imgs[i].offset < 0 || imgs[i].h <= 0 || imgs[i].w <= 0 ||
+            imgs[i].offset + static_cast<int64_t>(imgs[i].h) * imgs[i].w * 3 > slab_bytes) {
+            set_error(h, "image %d: [%lld, +%d x %d x 3) is outside the %lld-byte slab", i, (long long)imgs[i].offset,
+                      imgs[i].h, imgs[i].w, (long long)slab_bytes);
+            return B2P_E_ARG;
+        }
+    }
     B2P_CUDA(h, cudaSetDevice(h->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int si = h->slab_idx;

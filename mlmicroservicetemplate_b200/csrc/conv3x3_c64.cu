@@ -17,6 +17,7 @@
 //   * the nine 64x64 weight tiles (72 KB) stay in shared memory for the lifetime of the CTA;
 //   * epilogue: two groups of four warps (one per TMEM stage): bias, residual (TMA-loaded), ReLU, bf16,
 //     swizzled staging, two 56-row TMA stores.
+#include <atomic>
 #include <cstdio>
 #include <cudaTypedefs.h>
 #include "kernels.h"
@@ -339,25 +340,25 @@ bool conv3x3_c64_plan_set(Conv3x3Plan& p, const void* src, void* dst, const void
 cudaError_t conv3x3_c64_launch(const Conv3x3Plan& p, int n, int relu, int reverse, int num_sms, cudaStream_t s) {
     const int total = n * (HW / 2);
     const int grid = total < num_sms ? total : num_sms;
-    static bool attr_set[64][2] = {};
+    static std::atomic<bool> attr_set[64][2];   // zero-initialised; replicas of different GPUs launch from different threads
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
     if (p.has_res) {
-        if (!attr_set[dev][1]) {
+        if (!attr_set[dev][1].load(std::memory_order_acquire)) {
             cudaError_t e = cudaFuncSetAttribute(conv3x3_c64_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                  C3Cfg<true>::SMEM);
             if (e != cudaSuccess) return e;
-            attr_set[dev][1] = true;
+            attr_set[dev][1].store(true, std::memory_order_release);
         }
         return launch_pdl(conv3x3_c64_kernel<true>, dim3(grid), dim3(C3_THREADS), C3Cfg<true>::SMEM, s, p.tmap_in, p.tmap_out, p.tmap_res,
                           p.tmap_w, p.bias, n, relu, reverse);
     }
-    if (!attr_set[dev][0]) {
+    if (!attr_set[dev][0].load(std::memory_order_acquire)) {
         cudaError_t e = cudaFuncSetAttribute(conv3x3_c64_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              C3Cfg<false>::SMEM);
         if (e != cudaSuccess) return e;
-        attr_set[dev][0] = true;
+        attr_set[dev][0].store(true, std::memory_order_release);
     }
     return launch_pdl(conv3x3_c64_kernel<false>, dim3(grid), dim3(C3_THREADS), C3Cfg<false>::SMEM, s, p.tmap_in, p.tmap_out, p.tmap_res,
                       p.tmap_w, p.bias, n, relu, reverse);

@@ -24,6 +24,7 @@
 //
 // Oracle-side equivalent: nn.Conv2d + BatchNorm2d(eval) + ReLU as wired in
 // SP/torchvision/models/resnet.py:89-105,143-163 (BN folded on the host, see program.py: fold_bn).
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -499,15 +500,15 @@ template <int BLOCK_N, int BLOCK_K, bool IM2COL, bool OUT_F32, bool HAS_RES, boo
 cudaError_t launch_variant(const GemmPlan& p, const GemmArgs& a, int grid, cudaStream_t stream) {
     using C = Cfg<BLOCK_N, BLOCK_K, OUT_F32, HAS_RES, CTA2>;
     auto kern = conv_gemm_kernel<BLOCK_N, BLOCK_K, IM2COL, OUT_F32, HAS_RES, CTA2>;
-    static bool attr_set[64] = {};   // per instantiation, per device (one replica thread per device)
+    static std::atomic<bool> attr_set[64];   // per instantiation, per device; zero-initialised, set from any thread
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
-    if (!attr_set[dev]) {
+    if (!attr_set[dev].load(std::memory_order_acquire)) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                              C::SMEM_BYTES);
         if (e != cudaSuccess) return e;
-        attr_set[dev] = true;
+        attr_set[dev].store(true, std::memory_order_release);
     }
     if (!CTA2) {
         return launch_pdl(kern, dim3(grid), dim3(NUM_THREADS), C::SMEM_BYTES, stream, p.tmap_a, p.tmap_b, p.tmap_out,
@@ -627,7 +628,7 @@ bool gemm_plan_init(GemmPlan& p, const b2p_op& op, const void* weight_dev, int64
     // Tile width: fewest (waves x tile width) at capacity; ties go to the wider tile, which
     // re-reads the activation tile fewer times.
     // CTA pairs (cta_group::2, 256-row MMAs) halve the weight traffic per SM.  Measured per layer on ResNet-50 b256
-    // (profiles/r01g_cta2_layers.md): 5-12 % faster for 256-wide tiles without a residual, 15-35 % SLOWER for
+    // (profiles/r01g_cta2_ab.txt): 5-12 % faster for 256-wide tiles without a residual, 15-35 % SLOWER for
     // 128-wide tiles and slightly slower with a residual stream, so that is the policy.  B2P_CTA2=all / none
     // overrides it for A/B measurements.
     static const char* cta2_env = getenv("B2P_CTA2");

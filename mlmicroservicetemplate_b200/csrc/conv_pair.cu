@@ -14,6 +14,7 @@
 // each).  TMEM: two 128-column accumulators for GEMM1 (double buffered) + N2 columns for GEMM2.
 // Warps: 0 = TMA producer (A, W3), 1 = TMEM owner + MMA issuer (both GEMMs), 2 = loader for the
 // residual chunks and W1 tiles, 3 = idle, 4..7 / 8..11 = two epilogue groups (left / right 64 columns of a sub-tile).
+#include <atomic>
 #include <cstdio>
 #include <cudaTypedefs.h>
 #include "kernels.h"
@@ -412,14 +413,14 @@ bool pair_encode(CUtensorMap* m, const void* base, uint64_t cols, uint64_t rows,
 
 template <int N2>
 cudaError_t launch_pair(const PairPlan& p, const PairArgs& a, int grid, cudaStream_t s) {
-    static bool attr_set[64] = {};
+    static std::atomic<bool> attr_set[64];   // zero-initialised; replicas of different GPUs launch from different threads
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
-    if (!attr_set[dev]) {
+    if (!attr_set[dev].load(std::memory_order_acquire)) {
         cudaError_t e = cudaFuncSetAttribute(conv_pair_kernel<N2>, cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM);
         if (e != cudaSuccess) return e;
-        attr_set[dev] = true;
+        attr_set[dev].store(true, std::memory_order_release);
     }
     return launch_pdl(conv_pair_kernel<N2>, dim3(grid), dim3(PAIR_THREADS), PAIR_SMEM, s, p.tmap_a, p.tmap_w3, p.tmap_res,
                       p.tmap_out1, p.tmap_w1, p.tmap_out2, p.tmap_a2, a);

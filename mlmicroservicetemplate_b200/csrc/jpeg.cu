@@ -1228,7 +1228,7 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
         }();
         int64_t want = (max_seg_bits + min_chunk - 1) / min_chunk;
         want = (want + 31) / 32 * 32;
-        const int debug_rounds = getenv("B2P_JPEG_DEBUG_ROUNDS") != nullptr;
+        static const int debug_rounds = getenv("B2P_JPEG_DEBUG_ROUNDS") != nullptr;   // read once
         // segments that want more than one CTA's worth of threads are spread over a cluster of CTAs (other SMs):
         // B2P_JPEG_CLUSTER caps the cluster size (1 = never; default 4: measured on 32 x 1080p files the Huffman
         // kernel takes 2.43 / 1.39 / 1.07 / 3.1 ms with 1 / 2 / 4 / 8 CTAs per file — 1024-thread CTAs are one per SM,

@@ -17,6 +17,7 @@
 // vertical max in registers, applies bias+ReLU (both commute with max), rounds to bf16, exchanges
 // columns through shared memory for the horizontal 3-tap max and TMA-stores the pooled row
 // [56][64].  The 411 MB/256-image stem activation never reaches HBM.
+#include <atomic>
 #include <cstdio>
 #include <cuda_bf16.h>
 #include <cudaTypedefs.h>
@@ -365,25 +366,25 @@ bool stem_plan_init(StemPlan& p, const void* src_s2d, void* dst, int batch_cap, 
 cudaError_t stem_plan_launch(const StemPlan& p, int n, int relu, int num_sms, cudaStream_t stream) {
     const int total = n * (p.pool ? 56 : 112);
     const int grid = total < num_sms ? total : num_sms;
-    static bool attr_set[64][2] = {};
+    static std::atomic<bool> attr_set[64][2];   // zero-initialised; replicas of different GPUs launch from different threads
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
     if (p.pool) {
-        if (!attr_set[dev][1]) {
+        if (!attr_set[dev][1].load(std::memory_order_acquire)) {
             cudaError_t e = cudaFuncSetAttribute(stem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                  StemCfg<true>::SMEM_BYTES);
             if (e != cudaSuccess) return e;
-            attr_set[dev][1] = true;
+            attr_set[dev][1].store(true, std::memory_order_release);
         }
         return launch_pdl(stem_kernel<true>, dim3(grid), dim3(STEM_THREADS), StemCfg<true>::SMEM_BYTES, stream, p.tmap_in,
                           p.tmap_out, p.w_image, p.bias, n, relu);
     } else {
-        if (!attr_set[dev][0]) {
+        if (!attr_set[dev][0].load(std::memory_order_acquire)) {
             cudaError_t e = cudaFuncSetAttribute(stem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                                  StemCfg<false>::SMEM_BYTES);
             if (e != cudaSuccess) return e;
-            attr_set[dev][0] = true;
+            attr_set[dev][0].store(true, std::memory_order_release);
         }
         return launch_pdl(stem_kernel<false>, dim3(grid), dim3(STEM_THREADS), StemCfg<false>::SMEM_BYTES, stream, p.tmap_in,
                           p.tmap_out, p.w_image, p.bias, n, relu);

@@ -8,6 +8,7 @@
 // The linear layers around them (packed QKV, out-proj, MLP fc1+GELU, fc2) run on the generic
 // conv_gemm kernel as 1x1 convolutions over a 197x1 "image".
 #include <cfloat>
+#include <atomic>
 #include <cstdio>
 #include <cstdlib>
 #include <cudaTypedefs.h>
@@ -634,14 +635,14 @@ bool attention_plan_init(AttentionPlan& p, const void* qkv, int batch_cap, int s
 }
 
 cudaError_t attention_plan_launch(const AttentionPlan& p, void* out, int n, cudaStream_t s) {
-    static bool attr_set[64] = {};
+    static std::atomic<bool> attr_set[64];   // zero-initialised; replicas of different GPUs launch from different threads
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
-    if (!attr_set[dev]) {
+    if (!attr_set[dev].load(std::memory_order_acquire)) {
         cudaError_t e = cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM);
         if (e != cudaSuccess) return e;
-        attr_set[dev] = true;
+        attr_set[dev].store(true, std::memory_order_release);
     }
     const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(HD));
     // persistent two-slot kernel unless B2P_ATT_V1 is set (the one-item-per-CTA version, kept for A/B runs) or the

@@ -4,9 +4,11 @@ round-robin dispatcher.
 The reference serves one request at a time on the event loop (src/server/main.py:135 calls
 predict() synchronously).  Here predict() enqueues a decoded uint8 HWC image and waits on a future;
 a batcher thread groups requests (up to MAX_BATCH, or whatever arrived within MAX_WAIT_US of the
-first one) and hands whole batches round-robin to one worker thread per GPU.  A worker copies the
-batch into its pinned host slab and makes ONE call into the C ABI (b2p_predict_host): H2D copy,
-K1 preprocess, K2 forward, K3 softmax/top-k and the D2H copy of k (prob, index) pairs per image.
+first one) and hands whole batches to one worker thread per GPU — to the replica with the fewest images
+in flight, in rotation while they are level.  A worker copies the batch into one of its TWO pinned host
+slabs and makes ONE asynchronous call into the C ABI (b2p_predict_host): H2D copy, K1 preprocess, K2
+forward, K3 softmax/top-k and the D2H copy of k (prob, index) pairs per image; it submits batch i+1
+before it waits for batch i, so the host-side packing of one batch runs under the GPU work of the other.
 Uploads that are baseline JPEGs can skip the host decoder altogether (JpegFile): their bytes are
 decoded by b2p_jpeg_decode straight into the device slab and the device-resident chain (b2p_predict)
 runs on it.
@@ -71,7 +73,10 @@ class _Request:
 
 
 class GpuReplicaWorker:
-    """One replica: a b2p handle on one GPU, its stream and a pinned host slab."""
+    """One replica: a b2p handle on one GPU, its stream and two pinned host slabs (+ result buffers), used
+    alternately so that batch i+1 is packed and submitted while batch i is still on the GPU."""
+
+    DEPTH = 2
 
     def __init__(self, device: int, program, max_batch: int, topk: int, mode: str, sub_batch: int = 0,
                  slab_bytes: int = 64 << 20):
@@ -88,37 +93,42 @@ class GpuReplicaWorker:
         with torch.cuda.device(device):
             self.replica = B.Replica(device, program, max_batch=max_batch, sub_batch=sub_batch)
             self.stream = torch.cuda.Stream(device=device)
-            self.slab = torch.empty(slab_bytes, dtype=torch.uint8, pin_memory=True)
-            self.probs = torch.empty((max_batch, topk), dtype=torch.float32, pin_memory=True)
-            self.idx = torch.empty((max_batch, topk), dtype=torch.int32, pin_memory=True)
-        self.slab_np = self.slab.numpy()
-        # GPU JPEG decode (created on first use): decoder object, device slab, device result buffers
+            self.slabs = [torch.empty(slab_bytes, dtype=torch.uint8, pin_memory=True) for _ in range(self.DEPTH)]
+            self.probs = [torch.empty((max_batch, topk), dtype=torch.float32, pin_memory=True) for _ in range(self.DEPTH)]
+            self.idx = [torch.empty((max_batch, topk), dtype=torch.int32, pin_memory=True) for _ in range(self.DEPTH)]
+            self.done = [torch.cuda.Event() for _ in range(self.DEPTH)]
+        self.slabs_np = [t.numpy() for t in self.slabs]
+        self.slot = 0
+        # GPU JPEG decode (created on first use): decoder object, device slabs, device result buffers
         self.jpeg = None
-        self.dev_slab = None
+        self.dev_slab = [None] * self.DEPTH
         self.dev_status = None
         self.dev_probs = None
         self.dev_idx = None
         self.status_host = None
 
-    def _ensure_jpeg(self, nbytes: int) -> None:
+    def _ensure_jpeg(self, slot: int, nbytes: int) -> None:
         torch = self.torch
+        dev = f"cuda:{self.device}"
         if self.jpeg is None:
             self.jpeg = self.B.JpegDecoder(self.device)
-            self.dev_status = torch.zeros(self.max_batch, dtype=torch.int32, device=f"cuda:{self.device}")
-            self.dev_probs = torch.empty((self.max_batch, self.topk), dtype=torch.float32, device=f"cuda:{self.device}")
-            self.dev_idx = torch.empty((self.max_batch, self.topk), dtype=torch.int32, device=f"cuda:{self.device}")
-            self.status_host = torch.zeros(self.max_batch, dtype=torch.int32, pin_memory=True)
-        if self.dev_slab is None or nbytes > self.dev_slab.numel():
+            self.dev_status = [torch.zeros(self.max_batch, dtype=torch.int32, device=dev) for _ in range(self.DEPTH)]
+            self.dev_probs = [torch.empty((self.max_batch, self.topk), dtype=torch.float32, device=dev) for _ in range(self.DEPTH)]
+            self.dev_idx = [torch.empty((self.max_batch, self.topk), dtype=torch.int32, device=dev) for _ in range(self.DEPTH)]
+            self.status_host = [torch.zeros(self.max_batch, dtype=torch.int32, pin_memory=True) for _ in range(self.DEPTH)]
+        if self.dev_slab[slot] is None or nbytes > self.dev_slab[slot].numel():
             self.stream.synchronize()
-            self.dev_slab = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=f"cuda:{self.device}")
+            self.dev_slab[slot] = torch.empty(int(nbytes * 1.25) + 256, dtype=torch.uint8, device=dev)
 
-    def _ensure_slab(self, nbytes: int) -> None:
-        if nbytes > self.slab.numel():
-            self.stream.synchronize()
-            self.slab = self.torch.empty(int(nbytes * 1.25), dtype=self.torch.uint8, pin_memory=True)
-            self.slab_np = self.slab.numpy()
+    def _ensure_slab(self, slot: int, nbytes: int) -> None:
+        if nbytes > self.slabs[slot].numel():
+            self.done[slot].synchronize()        # the previous batch of this slot has left the slab
+            self.slabs[slot] = self.torch.empty(int(nbytes * 1.25), dtype=self.torch.uint8, pin_memory=True)
+            self.slabs_np[slot] = self.slabs[slot].numpy()
 
-    def run_batch(self, images: Sequence[np.ndarray]):
+    def submit_batch(self, images: Sequence[np.ndarray]):
+        """Packs the batch into the next pinned slab and queues the whole chain on the stream; returns a ticket for
+        collect().  At most DEPTH tickets may be outstanding (the slab of a ticket is reused DEPTH submits later)."""
         n = len(images)
         if n == 0 or n > self.max_batch:
             raise ValueError(f"batch of {n} outside 1..{self.max_batch}")
@@ -137,46 +147,69 @@ class GpuReplicaWorker:
         descs = self.B.make_images(geoms)
         jpeg_items = [i for i, im in enumerate(images) if isinstance(im, JpegFile)]
         host_items = [i for i, im in enumerate(images) if not isinstance(im, JpegFile)]
+        s = self.slot
+        self.slot = (s + 1) % self.DEPTH
+        self.done[s].synchronize()               # slot s's previous batch (DEPTH submits ago) is complete
         if host_items:
-            self._ensure_slab(total)
+            self._ensure_slab(s, total)
+            slab_np = self.slabs_np[s]
             for i in host_items:
-                self.slab_np[offs[i]:offs[i] + images[i].size] = images[i].reshape(-1)
+                slab_np[offs[i]:offs[i] + images[i].size] = images[i].reshape(-1)
+        torch = self.torch
         if not jpeg_items:
-            with self.torch.cuda.device(self.device):
-                self.replica.predict_host(self.slab, total, descs, n, self.topk, self.probs, self.idx, stream=self.stream)
-                self.stream.synchronize()
-            return self.probs[:n].numpy().copy(), self.idx[:n].numpy().copy()
+            with torch.cuda.device(self.device):
+                self.replica.predict_host(self.slabs[s], total, descs, n, self.topk, self.probs[s], self.idx[s],
+                                          stream=self.stream)
+                self.done[s].record(self.stream)
+            return (s, n, ())
         # At least one file is decoded on the GPU: the batch slab lives in HBM.  Host-decoded images are copied
         # into it, JPEG files are decoded into it (K-J1..J3), then the device-resident predict chain runs.
-        torch = self.torch
         with torch.cuda.device(self.device), torch.cuda.stream(self.stream):
-            self._ensure_jpeg(total)
+            self._ensure_jpeg(s, total)
+            dev_slab = self.dev_slab[s]
             if host_items:
                 lo = min(offs[i] for i in host_items)
                 hi = max(offs[i] + shapes[i][0] * shapes[i][1] * 3 for i in host_items)
-                self.dev_slab[lo:hi].copy_(self.slab[lo:hi], non_blocking=True)
-            self.jpeg.decode([images[i].data for i in jpeg_items], self.dev_slab, self.dev_slab.numel(),
-                             [offs[i] for i in jpeg_items], status=self.dev_status, stream=self.stream)
-            self.replica.predict(self.dev_slab, descs, n, self.topk, self.dev_probs, self.dev_idx, stream=self.stream)
-            self.probs[:n].copy_(self.dev_probs[:n], non_blocking=True)
-            self.idx[:n].copy_(self.dev_idx[:n], non_blocking=True)
-            self.status_host[:len(jpeg_items)].copy_(self.dev_status[:len(jpeg_items)], non_blocking=True)
-            self.stream.synchronize()
+                dev_slab[lo:hi].copy_(self.slabs[s][lo:hi], non_blocking=True)
+            self.jpeg.decode([images[i].data for i in jpeg_items], dev_slab, dev_slab.numel(),
+                             [offs[i] for i in jpeg_items], status=self.dev_status[s], stream=self.stream)
+            self.replica.predict(dev_slab, descs, n, self.topk, self.dev_probs[s], self.dev_idx[s], stream=self.stream)
+            self.probs[s][:n].copy_(self.dev_probs[s][:n], non_blocking=True)
+            self.idx[s][:n].copy_(self.dev_idx[s][:n], non_blocking=True)
+            self.status_host[s][:len(jpeg_items)].copy_(self.dev_status[s][:len(jpeg_items)], non_blocking=True)
+            self.done[s].record(self.stream)
+        return (s, n, tuple(jpeg_items))
+
+    def collect(self, ticket):
+        """Waits for a submitted batch; returns (probs[n,k], idx[n,k], {image index: exception})."""
+        s, n, jpeg_items = ticket
+        self.done[s].synchronize()
         errors = {}
-        st = self.status_host[:len(jpeg_items)].numpy()
-        for j, i in enumerate(jpeg_items):
-            if st[j]:
-                errors[i] = CorruptImage(f"JPEG entropy-coded data is damaged (decoder status {int(st[j])})")
-        return self.probs[:n].numpy().copy(), self.idx[:n].numpy().copy(), errors
+        if jpeg_items:
+            st = self.status_host[s][:len(jpeg_items)].numpy()
+            for j, i in enumerate(jpeg_items):
+                if st[j]:
+                    errors[i] = CorruptImage(f"JPEG entropy-coded data is damaged (decoder status {int(st[j])})")
+        return self.probs[s][:n].numpy().copy(), self.idx[s][:n].numpy().copy(), errors
+
+    def run_batch(self, images: Sequence[np.ndarray]):
+        """Synchronous form: one batch, results on return."""
+        return self.collect(self.submit_batch(images))
 
     def close(self) -> None:
+        for e in self.done:
+            e.synchronize()
         if self.jpeg is not None:
             self.jpeg.close()
         self.replica.close()
 
 
 class Engine:
-    """Micro-batching queue + round-robin dispatch over replica workers."""
+    """Micro-batching queue + least-loaded dispatch over replica workers.
+
+    Workers are duck-typed.  The minimum is `run_batch(images) -> (probs, idx[, errors])`; a worker that also has
+    `submit_batch(images) -> ticket` / `collect(ticket)` (GpuReplicaWorker) is driven with up to `worker.DEPTH`
+    batches in flight."""
 
     def __init__(self, workers: Sequence, max_batch: int = 64, max_wait_us: int = 2000):
         if not workers:
@@ -188,6 +221,8 @@ class Engine:
         self._worker_q: List["queue.Queue[Optional[List[_Request]]]"] = [queue.Queue(maxsize=4) for _ in self.workers]
         self._rr = 0
         self._closed = False
+        self._load = [0] * len(self.workers)       # images handed to a replica and not yet answered
+        self._load_lock = threading.Lock()
         self.batch_sizes: List[int] = []          # achieved batch-size histogram source
         self.dispatch_log: List[Tuple[int, int]] = []   # (worker index, batch size)
         self._threads = [threading.Thread(target=self._batcher, name="b2p-batcher", daemon=True)]
@@ -208,6 +243,17 @@ class Engine:
         futs = [self.submit(im) for im in images]
         return [f.result() for f in futs]
 
+    def _pick_worker(self, n: int) -> int:
+        """The replica with the fewest images in flight; while they are level the choice simply rotates, so an idle
+        engine hands whole batches round-robin (north_star) and one slow GPU no longer stalls dispatch to the rest."""
+        nw = len(self.workers)
+        with self._load_lock:
+            w = min(range(nw), key=lambda i: (self._load[(self._rr + i) % nw], i))
+            w = (self._rr + w) % nw
+            self._load[w] += n
+        self._rr = (w + 1) % nw
+        return w
+
     # ---- batcher thread
     def _batcher(self) -> None:
         while True:
@@ -227,8 +273,7 @@ class Engine:
                     stop = True
                     break
                 batch.append(nxt)
-            w = self._rr
-            self._rr = (self._rr + 1) % len(self.workers)
+            w = self._pick_worker(len(batch))
             self.batch_sizes.append(len(batch))
             self.dispatch_log.append((w, len(batch)))
             self._worker_q[w].put(batch)
@@ -238,25 +283,70 @@ class Engine:
             q.put(None)
 
     # ---- one thread per replica
-    def _worker_loop(self, i: int) -> None:
-        worker = self.workers[i]
-        while True:
-            batch = self._worker_q[i].get()
-            if batch is None:
-                break
-            try:
-                out = worker.run_batch([r.image for r in batch])
+    def _answer(self, i: int, batch: List[_Request], out=None, exc: Optional[BaseException] = None) -> None:
+        try:
+            if exc is None:
                 probs, idx = out[0], out[1]
                 errors = out[2] if len(out) > 2 else {}      # per-image failures do not fail the whole batch
-                for j, r in enumerate(batch):
-                    if j in errors:
-                        r.future.set_exception(errors[j])
-                    else:
-                        r.future.set_result((probs[j], idx[j]))
-            except BaseException as e:          # propagate to every waiter: predict() re-raises -> HTTP 500
-                for r in batch:
-                    if not r.future.done():
-                        r.future.set_exception(e)
+            for j, r in enumerate(batch):
+                if r.future.done():
+                    continue
+                if exc is not None:
+                    r.future.set_exception(exc)      # propagate to every waiter: predict() re-raises -> HTTP 500
+                elif j in errors:
+                    r.future.set_exception(errors[j])
+                else:
+                    r.future.set_result((probs[j], idx[j]))
+        finally:
+            with self._load_lock:
+                self._load[i] -= len(batch)
+
+    def _worker_loop(self, i: int) -> None:
+        worker = self.workers[i]
+        pipelined = hasattr(worker, "submit_batch") and hasattr(worker, "collect")
+        depth = int(getattr(worker, "DEPTH", 1)) if pipelined else 1
+        inflight: List[Tuple[List[_Request], object]] = []       # (batch, ticket), oldest first
+        q = self._worker_q[i]
+        stopping = False
+
+        def finish_oldest():
+            batch, ticket = inflight.pop(0)
+            try:
+                self._answer(i, batch, out=worker.collect(ticket))
+            except BaseException as e:
+                self._answer(i, batch, exc=e)
+
+        while not (stopping and not inflight):
+            batch = None
+            if not stopping:
+                try:
+                    # with work on the GPU only look at the queue; with none, sleep on it
+                    batch = q.get_nowait() if inflight else q.get()
+                    if batch is None:
+                        stopping = True
+                except queue.Empty:
+                    batch = None
+            if batch:
+                n_before = len(batch)
+                # A waiter may have given up while its request was queued (client disconnect, timeout, shutdown:
+                # asyncio.wrap_future cancels the future).  Mark the rest running so they can no longer be cancelled
+                # under us, and drop the cancelled ones instead of letting set_result() raise for the whole batch.
+                batch = [r for r in batch if r.future.set_running_or_notify_cancel()]
+                if n_before != len(batch):
+                    with self._load_lock:
+                        self._load[i] -= n_before - len(batch)
+                if batch:
+                    try:
+                        if pipelined:
+                            inflight.append((batch, worker.submit_batch([r.image for r in batch])))
+                        else:
+                            self._answer(i, batch, out=worker.run_batch([r.image for r in batch]))
+                    except BaseException as e:
+                        self._answer(i, batch, exc=e)
+                if len(inflight) < depth and not stopping:
+                    continue                      # room for one more before waiting on the oldest
+            if inflight:
+                finish_oldest()
 
     def close(self) -> None:
         """Drains the queue (queued requests are still served), stops the threads, frees the replicas."""

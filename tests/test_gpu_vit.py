@@ -154,3 +154,46 @@ def test_vit_b16_end_to_end(cuda_device):
     assert err <= 6e-2 and err / scale <= 3e-2
     # top-1 must agree wherever the fp32 margin exceeds the observed error band
     assert bool(agree[margins > 2 * err].all())
+
+
+def test_vit_b16_b64_vs_oracle(cuda_device):
+    """BASELINE.json configs[4] per-GPU size: 64 distinct uint8 images through the whole chain (b2p_predict) against
+    the oracle's CPU fp32 path, every image: logits, top-1 where the fp32 margin exceeds the error band, top-k
+    probabilities."""
+    import numpy as np
+    from mlmicroservicetemplate_b200 import backend as B, program as P
+    from oracle import images, model as om
+    model = om.build_model("vit_b_16")
+    prog = P.build_program(model, "vit_b_16")
+    ims = images.synthetic_batch(100, 64, 224, 224)
+    n = len(ims)
+    rep = B.Replica(0, prog, max_batch=n)
+    stride = (224 * 224 * 3 + 255) // 256 * 256
+    slab = np.zeros(n * stride, np.uint8)
+    for i, im in enumerate(ims):
+        slab[i * stride:i * stride + im.size] = im.reshape(-1)
+    descs = B.make_images([(i * stride, 224, 224, 224, 224, 0, 0) for i in range(n)])
+    probs = torch.empty(n, 5, device="cuda")
+    idx = torch.empty(n, 5, dtype=torch.int32, device="cuda")
+    rep.predict(torch.from_numpy(slab).cuda(), descs, n, 5, probs, idx)
+    torch.cuda.synchronize()
+    logits = torch.empty(n, 1000, device="cuda")
+    x = torch.empty(n, 3, 224, 224, dtype=torch.bfloat16, device="cuda")
+    rep.preprocess(torch.from_numpy(slab).cuda(), descs, n, x)
+    rep.forward(x, n, logits)
+    torch.cuda.synchronize()
+    rep.close()
+    ref, ref_probs, ref_idx = om.predict_arrays(ims, mode="direct", k=5, model=model)
+    got = logits.cpu()
+    err = (got - ref).abs().max().item()
+    scale = ref.abs().max().item()
+    srt = ref.sort(dim=1, descending=True).values
+    margins = srt[:, 0] - srt[:, 1]
+    agree = got.argmax(1) == ref.argmax(1)
+    print(f"vit_b_16 b64: logits max_abs_err={err:.4g} max|logit|={scale:.4g} rel={err / scale:.3g} "
+          f"top1_agree={agree.float().mean().item():.3f} min_margin={margins.min().item():.4g} "
+          f"distinct_top1={ref.argmax(1).unique().numel()}")
+    assert not torch.isnan(got).any()
+    assert err <= 6e-2 and err / scale <= 3e-2
+    assert bool(agree[margins > 2 * err].all())
+    assert (probs.cpu() - ref_probs).abs().max().item() < 5e-3

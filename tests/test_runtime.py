@@ -111,3 +111,63 @@ def test_geometry_modes():
     assert image_geometry(480, 640, "preset") == (256, 341, 16, 58)
     with pytest.raises(ValueError):
         image_geometry(1, 1, "nope")
+
+
+class PipelinedWorker(RecordingWorker):
+    """Stand-in with the asynchronous duck type of GpuReplicaWorker: submit_batch() returns a ticket, collect()
+    waits for it; records how many tickets were outstanding at each submit."""
+    DEPTH = 2
+
+    def __init__(self, delay=0.0):
+        super().__init__(delay=delay)
+        self.outstanding = 0
+        self.max_outstanding = 0
+
+    def submit_batch(self, images):
+        self.outstanding += 1
+        self.max_outstanding = max(self.max_outstanding, self.outstanding)
+        assert self.outstanding <= self.DEPTH, "the engine must not exceed the worker's pipeline depth"
+        return (time.perf_counter() + self.delay, list(images))
+
+    def collect(self, ticket):
+        ready, images = ticket
+        time.sleep(max(0.0, ready - time.perf_counter()))
+        self.outstanding -= 1
+        self.batches.append(len(images))
+        idx = np.array([[int(im[0, 0, 0])] for im in images], dtype=np.int32)
+        return np.ones((len(images), 1), np.float32), idx, {}
+
+
+def test_pipelined_worker_gets_the_next_batch_before_the_previous_one_is_collected():
+    w = PipelinedWorker(delay=0.02)
+    eng = Engine([w], max_batch=4, max_wait_us=500)
+    futs = [eng.submit(_img(i)) for i in range(40)]
+    assert [int(f.result(timeout=10)[1][0]) for f in futs] == list(range(40))
+    assert w.max_outstanding == 2, "batch i+1 must be submitted while batch i is still in flight"
+    eng.close()
+    assert w.outstanding == 0
+
+
+def test_least_loaded_dispatch_routes_around_a_slow_replica():
+    slow, fast = RecordingWorker(delay=0.05), RecordingWorker(delay=0.001)
+    eng = Engine([slow, fast], max_batch=1, max_wait_us=50)
+    futs = []
+    for i in range(60):
+        futs.append(eng.submit(_img(i)))
+        time.sleep(0.002)
+    assert [int(f.result(timeout=20)[1][0]) for f in futs] == list(range(60))
+    assert len(fast.batches) > 2 * len(slow.batches), (len(fast.batches), len(slow.batches))
+    eng.close()
+
+
+def test_a_request_cancelled_while_queued_does_not_poison_its_batch():
+    w = RecordingWorker(delay=0.05)
+    eng = Engine([w], max_batch=4, max_wait_us=1000)
+    first = eng.submit(_img(1))               # occupies the worker
+    time.sleep(0.01)
+    futs = [eng.submit(_img(t)) for t in (2, 3, 4)]
+    assert futs[1].cancel()                   # what asyncio.wrap_future does when the handler task is cancelled
+    assert int(first.result(timeout=5)[1][0]) == 1
+    assert int(futs[0].result(timeout=5)[1][0]) == 2 and int(futs[2].result(timeout=5)[1][0]) == 4
+    assert futs[1].cancelled()
+    eng.close()
