@@ -46,6 +46,18 @@ class Ranks:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def same_on_all_ranks(self, digest: bytes) -> bool:
+        """True when every rank holds the same digest (the same batch through the replica on any GPU must
+        give bit-identical logits).  48 bits of it travel as an exact float64 through a MAX and a MIN reduction."""
+        v = float(int.from_bytes(digest[:6], "big"))
+        if self.world == 1:
+            return True
+        import torch.distributed as dist
+        hi, lo = self._tensor(v), self._tensor(v)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        return float(hi.item()) == float(lo.item())
+
     def job_throughput(self, units_per_rank: int, elapsed_ms: float) -> float:
         """Whole-job units/s: every rank processed `units_per_rank`; the job took the slowest rank's time."""
         return self.world * units_per_rank / (self.max_over_ranks(elapsed_ms) * 1e-3)

@@ -61,6 +61,21 @@ class JpegFile:
     width: int
 
 
+@dataclass
+class PackedBatch:
+    """A whole batch that is already packed the way the C ABI wants it: `slab` is a pinned uint8 torch tensor holding
+    n decoded HWC images back to back, `geoms` their (offset, h, w, res_h, res_w, top, left) tuples.  Producers that
+    own pinned memory (decode threads, the ingest processes' shared slab, bench.py) hand such batches to
+    Engine.submit_batch(): no pixel is copied again on the host."""
+    slab: object
+    nbytes: int
+    geoms: Sequence[Tuple[int, int, int, int, int, int, int]]
+    descs: object = None               # b2p_image array, built once by the first replica that sees the batch
+
+    def __len__(self) -> int:
+        return len(self.geoms)
+
+
 class CorruptImage(ValueError):
     """The entropy-coded data of one upload was damaged (the GPU decoder's status word was non-zero)."""
 
@@ -70,6 +85,13 @@ class _Request:
     image: object                      # np.ndarray (uint8 HWC) or JpegFile
     future: Future
     t_enqueue: float = field(default_factory=time.perf_counter)
+
+
+@dataclass
+class _BatchRequest:
+    images: object                     # list of images / JpegFiles, or a PackedBatch
+    future: Future
+    n: int
 
 
 class GpuReplicaWorker:
@@ -132,6 +154,18 @@ class GpuReplicaWorker:
         n = len(images)
         if n == 0 or n > self.max_batch:
             raise ValueError(f"batch of {n} outside 1..{self.max_batch}")
+        if isinstance(images, PackedBatch):
+            # already in pinned memory in slab layout: one asynchronous call, nothing to pack
+            if images.descs is None:
+                images.descs = self.B.make_images(list(images.geoms))
+            s = self.slot
+            self.slot = (s + 1) % self.DEPTH
+            self.done[s].synchronize()
+            with self.torch.cuda.device(self.device):
+                self.replica.predict_host(images.slab, images.nbytes, images.descs, n, self.topk, self.probs[s],
+                                          self.idx[s], stream=self.stream)
+                self.done[s].record(self.stream)
+            return (s, n, ())
         offs, shapes, total = [], [], 0
         for im in images:
             if isinstance(im, JpegFile):
@@ -239,6 +273,18 @@ class Engine:
         self._inbox.put(_Request(image, fut))
         return fut
 
+    def submit_batch(self, images) -> Future:
+        """A whole batch (a list of images / JpegFiles, or a PackedBatch) that bypasses the micro-batcher and goes
+        straight to the least-loaded replica.  The future resolves to (probs[n,k], idx[n,k], {index: exception})."""
+        if self._closed:
+            raise RuntimeError("engine is shut down")
+        fut: Future = Future()
+        n = len(images)
+        w = self._pick_worker(n)
+        self.dispatch_log.append((w, n))
+        self._worker_q[w].put(_BatchRequest(images, fut, n))
+        return fut
+
     def predict_many(self, images: Sequence[np.ndarray]):
         futs = [self.submit(im) for im in images]
         return [f.result() for f in futs]
@@ -283,7 +329,18 @@ class Engine:
             q.put(None)
 
     # ---- one thread per replica
-    def _answer(self, i: int, batch: List[_Request], out=None, exc: Optional[BaseException] = None) -> None:
+    def _answer(self, i: int, batch, out=None, exc: Optional[BaseException] = None) -> None:
+        if isinstance(batch, _BatchRequest):
+            try:
+                if not batch.future.done():
+                    if exc is not None:
+                        batch.future.set_exception(exc)
+                    else:
+                        batch.future.set_result((out[0], out[1], out[2] if len(out) > 2 else {}))
+            finally:
+                with self._load_lock:
+                    self._load[i] -= batch.n
+            return
         try:
             if exc is None:
                 probs, idx = out[0], out[1]
@@ -326,7 +383,21 @@ class Engine:
                         stopping = True
                 except queue.Empty:
                     batch = None
-            if batch:
+            if isinstance(batch, _BatchRequest):
+                if not batch.future.set_running_or_notify_cancel():
+                    with self._load_lock:
+                        self._load[i] -= batch.n
+                else:
+                    try:
+                        if pipelined:
+                            inflight.append((batch, worker.submit_batch(batch.images)))
+                        else:
+                            self._answer(i, batch, out=worker.run_batch(batch.images))
+                    except BaseException as e:
+                        self._answer(i, batch, exc=e)
+                if len(inflight) < depth and not stopping:
+                    continue
+            elif batch:
                 n_before = len(batch)
                 # A waiter may have given up while its request was queued (client disconnect, timeout, shutdown:
                 # asyncio.wrap_future cancels the future).  Mark the rest running so they can no longer be cancelled

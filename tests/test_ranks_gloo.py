@@ -17,7 +17,8 @@ WORKER = textwrap.dedent("""
     r.barrier()
     elapsed = 10.0 if r.rank == 0 else 25.0            # rank 1 is the slow one
     out = {"rank": r.rank, "world": r.world, "max": r.max_over_ranks(elapsed),
-           "value": r.job_throughput(256 * 4, elapsed), "shard": list(r.shard(7))}
+           "value": r.job_throughput(256 * 4, elapsed), "shard": list(r.shard(7)),
+           "same": r.same_on_all_ranks(b"identical-digest"), "differ": r.same_on_all_ranks(bytes([r.rank]) * 8)}
     r.barrier()
     r.close()
     print("RESULT " + json.dumps(out))
@@ -46,6 +47,7 @@ def test_two_gloo_ranks():
     assert all(d["max"] == 25.0 for d in outs), "every rank must see the slowest rank's time"
     assert all(abs(d["value"] - 2 * 1024 / 0.025) < 1e-6 for d in outs), "value = all ranks' units / max time"
     assert outs[0]["shard"] + outs[1]["shard"] == list(range(7)), "shards partition the work with no overlap"
+    assert all(d["same"] for d in outs) and not any(d["differ"] for d in outs), "digest comparison across ranks"
 
 
 def test_single_rank_needs_no_process_group():

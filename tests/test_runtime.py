@@ -171,3 +171,15 @@ def test_a_request_cancelled_while_queued_does_not_poison_its_batch():
     assert int(futs[0].result(timeout=5)[1][0]) == 2 and int(futs[2].result(timeout=5)[1][0]) == 4
     assert futs[1].cancelled()
     eng.close()
+
+
+def test_whole_batches_bypass_the_micro_batcher_and_spread_over_replicas():
+    ws = [PipelinedWorker(delay=0.01) for _ in range(4)]
+    eng = Engine(ws, max_batch=8, max_wait_us=1000)
+    futs = [eng.submit_batch([_img(10 * b + j) for j in range(8)]) for b in range(16)]
+    for b, f in enumerate(futs):
+        probs, idx, errors = f.result(timeout=10)
+        assert [int(v[0]) for v in idx] == [10 * b + j for j in range(8)] and not errors
+    assert all(sum(w.batches) == 32 for w in ws), [w.batches for w in ws]
+    assert [w for w, _ in eng.dispatch_log[:4]] == [0, 1, 2, 3]
+    eng.close()
