@@ -14,6 +14,7 @@ class Ranks:
     local_rank: int = 0
     world: int = 1
     backend: str = ""
+    _cpu_group: object = None
 
     @classmethod
     def from_env(cls, backend: str = "nccl", device=None) -> "Ranks":
@@ -23,7 +24,16 @@ class Ranks:
             import torch.distributed as dist
             kw = {"device_id": device} if (device is not None and backend == "nccl") else {}
             dist.init_process_group(backend, **kw)
+            # a host-only group: waiting on it launches nothing on the GPUs (an NCCL barrier parks a spinning
+            # kernel on every rank's device, which would sit on SMs another process is measuring)
+            r._cpu_group = dist.new_group(backend="gloo") if backend == "nccl" else None
         return r
+
+    def host_barrier(self) -> None:
+        """Barrier that touches no GPU (bench.py: the other ranks idle here while rank 0 drives all GPUs)."""
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier(group=self._cpu_group) if self._cpu_group is not None else dist.barrier()
 
     def _tensor(self, v: float):
         import torch
