@@ -75,7 +75,7 @@ class ClockSampler:
         self.proc = None
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50", "-i", str(device)],
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "25", "-i", str(device)],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
@@ -350,36 +350,33 @@ def main():
                    "what": "every rank ran the seed-1 batch of 256 images through K1+K2 on its own GPU"}
     del common
 
-    def step_resident(i, evs=None):
-        slab = dev_slabs[i % POOL_SLABS]
-        if evs: evs[0].record(stream)
-        rep.preprocess(slab, descs, BATCH, x, stream=stream)
-        if evs: evs[1].record(stream)
-        rep.forward(x, BATCH, logits, stream=stream)
-        if evs: evs[2].record(stream)
-        rep.softmax_topk(logits, BATCH, prog.out_elems, TOPK, probs, idx, stream=stream)
-        if evs: evs[3].record(stream)
+    def step_resident(i):
+        # the chained device-resident entry point: K1 (crop-only images go straight into the stem's layout),
+        # K2, K3 on one stream; the library records CUDA events around each stage (b2p_stats)
+        rep.predict(dev_slabs[i % POOL_SLABS], descs, BATCH, TOPK, probs, idx, stream=stream)
 
-    def timed_rounds(step, min_seconds, with_stage_events=False, max_rounds=60):
+    def timed_rounds(step, min_seconds, with_stage_times=False, max_rounds=60):
         """Rounds of exactly K steps, each bracketed by a barrier + synchronize; returns the per-round times
-        (max over ranks, ms) and, optionally, the per-stage event times of every step."""
+        (max over ranks, ms) and, optionally, the mean per-stage CUDA-event times of each round's calls."""
         rounds, stages = [], []
         total = 0.0
         it = 0
         while True:
-            evs = [[torch.cuda.Event(enable_timing=True) for _ in range(4)] for _ in range(K)] if with_stage_events else None
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if with_stage_times:
+                rep.stats()                   # start a fresh averaging window
             barrier()
             e0.record(stream)
             for i in range(K):
-                step(it, evs[i] if evs else None)
+                step(it)
                 it += 1
             e1.record(stream)
             barrier()
             ms = max_over_ranks(e0.elapsed_time(e1))
             rounds.append(ms)
-            if evs:
-                stages += [(e[0].elapsed_time(e[1]), e[1].elapsed_time(e[2]), e[2].elapsed_time(e[3])) for e in evs]
+            if with_stage_times:
+                st = rep.stats()
+                stages.append((st["ms_preprocess"], st["ms_forward"], st["ms_epilogue"]))
             total += ms
             if (total >= min_seconds * 1e3 and len(rounds) >= 3) or len(rounds) >= max_rounds:
                 return rounds, stages
@@ -390,7 +387,7 @@ def main():
     launches0 = rep.stats()["kernel_launches"]
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
-    res_rounds, stages = timed_rounds(step_resident, args.min_seconds, with_stage_events=True)
+    res_rounds, stages = timed_rounds(step_resident, args.min_seconds, with_stage_times=True)
     clocks = sampler.stop() if sampler else None
     launches_per_round = (rep.stats()["kernel_launches"] - launches0) // len(res_rounds)
     total_ms = statistics.median(res_rounds)
@@ -400,7 +397,7 @@ def main():
     value = world * BATCH * K / (total_ms * 1e-3)
 
     # ---------------------------------------------------------------- end to end through host buffers (`e2e`)
-    def step_host(i, _evs=None):
+    def step_host(i):
         rep.predict_host(host_slabs[i % POOL_SLABS], slab_bytes, descs, BATCH, TOPK, probs_h, idx_h, stream=stream)
     for i in range(W):
         step_host(i)
@@ -427,7 +424,7 @@ def main():
     joffs = [i * stride for i in range(BATCH)]
     rotated = [files[s:] + files[:s] for s in range(POOL_SLABS)]
 
-    def step_jpeg(i, _evs=None):
+    def step_jpeg(i):
         dec.decode(rotated[i % POOL_SLABS], jslab, slab_bytes, joffs, status=jstatus, stream=stream)
         rep.predict(jslab, descs, BATCH, TOPK, probs, idx, stream=stream)
         with torch.cuda.stream(stream):

@@ -39,6 +39,8 @@ struct b2p_handle {
     int max_batch = 0;
     int chunk = 0;                       // images per pass through the program
     bool alternate = true;               // alternate the tile direction layer by layer (B2P_NO_ALTERNATE, read at create)
+    int fused_input_slot = -1;           // >= 0: op 0 is the stem's space-to-depth pack of the external input and nothing
+                                         // else reads that input, so the predict chain may let K1 write this slot directly
     int64_t in_elems = 0, out_elems = 0;
     int classes = 0;
     std::vector<OpPlan> ops;
@@ -70,8 +72,15 @@ struct b2p_handle {
     float* norm_lut = nullptr;           // [3][256] normalisation table for K1's crop-only path
     float* probs_dev = nullptr;
     int32_t* idx_dev = nullptr;
-    cudaEvent_t ev[7] = {};   // copy begin/end (copy stream), K1 begin, K1/K2/K3 end, D2H end (caller's stream)
+    cudaEvent_t ev[7] = {};   // [0],[1] copy begin/end (copy stream), [6] D2H end (caller's stream); [2..5] unused
     bool ev_valid = false;
+    // per-stage events of the predict chains: K1 begin, K1 / K2 / K3 end, one set per call in a ring, so that
+    // b2p_stats_get can average the stages over every call since the previous read
+    static constexpr int SRING = 64;
+    cudaEvent_t sev[SRING][4] = {};
+    int sev_pos = 0;          // next set to record into
+    int sev_unread = 0;       // sets recorded since the last b2p_stats_get (saturates at SRING)
+    int sev_last = -1;
     b2p_stats stats = {};
     char err[512] = "";
 };
@@ -155,7 +164,7 @@ int validate_desc(const b2p_model_desc* d) {
     return B2P_OK;
 }
 
-int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st) {
+int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st, size_t first_op = 0) {
     // Tile direction: a GEMM layer walks its row tiles in the direction OPPOSITE to the last op that
     // touched its input, so it starts on the rows that are still resident in L2 (126 MB) instead of on
     // the ones that were evicted first.  Slot -> direction of the last toucher (0 = ascending).
@@ -164,7 +173,8 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st)
     auto touch_of = [&](int slot) -> int& { return touch[slot >= 0 && slot < (int)h->slots.size() ? slot : h->slots.size()]; };
     for (int off = 0; off < n; off += h->chunk) {
         const int nb = (n - off) < h->chunk ? (n - off) : h->chunk;
-        for (OpPlan& p : h->ops) {
+        for (size_t op_i = first_op; op_i < h->ops.size(); ++op_i) {
+            OpPlan& p = h->ops[op_i];
             int op_dir = 0;
             {
                 const bool directed = p.is_gemm || p.op.kind == B2P_OP_CONV_PAIR;
@@ -357,6 +367,7 @@ int32_t b2p_destroy(b2p_handle* h) {
     if (h->probs_dev) cudaFree(h->probs_dev);
     if (h->idx_dev) cudaFree(h->idx_dev);
     if (h->ev_valid) for (auto& e : h->ev) cudaEventDestroy(e);
+    for (auto& set : h->sev) for (auto& e : set) if (e) cudaEventDestroy(e);
     delete h;
     return B2P_OK;
 }
@@ -583,6 +594,18 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
         }
         if (o.kind == B2P_OP_LINEAR && o.dst == B2P_SLOT_OUTPUT) h->classes = o.out_c;
     }
+    // K1 -> stem fusion for the predict chain: possible when the program opens with the space-to-depth pack of the
+    // 224x224 input into a workspace slot, no later op reads the external input, and the batch is not chunked
+    if (desc->n_ops > 1 && getenv("B2P_NO_FUSED_INPUT") == nullptr) {
+        const b2p_op& o0 = desc->ops[0];
+        bool ok = o0.kind == B2P_OP_STEM_PACK && o0.src == B2P_SLOT_INPUT && o0.dst > 0 && o0.in_h == B2P_OUT_HW &&
+                  o0.in_w == B2P_OUT_HW && h->chunk == h->max_batch;
+        for (int i = 1; i < desc->n_ops && ok; ++i) {
+            const b2p_op& o = desc->ops[i];
+            ok = o.src != B2P_SLOT_INPUT && o.res != B2P_SLOT_INPUT && !(o.src2_c > 0 && o.src2 == B2P_SLOT_INPUT);
+        }
+        if (ok) h->fused_input_slot = o0.dst;
+    }
     // predict-chain staging
     const size_t nb = static_cast<size_t>(h->max_batch);
     for (int r = 0; r < b2p_handle::RING; ++r) {
@@ -600,6 +623,9 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
         B2P_FAIL(B2P_E_NOMEM, "normalisation table set-up failed");
     for (auto& e : h->ev)
         if (cudaEventCreate(&e) != cudaSuccess) B2P_FAIL(B2P_E_CUDA, "cudaEventCreate failed");
+    for (auto& set : h->sev)
+        for (auto& e : set)
+            if (cudaEventCreate(&e) != cudaSuccess) B2P_FAIL(B2P_E_CUDA, "cudaEventCreate failed");
     if (cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking) != cudaSuccess)
         B2P_FAIL(B2P_E_CUDA, "copy stream creation failed");
     for (int i = 0; i < 2; ++i)
@@ -617,18 +643,32 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
 // synchronised the stream; events that have not completed yet leave the previous values in place.
 int32_t b2p_stats_get(b2p_handle* h, b2p_stats* out) {
     if (!h || !out) return B2P_E_ARG;
-    if (h->ev_valid && h->stats.calls > 0) {
-        float ms[5];
-        const int from[5] = {0, 2, 3, 4, 5};
-        bool ok = true;
-        for (int i = 0; i < 5 && ok; ++i)
-            ok = cudaEventElapsedTime(&ms[i], h->ev[from[i]], h->ev[from[i] + 1]) == cudaSuccess;
-        if (ok) {
-            h->stats.ms_h2d = ms[0];
-            h->stats.ms_preprocess = ms[1];
-            h->stats.ms_forward = ms[2];
-            h->stats.ms_epilogue = ms[3];
-            h->stats.ms_d2h = ms[4];
+    if (h->ev_valid && h->sev_unread > 0) {
+        // stage times: mean over the calls since the previous read whose work has completed
+        double sum[3] = {0, 0, 0};
+        int got = 0;
+        for (int j = 0; j < h->sev_unread; ++j) {
+            const int r = ((h->sev_pos - 1 - j) % b2p_handle::SRING + b2p_handle::SRING) % b2p_handle::SRING;
+            float ms[3];
+            bool ok = true;
+            for (int i = 0; i < 3 && ok; ++i) ok = cudaEventElapsedTime(&ms[i], h->sev[r][i], h->sev[r][i + 1]) == cudaSuccess;
+            if (!ok) { cudaGetLastError(); continue; }
+            for (int i = 0; i < 3; ++i) sum[i] += ms[i];
+            ++got;
+        }
+        if (got > 0) {
+            h->stats.ms_preprocess = static_cast<float>(sum[0] / got);
+            h->stats.ms_forward = static_cast<float>(sum[1] / got);
+            h->stats.ms_epilogue = static_cast<float>(sum[2] / got);
+            h->sev_unread = 0;
+        }
+    }
+    if (h->ev_valid && h->stats.calls > 0 && h->sev_last >= 0) {
+        float a = 0.f, b = 0.f;
+        if (cudaEventElapsedTime(&a, h->ev[0], h->ev[1]) == cudaSuccess &&
+            cudaEventElapsedTime(&b, h->sev[h->sev_last][3], h->ev[6]) == cudaSuccess) {
+            h->stats.ms_h2d = a;
+            h->stats.ms_d2h = b;
         } else {
             cudaGetLastError();
         }
@@ -670,14 +710,46 @@ int32_t b2p_softmax_topk(b2p_handle* h, const float* logits, int32_t n, int32_t 
     return B2P_OK;
 }
 
+// K1 of the predict chain.  Crop-only batches of a ResNet-style program are written straight into the stem's
+// space-to-depth slot (one pass instead of K1 + pack: bit-identical values); *first_op says where K2 then starts.
+static int chain_preprocess(b2p_handle* h, const uint8_t* slab, const b2p_image* imgs, int32_t n, void* stream,
+                            size_t* first_op) {
+    *first_op = 0;
+    if (h->fused_input_slot < 0 || !imgs || n <= 0 || n > h->max_batch || !preprocess_all_identity(imgs, n))
+        return b2p_preprocess(h, slab, imgs, n, h->x_dev, 0, stream);
+    if (!slab) return B2P_E_ARG;
+    B2P_CUDA(h, cudaSetDevice(h->device));
+    int rc = check_images(h, imgs, n);
+    if (rc != B2P_OK) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    rc = stage_images(h, imgs, n, st);
+    if (rc != B2P_OK) return rc;
+    B2P_CUDA(h, launch_preprocess_s2d(slab, h->cur_imgs_dev, n, h->slots[h->fused_input_slot], h->norm_lut, st));
+    h->stats.kernel_launches += 1;
+    *first_op = 1;
+    return B2P_OK;
+}
+
 int32_t b2p_predict(b2p_handle* h, const uint8_t* slab, const b2p_image* imgs, int32_t n, int32_t k,
                     float* probs, int32_t* idx, void* stream) {
     if (!h || h->classes <= 0) { if (h) set_error(h, "program has no classifier output"); return B2P_E_ARG; }
-    int rc = b2p_preprocess(h, slab, imgs, n, h->x_dev, 0, stream);
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    B2P_CUDA(h, cudaSetDevice(h->device));
+    cudaEvent_t* sev = h->sev[h->sev_pos];
+    B2P_CUDA(h, cudaEventRecord(sev[0], st));
+    size_t first_op = 0;
+    int rc = chain_preprocess(h, slab, imgs, n, stream, &first_op);
     if (rc != B2P_OK) return rc;
-    rc = b2p_forward(h, h->x_dev, n, h->logits_dev, stream);
+    B2P_CUDA(h, cudaEventRecord(sev[1], st));
+    rc = run_program(h, h->x_dev, n, h->logits_dev, st, first_op);
     if (rc != B2P_OK) return rc;
-    return b2p_softmax_topk(h, h->logits_dev, n, h->classes, k, probs, idx, stream);
+    B2P_CUDA(h, cudaEventRecord(sev[2], st));
+    rc = b2p_softmax_topk(h, h->logits_dev, n, h->classes, k, probs, idx, stream);
+    if (rc != B2P_OK) return rc;
+    B2P_CUDA(h, cudaEventRecord(sev[3], st));
+    h->sev_pos = (h->sev_pos + 1) % b2p_handle::SRING;
+    if (h->sev_unread < b2p_handle::SRING) ++h->sev_unread;
+    return B2P_OK;
 }
 
 int32_t b2p_predict_host(b2p_handle* h, const uint8_t* slab_host, int64_t slab_bytes, const b2p_image* imgs,
@@ -722,18 +794,23 @@ int32_t b2p_predict_host(b2p_handle* h, const uint8_t* slab_host, int64_t slab_b
     B2P_CUDA(h, cudaEventRecord(h->ev[1], h->copy_stream));
     B2P_CUDA(h, cudaEventRecord(h->ev_copied[si], h->copy_stream));
     B2P_CUDA(h, cudaStreamWaitEvent(st, h->ev_copied[si], 0));
-    B2P_CUDA(h, cudaEventRecord(h->ev[2], st));
-    int rc = b2p_preprocess(h, h->slab_dev[si], imgs, n, h->x_dev, 0, stream);
+    cudaEvent_t* sev = h->sev[h->sev_pos];
+    B2P_CUDA(h, cudaEventRecord(sev[0], st));
+    size_t first_op = 0;
+    int rc = chain_preprocess(h, h->slab_dev[si], imgs, n, stream, &first_op);
     if (rc != B2P_OK) return rc;
-    B2P_CUDA(h, cudaEventRecord(h->ev[3], st));
+    B2P_CUDA(h, cudaEventRecord(sev[1], st));
     B2P_CUDA(h, cudaEventRecord(h->ev_consumed[si], st));
     h->slab_used[si] = true;
-    rc = b2p_forward(h, h->x_dev, n, h->logits_dev, stream);
+    rc = run_program(h, h->x_dev, n, h->logits_dev, st, first_op);
     if (rc != B2P_OK) return rc;
-    B2P_CUDA(h, cudaEventRecord(h->ev[4], st));
+    B2P_CUDA(h, cudaEventRecord(sev[2], st));
     rc = b2p_softmax_topk(h, h->logits_dev, n, h->classes, k, h->probs_dev, h->idx_dev, stream);
     if (rc != B2P_OK) return rc;
-    B2P_CUDA(h, cudaEventRecord(h->ev[5], st));
+    B2P_CUDA(h, cudaEventRecord(sev[3], st));
+    h->sev_last = h->sev_pos;
+    h->sev_pos = (h->sev_pos + 1) % b2p_handle::SRING;
+    if (h->sev_unread < b2p_handle::SRING) ++h->sev_unread;
     B2P_CUDA(h, cudaMemcpyAsync(probs_host, h->probs_dev, sizeof(float) * static_cast<size_t>(n) * k,
                                 cudaMemcpyDeviceToHost, st));
     B2P_CUDA(h, cudaMemcpyAsync(idx_host, h->idx_dev, sizeof(int32_t) * static_cast<size_t>(n) * k,

@@ -160,4 +160,10 @@ cudaError_t launch_preprocess(const uint8_t* slab, const b2p_image* imgs_dev,
                               const b2p_image* imgs_host, int n, void* out, int out_f32,
                               const float* norm_lut, cudaStream_t s, int* launches);
 
+// Crop-only batches (every image already has its resized size) written directly as the stem's 2x2 space-to-depth
+// input [n,112,112,16] bf16; bit-identical to launch_preprocess (bf16 NCHW) followed by launch_stem_pack.
+bool preprocess_all_identity(const b2p_image* imgs_host, int n);
+cudaError_t launch_preprocess_s2d(const uint8_t* slab, const b2p_image* imgs_dev, int n, void* out_s2d,
+                                  const float* norm_lut, cudaStream_t s);
+
 }  // namespace b2p

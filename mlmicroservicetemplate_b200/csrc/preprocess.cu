@@ -347,6 +347,63 @@ preprocess_identity_kernel(const uint8_t* __restrict__ slab, const b2p_image* __
     }
 }
 
+// Crop-only images straight into the stem's input layout: the 2x2 space-to-depth tensor [n,112,112,16] bf16 that
+// OP_STEM_PACK would otherwise build from the NCHW tensor (channel = (di*2+dj)*3 + c, channels 12..15 zero; see
+// misc_kernels.cu: stem_pack_kernel).  Same table, same rounding, so the values are bit-identical to K1 followed by
+// the pack; what disappears is one write and one read of the 77 MB NCHW tensor per 256 images and one launch.
+// One thread = four s2d pixels of one row: 2 source rows x 24 bytes (seven aligned 32-bit words + funnel shifts, any
+// byte alignment - the load pattern of preprocess_identity_kernel) in, 128 contiguous bytes out.
+__global__ void __launch_bounds__(256)
+preprocess_identity_s2d_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict__ imgs,
+                               uint4* __restrict__ out, const float* __restrict__ lut_g, int n) {
+    __shared__ float lut[3 * 256];
+    for (int i = threadIdx.x; i < 3 * 256; i += 256) lut[i] = __ldg(lut_g + i);
+    __syncthreads();
+    constexpr int HALF = OUT / 2;                    // 112 s2d pixels per row
+    constexpr int GROUPS = HALF / 4;                 // 28 groups of 4
+    const long t = blockIdx.x * 256L + threadIdx.x;
+    if (t >= static_cast<long>(n) * HALF * GROUPS) return;
+    const int g = static_cast<int>(t % GROUPS);
+    const int oi = static_cast<int>((t / GROUPS) % HALF);
+    const int img = static_cast<int>(t / (GROUPS * HALF));
+    const b2p_image im = imgs[img];
+    uint32_t q[4][6];                                // [s2d pixel][channel pair]
+#pragma unroll
+    for (int di = 0; di < 2; ++di) {
+        const uint8_t* src = slab + im.offset + (static_cast<size_t>(im.top + 2 * oi + di) * im.w + im.left + 8 * g) * 3;
+        const uint32_t sh = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(src) & 3u) * 8u;
+        const uint32_t* w = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(src) & ~static_cast<uintptr_t>(3));
+        uint32_t raw[7];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) raw[k] = __ldg(w + k);
+        raw[6] = sh ? __ldg(w + 6) : 0u;             // only touched when the 24 bytes straddle a 7th word
+        uint32_t b[6];
+#pragma unroll
+        for (int k = 0; k < 6; ++k) b[k] = __funnelshift_r(raw[k], raw[k + 1], sh);
+        // b[] = 24 bytes r0 g0 b0 r1 g1 b1 ...; s2d pixel p takes source pixels 2p (dj = 0) and 2p+1 (dj = 1)
+#pragma unroll
+        for (int p = 0; p < 4; ++p) {
+            float v[6];
+#pragma unroll
+            for (int e = 0; e < 6; ++e) {
+                const int byte = p * 6 + e;
+                v[e] = lut[(e % 3) * 256 + ((b[byte >> 2] >> ((byte & 3) * 8)) & 0xFFu)];
+            }
+#pragma unroll
+            for (int k = 0; k < 3; ++k) q[p][di * 3 + k] = pack_bf16x2(v[2 * k], v[2 * k + 1]);
+        }
+    }
+    uint4* o = out + 2 * ((static_cast<long>(img) * HALF + oi) * HALF + 4 * g);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        uint4 a, c;
+        a.x = q[p][0]; a.y = q[p][1]; a.z = q[p][2]; a.w = q[p][3];
+        c.x = q[p][4]; c.y = q[p][5]; c.z = 0u;      c.w = 0u;
+        o[2 * p] = a;
+        o[2 * p + 1] = c;
+    }
+}
+
 inline int host_max_taps(int in_size, int out_size) {
     const float scale = static_cast<float>(in_size) / static_cast<float>(out_size);
     const float support = scale >= 1.0f ? scale : 1.0f;
@@ -357,6 +414,20 @@ inline int host_max_taps(int in_size, int out_size) {
 
 cudaError_t launch_norm_lut(float* lut, cudaStream_t s) {
     norm_lut_kernel<<<1, 256, 0, s>>>(lut);
+    return cudaGetLastError();
+}
+
+bool preprocess_all_identity(const b2p_image* imgs_host, int n) {
+    for (int i = 0; i < n; ++i)
+        if (imgs_host[i].h != imgs_host[i].res_h || imgs_host[i].w != imgs_host[i].res_w) return false;
+    return true;
+}
+
+cudaError_t launch_preprocess_s2d(const uint8_t* slab, const b2p_image* imgs_dev, int n, void* out_s2d,
+                                  const float* norm_lut, cudaStream_t s) {
+    const long threads = static_cast<long>(n) * (OUT / 2) * (OUT / 8);
+    preprocess_identity_s2d_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, s>>>(
+        slab, imgs_dev, static_cast<uint4*>(out_s2d), norm_lut, n);
     return cudaGetLastError();
 }
 
