@@ -133,7 +133,7 @@ __device__ __forceinline__ void lds_pixel(uint32_t addr, f32x2& rg, f32x2& bx) {
 template <bool OUT_F32>
 __global__ void __launch_bounds__(THREADS)
 preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict__ imgs, void* __restrict__ out,
-                  int wh_taps, int wv_taps, int rowbuf_bytes, int frow_bytes, float one_f) {
+                  int wh_taps, int wv_taps, int rowbuf_bytes, int frow_bytes, float one_f, int cols, int skip_identity) {
     extern __shared__ __align__(16) uint8_t smem[];
     const f32x2 one = pack2(one_f, one_f);
     float* wh = reinterpret_cast<float*>(smem);                       // [wh_taps][OUT]
@@ -143,18 +143,27 @@ preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict_
     float4* frow = reinterpret_cast<float4*>(rowbuf + RING * rowbuf_bytes);   // the current row as fp32 (R,G,B,0) pixels
 
     const b2p_image im = imgs[blockIdx.y];
+    if (skip_identity && im.h == im.res_h && im.w == im.res_w) return;   // the crop-only kernel takes this image
     const int band0 = blockIdx.x * BAND;
     const int tid = threadIdx.x;
+    // A CTA covers `cols` output columns starting at col0 (224 for ordinary widths; fewer for very wide sources, so
+    // that the staged window of a source row always fits shared memory whatever the image width).
+    const int col0 = blockIdx.z * cols;
+    const bool active = tid < cols;
+    const int ocol = col0 + tid;                                  // this thread's output column (within the crop)
     const uint8_t* src = slab + im.offset;
     const int row_bytes = im.w * 3;
     (void)frow_bytes;
+    __shared__ int s_win[2];
 
     // ---- horizontal weights for this thread's output column, transposed into smem
     int xmin = 0, xsize = 0;
-    if (tid < OUT) {
+    if (active) {
         const AxisGeom g = axis_geom(im.w, im.res_w);
         float center;
-        axis_range(g, im.left + tid, im.w, center, xmin, xsize);
+        axis_range(g, im.left + ocol, im.w, center, xmin, xsize);
+        if (tid == 0) s_win[0] = xmin;                            // ranges are monotone in the output column
+        if (tid == cols - 1) s_win[1] = xmin + xsize;
         float total = 0.f;
         for (int j = 0; j < xsize; ++j) {
             const float w = axis_raw_weight(g, center, xmin, j);
@@ -184,19 +193,23 @@ preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict_
     __syncthreads();
     const int iy0 = vmeta[0];
     const int iy1 = vmeta[BAND - 1] + vmeta[2 * BAND - 1];   // ranges are monotone in the output row
+    const int win_lo = s_win[0];                              // source pixels [win_lo, win_hi) feed this CTA's columns
+    const int win_px = s_win[1] - win_lo;
+    const int win_bytes = win_px * 3;
+    src += static_cast<size_t>(win_lo) * 3;
 
     f32x2 acc_rg[BAND], acc_b[BAND];
 #pragma unroll
     for (int r = 0; r < BAND; ++r) acc_rg[r] = acc_b[r] = 0ull;
 
     const int hmain = xsize > 0 ? ((xsize - 1) >> 2) << 2 : 0;   // taps 1..hmain: mul then add
-    const uint32_t frow_base = smem_u32(frow) + static_cast<uint32_t>(xmin) * 16u;
+    const uint32_t frow_base = smem_u32(frow) + static_cast<uint32_t>(xmin - win_lo) * 16u;
 
     // raw rows stream through a ring of RING buffers: a row is requested RING iterations before it is
     // consumed, so the ~1 us global-memory latency is overlapped instead of paid once per row
 #pragma unroll
     for (int k = 0; k < RING; ++k) {
-        if (iy0 + k < iy1) stage_row(rowbuf + k * rowbuf_bytes, src + static_cast<size_t>(iy0 + k) * row_bytes, row_bytes);
+        if (iy0 + k < iy1) stage_row(rowbuf + k * rowbuf_bytes, src + static_cast<size_t>(iy0 + k) * row_bytes, win_bytes);
         cp_async_commit();
     }
 
@@ -207,16 +220,16 @@ preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict_
         {   // uint8 -> fp32 once per source sample (exact), all 256 threads
             const uint8_t* g = src + static_cast<size_t>(iy) * row_bytes;
             const uint8_t* raw = rowbuf + cur * rowbuf_bytes + (reinterpret_cast<uintptr_t>(g) & 15u);
-            for (int px = tid; px < im.w; px += THREADS)
+            for (int px = tid; px < win_px; px += THREADS)
                 frow[px] = make_float4(static_cast<float>(raw[3 * px]), static_cast<float>(raw[3 * px + 1]),
                                        static_cast<float>(raw[3 * px + 2]), 0.f);
         }
         __syncthreads();                     // frow complete, raw buffer `cur` free again
         if (iy + RING < iy1)
-            stage_row(rowbuf + cur * rowbuf_bytes, src + static_cast<size_t>(iy + RING) * row_bytes, row_bytes);
+            stage_row(rowbuf + cur * rowbuf_bytes, src + static_cast<size_t>(iy + RING) * row_bytes, win_bytes);
         cp_async_commit();
 
-        if (tid < OUT) {
+        if (active) {
             // horizontal pass: t = x0*w0; taps 1..hmain un-fused; the rest fused (torch's loop shape)
             float w = wh[tid];
             f32x2 w2 = pack2(w, w), prg, pb;
@@ -264,7 +277,7 @@ preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict_
         }
     }
 
-    if (tid < OUT) {
+    if (active) {
         const float mean[3] = {0.485f, 0.456f, 0.406f};
         const float stdv[3] = {0.229f, 0.224f, 0.225f};
 #pragma unroll
@@ -276,7 +289,7 @@ preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict_
 #pragma unroll
             for (int c = 0; c < 3; ++c) {
                 const float v = __fdiv_rn(__fsub_rn(__fdiv_rn(a[c], 255.0f), mean[c]), stdv[c]);
-                const size_t o = ((static_cast<size_t>(blockIdx.y) * 3 + c) * OUT + oy) * OUT + tid;
+                const size_t o = ((static_cast<size_t>(blockIdx.y) * 3 + c) * OUT + oy) * OUT + ocol;
                 if (OUT_F32) reinterpret_cast<float*>(out)[o] = v;
                 else reinterpret_cast<__nv_bfloat16*>(out)[o] = __float2bfloat16_rn(v);
             }
@@ -312,6 +325,7 @@ preprocess_identity_kernel(const uint8_t* __restrict__ slab, const b2p_image* __
     const int row = static_cast<int>((t / GROUPS) % OUT);
     const int img = static_cast<int>(t / (GROUPS * OUT));
     const b2p_image im = imgs[img];
+    if (im.h != im.res_h || im.w != im.res_w) return;   // mixed batch: the general kernel takes this image
     const uint8_t* src = slab + im.offset + (static_cast<size_t>(im.top + row) * im.w + im.left + 8 * g) * 3;
     const uint32_t sh = static_cast<uint32_t>(reinterpret_cast<uintptr_t>(src) & 3u) * 8u;
     const uint32_t* w = reinterpret_cast<const uint32_t*>(reinterpret_cast<uintptr_t>(src) & ~static_cast<uintptr_t>(3));
@@ -357,15 +371,17 @@ __global__ void __launch_bounds__(256)
 preprocess_identity_s2d_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict__ imgs,
                                uint4* __restrict__ out, const float* __restrict__ lut_g, int n) {
     __shared__ float lut[3 * 256];
+    __shared__ uint4 stage[256 * 8];                 // 32 KB: one 4 KB transposition buffer per warp
     for (int i = threadIdx.x; i < 3 * 256; i += 256) lut[i] = __ldg(lut_g + i);
     __syncthreads();
     constexpr int HALF = OUT / 2;                    // 112 s2d pixels per row
     constexpr int GROUPS = HALF / 4;                 // 28 groups of 4
     const long t = blockIdx.x * 256L + threadIdx.x;
-    if (t >= static_cast<long>(n) * HALF * GROUPS) return;
-    const int g = static_cast<int>(t % GROUPS);
-    const int oi = static_cast<int>((t / GROUPS) % HALF);
-    const int img = static_cast<int>(t / (GROUPS * HALF));
+    const long t_max = static_cast<long>(n) * HALF * GROUPS - 1;
+    const long tc = t < t_max ? t : t_max;           // threads past the end recompute the last group (never stored)
+    const int g = static_cast<int>(tc % GROUPS);
+    const int oi = static_cast<int>((tc / GROUPS) % HALF);
+    const int img = static_cast<int>(tc / (GROUPS * HALF));
     const b2p_image im = imgs[img];
     uint32_t q[4][6];                                // [s2d pixel][channel pair]
 #pragma unroll
@@ -393,14 +409,29 @@ preprocess_identity_s2d_kernel(const uint8_t* __restrict__ slab, const b2p_image
             for (int k = 0; k < 3; ++k) q[p][di * 3 + k] = pack_bf16x2(v[2 * k], v[2 * k + 1]);
         }
     }
-    uint4* o = out + 2 * ((static_cast<long>(img) * HALF + oi) * HALF + 4 * g);
+    // Thread t owns output bytes [128 t, 128 t + 128) of the tensor (t enumerates (img, row, group) in memory order),
+    // so a warp owns 4 KB.  Written directly, every store instruction would scatter 16-byte pieces 128 bytes apart;
+    // instead the warp transposes through shared memory (XOR-swizzled, conflict-free) and stores 512 contiguous
+    // bytes per instruction.
+    const int lane = threadIdx.x & 31;
+    uint4* wbuf = stage + (threadIdx.x & ~31) * 8;        // this warp's 32 x 8 uint4
 #pragma unroll
     for (int p = 0; p < 4; ++p) {
         uint4 a, c;
         a.x = q[p][0]; a.y = q[p][1]; a.z = q[p][2]; a.w = q[p][3];
         c.x = q[p][4]; c.y = q[p][5]; c.z = 0u;      c.w = 0u;
-        o[2 * p] = a;
-        o[2 * p + 1] = c;
+        wbuf[lane * 8 + ((2 * p) ^ (lane & 7))] = a;
+        wbuf[lane * 8 + ((2 * p + 1) ^ (lane & 7))] = c;
+    }
+    __syncwarp();
+    const long total16 = static_cast<long>(n) * HALF * GROUPS * 8;          // uint4 elements in the tensor
+    const long warp_base = (t - lane) * 8;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const int e = j * 32 + lane;                      // element of the warp's 4 KB, in memory order
+        const int src_t = e >> 3, src_c = e & 7;
+        const uint4 v = wbuf[src_t * 8 + (src_c ^ (src_t & 7))];
+        if (warp_base + e < total16) out[warp_base + e] = v;
     }
 }
 
@@ -431,45 +462,85 @@ cudaError_t launch_preprocess_s2d(const uint8_t* slab, const b2p_image* imgs_dev
     return cudaGetLastError();
 }
 
+// Host mirror of axis_range(): first source index and one-past-last of the taps of output index i.
+static void host_tap_window(int in_size, int out_size, int i, int* lo, int* hi) {
+    const float scale = static_cast<float>(in_size) / static_cast<float>(out_size);
+    const float support = scale >= 1.0f ? scale : 1.0f;
+    const int max_taps = static_cast<int>(ceilf(support)) * 2 + 1;
+    const float center = static_cast<float>(static_cast<double>(scale) * (static_cast<double>(i) + 0.5));
+    const long long a = static_cast<long long>(static_cast<double>(center - support) + 0.5);
+    const long long b = static_cast<long long>(static_cast<double>(center + support) + 0.5);
+    const int xmin = static_cast<int>(a > 0 ? a : 0);
+    int xs = static_cast<int>(b < in_size ? b : in_size) - xmin;
+    xs = xs < 0 ? 0 : (xs > max_taps ? max_taps : xs);
+    *lo = xmin;
+    *hi = xmin + xs;
+}
+
 cudaError_t launch_preprocess(const uint8_t* slab, const b2p_image* imgs_dev, const b2p_image* imgs_host,
                               int n, void* out, int out_f32, const float* norm_lut, cudaStream_t s, int* launches) {
     if (n <= 0) return cudaSuccess;
-    int wh_taps = 1, wv_taps = 1, max_w = 1;
-    for (int i = 0; i < n; ++i) {
-        const b2p_image& im = imgs_host[i];
-        const int th = host_max_taps(im.w, im.res_w), tv = host_max_taps(im.h, im.res_h);
-        wh_taps = th > wh_taps ? th : wh_taps;
-        wv_taps = tv > wv_taps ? tv : wv_taps;
-        max_w = im.w > max_w ? im.w : max_w;
-    }
-    bool all_identity = true;
+    int n_identity = 0;
     for (int i = 0; i < n; ++i)
-        all_identity = all_identity && imgs_host[i].h == imgs_host[i].res_h && imgs_host[i].w == imgs_host[i].res_w;
-    if (all_identity && norm_lut != nullptr) {
+        n_identity += imgs_host[i].h == imgs_host[i].res_h && imgs_host[i].w == imgs_host[i].res_w;
+    const bool lut_path = norm_lut != nullptr && n_identity > 0;
+    if (lut_path) {
+        // crop-only images (all of them, or the crop-only part of a mixed batch): table look-up kernel
         const long threads = static_cast<long>(n) * OUT * (OUT / 8);
         const unsigned grid = static_cast<unsigned>((threads + 255) / 256);
         if (out_f32) preprocess_identity_kernel<true><<<grid, 256, 0, s>>>(slab, imgs_dev, out, norm_lut, n);
         else preprocess_identity_kernel<false><<<grid, 256, 0, s>>>(slab, imgs_dev, out, norm_lut, n);
         if (launches) *launches += 1;
-        return cudaGetLastError();
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess || n_identity == n) return e;
     }
-    const int rowbuf_bytes = ((max_w * 3 + 15) / 16) * 16 + 32;
-    const int frow_bytes = max_w * 16 + 16;
-    const size_t smem = static_cast<size_t>(wh_taps) * OUT * 4 + static_cast<size_t>(BAND) * wv_taps * 4 +
-                        2 * BAND * 4 + RING * static_cast<size_t>(rowbuf_bytes) + frow_bytes;
-    if (smem > 200 * 1024) return cudaErrorInvalidValue;
-    dim3 grid(OUT / BAND, n);
+    // General kernel for the images that need a real resize.  Shared memory holds the tap tables plus the window of
+    // a source row that feeds a CTA's output columns; very wide sources are handled by giving a CTA fewer columns
+    // (224 / 112 / 56 / 32 / 16 / 8), so no image width is refused.
+    int wh_taps = 1, wv_taps = 1;
+    for (int i = 0; i < n; ++i) {
+        const b2p_image& im = imgs_host[i];
+        if (lut_path && im.h == im.res_h && im.w == im.res_w) continue;
+        const int th = host_max_taps(im.w, im.res_w), tv = host_max_taps(im.h, im.res_h);
+        wh_taps = th > wh_taps ? th : wh_taps;
+        wv_taps = tv > wv_taps ? tv : wv_taps;
+    }
+    const int col_choices[6] = {224, 112, 56, 32, 16, 8};
+    int cols = 0, rowbuf_bytes = 0, frow_bytes = 0;
+    size_t smem = 0;
+    for (int c : col_choices) {
+        int max_win = 1;
+        for (int i = 0; i < n; ++i) {
+            const b2p_image& im = imgs_host[i];
+            if (lut_path && im.h == im.res_h && im.w == im.res_w) continue;
+            for (int c0 = 0; c0 < OUT; c0 += c) {
+                int lo, hi, lo2, hi2;
+                host_tap_window(im.w, im.res_w, im.left + c0, &lo, &hi);
+                host_tap_window(im.w, im.res_w, im.left + c0 + c - 1, &lo2, &hi2);
+                max_win = hi2 - lo > max_win ? hi2 - lo : max_win;
+            }
+        }
+        rowbuf_bytes = ((max_win * 3 + 15) / 16) * 16 + 32;
+        frow_bytes = max_win * 16 + 16;
+        smem = static_cast<size_t>(wh_taps) * OUT * 4 + static_cast<size_t>(BAND) * wv_taps * 4 + 2 * BAND * 4 +
+               RING * static_cast<size_t>(rowbuf_bytes) + frow_bytes;
+        if (smem <= 200 * 1024) { cols = c; break; }
+    }
+    if (cols == 0) return cudaErrorInvalidValue;     // not reachable for images below ~1.4 M pixels per row
+    dim3 grid(OUT / BAND, n, OUT / cols);
     cudaError_t e;
     if (out_f32) {
         e = cudaFuncSetAttribute(preprocess_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  static_cast<int>(smem));
         if (e != cudaSuccess) return e;
-        preprocess_kernel<true><<<grid, THREADS, smem, s>>>(slab, imgs_dev, out, wh_taps, wv_taps, rowbuf_bytes, frow_bytes, 1.0f);
+        preprocess_kernel<true><<<grid, THREADS, smem, s>>>(slab, imgs_dev, out, wh_taps, wv_taps, rowbuf_bytes, frow_bytes,
+                                                             1.0f, cols, lut_path ? 1 : 0);
     } else {
         e = cudaFuncSetAttribute(preprocess_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  static_cast<int>(smem));
         if (e != cudaSuccess) return e;
-        preprocess_kernel<false><<<grid, THREADS, smem, s>>>(slab, imgs_dev, out, wh_taps, wv_taps, rowbuf_bytes, frow_bytes, 1.0f);
+        preprocess_kernel<false><<<grid, THREADS, smem, s>>>(slab, imgs_dev, out, wh_taps, wv_taps, rowbuf_bytes, frow_bytes,
+                                                              1.0f, cols, lut_path ? 1 : 0);
     }
     if (launches) *launches += 1;
     return cudaGetLastError();

@@ -101,3 +101,22 @@ def test_k1_rejects_bad_geometry(cuda_device):
     with pytest.raises(B.B2PError):
         rep.preprocess(slab, B.make_images([(0, 300, 300, 256, 256, 40, 0)]), 1, out)   # crop leaves the image
     rep.close()
+
+
+def test_k1_very_wide_sources(cuda_device):
+    """Panoramas / 45+ Mpixel-camera widths: the staged window of a source row no longer grows with the image width
+    (a CTA takes fewer output columns instead), so no width is refused.  Pillow accepts such uploads (reference
+    src/model/model.py:23) and the whole micro-batch used to fail with them."""
+    from oracle import images
+    _check([images.synthetic_image(61, 230, 9000), images.synthetic_image(62, 300, 12000)], "direct")
+    _check([images.synthetic_image(63, 260, 10000), images.synthetic_image(64, 2000, 8192)], "preset")
+
+
+def test_k1_mixed_crop_only_and_resized_batch(cuda_device):
+    """Crop-only images and images that need a resize in one call: the table kernel takes the former, the general
+    kernel the latter, each skipping the other's images."""
+    from oracle import images
+    sizes = [(224, 224), (480, 640), (224, 224), (333, 517), (224, 224)]
+    _check([images.synthetic_image(400 + i, h, w) for i, (h, w) in enumerate(sizes)], "direct")
+    sizes = [(256, 256), (720, 1280), (256, 300), (300, 256)]
+    _check([images.synthetic_image(500 + i, h, w) for i, (h, w) in enumerate(sizes)], "preset")
