@@ -105,7 +105,7 @@ SYMBOLS = [
     ("b2p_jpeg_destroy", C.c_int32, [C.c_void_p]),
     ("b2p_jpeg_last_error", C.c_char_p, [C.c_void_p]),
     ("b2p_jpeg_stats_get", C.c_int32, [C.c_void_p, C.POINTER(JpegStats)]),
-    ("b2p_jpeg_decode", C.c_int32, [C.c_void_p, C.POINTER(C.c_char_p), C.POINTER(C.c_int64), C.c_int32, C.c_void_p,
+    ("b2p_jpeg_decode", C.c_int32, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_int64), C.c_int32, C.c_void_p,
                                     C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p]),
 ]
 
@@ -179,7 +179,17 @@ class JpegDecoder:
     def decode(self, files: Sequence[bytes], slab, slab_bytes: int, offsets: Sequence[int], status=None, stream=None) -> None:
         """files -> uint8 HWC RGB images at slab + offsets[i] (device memory).  Asynchronous on `stream`."""
         n = len(files)
-        arr = (C.c_char_p * max(n, 1))(*files)
+        # a file is a bytes object, or anything with .address / .length (ingest.HostView: bytes that live in a
+        # shared-memory ring and are read in place); the library has consumed the host bytes when it returns
+        arr = (C.c_void_p * max(n, 1))()
+        keep = []
+        for i, f in enumerate(files):
+            if hasattr(f, "address"):
+                arr[i] = int(f.address)
+            else:
+                b = f if isinstance(f, bytes) else bytes(f)
+                keep.append(b)
+                arr[i] = C.cast(C.c_char_p(b), C.c_void_p).value
         lens = (C.c_int64 * max(n, 1))(*[len(f) for f in files])
         offs = (C.c_int64 * max(n, 1))(*[int(o) for o in offsets])
         rc = self.lib.b2p_jpeg_decode(self.h, arr, lens, n, Replica._ptr(slab), int(slab_bytes), offs,

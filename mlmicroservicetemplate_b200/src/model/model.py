@@ -12,7 +12,7 @@ enqueues the uint8 HWC pixels and blocks on a future, so concurrent callers are 
 `predict_async` is the awaitable twin the server uses so the event loop is never blocked.
 
 Environment knobs (defaults in brackets):
-    MODEL [resnet50]    resnet18 | resnet50 | template   (`template` = the reference's constant-dict
+    MODEL [resnet50]    resnet18 | resnet50 | vit_b_16 | template   (`template` = the reference's constant-dict
                         example plugin, no GPU involved — BASELINE.json configs[0])
     GPUS  [all]         comma-separated device indices
     MAX_BATCH [64]  MAX_WAIT_US [2000]  TOPK [5]  SEED [0]  PREPROCESS [preset] (preset | direct)
@@ -21,6 +21,8 @@ Environment knobs (defaults in brackets):
                         kernel layout + class names, loaded as-is (no torchvision at start-up); MODEL is then ignored
     CHECKPOINT          path of a torch.save'd torchvision state_dict for MODEL (default: seeded random init)
     LABELS              text file with one class name per line (default: positional names)
+    ENGINE_SOCKET       path of a GPU dispatcher's Unix socket (src/server/serve.py starts both): this process then
+                        builds no replica; uploads go to the dispatcher through a shared-memory ring of INGEST_SHM_MB [256]
     DECODE [gpu]        gpu: uploads that are baseline JPEGs (b2p_jpeg_inspect) are decoded on the GPU, bit-exact
                         with Pillow; everything else (PNG, progressive / CMYK JPEG, ...) is decoded by Pillow
                         as in the reference.  host: every upload goes through Pillow.
@@ -60,6 +62,16 @@ def init() -> None:
         if arch == "template":
             return
         from concurrent.futures import ThreadPoolExecutor
+        if os.getenv("ENGINE_SOCKET"):
+            # Front-end process of a multi-process deployment (ingest.py): the replicas live in
+            # the dispatcher process; this process parses uploads and hands their bytes over through shared memory.
+            from ...ingest import RemoteEngine
+            engine = RemoteEngine(os.environ["ENGINE_SOCKET"], ring_bytes=int(os.getenv("INGEST_SHM_MB", "256")) << 20)
+            _state["engine"] = engine
+            _state["decode"] = engine.info.get("decode", "gpu")
+            _state["classes"] = list(engine.info["classes"])
+            _state["decode_pool"] = ThreadPoolExecutor(max_workers=int(os.getenv("DECODE_THREADS", "4")))
+            return
         from ...runtime import build_gpu_engine
         gpus = os.getenv("GPUS")
         devs = [int(g) for g in gpus.split(",")] if gpus else None
