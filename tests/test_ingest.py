@@ -142,3 +142,56 @@ def test_remote_engine_in_process_round_trip_and_dispatcher_loss():
         remote.close()
         srv.close()
         eng.close()
+
+
+def test_http_front_end_process_uses_the_dispatcher(tmp_path):
+    """A real uvicorn front-end process (src/server/main.py unchanged, ENGINE_SOCKET set) in front of a dispatcher:
+    POST /predict answers in the reference's envelope (reference src/server/main.py:137-140) with the dispatcher's
+    class names, and the JPEG bytes reached the dispatcher in place (HostView)."""
+    import http.client
+    import io
+    import socket
+    import time
+    from PIL import Image
+    sys.path.insert(0, os.path.join(ROOT, "benchmarks"))
+    from serve_http import multipart
+    w = EchoWorker()
+    eng = Engine([w], max_batch=4, max_wait_us=500)
+    sock = str(tmp_path / "d.sock")
+    names = [f"c{i}" for i in range(256)]
+    srv = DispatcherServer(eng, sock, {"classes": names, "n_classes": 256, "decode": "gpu", "gpus": 1})
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    env = dict(os.environ, ENGINE_SOCKET=sock, MODEL="resnet50", REGISTER="0", PYTHONPATH=ROOT)
+    proc = subprocess.Popen([sys.executable, "-m", "uvicorn", "mlmicroservicetemplate_b200.src.server.main:app",
+                             "--host", "127.0.0.1", "--port", str(port), "--log-level", "warning"], env=env, cwd=ROOT)
+    try:
+        t0 = time.time()
+        status = None
+        while time.time() - t0 < 60:
+            try:
+                c = http.client.HTTPConnection("127.0.0.1", port, timeout=5)
+                c.request("GET", "/status")
+                r = c.getresponse(); r.read(); status = r.status; c.close()
+                if status == 200:
+                    break
+            except OSError:
+                pass
+            time.sleep(0.2)
+        assert status == 200
+        buf = io.BytesIO()
+        Image.fromarray(np.full((32, 32, 3), 120, np.uint8)).save(buf, format="JPEG", quality=90)
+        jpeg = buf.getvalue()
+        body, ctype = multipart(jpeg, "x.jpg")
+        c = http.client.HTTPConnection("127.0.0.1", port, timeout=30)
+        c.request("POST", "/predict", body=body, headers={"Content-Type": ctype})
+        r = c.getresponse()
+        out = json.loads(r.read())
+        assert r.status == 200 and out["status"] == "success"
+        assert out["result"]["classes"] == names
+        assert set(out["result"]["result"]) == {names[jpeg[0]], names[len(jpeg) % 251]}
+        assert w.saw_host_view == 1
+    finally:
+        proc.terminate()
+        proc.wait(timeout=30)
+        srv.close()
+        eng.close()
