@@ -121,7 +121,8 @@ def main():
         if args.gpus:
             env["GPUS"] = args.gpus
         srv = subprocess.Popen([sys.executable, "-m", "mlmicroservicetemplate_b200.src.server.serve", "--workers", str(nw),
-                                "--host", "127.0.0.1", "--port", str(port)], env=env, cwd=ROOT)
+                                "--host", "127.0.0.1", "--port", str(port)], env=env, cwd=ROOT,
+                               start_new_session=True, stdout=subprocess.DEVNULL)
         try:
             wait_ready(port, srv)
             # every front-end worker initialises lazily on its first requests: warm them all
@@ -149,11 +150,17 @@ def main():
             results.append(r)
             print(json.dumps(r), flush=True)
         finally:
+            # the launcher, its uvicorn workers and the dispatcher form one process group: stop them all
+            import signal
             srv.terminate()
             try:
-                srv.wait(timeout=60)
+                srv.wait(timeout=20)
             except subprocess.TimeoutExpired:
-                srv.kill()
+                pass
+            try:
+                os.killpg(srv.pid, signal.SIGKILL)
+            except (ProcessLookupError, PermissionError):
+                pass
     if args.out:
         json.dump(results, open(args.out, "w"), indent=1)
 

@@ -594,6 +594,34 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
         }
         if (o.kind == B2P_OP_LINEAR && o.dst == B2P_SLOT_OUTPUT) h->classes = o.out_c;
     }
+    // L2 cache policies (B2P_L2_HINTS: 0 = none, 1 = default, 2 = also stream very large outputs).  An operand at
+    // its LAST use (no later op reads the slot before it is overwritten) is loaded evict-first: it is dead afterwards,
+    // and without the hint it would push the tensor being WRITTEN - which the next layer reads - out of the L2.
+    // Applied to residuals and to the inputs of 1x1 layers (read once); 3x3 inputs are re-read per tap and stay normal.
+    {
+        const char* e = getenv("B2P_L2_HINTS");
+        const int level = e ? atoi(e) : 1;
+        const uint64_t EVICT_FIRST = 0x12F0000000000000ull;
+        auto last_use = [&](int i, int slot) {
+            if (slot == B2P_SLOT_NONE || slot == B2P_SLOT_OUTPUT) return false;
+            for (int j = i + 1; j < desc->n_ops; ++j) {
+                const b2p_op& o = desc->ops[j];
+                if (o.src == slot || o.res == slot || (o.src2_c > 0 && o.src2 == slot)) return false;
+                if (o.dst == slot || (o.kind == B2P_OP_CONV_PAIR && o.reserved[0] == slot)) return true;
+            }
+            return true;
+        };
+        for (int i = 0; i < desc->n_ops && level > 0; ++i) {
+            OpPlan& p = h->ops[i];
+            const b2p_op& o = p.op;
+            if (!p.is_gemm || p.use_c3) continue;
+            if (o.res != B2P_SLOT_NONE && last_use(i, o.res)) p.gemm.pol_res = EVICT_FIRST;
+            if (!p.gemm.im2col && o.src != o.res && last_use(i, o.src)) p.gemm.pol_a = EVICT_FIRST;
+            if (level >= 2 && o.kind == B2P_OP_CONV &&
+                static_cast<int64_t>(h->chunk) * o.out_h * o.out_w * o.out_c * 2 > (110ll << 20))
+                p.gemm.pol_out = EVICT_FIRST;
+        }
+    }
     // K1 -> stem fusion for the predict chain: possible when the program opens with the space-to-depth pack of the
     // 224x224 input into a workspace slot, no later op reads the external input, and the batch is not chunked
     if (desc->n_ops > 1 && getenv("B2P_NO_FUSED_INPUT") == nullptr) {

@@ -63,6 +63,7 @@ struct GemmArgs {
     int split_ways;   // a nearly empty last wave costs a fraction of a tile time instead of a whole one (0 = off)
     const float* bias;
     void* out;        // only used by the fp32 (linear) epilogue
+    uint64_t pol_a, pol_b, pol_res, pol_out;   // L2 cache policies of the four TMA streams (ptx.cuh: L2_EVICT_*)
 };
 
 // GELU(x) = 0.5 x (1 + erf(x / sqrt 2)) with erf from Abramowitz & Stegun 7.1.26 (|error| <= 1.5e-7, far
@@ -215,17 +216,17 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 uint8_t* dst = smem_a + stg * C::A_BYTES;
                 if (CTA2) {
                     const uint32_t bar = full0 + static_cast<uint32_t>(stg * 8);
-                    if (im2col) tma_load_im2col_4d_pair(map, bar, dst, c, w, h, n, static_cast<uint16_t>(s_), static_cast<uint16_t>(r_));
-                    else tma_load_2d_pair(map, bar, dst, c, w);
+                    if (im2col) tma_load_im2col_4d_pair_hint(map, bar, dst, c, w, h, n, static_cast<uint16_t>(s_), static_cast<uint16_t>(r_), args.pol_a);
+                    else tma_load_2d_pair_hint(map, bar, dst, c, w, args.pol_a);
                 } else {
-                    if (im2col) tma_load_im2col_4d(map, &full_bar[stg], dst, c, w, h, n, static_cast<uint16_t>(s_), static_cast<uint16_t>(r_));
-                    else tma_load_2d(map, &full_bar[stg], dst, c, w);
+                    if (im2col) tma_load_im2col_4d_hint(map, &full_bar[stg], dst, c, w, h, n, static_cast<uint16_t>(s_), static_cast<uint16_t>(r_), args.pol_a);
+                    else tma_load_2d_hint(map, &full_bar[stg], dst, c, w, args.pol_a);
                 }
             };
             auto load_b = [&](int stg, int kcol, int nrow, bool piece) {
                 uint8_t* dst = smem_b + stg * C::B_BYTES;
-                if (CTA2) tma_load_2d_pair(&tmap_b, full0 + static_cast<uint32_t>(stg * 8), dst, kcol, nrow);
-                else tma_load_2d(piece ? &tmap_b64 : &tmap_b, &full_bar[stg], dst, kcol, nrow);
+                if (CTA2) tma_load_2d_pair_hint(&tmap_b, full0 + static_cast<uint32_t>(stg * 8), dst, kcol, nrow, args.pol_b);
+                else tma_load_2d_hint(piece ? &tmap_b64 : &tmap_b, &full_bar[stg], dst, kcol, nrow, args.pol_b);
             };
             for (int tile = first_tile; tile < total_items; tile += tile_step) {
                 int m_blk, n_blk, sub;
@@ -321,8 +322,8 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 for (int c64 = 0; c64 < n_chunks; ++c64) {
                     mbar_wait(&res_empty_bar[rs], rphase ^ 1u);
                     mbar_arrive_expect_tx(&res_full_bar[rs], OUT_CHUNK_BYTES);
-                    tma_load_2d(&tmap_res, &res_full_bar[rs], smem_res + rs * OUT_CHUNK_BYTES,
-                                n_blk * BLOCK_N + (sub >= 0 ? sub : c64) * 64, m_blk * BLOCK_M);
+                    tma_load_2d_hint(&tmap_res, &res_full_bar[rs], smem_res + rs * OUT_CHUNK_BYTES,
+                                     n_blk * BLOCK_N + (sub >= 0 ? sub : c64) * 64, m_blk * BLOCK_M, args.pol_res);
                     if (++rs == RES_STAGES) { rs = 0; rphase ^= 1u; }
                 }
             }
@@ -458,7 +459,7 @@ conv_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     fence_proxy_async_smem();
                     named_bar_sync(bar_id, EPI_THREADS);
                     if (store_leader) {
-                        tma_store_2d(&tmap_out, stage_tile, col0, m_blk * BLOCK_M);
+                        tma_store_2d_hint(&tmap_out, stage_tile, col0, m_blk * BLOCK_M, args.pol_out);
                         tma_store_commit();
                     }
                 }
@@ -779,6 +780,10 @@ cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, bool has_res, void* 
     a.reverse = p.reverse;
     a.bias = p.bias;
     a.out = out_f32;
+    a.pol_a = p.pol_a;
+    a.pol_b = L2_EVICT_LAST;        // weights: re-read by every tile of every CTA
+    a.pol_res = p.pol_res;
+    a.pol_out = p.pol_out;
     int total = a.m_tiles * a.n_tiles;
     if (total <= 0) return cudaSuccess;
     if (p.cta2) total = 2 * ((a.m_tiles + 1) / 2) * a.n_tiles;      // CTAs, two per 256-row tile

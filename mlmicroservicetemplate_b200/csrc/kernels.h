@@ -54,6 +54,9 @@ struct GemmPlan {
                           // starts on the rows its predecessor wrote last (still resident in the 126 MB L2)
     const float* bias = nullptr;
     const void* weight = nullptr;
+    // L2 cache policies of the activation / residual loads and the output store (ptx.cuh L2_EVICT_*; the default is
+    // the ordinary policy).  api.cu marks operands at their LAST use as evict-first.
+    uint64_t pol_a = 0x1000000000000000ull, pol_res = 0x1000000000000000ull, pol_out = 0x1000000000000000ull;
 };
 
 // Resolves the driver's tensor-map encoders once per process. Returns false if unavailable.
