@@ -20,6 +20,7 @@ import os
 import socket
 import subprocess
 import sys
+import tempfile
 import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -120,6 +121,8 @@ def main():
                    PYTHONPATH=ROOT + os.pathsep + os.environ.get("PYTHONPATH", ""))
         if args.gpus:
             env["GPUS"] = args.gpus
+        stats_path = os.path.join(tempfile.gettempdir(), f"b2p-dispatch-stats-{os.getpid()}-{nw}.json")
+        env["B2P_DISPATCH_STATS"] = stats_path
         srv = subprocess.Popen([sys.executable, "-m", "mlmicroservicetemplate_b200.src.server.serve", "--workers", str(nw),
                                 "--host", "127.0.0.1", "--port", str(port)], env=env, cwd=ROOT,
                                start_new_session=True, stdout=subprocess.DEVNULL)
@@ -148,7 +151,6 @@ def main():
                  "max_batch": args.max_batch, "max_wait_us": args.max_wait_us,
                  "transport": "real HTTP on 127.0.0.1, keep-alive; uploads -> dispatcher through shared memory"}
             results.append(r)
-            print(json.dumps(r), flush=True)
         finally:
             # the launcher, its uvicorn workers and the dispatcher form one process group: stop them all
             import signal
@@ -161,6 +163,12 @@ def main():
                 os.killpg(srv.pid, signal.SIGKILL)
             except (ProcessLookupError, PermissionError):
                 pass
+            if results and results[-1].get("http_workers") == nw:
+                try:
+                    results[-1]["dispatcher"] = json.load(open(stats_path))     # includes the warm-up requests
+                except (OSError, ValueError):
+                    results[-1]["dispatcher"] = None
+                print(json.dumps(results[-1]), flush=True)
     if args.out:
         json.dump(results, open(args.out, "w"), indent=1)
 

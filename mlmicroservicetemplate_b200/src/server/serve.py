@@ -41,6 +41,21 @@ def run_dispatcher(socket_path: str) -> int:
     print(f"dispatcher ready on {socket_path}: {info['gpus']} GPU replica(s), {info['n_classes']} classes", flush=True)
     stop.wait()
     server.close()
+    stats_path = os.getenv("B2P_DISPATCH_STATS")
+    if stats_path:
+        # what the micro-batcher achieved: batch-size histogram and each GPU's share of the images
+        import collections
+        import json
+        hist = collections.Counter(engine.batch_sizes)
+        share = collections.Counter()
+        for w, n in engine.dispatch_log:
+            share[w] += n
+        total = max(1, sum(share.values()))
+        with open(stats_path, "w") as f:
+            json.dump({"requests": server.requests, "batches": len(engine.batch_sizes),
+                       "mean_batch": sum(engine.batch_sizes) / max(1, len(engine.batch_sizes)),
+                       "batch_histogram": {str(k): v for k, v in sorted(hist.items())},
+                       "per_gpu_share": {str(g): share.get(g, 0) / total for g in range(info["gpus"])}}, f)
     plugin.shutdown()
     return 0
 
