@@ -66,10 +66,18 @@ enum b2p_op_kind {
                               reserved[0] = 1: only token 0 of each image -> [n, c]                      */
     B2P_OP_ATTENTION = 11, /* softmax(Q K^T / sqrt(64)) V per head on packed QKV [n,in_h,3c] -> [n,in_h,c];
                               reserved[0] = number of heads (head dim 64)                                */
-    B2P_OP_CONV_PAIR = 12  /* two chained 1x1/s1 convs in one kernel (a bottleneck's conv3 and the next block's
+    B2P_OP_CONV_PAIR = 12, /* two chained 1x1/s1 convs in one kernel (a bottleneck's conv3 and the next block's
                               conv1): dst = relu(conv(src) + bias + res) as OP_CONV, and additionally
                               slot reserved[0] = relu(conv(dst) + bias2) with weight blob reserved[1] and bias blob
                               reserved[2], reserved[3] = its output channels (64, 128 or 256)                 */
+    B2P_OP_BOTTLENECK = 13 /* a whole bottleneck block of the 56x56 stage in one kernel
+                              (SP/torchvision/models/resnet.py:143-163): t1 = relu(conv1x1(src)), t2 = relu(conv3x3(t1)),
+                              dst = relu(conv1x1(t2) + shortcut).  in_c = block input channels, reserved2 = bottleneck width
+                              (64), out_c = 256.  Blobs: weight / bias = conv1 [64][in_c], reserved[0] / [1] = conv2
+                              [64][3][3][64] and its bias, reserved[2] / [3] = conv3 and its bias.  res == src: identity
+                              shortcut (in_c = 256, conv3 [256][64]); res == B2P_SLOT_NONE: projection shortcut folded
+                              into conv3 as extra K columns (in_c = 64, conv3 [256][64 + 64], biases summed).  src and
+                              dst are workspace slots.                                                             */
 };
 
 typedef struct b2p_op {

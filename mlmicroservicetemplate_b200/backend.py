@@ -17,7 +17,7 @@ LIB_PATH = Path(os.environ.get("B2P_LIB", PKG / "lib" / "libb200predict.so"))   
 ABI_VERSION = 3
 SLOT_INPUT, SLOT_OUTPUT, SLOT_NONE = 0, -2, -1
 OP_CONV, OP_LINEAR, OP_MAXPOOL, OP_AVGPOOL, OP_STEM_PACK, OP_NCHW_TO_NHWC, OP_STEM_CONV = 1, 2, 3, 4, 5, 6, 7
-OP_PATCHIFY, OP_TOKENS, OP_LAYERNORM, OP_ATTENTION, OP_CONV_PAIR = 8, 9, 10, 11, 12
+OP_PATCHIFY, OP_TOKENS, OP_LAYERNORM, OP_ATTENTION, OP_CONV_PAIR, OP_BOTTLENECK = 8, 9, 10, 11, 12, 13
 ACT_NONE, ACT_RELU, ACT_GELU = 0, 1, 2
 OUT_HW = 224
 MAX_TOPK = 8

@@ -23,6 +23,7 @@ struct OpPlan {
     AttentionPlan att;    // valid for ATTENTION
     PairPlan pair;        // valid for CONV_PAIR
     Conv3x3Plan c3;       // valid for CONV ops taken by the patch-resident 3x3 kernel
+    BneckPlan bneck;      // valid for BOTTLENECK
     bool use_c3 = false;
     void* stem_image = nullptr;
     bool is_gemm = false;
@@ -121,7 +122,7 @@ int validate_desc(const b2p_model_desc* d) {
     if (d->sub_batch < 0) return B2P_E_ARG;
     for (int i = 0; i < d->n_ops; ++i) {
         const b2p_op& o = d->ops[i];
-        if (o.kind < B2P_OP_CONV || o.kind > B2P_OP_CONV_PAIR) return B2P_E_ARG;
+        if (o.kind < B2P_OP_CONV || o.kind > B2P_OP_BOTTLENECK) return B2P_E_ARG;
         auto ok_slot = [&](int s, bool allow_none) {
             if (s == B2P_SLOT_NONE) return allow_none;
             if (s == B2P_SLOT_OUTPUT) return true;
@@ -138,8 +139,14 @@ int validate_desc(const b2p_model_desc* d) {
                 o.dst == B2P_SLOT_OUTPUT || o.res == B2P_SLOT_INPUT || (o.res == B2P_SLOT_NONE && o.src2_c <= 0))
                 return B2P_E_ARG;
         }
+        if (o.kind == B2P_OP_BOTTLENECK) {
+            for (int r = 0; r < 4; ++r)
+                if (o.reserved[r] < 0 || o.reserved[r] >= d->n_blobs) return B2P_E_ARG;
+            if (o.src <= 0 || o.dst <= 0 || o.src == o.dst || (o.res != B2P_SLOT_NONE && o.res != o.src)) return B2P_E_ARG;
+        }
         if (o.kind == B2P_OP_CONV || o.kind == B2P_OP_LINEAR || o.kind == B2P_OP_STEM_CONV ||
-            o.kind == B2P_OP_TOKENS || o.kind == B2P_OP_LAYERNORM || o.kind == B2P_OP_CONV_PAIR) {
+            o.kind == B2P_OP_TOKENS || o.kind == B2P_OP_LAYERNORM || o.kind == B2P_OP_CONV_PAIR ||
+            o.kind == B2P_OP_BOTTLENECK) {
             if (o.weight < 0 || o.weight >= d->n_blobs || o.bias < 0 || o.bias >= d->n_blobs) return B2P_E_ARG;
         }
         // every op: the slots it touches must hold the tensors its shape fields describe (a malformed program
@@ -238,6 +245,9 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st,
                     e = stem_plan_launch(p.stem, nb, o.relu, h->num_sms, st);
                     break;
                 }
+                case B2P_OP_BOTTLENECK:
+                    e = bneck56_launch(p.bneck, nb, h->num_sms, st);
+                    break;
                 case B2P_OP_CONV_PAIR:
                     e = pair_plan_launch(p.pair, nb * o.out_h * o.out_w, op_dir, h->num_sms, st);
                     break;
@@ -577,6 +587,23 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
                                 h->blobs[o.reserved[1]], static_cast<const float*>(h->blobs[o.reserved[2]]), eb, sizeof eb) ||
                 !pair_plan_set_src2(p.pair, s_src2, h->chunk, o.out_h, o.out_w, o.src2_stride > 0 ? o.src2_stride : 1, eb, sizeof eb) ||
                 !pair_plan_set_buffers(p.pair, s_src, s_res, s_dst, s_dst2, static_cast<int>(rows_cap), eb, sizeof eb))
+                B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
+        } else if (o.kind == B2P_OP_BOTTLENECK) {
+            const bool proj = o.res == B2P_SLOT_NONE;
+            const int mid = o.reserved2;
+            const int64_t k3 = proj ? mid + o.in_c : mid;
+            if (!bneck56_supported(o.in_h, o.in_w, o.in_c, mid, o.out_c, proj) || o.out_h != o.in_h || o.out_w != o.in_w ||
+                h->blob_bytes[o.weight] != static_cast<int64_t>(mid) * o.in_c * 2 ||
+                h->blob_bytes[o.reserved[0]] != static_cast<int64_t>(mid) * 9 * mid * 2 ||
+                h->blob_bytes[o.reserved[2]] != static_cast<int64_t>(o.out_c) * k3 * 2 ||
+                h->blob_bytes[o.bias] < mid * 4 || h->blob_bytes[o.reserved[1]] < mid * 4 ||
+                h->blob_bytes[o.reserved[3]] < o.out_c * 4)
+                B2P_FAIL(B2P_E_ARG, "op %d: malformed BOTTLENECK (56x56, width 64, 256 outputs; identity needs in_c 256, projection in_c 64)", i);
+            if (!h->slots[o.src] || !h->slots[o.dst]) B2P_FAIL(B2P_E_ARG, "op %d uses an empty slot", i);
+            if (!bneck56_plan_init(p.bneck, o.in_c, proj, h->blobs[o.weight], static_cast<const float*>(h->blobs[o.bias]),
+                                   h->blobs[o.reserved[0]], static_cast<const float*>(h->blobs[o.reserved[1]]),
+                                   h->blobs[o.reserved[2]], static_cast<const float*>(h->blobs[o.reserved[3]]), eb, sizeof eb) ||
+                !bneck56_plan_set(p.bneck, h->slots[o.src], h->slots[o.dst], h->chunk, eb, sizeof eb))
                 B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
         } else if (o.kind == B2P_OP_ATTENTION) {
             if (o.src != B2P_SLOT_INPUT) {

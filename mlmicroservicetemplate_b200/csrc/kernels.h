@@ -120,6 +120,25 @@ bool pair_plan_set_buffers(PairPlan& p, const void* a, const void* res, void* ou
                            size_t err_len);
 cudaError_t pair_plan_launch(const PairPlan& p, int m_rows, int reverse, int num_sms, cudaStream_t s);
 
+// ------------------------------------------------------------------ whole bottleneck block, 56x56 stage (bottleneck56.cu)
+struct BneckPlan {
+    CUtensorMap tmap_x;      // block input [n,56,56,cin] bf16, 4-D tiled, [64 ch x 64 px x 2 rows] boxes
+    CUtensorMap tmap_w1;     // [64][cin], 32-row boxes (each CTA of a pair holds half of the output rows)
+    CUtensorMap tmap_w2;     // [64][9*64], 32-row boxes
+    CUtensorMap tmap_w3;     // [256][64 (+64 with a folded projection shortcut)], 128-row boxes
+    CUtensorMap tmap_res;    // [n*56*56, 256] view of the block input: residual rows (identity blocks)
+    CUtensorMap tmap_out;    // [n*56*56, 256] block output
+    const float* b1 = nullptr;
+    const float* b2 = nullptr;
+    const float* b3 = nullptr;
+    int cin = 0, proj = 0;
+};
+bool bneck56_supported(int in_h, int in_w, int cin, int mid, int cout, bool proj);
+bool bneck56_plan_init(BneckPlan& p, int cin, bool proj, const void* w1, const float* b1, const void* w2, const float* b2,
+                       const void* w3, const float* b3, char* err, size_t err_len);
+bool bneck56_plan_set(BneckPlan& p, const void* src, void* dst, int batch_cap, char* err, size_t err_len);
+cudaError_t bneck56_launch(const BneckPlan& p, int n, int num_sms, cudaStream_t s);
+
 // ------------------------------------------------------------------ ViT pieces (vit.cu)
 struct AttentionPlan {
     CUtensorMap tmap_q;     // packed QKV [n*seq, 3*dim] bf16, 64 x 128 boxes (query tiles)

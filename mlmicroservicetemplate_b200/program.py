@@ -151,8 +151,28 @@ class _Builder:
         return dst, (oh, ow, oc)
 
 
+def bottleneck_op(p: Program, src: int, dst: int, hw: int, cin: int, w1, b1, w2, b2, w3, b3, shortcut=None) -> None:
+    """Appends one OP_BOTTLENECK (a whole 56x56 bottleneck block in one kernel).  w1 [64,cin,1,1], w2 [64,64,3,3],
+    w3 [256,64,1,1] fp32 with BN folded; shortcut = (wd [256,cin,1,1], bd) for the projection block (folded into conv3
+    as extra K columns, biases summed), None for an identity block (the residual is the block input)."""
+    mid, cout = w1.shape[0], w3.shape[0]
+    w3p, b3p = pack_conv_weight(w3).view(cout, -1), b3
+    if shortcut is not None:
+        wd, bd = shortcut
+        w3p = torch.cat([w3p, _bf16(wd.float().view(cout, -1))], dim=1).contiguous()
+        b3p = b3 + bd
+        p.flops_per_image += 2.0 * hw * hw * cout * wd.shape[1]
+    blobs = [p.add_blob(pack_conv_weight(w1)), p.add_blob(pad_bias(b1, mid)), p.add_blob(pack_conv_weight(w2)),
+             p.add_blob(pad_bias(b2, mid)), p.add_blob(w3p), p.add_blob(pad_bias(b3p, cout))]
+    op = _mk_op(B.OP_BOTTLENECK, src, dst, B.SLOT_NONE if shortcut is not None else src, (hw, hw, cin), (hw, hw, cout),
+                (3, 3), 1, (1, 1), 1, blobs[0], blobs[1], reserved=(blobs[2], blobs[3], blobs[4], blobs[5]))
+    op.reserved2 = mid
+    p.ops.append(op)
+    p.flops_per_image += 2.0 * hw * hw * (mid * cin + mid * mid * 9 + cout * mid)
+
+
 def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_stem: bool = True,
-                         fuse_pairs: bool = True, fold_shortcut: bool = True) -> Program:
+                         fuse_pairs: bool = True, fold_shortcut: bool = True, fuse_blocks: Optional[bool] = None) -> Program:
     """Walks a torchvision ResNet (SP/torchvision/models/resnet.py:266-282: conv1-bn1-relu-maxpool,
     layer1..4, avgpool, fc) and emits the program.  Works for BasicBlock and Bottleneck nets."""
     from torchvision.models.resnet import BasicBlock, Bottleneck
@@ -190,10 +210,30 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
         p.release(c1)
     x, hwc = mp, (56, 56, 64)
 
+    import os
+    if fuse_blocks is None:
+        fuse_blocks = os.getenv("B2P_FUSE_BLOCKS", "1") != "0"
     blocks = [blk for layer in (model.layer1, model.layer2, model.layer3, model.layer4) for blk in layer]
     carry = None          # (t1 slot, hwc1) when the previous block's CONV_PAIR already computed this block's conv1
     for bi_, blk in enumerate(blocks):
         if True:
+            # A 56x56 bottleneck (ResNet-50/101/152 layer1) runs as ONE kernel: only the block input is read and the
+            # block output written (measured against the layer-by-layer form with its conv3 -> next-conv1 pairing).
+            if (fuse_blocks and carry is None and isinstance(blk, Bottleneck)
+                    and hwc[0] == 56 and hwc[1] == 56 and blk.conv1.out_channels == 64 and blk.conv3.out_channels == 256
+                    and blk.conv2.stride == (1, 1) and blk.conv2.groups == 1 and blk.conv2.dilation == (1, 1)
+                    and ((blk.downsample is None and hwc[2] == 256) or
+                         (blk.downsample is not None and hwc[2] == 64 and blk.downsample[0].stride == (1, 1)
+                          and tuple(blk.downsample[0].kernel_size) == (1, 1)))):
+                w1, b1 = fold_bn(blk.conv1.weight, blk.bn1)
+                w2, b2 = fold_bn(blk.conv2.weight, blk.bn2)
+                w3, b3 = fold_bn(blk.conv3.weight, blk.bn3)
+                sc = fold_bn(blk.downsample[0].weight, blk.downsample[1]) if blk.downsample is not None else None
+                out = p.alloc(56 * 56 * 256)
+                bottleneck_op(p, x, out, 56, hwc[2], w1, b1, w2, b2, w3, b3, shortcut=sc)
+                p.release(x)
+                x, hwc = out, (56, 56, 256)
+                continue
             if isinstance(blk, Bottleneck):
                 w1, b1 = fold_bn(blk.conv1.weight, blk.bn1)
                 w2, b2 = fold_bn(blk.conv2.weight, blk.bn2)

@@ -293,3 +293,48 @@ def test_conv_with_tail_split(case, cuda_device, monkeypatch):
     monkeypatch.setenv("B2P_TAIL_SPLIT", "1")
     n, hwc, oc, k, stride, pad, relu, residual = case
     _run_conv(n, hwc, oc, k, stride, pad, relu, residual, seed=77)
+
+
+@pytest.mark.parametrize("proj,n", [(False, 2), (True, 3), (False, 5)])
+def test_bottleneck56_fused_block(proj, n, cuda_device):
+    """OP_BOTTLENECK - conv1x1 -> conv3x3 -> conv1x1 + shortcut of a 56x56 bottleneck in one CTA-pair kernel - against
+    torch fp32 with the same bf16 roundings of the two intermediates (SP/torchvision/models/resnet.py:143-163).
+    proj: the first block of the stage (64-channel input, projection shortcut folded into conv3)."""
+    from mlmicroservicetemplate_b200 import backend as B, program as P
+    g = torch.Generator().manual_seed(56 + int(proj) + n)
+    cin = 64 if proj else 256
+    x = _bf16r(torch.randn(n, 56, 56, cin, generator=g))
+    w1 = _bf16r(torch.randn(64, cin, 1, 1, generator=g) / cin ** 0.5)
+    w2 = _bf16r(torch.randn(64, 64, 3, 3, generator=g) / 576 ** 0.5)
+    w3 = _bf16r(torch.randn(256, 64, 1, 1, generator=g) / 64 ** 0.5)
+    wd = _bf16r(torch.randn(256, cin, 1, 1, generator=g) / cin ** 0.5)
+    b1, b2, b3, bd = (torch.randn(c, generator=g) * 0.1 for c in (64, 64, 256, 256))
+    p = P.Program(name="bneck")
+    p.in_elems = 56 * 56 * cin
+    p.out_elems = 56 * 56 * 256
+    xs, out = p.alloc(56 * 56 * cin), p.alloc(56 * 56 * 256)
+    # the block works slot to slot: a 1x1 max pool is an exact copy in and out of the workspace
+    p.ops.append(P._mk_op(B.OP_MAXPOOL, B.SLOT_INPUT, xs, in_hwc=(56, 56, cin), out_hwc=(56, 56, cin), k=(1, 1), stride=1))
+    P.bottleneck_op(p, xs, out, 56, cin, w1, b1, w2, b2, w3, b3, shortcut=(wd, bd) if proj else None)
+    p.ops.append(P._mk_op(B.OP_MAXPOOL, out, B.SLOT_OUTPUT, in_hwc=(56, 56, 256), out_hwc=(56, 56, 256), k=(1, 1), stride=1))
+    rep = B.Replica(0, p, max_batch=n)
+    got = torch.full((n, 56, 56, 256), float("nan"), dtype=torch.bfloat16, device="cuda")
+    rep.forward(x.to(torch.bfloat16).cuda(), n, got)
+    torch.cuda.synchronize()
+    got2 = torch.full((n, 56, 56, 256), float("nan"), dtype=torch.bfloat16, device="cuda")
+    rep.forward(x.to(torch.bfloat16).cuda(), n, got2)          # second call: every barrier phase / buffer reused
+    torch.cuda.synchronize()
+    rep.close()
+    xin = x.permute(0, 3, 1, 2)
+    t1 = _bf16r(F.conv2d(xin, w1, b1).relu())
+    t2 = _bf16r(F.conv2d(t1, w2, b2, padding=1).relu())
+    ref = F.conv2d(t2, w3, b3) + (F.conv2d(xin, wd, bd) if proj else xin)
+    ref = ref.relu().permute(0, 2, 3, 1)
+    g_ = got.float().cpu()
+    err = (g_ - ref).abs()
+    # two bf16-rounded intermediates upstream: an input ulp flips now and then, so allow two result ulps
+    bad = (err > 2.0 ** -6 * ref.abs() + 3e-2).sum().item()
+    print(f"bottleneck56 proj={proj} n={n}: max_err={err.max().item():.4g} max_ref={ref.abs().max().item():.4g} bad={bad}")
+    assert not torch.isnan(g_).any()
+    assert bad == 0
+    assert torch.equal(got, got2)

@@ -55,6 +55,20 @@ def interpret(prog: P.Program, x_nchw: torch.Tensor) -> torch.Tensor:
             y2 = F.conv2d(y.permute(0, 3, 1, 2), w2.permute(0, 3, 1, 2), prog.blobs[bi2][:n2]).relu().permute(0, 2, 3, 1)
             assert y2[0].numel() <= prog.slot_elems[dst2]
             slots[dst2] = y2
+        elif op.kind == B.OP_BOTTLENECK:
+            mid = op.reserved2
+            xin = src.permute(0, 3, 1, 2)
+            w1 = prog.blobs[op.weight].float()[:mid].permute(0, 3, 1, 2)
+            w2 = prog.blobs[op.reserved[0]].float()[:mid].permute(0, 3, 1, 2)
+            w3 = prog.blobs[op.reserved[2]].float()[: op.out_c].reshape(op.out_c, -1)
+            t1 = F.conv2d(xin, w1, prog.blobs[op.bias][:mid]).relu()
+            t2 = F.conv2d(t1, w2, prog.blobs[op.reserved[1]][:mid], padding=1).relu()
+            y = F.conv2d(t2, w3[:, :mid].reshape(op.out_c, mid, 1, 1), prog.blobs[op.reserved[3]][: op.out_c])
+            if op.res == B.SLOT_NONE:     # projection shortcut folded into conv3 as extra K columns
+                y = y + F.conv2d(xin, w3[:, mid:].reshape(op.out_c, op.in_c, 1, 1))
+            else:
+                y = y + xin
+            y = y.relu().permute(0, 2, 3, 1)
         elif op.kind == B.OP_STEM_CONV:
             w = prog.blobs[op.weight].float()[: op.out_c]
             b = prog.blobs[op.bias][: op.out_c]
