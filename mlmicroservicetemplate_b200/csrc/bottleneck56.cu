@@ -1,33 +1,36 @@
-// K2 fusion: a whole ResNet bottleneck block of the 56x56 stage as ONE persistent tcgen05 kernel
+// K2 fusion: a whole identity bottleneck block of the 56x56 stage as ONE persistent tcgen05 kernel
 // (SP/torchvision/models/resnet.py:143-163):
 //
-//   t1  = relu(W1 x  + b1)                 1x1, Cin (64 | 256) -> 64
-//   t2  = relu(W2 * t1 + b2)               3x3 / pad 1, 64 -> 64
-//   out = relu(W3 t2 + b3 + x)             1x1, 64 -> 256, identity shortcut          (Cin = 256)
-//   out = relu([W3 | Wd] [t2 ; x] + b3+bd) projection shortcut folded into the GEMM   (Cin = 64, first block)
+//   t1  = relu(W1 x  + b1)        1x1, 256 -> 64
+//   t2  = relu(W2 * t1 + b2)      3x3 / pad 1, 64 -> 64
+//   out = relu(W3 t2 + b3 + x)    1x1, 64 -> 256, identity shortcut
 //
 // Layer by layer the two 64-channel intermediates make an HBM round trip each (4 x 103 MB per 256 images and block)
 // and the 3x3 runs as a kernel of its own.  Here only the block input is read and the block output written.
 //
-// Work unit: a CTA PAIR (2-CTA cluster, the two SMs of a TPC, tcgen05 cta_group::2) takes four output rows of one
-// image, two per CTA.  Running as a pair is what makes the block fit: every MMA is a 256-row MMA whose B operand
-// (the weights) is split across the two CTAs, so each SM keeps only HALF of W1, W2 and W3 resident (68 KB
-// instead of 136 KB) next to its activations.  Per CTA and tile:
-//   * the x patch - 4 input rows (2 output rows + halo) x 64 pixels (58 used) x Cin - streams through a ring of
-//     [2 rows x 64 px x 64 ch] TMA boxes (128B swizzle, out-of-image pixels arrive as zeros); conv1 runs on all four
-//     rows (the halo rows are recomputed: 2x the conv1 math, no exchange between CTAs);
-//   * epilogue A turns the conv1 accumulator into the bf16 t1 PATCH in shared memory (zero outside the image: that
-//     is conv2's padding) in exactly the K-major swizzled layout a TMA load would have produced;
+// Work unit: one CTA takes two output rows of one image.
+//   * the x patch - 4 input rows (2 output rows + halo) x 64 pixels (58 used) x 256 ch - streams through a ring of
+//     [2 rows x 64 px x 64 ch] TMA boxes (128B swizzle, out-of-image pixels arrive as zeros), each with its 64-column
+//     slice of W1; conv1 runs on all four rows (the halo rows are recomputed: 2x the conv1 math, no exchange between
+//     CTAs).  The boxes of the tile after next are requested into the L2 ahead of time (TMA prefetch);
+//   * epilogues A / C turn the conv1 accumulator into the bf16 t1 PATCH in shared memory (zero outside the image:
+//     that is conv2's padding) in exactly the K-major swizzled layout a TMA load would have produced;
 //   * conv2 = 9 taps x 4 K-steps of MMAs whose A descriptor is the patch start shifted by (r * 64 + s) pixels
-//     (the row-shift trick of conv3x3_c64.cu); epilogue A writes t2 as the next A operand;
-//   * conv3 (N = 256) accumulates into 256 TMEM columns; epilogue B adds bias and the residual (TMA-loaded into the
-//     staging tile, updated in place), applies ReLU and TMA-stores two 56-pixel rows per 64-channel chunk.
+//     (the row-shift trick of conv3x3_c64.cu), W2 (72 KB) resident; epilogue A writes t2 as the next A operand;
+//   * conv3 (N = 256, W3 resident) accumulates into 256 TMEM columns; epilogue B adds bias and the residual (read from
+//     global memory: the same pixels went through the x ring a moment ago, so it is an L2 hit), applies ReLU and
+//     TMA-stores two 56-pixel rows per 64-channel chunk.
 // TMEM (512 columns): conv1 2 x 64 | conv2 64 | - | conv3 256.
 //
-// Warps (512 threads): 0 = TMA producer (weights once, then x boxes), 1 = TMEM owner + MMA issuer (leader CTA only),
-// 2 = residual / shortcut-input loader, 3 idle, 4-7 = epilogue A, 8-15 = epilogue B (two groups, alternate chunks).
-// The MMA order per tile i is conv2(i), conv1(i+1), conv3(i), so the tensor pipe works on the next tile's conv1
-// while epilogue A produces t2(i).
+// Why not a CTA pair (cta_group::2) with the weights split across two SMs, which would leave room for deeper rings:
+// measured, a cta_group::2 MMA with N = 64 takes as long as one with N = 256 (the kernel ran its tensor pipe
+// back to back at 24 % of the peak op rate: profiles/r02k_bottleneck_pair_ncu.txt), so the 68 narrow MMAs of
+// conv1 + conv2 cost four times their single-CTA price.
+//
+// Warps (512 threads): 0 = TMA producer (weights once, then x / W1 boxes), 1 = TMEM owner + MMA issuer, 2-3 idle,
+// 4-7 = epilogue A (t1 patch rows 0-1, then t2), 12-15 = epilogue C (t1 patch rows 2-3), 8-11 = epilogue B (conv3
+// accumulator + residual -> output).  The MMA order per tile i is conv2(i), conv1(i+1), conv3(i), so the tensor pipe
+// works on the next tile's conv1 while epilogue A produces t2(i).
 #include <atomic>
 #include <cstdio>
 #include <cudaTypedefs.h>
@@ -73,6 +76,14 @@ __device__ __forceinline__ void tma_load_4d_pair(const CUtensorMap* m, uint32_t 
         " [%0], [%1, {%3, %4, %5, %6}], [%2], %7;" ::"r"(smem_u32(dst)),
         "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "l"(policy)
         : "memory");
+}
+// Asks the L2 for a box ahead of time (no shared-memory destination, no barrier): the x ring is only three boxes deep,
+// so a box that still has to come from HBM when it is requested (~2 us under load) would bound a CTA at ~25 GB/s.
+__device__ __forceinline__ void tma_prefetch_4d(const CUtensorMap* m, int32_t c0, int32_t c1, int32_t c2, int32_t c3) {
+    asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];" ::"l"(
+                     reinterpret_cast<uint64_t>(m)),
+                 "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
 }
 // Cluster-scope release / acquire on mbarriers: the data they order (the t1 patch, the t2 tile) is written by one
 // CTA's threads and consumed by MMAs the OTHER CTA's thread issues.
@@ -123,15 +134,15 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     uint64_t* x_full = bars;                    // [X_STAGES]  leader's copy counts the bytes of both CTAs
     uint64_t* x_empty = x_full + X_STAGES;      // [X_STAGES]  multicast commit
     uint64_t* acc1_full = x_empty + X_STAGES;   // commit
-    uint64_t* acc1_empty = acc1_full + 1;       // leader's: 8 warp arrivals (epilogue A of both CTAs)
-    uint64_t* t1_ready = acc1_empty + 1;        // leader's: 8 warp arrivals
+    uint64_t* acc1_empty = acc1_full + 1;       // leader's: 16 warp arrivals (the two conv1 epilogue groups of both CTAs)
+    uint64_t* t1_ready = acc1_empty + 1;        // leader's: 16 warp arrivals
     uint64_t* t1_free = t1_ready + 1;           // commit
     uint64_t* acc2_full = t1_free + 1;          // commit
     uint64_t* acc2_empty = acc2_full + 1;       // leader's: 8
     uint64_t* t2_ready = acc2_empty + 1;        // leader's: 8
     uint64_t* t2_free = t2_ready + 1;           // commit
     uint64_t* acc3_full = t2_free + 1;          // commit
-    uint64_t* acc3_empty = acc3_full + 1;       // leader's: 16 (epilogue B of both CTAs)
+    uint64_t* acc3_empty = acc3_full + 1;       // leader's: 8 (epilogue B of both CTAs)
     uint64_t* xc_full = acc3_empty + 1;         // leader's, bytes of both CTAs (PROJ)
     uint64_t* xc_free = xc_full + 1;            // commit (PROJ)
     uint64_t* w_bar = xc_free + 1;              // leader's, bytes of both CTAs
@@ -153,11 +164,11 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     } else if (warp_idx == 1) {
         if (elect_one()) {
             for (int i = 0; i < X_STAGES; ++i) { mbar_init(&x_full[i], 1); mbar_init(&x_empty[i], 1); }
-            mbar_init(acc1_full, 1); mbar_init(acc1_empty, 8);
-            mbar_init(t1_ready, 8);  mbar_init(t1_free, 1);
+            mbar_init(acc1_full, 1); mbar_init(acc1_empty, 16);
+            mbar_init(t1_ready, 16); mbar_init(t1_free, 1);
             mbar_init(acc2_full, 1); mbar_init(acc2_empty, 8);
             mbar_init(t2_ready, 8);  mbar_init(t2_free, 1);
-            mbar_init(acc3_full, 1); mbar_init(acc3_empty, 16);
+            mbar_init(acc3_full, 1); mbar_init(acc3_empty, 8);
             mbar_init(xc_full, 1);   mbar_init(xc_free, 1);
             mbar_init(w_bar, 1);
             for (int i = 0; i < 3; ++i) { mbar_init(&res_full[i], 1); mbar_init(&res_empty[i], 1); }
@@ -194,9 +205,23 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             const uint32_t full0 = mapa_shared(smem_u32(&x_full[0]), 0);
             int stage = 0;
             uint32_t phase = 0;
+            auto prefetch_tile = [&](int T) {
+                if (T >= pair_tiles) return;
+                int img, row0;
+                tile_pos(T, img, row0);
+                // this CTA's four input rows; rank 1's upper two are rank 0's lower two, so each CTA asks only for the
+                // rows it reads FIRST (rank 0: rows 0-1, rank 1: rows 2-3 of its patch reach the L2 via the peer)
+                for (int kc = 0; kc < KC1; ++kc) {
+                    tma_prefetch_4d(&tmap_x, kc * 64, -1, row0 - 1, img);
+                    tma_prefetch_4d(&tmap_x, kc * 64, -1, row0 + 1, img);
+                }
+            };
+            prefetch_tile(first);
+            prefetch_tile(first + step);
             for (int T = first; T < pair_tiles; T += step) {
                 int img, row0;
                 tile_pos(T, img, row0);
+                prefetch_tile(T + 2 * step);
                 for (int j = 0; j < 2; ++j) {
                     for (int kc = 0; kc < KC1; ++kc) {
                         mbar_wait_wd(&x_empty[stage], phase ^ 1u);
@@ -323,11 +348,14 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
                 }
             }
         }
-    } else if (warp_idx >= 4 && warp_idx < 8) {
-        // ================================================================ epilogue A: acc1 -> t1 patch, acc2 -> t2
+    } else if ((warp_idx >= 4 && warp_idx < 8) || warp_idx >= 12) {
+        // ================================================================ epilogues A / C: acc1 -> t1 patch, acc2 -> t2
+        // conv1 -> this epilogue -> conv2 is the serial chain of a tile, so the two 128-row halves of the patch are
+        // converted by two warp groups at once: warps 4-7 take patch rows 0-1 (and then t2), warps 12-15 rows 2-3.
         const int quad = warp_idx & 3;
         const int lane = static_cast<int>(lane_id());
         const int m = quad * 32 + lane;                              // accumulator row
+        const int j = warp_idx >= 12 ? 1 : 0;                        // which half of the patch
         const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
         const uint32_t acc1_empty0 = mapa_shared(smem_u32(acc1_empty), 0), t1_ready0 = mapa_shared(smem_u32(t1_ready), 0);
         const uint32_t acc2_empty0 = mapa_shared(smem_u32(acc2_empty), 0), t2_ready0 = mapa_shared(smem_u32(t2_ready), 0);
@@ -340,8 +368,7 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             mbar_wait_wd(acc1_full, par);
             tc_fence_after();
             mbar_wait_wd(t1_free, par ^ 1u);                         // conv2 of the previous tile has read the patch
-#pragma unroll
-            for (int j = 0; j < 2; ++j) {
+            {
                 const int pr = j * 128 + m;                          // patch-linear pixel
                 const int irow = row0 - 1 + (pr >> 6), icol = (pr & 63) - 1;
                 const bool inside = irow >= 0 && irow < HW && icol >= 0 && icol < HW;
@@ -376,7 +403,8 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
                 mbar_arrive_remote_release(t1_ready0);
                 mbar_arrive_remote_release(acc1_empty0);
             }
-            // ---- t2 tile
+            if (j != 0) continue;
+            // ---- t2 tile (warps 4-7)
             mbar_wait_wd(acc2_full, par);
             tc_fence_after();
             {
@@ -411,13 +439,11 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             }
         }
     } else if (warp_idx >= 8) {
-        // ================================================================ epilogue B: acc3 (+ residual) -> out
+        // ================================================================ epilogue B (warps 8-11): acc3 (+ residual) -> out
         const int quad = warp_idx & 3;
         const int lane = static_cast<int>(lane_id());
         const int m = quad * 32 + lane;
-        const int group = (warp_idx - 8) >> 2;
-        const bool leader = ((warp_idx - 8) & 3) == 0 && lane == 0;
-        const uint32_t bar_id = 1u + static_cast<uint32_t>(group);
+        const bool leader = warp_idx == 8 && lane == 0;
         const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
         const uint32_t acc3_empty0 = mapa_shared(smem_u32(acc3_empty), 0);
         const uint32_t swz = static_cast<uint32_t>(m & 7);
@@ -431,11 +457,20 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             tc_fence_after();
 #pragma unroll 1
             for (int c = 0; c < 4; ++c, ++q) {
-                if ((c & 1) != group) continue;
-                const uint32_t slot = PROJ ? static_cast<uint32_t>(group) : q % 3u;
+                // identity blocks: a ring of three tiles that are residual input and output staging at once (the loader
+                // fills a tile, the accumulator is added in place, the tile is stored from where it lies).  Projection
+                // block: two plain staging tiles used alternately.
+                const uint32_t slot = PROJ ? (q & 1u) : q % 3u;
                 uint8_t* tile = s_io + slot * TILE16K;
                 const uint32_t row_addr = smem_u32(tile) + static_cast<uint32_t>(m * 128);
-                if (!PROJ) mbar_wait_wd(&res_full[slot], (q / 3u) & 1u);
+                if (!PROJ) {
+                    if (leader && q > 0) {
+                        // the previous chunk's store has read its tile: hand that tile back to the loader
+                        tma_store_wait_read<0>();
+                        mbar_arrive(&res_empty[(q - 1u) % 3u]);
+                    }
+                    mbar_wait_wd(&res_full[slot], (q / 3u) & 1u);
+                }
                 uint4 packed[8];
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
@@ -470,29 +505,25 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
                         packed[h * 4 + g].w = pack_bf16x2(fmaxf(f[8 * g + 6], 0.f), fmaxf(f[8 * g + 7], 0.f));
                     }
                 }
-                if (c >= 2) {
-                    // this group's last chunk of the tile: its TMEM reads are done, hand the accumulator back
+                if (c == 3) {
+                    // last chunk of the tile: this warp's TMEM reads are done, hand the accumulator back
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive_remote_release(acc3_empty0);
                 }
                 if (PROJ) {
-                    // plain staging tile: the previous store from it must have been read
-                    if (leader) tma_store_wait_read<0>();
-                    named_bar_sync(bar_id, 128);
+                    // the store issued from this tile two chunks ago must have been read (at most one may be pending)
+                    if (leader) tma_store_wait_read<1>();
+                    named_bar_sync(1, 128);
                 }
 #pragma unroll
                 for (int g = 0; g < 8; ++g) st_shared_v4(row_addr + ((static_cast<uint32_t>(g) ^ swz) << 4), packed[g]);
                 fence_proxy_async_smem();
-                named_bar_sync(bar_id, 128);
+                named_bar_sync(1, 128);
                 if (leader) {
                     tma_store_2d(&tmap_out, tile, c * 64, grow);
                     tma_store_2d(&tmap_out, tile + 64 * 128, c * 64, grow + HW);
                     tma_store_commit();
-                    if (!PROJ) {
-                        tma_store_wait_read<0>();                    // the tile may take the next residual
-                        mbar_arrive(&res_empty[slot]);
-                    }
                 }
             }
         }

@@ -212,7 +212,7 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
 
     import os
     if fuse_blocks is None:
-        fuse_blocks = os.getenv("B2P_FUSE_BLOCKS", "1") != "0"
+        fuse_blocks = os.getenv("B2P_FUSE_BLOCKS", "0") != "0"
     blocks = [blk for layer in (model.layer1, model.layer2, model.layer3, model.layer4) for blk in layer]
     carry = None          # (t1 slot, hwc1) when the previous block's CONV_PAIR already computed this block's conv1
     for bi_, blk in enumerate(blocks):
