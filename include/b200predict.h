@@ -70,14 +70,13 @@ enum b2p_op_kind {
                               conv1): dst = relu(conv(src) + bias + res) as OP_CONV, and additionally
                               slot reserved[0] = relu(conv(dst) + bias2) with weight blob reserved[1] and bias blob
                               reserved[2], reserved[3] = its output channels (64, 128 or 256)                 */
-    B2P_OP_BOTTLENECK = 13 /* a whole bottleneck block of the 56x56 stage in one kernel
+    B2P_OP_BOTTLENECK = 13 /* a whole identity bottleneck block of the 56x56 stage in one kernel
                               (SP/torchvision/models/resnet.py:143-163): t1 = relu(conv1x1(src)), t2 = relu(conv3x3(t1)),
-                              dst = relu(conv1x1(t2) + shortcut).  in_c = block input channels, reserved2 = bottleneck width
-                              (64), out_c = 256.  Blobs: weight / bias = conv1 [64][in_c], reserved[0] / [1] = conv2
-                              [64][3][3][64] and its bias, reserved[2] / [3] = conv3 and its bias.  res == src: identity
-                              shortcut (in_c = 256, conv3 [256][64]); res == B2P_SLOT_NONE: projection shortcut folded
-                              into conv3 as extra K columns (in_c = 64, conv3 [256][64 + 64], biases summed).  src and
-                              dst are workspace slots.                                                             */
+                              dst = relu(conv1x1(t2) + src).  in_c = 256, reserved2 = bottleneck width (64), out_c = 256,
+                              res == src.  Blobs: weight / bias = conv1 [64][256], reserved[0] / [1] = conv2 [64][3][3][64]
+                              and its bias, reserved[2] / [3] = conv3 [256][64] and its bias.  src and dst are
+                              workspace slots.  (res == B2P_SLOT_NONE would describe a projection block with the
+                              shortcut folded into conv3; b2p_create refuses it: no kernel covers it.)              */
 };
 
 typedef struct b2p_op {

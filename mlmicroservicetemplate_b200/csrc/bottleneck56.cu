@@ -33,6 +33,7 @@
 // works on the next tile's conv1 while epilogue A produces t2(i).
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cudaTypedefs.h>
 #include "kernels.h"
 #include "ptx.cuh"
@@ -41,54 +42,47 @@ namespace b2p {
 namespace {
 
 constexpr int HW = 56;
+constexpr int CIN = 256;
 constexpr int MID = 64;                     // bottleneck width of the 56x56 stage
 constexpr int OUTC = 256;
+constexpr int KC1 = CIN / 64;               // conv1 K chunks
 constexpr int PITCH = 64;                   // patch row pitch in pixels
 constexpr int TILE16K = 128 * 128;          // 128 rows x 64 ch bf16
+constexpr int W1_CHUNK = 64 * 128;          // 64 output rows x 64 K
 constexpr int PATCH_BYTES = 4 * PITCH * 128 + 1024;   // 4 rows + the rows a shifted descriptor reads past the end
-constexpr int X_STAGES = 3;
+constexpr int X_STAGES = 2;
+constexpr int X_STAGE_BYTES = TILE16K + W1_CHUNK;     // x box + its W1 slice
+constexpr int W2_BYTES = 9 * 64 * 128;
+constexpr int W3_BYTES = OUTC * 128;
 constexpr int BN_THREADS = 512;
+constexpr int BN_SMEM = 1024 + W2_BYTES + W3_BYTES + PATCH_BYTES + TILE16K + X_STAGES * X_STAGE_BYTES + TILE16K + 512;
+static_assert(BN_SMEM <= 227 * 1024, "shared memory budget");
 constexpr uint32_t COL_ACC1 = 0, COL_ACC2 = 128, COL_ACC3 = 256;
-
-template <int KC1, bool PROJ>
-struct BnCfg {
-    static constexpr int W1_BYTES = KC1 * 32 * 128;            // this CTA's 32 of the 64 conv1 output rows
-    static constexpr int W2_BYTES = 9 * 32 * 128;
-    static constexpr int W3_BYTES = (PROJ ? 2 : 1) * 128 * 128;  // this CTA's 128 of the 256 conv3 output rows
-    static constexpr int IO_TILES = PROJ ? 2 : 3;               // staging tiles (identity blocks: residual in, result out)
-    static constexpr int XC_BYTES = PROJ ? TILE16K : 0;         // the block input at the output pixels (shortcut operand)
-    static constexpr int SMEM = 1024 + W1_BYTES + W2_BYTES + W3_BYTES + PATCH_BYTES + TILE16K + XC_BYTES +
-                                X_STAGES * TILE16K + IO_TILES * TILE16K + 512;
-    static_assert(SMEM <= 227 * 1024, "shared memory budget");
-};
 
 struct BnArgs {
     int n_imgs;
     const float* b1;
     const float* b2;
     const float* b3;
+    const uint16_t* x;      // the block input again, for the residual (bf16 NHWC)
+    int trace;              // B2P_BNECK_TRACE=1: CTA 0 prints clock stamps of its first tiles (development aid)
 };
 
-__device__ __forceinline__ void tma_load_4d_pair(const CUtensorMap* m, uint32_t bar_cluster_addr, void* dst, int32_t c0,
-                                                 int32_t c1, int32_t c2, int32_t c3, uint64_t policy) {
+__device__ __forceinline__ void tma_load_4d_hint(const CUtensorMap* m, uint64_t* bar, void* dst, int32_t c0, int32_t c1,
+                                                 int32_t c2, int32_t c3, uint64_t policy) {
     asm volatile(
-        "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
+        "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint"
         " [%0], [%1, {%3, %4, %5, %6}], [%2], %7;" ::"r"(smem_u32(dst)),
-        "l"(reinterpret_cast<uint64_t>(m)), "r"(bar_cluster_addr), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "l"(policy)
+        "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "l"(policy)
         : "memory");
 }
-// Asks the L2 for a box ahead of time (no shared-memory destination, no barrier): the x ring is only three boxes deep,
-// so a box that still has to come from HBM when it is requested (~2 us under load) would bound a CTA at ~25 GB/s.
+// Asks the L2 for a box ahead of time (no shared-memory destination, no barrier): the x ring is only two boxes deep,
+// so a box that still has to come from HBM when it is requested (~2 us under load) would bound a CTA at ~20 GB/s.
 __device__ __forceinline__ void tma_prefetch_4d(const CUtensorMap* m, int32_t c0, int32_t c1, int32_t c2, int32_t c3) {
     asm volatile("cp.async.bulk.prefetch.tensor.4d.L2.global.tile [%0, {%1, %2, %3, %4}];" ::"l"(
                      reinterpret_cast<uint64_t>(m)),
                  "r"(c0), "r"(c1), "r"(c2), "r"(c3)
                  : "memory");
-}
-// Cluster-scope release / acquire on mbarriers: the data they order (the t1 patch, the t2 tile) is written by one
-// CTA's threads and consumed by MMAs the OTHER CTA's thread issues.
-__device__ __forceinline__ void mbar_arrive_remote_release(uint32_t cluster_addr) {
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // Waits with a watchdog: a protocol error becomes a trap (launch failure) after ~2 s instead of a hung GPU.
 __device__ __forceinline__ void mbar_wait_wd(uint64_t* bar, uint32_t parity) {
@@ -99,7 +93,7 @@ __device__ __forceinline__ void mbar_wait_wd(uint64_t* bar, uint32_t parity) {
         asm volatile(
             "{\n"
             ".reg .pred p;\n"
-            "mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
             "selp.u32 %0, 1, 0, p;\n"
             "}\n"
             : "=r"(done)
@@ -113,104 +107,86 @@ __device__ __forceinline__ void mbar_wait_wd(uint64_t* bar, uint32_t parity) {
     }
 }
 
-template <int KC1, bool PROJ>
 __global__ void __launch_bounds__(BN_THREADS, 1)
 bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w1,
                     const __grid_constant__ CUtensorMap tmap_w2, const __grid_constant__ CUtensorMap tmap_w3,
-                    const __grid_constant__ CUtensorMap tmap_res, const __grid_constant__ CUtensorMap tmap_out,
-                    const BnArgs args) {
-    using C = BnCfg<KC1, PROJ>;
+                    const __grid_constant__ CUtensorMap tmap_out, const BnArgs args) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-    uint8_t* s_w1 = smem;
-    uint8_t* s_w2 = s_w1 + C::W1_BYTES;
-    uint8_t* s_w3 = s_w2 + C::W2_BYTES;
-    uint8_t* s_patch = s_w3 + C::W3_BYTES;
+    uint8_t* s_w2 = smem;
+    uint8_t* s_w3 = s_w2 + W2_BYTES;
+    uint8_t* s_patch = s_w3 + W3_BYTES;
     uint8_t* s_t2 = s_patch + PATCH_BYTES;
-    uint8_t* s_xc = s_t2 + TILE16K;
-    uint8_t* s_x = s_xc + C::XC_BYTES;
-    uint8_t* s_io = s_x + X_STAGES * TILE16K;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(s_io + C::IO_TILES * TILE16K);
-    uint64_t* x_full = bars;                    // [X_STAGES]  leader's copy counts the bytes of both CTAs
-    uint64_t* x_empty = x_full + X_STAGES;      // [X_STAGES]  multicast commit
+    uint8_t* s_x = s_t2 + TILE16K;                      // X_STAGES x (x box | W1 slice)
+    uint8_t* s_out = s_x + X_STAGES * X_STAGE_BYTES;    // output staging tile
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_out + TILE16K);
+    uint64_t* x_full = bars;                    // [X_STAGES]
+    uint64_t* x_empty = x_full + X_STAGES;      // [X_STAGES]  commit
     uint64_t* acc1_full = x_empty + X_STAGES;   // commit
-    uint64_t* acc1_empty = acc1_full + 1;       // leader's: 16 warp arrivals (the two conv1 epilogue groups of both CTAs)
-    uint64_t* t1_ready = acc1_empty + 1;        // leader's: 16 warp arrivals
+    uint64_t* acc1_empty = acc1_full + 1;       // 8 warp arrivals (epilogues A and C)
+    uint64_t* t1_ready = acc1_empty + 1;        // 8 warp arrivals
     uint64_t* t1_free = t1_ready + 1;           // commit
     uint64_t* acc2_full = t1_free + 1;          // commit
-    uint64_t* acc2_empty = acc2_full + 1;       // leader's: 8
-    uint64_t* t2_ready = acc2_empty + 1;        // leader's: 8
+    uint64_t* acc2_empty = acc2_full + 1;       // 4
+    uint64_t* t2_ready = acc2_empty + 1;        // 4
     uint64_t* t2_free = t2_ready + 1;           // commit
     uint64_t* acc3_full = t2_free + 1;          // commit
-    uint64_t* acc3_empty = acc3_full + 1;       // leader's: 8 (epilogue B of both CTAs)
-    uint64_t* xc_full = acc3_empty + 1;         // leader's, bytes of both CTAs (PROJ)
-    uint64_t* xc_free = xc_full + 1;            // commit (PROJ)
-    uint64_t* w_bar = xc_free + 1;              // leader's, bytes of both CTAs
-    uint64_t* res_full = w_bar + 1;             // [3] local
-    uint64_t* res_empty = res_full + 3;         // [3] local
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(res_empty + 3);
+    uint64_t* acc3_empty = acc3_full + 1;       // 4
+    uint64_t* w_bar = acc3_empty + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_bar + 1);
 
     const int warp_idx = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
-    const uint32_t rank = cluster_ctarank();
-    const int pair_tiles = args.n_imgs * (HW / 4);
-    const int first = static_cast<int>(blockIdx.x >> 1), step = static_cast<int>(gridDim.x >> 1);
+    __shared__ long long s_trace[8][24];        // [tile][event] clock stamps of CTA 0 (args.trace)
+    const bool tracing = args.trace && blockIdx.x == 0;
+#define BN_TRACE(it_, ev_) do { if (tracing && (it_) >= 8 && (it_) < 16) s_trace[(it_) - 8][ev_] = clock64(); } while (0)
+    const int tiles = args.n_imgs * (HW / 2);
+    const int first = static_cast<int>(blockIdx.x), step = static_cast<int>(gridDim.x);
 
     if (warp_idx == 0) {
         if (elect_one()) {
             tma_prefetch_desc(&tmap_x); tma_prefetch_desc(&tmap_w1); tma_prefetch_desc(&tmap_w2);
             tma_prefetch_desc(&tmap_w3); tma_prefetch_desc(&tmap_out);
-            if (!PROJ) tma_prefetch_desc(&tmap_res);
         }
     } else if (warp_idx == 1) {
         if (elect_one()) {
             for (int i = 0; i < X_STAGES; ++i) { mbar_init(&x_full[i], 1); mbar_init(&x_empty[i], 1); }
-            mbar_init(acc1_full, 1); mbar_init(acc1_empty, 16);
-            mbar_init(t1_ready, 16); mbar_init(t1_free, 1);
-            mbar_init(acc2_full, 1); mbar_init(acc2_empty, 8);
-            mbar_init(t2_ready, 8);  mbar_init(t2_free, 1);
-            mbar_init(acc3_full, 1); mbar_init(acc3_empty, 8);
-            mbar_init(xc_full, 1);   mbar_init(xc_free, 1);
+            mbar_init(acc1_full, 1); mbar_init(acc1_empty, 8);
+            mbar_init(t1_ready, 8);  mbar_init(t1_free, 1);
+            mbar_init(acc2_full, 1); mbar_init(acc2_empty, 4);
+            mbar_init(t2_ready, 4);  mbar_init(t2_free, 1);
+            mbar_init(acc3_full, 1); mbar_init(acc3_empty, 4);
             mbar_init(w_bar, 1);
-            for (int i = 0; i < 3; ++i) { mbar_init(&res_full[i], 1); mbar_init(&res_empty[i], 1); }
             fence_mbar_init();
         }
         __syncwarp();
-        tmem_alloc_pair(tmem_slot, 512);
-        tmem_relinquish_pair();
+        tmem_alloc(tmem_slot, 512);
+        tmem_relinquish();
     }
     pdl_launch_dependents();
     tc_fence_before();
-    cluster_sync_all();
+    __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
     pdl_wait();
 
-    // tile -> (image, first output row of THIS CTA)
+    // tile -> (image, first output row)
     auto tile_pos = [&](int T, int& img, int& row0) {
-        img = T / (HW / 4);
-        row0 = (T - img * (HW / 4)) * 4 + 2 * static_cast<int>(rank);
+        img = T / (HW / 2);
+        row0 = (T - img * (HW / 2)) * 2;
     };
 
     if (warp_idx == 0) {
-        // ================================================================ TMA producer: weights once, then x boxes
+        // ================================================================ TMA producer: W2, W3 once, then x + W1 boxes
         if (elect_one()) {
-            const uint32_t w_bar0 = mapa_shared(smem_u32(w_bar), 0);
-            if (rank == 0) mbar_arrive_expect_tx(w_bar, 2u * (C::W1_BYTES + C::W2_BYTES + C::W3_BYTES));
-            for (int kc = 0; kc < KC1; ++kc)
-                tma_load_2d_pair_hint(&tmap_w1, w_bar0, s_w1 + kc * 4096, kc * 64, static_cast<int>(rank) * 32, L2_EVICT_LAST);
+            mbar_arrive_expect_tx(w_bar, W2_BYTES + W3_BYTES);
             for (int tap = 0; tap < 9; ++tap)
-                tma_load_2d_pair_hint(&tmap_w2, w_bar0, s_w2 + tap * 4096, tap * 64, static_cast<int>(rank) * 32, L2_EVICT_LAST);
-            for (int kc = 0; kc < (PROJ ? 2 : 1); ++kc)
-                tma_load_2d_pair_hint(&tmap_w3, w_bar0, s_w3 + kc * TILE16K, kc * 64, static_cast<int>(rank) * 128, L2_EVICT_LAST);
-            const uint32_t full0 = mapa_shared(smem_u32(&x_full[0]), 0);
-            int stage = 0;
-            uint32_t phase = 0;
+                tma_load_2d_hint(&tmap_w2, w_bar, s_w2 + tap * 8192, tap * 64, 0, L2_EVICT_LAST);
+            for (int h = 0; h < 2; ++h)
+                tma_load_2d_hint(&tmap_w3, w_bar, s_w3 + h * TILE16K, 0, h * 128, L2_EVICT_LAST);
             auto prefetch_tile = [&](int T) {
-                if (T >= pair_tiles) return;
+                if (T >= tiles) return;
                 int img, row0;
                 tile_pos(T, img, row0);
-                // this CTA's four input rows; rank 1's upper two are rank 0's lower two, so each CTA asks only for the
-                // rows it reads FIRST (rank 0: rows 0-1, rank 1: rows 2-3 of its patch reach the L2 via the peer)
                 for (int kc = 0; kc < KC1; ++kc) {
                     tma_prefetch_4d(&tmap_x, kc * 64, -1, row0 - 1, img);
                     tma_prefetch_4d(&tmap_x, kc * 64, -1, row0 + 1, img);
@@ -218,27 +194,30 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             };
             prefetch_tile(first);
             prefetch_tile(first + step);
-            for (int T = first; T < pair_tiles; T += step) {
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int T = first; T < tiles; T += step) {
                 int img, row0;
                 tile_pos(T, img, row0);
                 prefetch_tile(T + 2 * step);
                 for (int j = 0; j < 2; ++j) {
                     for (int kc = 0; kc < KC1; ++kc) {
                         mbar_wait_wd(&x_empty[stage], phase ^ 1u);
-                        if (rank == 0) mbar_arrive_expect_tx(&x_full[stage], 2u * TILE16K);
+                        mbar_arrive_expect_tx(&x_full[stage], X_STAGE_BYTES);
+                        uint8_t* dst = s_x + stage * X_STAGE_BYTES;
                         // patch rows 2j, 2j+1 = image rows row0 - 1 + 2j ..; columns start at -1 (the left halo)
-                        tma_load_4d_pair(&tmap_x, full0 + static_cast<uint32_t>(stage * 8), s_x + stage * TILE16K, kc * 64, -1,
-                                         row0 - 1 + 2 * j, img, L2_EVICT_NORMAL);
+                        tma_load_4d_hint(&tmap_x, &x_full[stage], dst, kc * 64, -1, row0 - 1 + 2 * j, img, L2_EVICT_NORMAL);
+                        tma_load_2d_hint(&tmap_w1, &x_full[stage], dst + TILE16K, kc * 64, 0, L2_EVICT_LAST);
                         if (++stage == X_STAGES) { stage = 0; phase ^= 1u; }
                     }
                 }
             }
         }
     } else if (warp_idx == 1) {
-        // ================================================================ MMA issuer (leader CTA)
-        if (rank == 0 && elect_one()) {
-            constexpr uint32_t idesc64 = umma_idesc_bf16(256, MID);
-            constexpr uint32_t idesc256 = umma_idesc_bf16(256, OUTC);
+        // ================================================================ MMA issuer
+        if (elect_one()) {
+            constexpr uint32_t idesc64 = umma_idesc_bf16(128, MID);
+            constexpr uint32_t idesc256 = umma_idesc_bf16(128, OUTC);
             mbar_wait_wd(w_bar, 0);
             tc_fence_after();
             int stage = 0;
@@ -251,26 +230,28 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
                     for (int kc = 0; kc < KC1; ++kc) {
                         mbar_wait_wd(&x_full[stage], phase);
                         tc_fence_after();
-                        const uint64_t a = umma_desc_kmajor(smem_u32(s_x + stage * TILE16K), 128);
-                        const uint64_t b = umma_desc_kmajor(smem_u32(s_w1 + kc * 4096), 128);
+                        const uint32_t base = smem_u32(s_x + stage * X_STAGE_BYTES);
+                        const uint64_t a = umma_desc_kmajor(base, 128);
+                        const uint64_t b = umma_desc_kmajor(base + TILE16K, 128);
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
-                            umma_bf16_pair(d, a + static_cast<uint64_t>(2 * k), b + static_cast<uint64_t>(2 * k), idesc64,
-                                           static_cast<uint32_t>((kc | k) != 0));
-                        umma_commit_pair(&x_empty[stage]);
+                            umma_bf16(d, a + static_cast<uint64_t>(2 * k), b + static_cast<uint64_t>(2 * k), idesc64,
+                                      static_cast<uint32_t>((kc | k) != 0));
+                        umma_commit(&x_empty[stage]);
                         if (++stage == X_STAGES) { stage = 0; phase ^= 1u; }
                     }
                 }
-                umma_commit_pair(acc1_full);
+                umma_commit(acc1_full);
             };
             int it = 0;
-            if (first < pair_tiles) conv1(0);
-            for (int T = first; T < pair_tiles; T += step, ++it) {
+            if (first < tiles) conv1(0);
+            for (int T = first; T < tiles; T += step, ++it) {
                 const uint32_t par = static_cast<uint32_t>(it) & 1u;
                 // ---- conv2(it): nine taps, each the t1 patch shifted by (r * 64 + s) pixels
                 mbar_wait_wd(t1_ready, par);
                 mbar_wait_wd(acc2_empty, par ^ 1u);
                 tc_fence_after();
+                BN_TRACE(it, 0);
                 {
                     const uint32_t patch = smem_u32(s_patch), w2 = smem_u32(s_w2);
                     const uint32_t d = tmem_base + COL_ACC2;
@@ -279,73 +260,38 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
 #pragma unroll
                         for (int s = 0; s < 3; ++s) {
                             const uint64_t a = umma_desc_kmajor(patch + static_cast<uint32_t>((r * PITCH + s) * 128), 128);
-                            const uint64_t b = umma_desc_kmajor(w2 + static_cast<uint32_t>((r * 3 + s) * 4096), 128);
+                            const uint64_t b = umma_desc_kmajor(w2 + static_cast<uint32_t>((r * 3 + s) * 8192), 128);
 #pragma unroll
                             for (int k = 0; k < 4; ++k)
-                                umma_bf16_pair(d, a + static_cast<uint64_t>(2 * k), b + static_cast<uint64_t>(2 * k), idesc64,
-                                               static_cast<uint32_t>((r | s | k) != 0));
+                                umma_bf16(d, a + static_cast<uint64_t>(2 * k), b + static_cast<uint64_t>(2 * k), idesc64,
+                                          static_cast<uint32_t>((r | s | k) != 0));
                         }
                     }
                 }
-                umma_commit_pair(t1_free);
-                umma_commit_pair(acc2_full);
+                umma_commit(t1_free);
+                umma_commit(acc2_full);
+                BN_TRACE(it, 1);
                 // ---- conv1 of the NEXT tile keeps the tensor pipe busy while epilogue A produces t2(it)
-                if (T + step < pair_tiles) conv1(it + 1);
+                if (T + step < tiles) conv1(it + 1);
+                BN_TRACE(it, 2);
                 // ---- conv3(it)
                 mbar_wait_wd(t2_ready, par);
-                if (PROJ) mbar_wait_wd(xc_full, par);
+                BN_TRACE(it, 3);
                 mbar_wait_wd(acc3_empty, par ^ 1u);
                 tc_fence_after();
+                BN_TRACE(it, 4);
                 {
                     const uint32_t d = tmem_base + COL_ACC3;
                     const uint64_t a = umma_desc_kmajor(smem_u32(s_t2), 128);
                     const uint64_t b = umma_desc_kmajor(smem_u32(s_w3), 128);
 #pragma unroll
                     for (int k = 0; k < 4; ++k)
-                        umma_bf16_pair(d, a + static_cast<uint64_t>(2 * k), b + static_cast<uint64_t>(2 * k), idesc256,
-                                       static_cast<uint32_t>(k != 0));
-                    if (PROJ) {
-                        const uint64_t a2 = umma_desc_kmajor(smem_u32(s_xc), 128);
-                        const uint64_t b2 = umma_desc_kmajor(smem_u32(s_w3 + TILE16K), 128);
-#pragma unroll
-                        for (int k = 0; k < 4; ++k)
-                            umma_bf16_pair(d, a2 + static_cast<uint64_t>(2 * k), b2 + static_cast<uint64_t>(2 * k), idesc256, 1u);
-                    }
+                        umma_bf16(d, a + static_cast<uint64_t>(2 * k), b + static_cast<uint64_t>(2 * k), idesc256,
+                                  static_cast<uint32_t>(k != 0));
                 }
-                umma_commit_pair(t2_free);
-                if (PROJ) umma_commit_pair(xc_free);
-                umma_commit_pair(acc3_full);
-            }
-        }
-    } else if (warp_idx == 2) {
-        // ================================================================ loader: residual tiles / shortcut input
-        if (elect_one()) {
-            if (PROJ) {
-                const uint32_t xc_full0 = mapa_shared(smem_u32(xc_full), 0);
-                int it = 0;
-                for (int T = first; T < pair_tiles; T += step, ++it) {
-                    int img, row0;
-                    tile_pos(T, img, row0);
-                    mbar_wait_wd(xc_free, (static_cast<uint32_t>(it) & 1u) ^ 1u);
-                    if (rank == 0) mbar_arrive_expect_tx(xc_full, 2u * TILE16K);
-                    // the block input at this CTA's 2 x 56 output pixels, in the accumulator's row order (m = r*64 + c)
-                    tma_load_4d_pair(&tmap_x, xc_full0, s_xc, 0, 0, row0, img, L2_EVICT_FIRST);
-                }
-            } else {
-                uint32_t q = 0;
-                for (int T = first; T < pair_tiles; T += step) {
-                    int img, row0;
-                    tile_pos(T, img, row0);
-                    const int grow = (img * HW + row0) * HW;          // row of the [n*56*56, 256] view
-                    for (int c = 0; c < 4; ++c, ++q) {
-                        const uint32_t slot = q % 3u;
-                        mbar_wait_wd(&res_empty[slot], ((q / 3u) & 1u) ^ 1u);
-                        mbar_arrive_expect_tx(&res_full[slot], 2u * HW * 128u);
-                        uint8_t* dst = s_io + slot * TILE16K;
-                        tma_load_2d_hint(&tmap_res, &res_full[slot], dst, c * 64, grow, L2_EVICT_FIRST);
-                        tma_load_2d_hint(&tmap_res, &res_full[slot], dst + 64 * 128, c * 64, grow + HW, L2_EVICT_FIRST);
-                    }
-                }
+                umma_commit(t2_free);
+                umma_commit(acc3_full);
+                BN_TRACE(it, 5);
             }
         }
     } else if ((warp_idx >= 4 && warp_idx < 8) || warp_idx >= 12) {
@@ -357,17 +303,17 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
         const int m = quad * 32 + lane;                              // accumulator row
         const int j = warp_idx >= 12 ? 1 : 0;                        // which half of the patch
         const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-        const uint32_t acc1_empty0 = mapa_shared(smem_u32(acc1_empty), 0), t1_ready0 = mapa_shared(smem_u32(t1_ready), 0);
-        const uint32_t acc2_empty0 = mapa_shared(smem_u32(acc2_empty), 0), t2_ready0 = mapa_shared(smem_u32(t2_ready), 0);
         int it = 0;
-        for (int T = first; T < pair_tiles; T += step, ++it) {
+        for (int T = first; T < tiles; T += step, ++it) {
             const uint32_t par = static_cast<uint32_t>(it) & 1u;
             int img, row0;
             tile_pos(T, img, row0);
             // ---- t1 patch
             mbar_wait_wd(acc1_full, par);
             tc_fence_after();
+            if (threadIdx.x == 128) BN_TRACE(it, 6);
             mbar_wait_wd(t1_free, par ^ 1u);                         // conv2 of the previous tile has read the patch
+            if (threadIdx.x == 128) BN_TRACE(it, 7);
             {
                 const int pr = j * 128 + m;                          // patch-linear pixel
                 const int irow = row0 - 1 + (pr >> 6), icol = (pr & 63) - 1;
@@ -400,13 +346,15 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
-                mbar_arrive_remote_release(t1_ready0);
-                mbar_arrive_remote_release(acc1_empty0);
+                mbar_arrive(t1_ready);
+                mbar_arrive(acc1_empty);
             }
+            if (threadIdx.x == 128) BN_TRACE(it, 8);
             if (j != 0) continue;
             // ---- t2 tile (warps 4-7)
             mbar_wait_wd(acc2_full, par);
             tc_fence_after();
+            if (threadIdx.x == 128) BN_TRACE(it, 9);
             {
                 uint4 packed[8];
 #pragma unroll
@@ -434,43 +382,37 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
-                mbar_arrive_remote_release(t2_ready0);
-                mbar_arrive_remote_release(acc2_empty0);
+                mbar_arrive(t2_ready);
+                mbar_arrive(acc2_empty);
             }
+            if (threadIdx.x == 128) BN_TRACE(it, 10);
         }
-    } else if (warp_idx >= 8) {
-        // ================================================================ epilogue B (warps 8-11): acc3 (+ residual) -> out
+    } else if (warp_idx >= 8 && warp_idx < 12) {
+        // ================================================================ epilogue B: acc3 + residual -> out
         const int quad = warp_idx & 3;
         const int lane = static_cast<int>(lane_id());
-        const int m = quad * 32 + lane;
+        const int m = quad * 32 + lane;                              // accumulator row: pixel (m >> 6, m & 63) of the tile
         const bool leader = warp_idx == 8 && lane == 0;
+        const bool real = (m & 63) < HW;                             // rows on the pitch padding carry nothing
         const uint32_t lane_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-        const uint32_t acc3_empty0 = mapa_shared(smem_u32(acc3_empty), 0);
         const uint32_t swz = static_cast<uint32_t>(m & 7);
-        uint32_t q = 0;                                              // chunk sequence number over this CTA's walk
+        const uint32_t row_addr = smem_u32(s_out) + static_cast<uint32_t>(m * 128);
         int it = 0;
-        for (int T = first; T < pair_tiles; T += step, ++it) {
+        for (int T = first; T < tiles; T += step, ++it) {
             int img, row0;
             tile_pos(T, img, row0);
-            const int grow = (img * HW + row0) * HW;
+            const int grow = (img * HW + row0) * HW;                 // row of the [n*56*56, 256] view
+            // this thread's residual pixel; the same bytes went through the x ring a moment ago (L2 hit)
+            const uint4* res = reinterpret_cast<const uint4*>(
+                args.x + (static_cast<size_t>(grow) + static_cast<size_t>((m >> 6) * HW + (m & 63))) * CIN);
             mbar_wait_wd(acc3_full, static_cast<uint32_t>(it) & 1u);
             tc_fence_after();
+            if (leader) BN_TRACE(it, 11);
 #pragma unroll 1
-            for (int c = 0; c < 4; ++c, ++q) {
-                // identity blocks: a ring of three tiles that are residual input and output staging at once (the loader
-                // fills a tile, the accumulator is added in place, the tile is stored from where it lies).  Projection
-                // block: two plain staging tiles used alternately.
-                const uint32_t slot = PROJ ? (q & 1u) : q % 3u;
-                uint8_t* tile = s_io + slot * TILE16K;
-                const uint32_t row_addr = smem_u32(tile) + static_cast<uint32_t>(m * 128);
-                if (!PROJ) {
-                    if (leader && q > 0) {
-                        // the previous chunk's store has read its tile: hand that tile back to the loader
-                        tma_store_wait_read<0>();
-                        mbar_arrive(&res_empty[(q - 1u) % 3u]);
-                    }
-                    mbar_wait_wd(&res_full[slot], (q / 3u) & 1u);
-                }
+            for (int c = 0; c < 4; ++c) {
+                uint4 r[8];
+#pragma unroll
+                for (int g = 0; g < 8; ++g) r[g] = real ? ld_nc_v4(res + c * 8 + g) : make_uint4(0u, 0u, 0u, 0u);
                 uint4 packed[8];
 #pragma unroll
                 for (int h = 0; h < 2; ++h) {
@@ -487,15 +429,13 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
                         f[4 * g + 2] = __uint_as_float(v[4 * g + 2]) + b.z;
                         f[4 * g + 3] = __uint_as_float(v[4 * g + 3]) + b.w;
                     }
-                    if (!PROJ) {
 #pragma unroll
-                        for (int g = 0; g < 4; ++g) {
-                            const uint4 r = ld_shared_v4(row_addr + ((static_cast<uint32_t>(h * 4 + g) ^ swz) << 4));
-                            f[8 * g + 0] += bf16_lo(r.x); f[8 * g + 1] += bf16_hi(r.x);
-                            f[8 * g + 2] += bf16_lo(r.y); f[8 * g + 3] += bf16_hi(r.y);
-                            f[8 * g + 4] += bf16_lo(r.z); f[8 * g + 5] += bf16_hi(r.z);
-                            f[8 * g + 6] += bf16_lo(r.w); f[8 * g + 7] += bf16_hi(r.w);
-                        }
+                    for (int g = 0; g < 4; ++g) {
+                        const uint4 rr = r[h * 4 + g];
+                        f[8 * g + 0] += bf16_lo(rr.x); f[8 * g + 1] += bf16_hi(rr.x);
+                        f[8 * g + 2] += bf16_lo(rr.y); f[8 * g + 3] += bf16_hi(rr.y);
+                        f[8 * g + 4] += bf16_lo(rr.z); f[8 * g + 5] += bf16_hi(rr.z);
+                        f[8 * g + 6] += bf16_lo(rr.w); f[8 * g + 7] += bf16_hi(rr.w);
                     }
 #pragma unroll
                     for (int g = 0; g < 4; ++g) {
@@ -509,21 +449,20 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
                     // last chunk of the tile: this warp's TMEM reads are done, hand the accumulator back
                     tc_fence_before();
                     __syncwarp();
-                    if (lane == 0) mbar_arrive_remote_release(acc3_empty0);
+                    if (lane == 0) mbar_arrive(acc3_empty);
                 }
-                if (PROJ) {
-                    // the store issued from this tile two chunks ago must have been read (at most one may be pending)
-                    if (leader) tma_store_wait_read<1>();
-                    named_bar_sync(1, 128);
-                }
+                // the single staging tile: the previous chunk's store must have read it
+                if (leader) tma_store_wait_read<0>();
+                named_bar_sync(1, 128);
 #pragma unroll
                 for (int g = 0; g < 8; ++g) st_shared_v4(row_addr + ((static_cast<uint32_t>(g) ^ swz) << 4), packed[g]);
                 fence_proxy_async_smem();
                 named_bar_sync(1, 128);
                 if (leader) {
-                    tma_store_2d(&tmap_out, tile, c * 64, grow);
-                    tma_store_2d(&tmap_out, tile + 64 * 128, c * 64, grow + HW);
+                    tma_store_2d(&tmap_out, s_out, c * 64, grow);
+                    tma_store_2d(&tmap_out, s_out + 64 * 128, c * 64, grow + HW);
                     tma_store_commit();
+                    BN_TRACE(it, 12 + c);
                 }
             }
         }
@@ -531,11 +470,19 @@ bottleneck56_kernel(const __grid_constant__ CUtensorMap tmap_x, const __grid_con
     }
 
     tc_fence_before();
-    __syncwarp();
-    cluster_sync_all();       // the leader's MMAs read the peer's shared memory and signal its barriers: leave together
+    __syncthreads();
+    if (tracing && threadIdx.x == 0) {
+        const long long t0 = s_trace[0][0];
+        for (int t = 0; t < 8; ++t) {
+            printf("tile %d:", t + 8);
+            for (int e = 0; e < 16; ++e) printf(" %lld", s_trace[t][e] - t0);
+            printf("\n");
+        }
+    }
+#undef BN_TRACE
     if (warp_idx == 1) {
         tc_fence_after();
-        tmem_dealloc_pair(tmem_base, 512);
+        tmem_dealloc(tmem_base, 512);
     }
 }
 
@@ -562,40 +509,10 @@ bool bn_encode_2d(CUtensorMap* m, const void* base, uint64_t cols, uint64_t rows
                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-template <int KC1, bool PROJ>
-cudaError_t bn_launch(const BneckPlan& p, const BnArgs& a, int grid, cudaStream_t s) {
-    using C = BnCfg<KC1, PROJ>;
-    auto kern = bottleneck56_kernel<KC1, PROJ>;
-    static std::atomic<bool> attr_set[64];
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
-    if (!attr_set[dev].load(std::memory_order_acquire)) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM);
-        if (e != cudaSuccess) return e;
-        attr_set[dev].store(true, std::memory_order_release);
-    }
-    cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(BN_THREADS);
-    cfg.dynamicSmemBytes = C::SMEM;
-    cfg.stream = s;
-    cudaLaunchAttribute attr[2];
-    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-    attr[0].val.programmaticStreamSerializationAllowed = 1;
-    attr[1].id = cudaLaunchAttributeClusterDimension;
-    attr[1].val.clusterDim.x = 2;
-    attr[1].val.clusterDim.y = 1;
-    attr[1].val.clusterDim.z = 1;
-    cfg.attrs = attr;
-    cfg.numAttrs = 2;
-    return cudaLaunchKernelEx(&cfg, kern, p.tmap_x, p.tmap_w1, p.tmap_w2, p.tmap_w3, p.tmap_res, p.tmap_out, a);
-}
-
 }  // namespace
 
 bool bneck56_supported(int in_h, int in_w, int cin, int mid, int cout, bool proj) {
-    return in_h == HW && in_w == HW && mid == MID && cout == OUTC && ((proj && cin == 64) || (!proj && cin == OUTC));
+    return in_h == HW && in_w == HW && mid == MID && cout == OUTC && !proj && cin == CIN;
 }
 
 bool bneck56_plan_init(BneckPlan& p, int cin, bool proj, const void* w1, const float* b1, const void* w2, const float* b2,
@@ -604,12 +521,15 @@ bool bneck56_plan_init(BneckPlan& p, int cin, bool proj, const void* w1, const f
         snprintf(err, err_len, "cuTensorMapEncodeTiled not available");
         return false;
     }
+    if (proj || cin != CIN) {
+        snprintf(err, err_len, "the fused bottleneck covers identity blocks with 256 input channels");
+        return false;
+    }
     p.cin = cin;
-    p.proj = proj ? 1 : 0;
+    p.proj = 0;
     p.b1 = b1; p.b2 = b2; p.b3 = b3;
-    const uint64_t k3 = proj ? 128 : 64;
-    if (!bn_encode_2d(&p.tmap_w1, w1, static_cast<uint64_t>(cin), MID, 64, 32) ||
-        !bn_encode_2d(&p.tmap_w2, w2, 9 * MID, MID, 64, 32) || !bn_encode_2d(&p.tmap_w3, w3, k3, OUTC, 64, 128)) {
+    if (!bn_encode_2d(&p.tmap_w1, w1, CIN, MID, 64, 64) || !bn_encode_2d(&p.tmap_w2, w2, 9 * MID, MID, 64, 64) ||
+        !bn_encode_2d(&p.tmap_w3, w3, MID, OUTC, 64, 128)) {
         snprintf(err, err_len, "bottleneck weight tensor maps failed");
         return false;
     }
@@ -617,9 +537,8 @@ bool bneck56_plan_init(BneckPlan& p, int cin, bool proj, const void* w1, const f
 }
 
 bool bneck56_plan_set(BneckPlan& p, const void* src, void* dst, int batch_cap, char* err, size_t err_len) {
-    cuuint64_t dims[4] = {static_cast<cuuint64_t>(p.cin), HW, HW, static_cast<cuuint64_t>(batch_cap)};
-    cuuint64_t strides[3] = {static_cast<cuuint64_t>(p.cin) * 2, static_cast<cuuint64_t>(p.cin) * 2 * HW,
-                             static_cast<cuuint64_t>(p.cin) * 2 * HW * HW};
+    cuuint64_t dims[4] = {CIN, HW, HW, static_cast<cuuint64_t>(batch_cap)};
+    cuuint64_t strides[3] = {CIN * 2, static_cast<cuuint64_t>(CIN) * 2 * HW, static_cast<cuuint64_t>(CIN) * 2 * HW * HW};
     cuuint32_t box[4] = {64, PITCH, 2, 1};
     cuuint32_t estr[4] = {1, 1, 1, 1};
     if (g_bn_encode(&p.tmap_x, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(src), dims, strides, box, estr,
@@ -629,12 +548,11 @@ bool bneck56_plan_set(BneckPlan& p, const void* src, void* dst, int batch_cap, c
         return false;
     }
     const uint64_t rows = static_cast<uint64_t>(batch_cap) * HW * HW;
-    // identity blocks read the residual from the block input itself ([rows, 256] view of the same buffer)
-    if (!bn_encode_2d(&p.tmap_out, dst, OUTC, rows, 64, HW) ||
-        !bn_encode_2d(&p.tmap_res, p.proj ? dst : src, OUTC, rows, 64, HW)) {
-        snprintf(err, err_len, "bottleneck output tensor maps failed");
+    if (!bn_encode_2d(&p.tmap_out, dst, OUTC, rows, 64, HW)) {
+        snprintf(err, err_len, "bottleneck output tensor map failed");
         return false;
     }
+    p.x = src;
     return true;
 }
 
@@ -643,11 +561,22 @@ cudaError_t bneck56_launch(const BneckPlan& p, int n, int num_sms, cudaStream_t 
     BnArgs a;
     a.n_imgs = n;
     a.b1 = p.b1; a.b2 = p.b2; a.b3 = p.b3;
-    const int pair_tiles = n * (HW / 4);
-    const int pairs = num_sms / 2;
-    const int grid = 2 * (pair_tiles < pairs ? pair_tiles : pairs);
-    if (p.proj) return bn_launch<1, true>(p, a, grid, s);
-    return bn_launch<4, false>(p, a, grid, s);
+    a.x = static_cast<const uint16_t*>(p.x);
+    static const int trace = getenv("B2P_BNECK_TRACE") != nullptr;
+    a.trace = trace;
+    const int tiles = n * (HW / 2);
+    const int grid = tiles < num_sms ? tiles : num_sms;
+    static std::atomic<bool> attr_set[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (!attr_set[dev].load(std::memory_order_acquire)) {
+        cudaError_t e = cudaFuncSetAttribute(bottleneck56_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BN_SMEM);
+        if (e != cudaSuccess) return e;
+        attr_set[dev].store(true, std::memory_order_release);
+    }
+    return launch_pdl(bottleneck56_kernel, dim3(grid), dim3(BN_THREADS), BN_SMEM, s, p.tmap_x, p.tmap_w1, p.tmap_w2, p.tmap_w3,
+                      p.tmap_out, a);
 }
 
 }  // namespace b2p

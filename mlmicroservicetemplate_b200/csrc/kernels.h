@@ -123,11 +123,11 @@ cudaError_t pair_plan_launch(const PairPlan& p, int m_rows, int reverse, int num
 // ------------------------------------------------------------------ whole bottleneck block, 56x56 stage (bottleneck56.cu)
 struct BneckPlan {
     CUtensorMap tmap_x;      // block input [n,56,56,cin] bf16, 4-D tiled, [64 ch x 64 px x 2 rows] boxes
-    CUtensorMap tmap_w1;     // [64][cin], 32-row boxes (each CTA of a pair holds half of the output rows)
-    CUtensorMap tmap_w2;     // [64][9*64], 32-row boxes
-    CUtensorMap tmap_w3;     // [256][64 (+64 with a folded projection shortcut)], 128-row boxes
-    CUtensorMap tmap_res;    // [n*56*56, 256] view of the block input: residual rows (identity blocks)
+    CUtensorMap tmap_w1;     // [64][cin], 64 x 64 boxes (one K slice travels with each input box)
+    CUtensorMap tmap_w2;     // [64][9*64], one 64 x 64 box per tap
+    CUtensorMap tmap_w3;     // [256][64], 128-row boxes
     CUtensorMap tmap_out;    // [n*56*56, 256] block output
+    const void* x = nullptr; // the block input again (residual, read by the output epilogue)
     const float* b1 = nullptr;
     const float* b2 = nullptr;
     const float* b3 = nullptr;

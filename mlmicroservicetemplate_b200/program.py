@@ -153,8 +153,9 @@ class _Builder:
 
 def bottleneck_op(p: Program, src: int, dst: int, hw: int, cin: int, w1, b1, w2, b2, w3, b3, shortcut=None) -> None:
     """Appends one OP_BOTTLENECK (a whole 56x56 bottleneck block in one kernel).  w1 [64,cin,1,1], w2 [64,64,3,3],
-    w3 [256,64,1,1] fp32 with BN folded; shortcut = (wd [256,cin,1,1], bd) for the projection block (folded into conv3
-    as extra K columns, biases summed), None for an identity block (the residual is the block input)."""
+    w3 [256,64,1,1] fp32 with BN folded; shortcut = None for an identity block (the residual is the block input).  The op
+    format also describes a projection block (shortcut = (wd [256,cin,1,1], bd), folded into conv3 as extra K columns);
+    the library's kernel covers identity blocks and b2p_create refuses the other form."""
     mid, cout = w1.shape[0], w3.shape[0]
     w3p, b3p = pack_conv_weight(w3).view(cout, -1), b3
     if shortcut is not None:
@@ -213,24 +214,24 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
     import os
     if fuse_blocks is None:
         fuse_blocks = os.getenv("B2P_FUSE_BLOCKS", "0") != "0"
+    def fusable(blk, in_hwc):
+        """An identity bottleneck of the 56x56 stage (256 -> 64 -> 64 -> 256): the shape bottleneck56.cu covers."""
+        return (fuse_blocks and isinstance(blk, Bottleneck) and tuple(in_hwc) == (56, 56, 256) and blk.downsample is None
+                and blk.conv1.out_channels == 64 and blk.conv3.out_channels == 256 and blk.conv2.stride == (1, 1)
+                and blk.conv2.groups == 1 and blk.conv2.dilation == (1, 1))
+
     blocks = [blk for layer in (model.layer1, model.layer2, model.layer3, model.layer4) for blk in layer]
     carry = None          # (t1 slot, hwc1) when the previous block's CONV_PAIR already computed this block's conv1
     for bi_, blk in enumerate(blocks):
         if True:
             # A 56x56 bottleneck (ResNet-50/101/152 layer1) runs as ONE kernel: only the block input is read and the
             # block output written (measured against the layer-by-layer form with its conv3 -> next-conv1 pairing).
-            if (fuse_blocks and carry is None and isinstance(blk, Bottleneck)
-                    and hwc[0] == 56 and hwc[1] == 56 and blk.conv1.out_channels == 64 and blk.conv3.out_channels == 256
-                    and blk.conv2.stride == (1, 1) and blk.conv2.groups == 1 and blk.conv2.dilation == (1, 1)
-                    and ((blk.downsample is None and hwc[2] == 256) or
-                         (blk.downsample is not None and hwc[2] == 64 and blk.downsample[0].stride == (1, 1)
-                          and tuple(blk.downsample[0].kernel_size) == (1, 1)))):
+            if carry is None and fusable(blk, hwc):
                 w1, b1 = fold_bn(blk.conv1.weight, blk.bn1)
                 w2, b2 = fold_bn(blk.conv2.weight, blk.bn2)
                 w3, b3 = fold_bn(blk.conv3.weight, blk.bn3)
-                sc = fold_bn(blk.downsample[0].weight, blk.downsample[1]) if blk.downsample is not None else None
                 out = p.alloc(56 * 56 * 256)
-                bottleneck_op(p, x, out, 56, hwc[2], w1, b1, w2, b2, w3, b3, shortcut=sc)
+                bottleneck_op(p, x, out, 56, hwc[2], w1, b1, w2, b2, w3, b3)
                 p.release(x)
                 x, hwc = out, (56, 56, 256)
                 continue
@@ -264,6 +265,7 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
                 nxt = blocks[bi_ + 1] if bi_ + 1 < len(blocks) else None
                 n1 = w3.shape[0]
                 can_pair = (fuse_pairs and isinstance(nxt, Bottleneck) and nxt.conv1.kernel_size == (1, 1)
+                            and not fusable(nxt, (hwc2[0], hwc2[1], w3.shape[0]))     # a fused next block has its own conv1
                             and nxt.conv1.stride == (1, 1) and nxt.conv1.out_channels in (64, 128)
                             and n1 % 128 == 0 and w3.shape[1] in (64, 128) and tuple(blk.conv3.kernel_size) == (1, 1))
                 # (wider pairs - K1 >= 256 or N2 = 256, i.e. ResNet-50's stage 3 - were measured slower than the two
