@@ -120,6 +120,14 @@ __device__ __forceinline__ void tma_store_2d_hint(const CUtensorMap* m, const vo
                  : "memory");
 }
 
+// Asks the L2 for a box ahead of time (no shared-memory destination, no barrier).  A CTA can keep only a few
+// 16 KB boxes in flight in shared memory; prefetching the NEXT tile's boxes turns their HBM latency into an L2 hit.
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* m, int32_t c0, int32_t c1) {
+    asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(reinterpret_cast<uint64_t>(m)),
+                 "r"(c0), "r"(c1)
+                 : "memory");
+}
+
 // 2-D tiled store shared -> global (bulk async group).  Rows/columns outside the tensor are clipped.
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* src, int32_t c0, int32_t c1) {
     asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
