@@ -354,6 +354,32 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
     asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
     return r;
 }
+// Packed fp32 pairs (sm_100: one instruction, two IEEE-rounded results - bit-identical to the scalar forms).
+__device__ __forceinline__ uint64_t f32x2_pack(uint32_t lo, uint32_t hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(lo), "r"(hi));
+    return r;
+}
+__device__ __forceinline__ uint64_t f32x2_pack(float lo, float hi) { return f32x2_pack(__float_as_uint(lo), __float_as_uint(hi)); }
+__device__ __forceinline__ uint64_t f32x2_add(uint64_t a, uint64_t b) {
+    uint64_t r;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+// a bf16 pair (two values in one 32-bit word) widened to an fp32 pair
+__device__ __forceinline__ uint64_t f32x2_from_bf16x2(uint32_t v) { return f32x2_pack(v << 16, v & 0xFFFF0000u); }
+// round an fp32 pair to a bf16 pair (low half = first element)
+__device__ __forceinline__ uint32_t bf16x2_from_f32x2(uint64_t a) {
+    uint32_t r;
+    asm("{\n.reg .b32 lo, hi;\nmov.b64 {lo, hi}, %1;\ncvt.rn.bf16x2.f32 %0, hi, lo;\n}" : "=r"(r) : "l"(a));
+    return r;
+}
+// ReLU on a bf16 pair.  Rounding is monotonic and keeps the sign, so relu(round(x)) == round(relu(x)).
+__device__ __forceinline__ uint32_t bf16x2_relu(uint32_t v) {
+    uint32_t r;
+    asm("max.bf16x2 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(0u));
+    return r;
+}
 __device__ __forceinline__ float bf16_lo(uint32_t v) { return __uint_as_float(v << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t v) { return __uint_as_float(v & 0xFFFF0000u); }
 
