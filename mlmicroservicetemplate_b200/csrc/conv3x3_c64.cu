@@ -200,41 +200,37 @@ conv3x3_c64_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_con
             if (HAS_RES) mbar_wait(&res_full_bar[acc], acc_phase);
             const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * CH);
             uint4 packed[8];
-#pragma unroll
-            for (int h = 0; h < 2; ++h) {
-                uint32_t v[32];
-                tmem_ld_32x32(t_addr + static_cast<uint32_t>(h * 32), v);
-                tmem_ld_wait();
-                const float4* b4 = reinterpret_cast<const float4*>(bias + h * 32);
-                float f[32];
-#pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    const float4 b = __ldg(b4 + j);
-                    f[4 * j + 0] = __uint_as_float(v[4 * j + 0]) + b.x;
-                    f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + b.y;
-                    f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + b.z;
-                    f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + b.w;
-                }
+            {
+                // both halves requested from TMEM before anything waits; packed fp32 pairs for the bias / residual adds,
+                // ReLU on the rounded bf16 pair (same roundings as the scalar form)
+                uint32_t v[64];
+                tmem_ld_32x32(t_addr, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+                tmem_ld_32x32(t_addr + 32u, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+                const float4* b4 = reinterpret_cast<const float4*>(bias);
+                uint4 r[8];
                 if (HAS_RES) {
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
-                        const uint4 r = ld_shared_v4(res_row + ((static_cast<uint32_t>(h * 4 + j) ^ swz) << 4));
-                        f[8 * j + 0] += bf16_lo(r.x); f[8 * j + 1] += bf16_hi(r.x);
-                        f[8 * j + 2] += bf16_lo(r.y); f[8 * j + 3] += bf16_hi(r.y);
-                        f[8 * j + 4] += bf16_lo(r.z); f[8 * j + 5] += bf16_hi(r.z);
-                        f[8 * j + 6] += bf16_lo(r.w); f[8 * j + 7] += bf16_hi(r.w);
+                    for (int j = 0; j < 8; ++j) r[j] = ld_shared_v4(res_row + ((static_cast<uint32_t>(j) ^ swz) << 4));
+                }
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const float4 ba = __ldg(b4 + 2 * j), bb = __ldg(b4 + 2 * j + 1);
+                    uint64_t a0 = f32x2_add(f32x2_pack(v[8 * j + 0], v[8 * j + 1]), f32x2_pack(ba.x, ba.y));
+                    uint64_t a1 = f32x2_add(f32x2_pack(v[8 * j + 2], v[8 * j + 3]), f32x2_pack(ba.z, ba.w));
+                    uint64_t a2 = f32x2_add(f32x2_pack(v[8 * j + 4], v[8 * j + 5]), f32x2_pack(bb.x, bb.y));
+                    uint64_t a3 = f32x2_add(f32x2_pack(v[8 * j + 6], v[8 * j + 7]), f32x2_pack(bb.z, bb.w));
+                    if (HAS_RES) {
+                        a0 = f32x2_add(a0, f32x2_from_bf16x2(r[j].x));
+                        a1 = f32x2_add(a1, f32x2_from_bf16x2(r[j].y));
+                        a2 = f32x2_add(a2, f32x2_from_bf16x2(r[j].z));
+                        a3 = f32x2_add(a3, f32x2_from_bf16x2(r[j].w));
                     }
-                }
-                if (relu) {
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) f[j] = fmaxf(f[j], 0.f);
-                }
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    packed[h * 4 + j].x = pack_bf16x2(f[8 * j + 0], f[8 * j + 1]);
-                    packed[h * 4 + j].y = pack_bf16x2(f[8 * j + 2], f[8 * j + 3]);
-                    packed[h * 4 + j].z = pack_bf16x2(f[8 * j + 4], f[8 * j + 5]);
-                    packed[h * 4 + j].w = pack_bf16x2(f[8 * j + 6], f[8 * j + 7]);
+                    uint4 o;
+                    o.x = bf16x2_from_f32x2(a0); o.y = bf16x2_from_f32x2(a1);
+                    o.z = bf16x2_from_f32x2(a2); o.w = bf16x2_from_f32x2(a3);
+                    if (relu) { o.x = bf16x2_relu(o.x); o.y = bf16x2_relu(o.y); o.z = bf16x2_relu(o.z); o.w = bf16x2_relu(o.w); }
+                    packed[j] = o;
                 }
             }
             tc_fence_before();

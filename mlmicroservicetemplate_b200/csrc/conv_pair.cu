@@ -278,37 +278,36 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     if (args.has_res) mbar_wait(&res_full[rb], rb_phase);
                     const uint32_t res_row = smem_u32(smem_res + rb * TILE16K) + static_cast<uint32_t>(row * 128);
                     uint4 packed[8];
-#pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        uint32_t v[32];
-                        tmem_ld_32x32(lane_addr + static_cast<uint32_t>(slot * BN1 + c * 64 + h * 32), v);
-                        tmem_ld_wait();
-                        const float4* b4 = reinterpret_cast<const float4*>(args.bias1 + col0 + h * 32);
-                        float f[32];
-#pragma unroll
-                        for (int j = 0; j < 8; ++j) {
-                            const float4 b = __ldg(b4 + j);
-                            f[4 * j + 0] = __uint_as_float(v[4 * j + 0]) + b.x;
-                            f[4 * j + 1] = __uint_as_float(v[4 * j + 1]) + b.y;
-                            f[4 * j + 2] = __uint_as_float(v[4 * j + 2]) + b.z;
-                            f[4 * j + 3] = __uint_as_float(v[4 * j + 3]) + b.w;
-                        }
+                    {
+                        // both halves of the chunk requested from TMEM before anything waits; packed fp32 pairs for the
+                        // bias / residual adds, ReLU on the rounded bf16 pair (same roundings as the scalar form)
+                        uint32_t v[64];
+                        tmem_ld_32x32(lane_addr + static_cast<uint32_t>(slot * BN1 + c * 64), *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+                        tmem_ld_32x32(lane_addr + static_cast<uint32_t>(slot * BN1 + c * 64 + 32), *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+                        const float4* b4 = reinterpret_cast<const float4*>(args.bias1 + col0);
+                        uint4 r[8];
                         if (args.has_res) {
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            const uint4 r = ld_shared_v4(res_row + ((static_cast<uint32_t>(h * 4 + j) ^ swz) << 4));
-                            f[8 * j + 0] += bf16_lo(r.x); f[8 * j + 1] += bf16_hi(r.x);
-                            f[8 * j + 2] += bf16_lo(r.y); f[8 * j + 3] += bf16_hi(r.y);
-                            f[8 * j + 4] += bf16_lo(r.z); f[8 * j + 5] += bf16_hi(r.z);
-                            f[8 * j + 6] += bf16_lo(r.w); f[8 * j + 7] += bf16_hi(r.w);
+                            for (int j = 0; j < 8; ++j) r[j] = ld_shared_v4(res_row + ((static_cast<uint32_t>(j) ^ swz) << 4));
                         }
-                        }
+                        tmem_ld_wait();
 #pragma unroll
-                        for (int j = 0; j < 4; ++j) {
-                            packed[h * 4 + j].x = pack_bf16x2(fmaxf(f[8 * j + 0], 0.f), fmaxf(f[8 * j + 1], 0.f));
-                            packed[h * 4 + j].y = pack_bf16x2(fmaxf(f[8 * j + 2], 0.f), fmaxf(f[8 * j + 3], 0.f));
-                            packed[h * 4 + j].z = pack_bf16x2(fmaxf(f[8 * j + 4], 0.f), fmaxf(f[8 * j + 5], 0.f));
-                            packed[h * 4 + j].w = pack_bf16x2(fmaxf(f[8 * j + 6], 0.f), fmaxf(f[8 * j + 7], 0.f));
+                        for (int j = 0; j < 8; ++j) {
+                            const float4 ba = __ldg(b4 + 2 * j), bb = __ldg(b4 + 2 * j + 1);
+                            uint64_t a0 = f32x2_add(f32x2_pack(v[8 * j + 0], v[8 * j + 1]), f32x2_pack(ba.x, ba.y));
+                            uint64_t a1 = f32x2_add(f32x2_pack(v[8 * j + 2], v[8 * j + 3]), f32x2_pack(ba.z, ba.w));
+                            uint64_t a2 = f32x2_add(f32x2_pack(v[8 * j + 4], v[8 * j + 5]), f32x2_pack(bb.x, bb.y));
+                            uint64_t a3 = f32x2_add(f32x2_pack(v[8 * j + 6], v[8 * j + 7]), f32x2_pack(bb.z, bb.w));
+                            if (args.has_res) {
+                                a0 = f32x2_add(a0, f32x2_from_bf16x2(r[j].x));
+                                a1 = f32x2_add(a1, f32x2_from_bf16x2(r[j].y));
+                                a2 = f32x2_add(a2, f32x2_from_bf16x2(r[j].z));
+                                a3 = f32x2_add(a3, f32x2_from_bf16x2(r[j].w));
+                            }
+                            packed[j].x = bf16x2_relu(bf16x2_from_f32x2(a0));
+                            packed[j].y = bf16x2_relu(bf16x2_from_f32x2(a1));
+                            packed[j].z = bf16x2_relu(bf16x2_from_f32x2(a2));
+                            packed[j].w = bf16x2_relu(bf16x2_from_f32x2(a3));
                         }
                     }
                     if (args.has_res) {
@@ -347,19 +346,19 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll 1
             for (int c2 = 0; c2 < N2 / 64; ++c2) {
                 uint4 packed[8];
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    uint32_t v[32];
-                    tmem_ld_32x32(lane_addr + ACC2_COL + static_cast<uint32_t>(c2 * 64 + h * 32), v);
+                {
+                    uint32_t v[64];
+                    tmem_ld_32x32(lane_addr + ACC2_COL + static_cast<uint32_t>(c2 * 64), *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+                    tmem_ld_32x32(lane_addr + ACC2_COL + static_cast<uint32_t>(c2 * 64 + 32), *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+                    const float4* b4 = reinterpret_cast<const float4*>(args.bias2 + c2 * 64);
                     tmem_ld_wait();
-                    const float4* b4 = reinterpret_cast<const float4*>(args.bias2 + c2 * 64 + h * 32);
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) {
+                    for (int j = 0; j < 8; ++j) {
                         const float4 ba = __ldg(b4 + 2 * j), bb = __ldg(b4 + 2 * j + 1);
-                        packed[h * 4 + j].x = pack_bf16x2(fmaxf(__uint_as_float(v[8 * j + 0]) + ba.x, 0.f), fmaxf(__uint_as_float(v[8 * j + 1]) + ba.y, 0.f));
-                        packed[h * 4 + j].y = pack_bf16x2(fmaxf(__uint_as_float(v[8 * j + 2]) + ba.z, 0.f), fmaxf(__uint_as_float(v[8 * j + 3]) + ba.w, 0.f));
-                        packed[h * 4 + j].z = pack_bf16x2(fmaxf(__uint_as_float(v[8 * j + 4]) + bb.x, 0.f), fmaxf(__uint_as_float(v[8 * j + 5]) + bb.y, 0.f));
-                        packed[h * 4 + j].w = pack_bf16x2(fmaxf(__uint_as_float(v[8 * j + 6]) + bb.z, 0.f), fmaxf(__uint_as_float(v[8 * j + 7]) + bb.w, 0.f));
+                        packed[j].x = bf16x2_relu(bf16x2_from_f32x2(f32x2_add(f32x2_pack(v[8 * j + 0], v[8 * j + 1]), f32x2_pack(ba.x, ba.y))));
+                        packed[j].y = bf16x2_relu(bf16x2_from_f32x2(f32x2_add(f32x2_pack(v[8 * j + 2], v[8 * j + 3]), f32x2_pack(ba.z, ba.w))));
+                        packed[j].z = bf16x2_relu(bf16x2_from_f32x2(f32x2_add(f32x2_pack(v[8 * j + 4], v[8 * j + 5]), f32x2_pack(bb.x, bb.y))));
+                        packed[j].w = bf16x2_relu(bf16x2_from_f32x2(f32x2_add(f32x2_pack(v[8 * j + 6], v[8 * j + 7]), f32x2_pack(bb.z, bb.w))));
                     }
                 }
                 if (c2 == N2 / 64 - 1) {
