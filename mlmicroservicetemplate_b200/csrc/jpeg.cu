@@ -90,14 +90,25 @@ const uint8_t h_zigzag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25, 18
 //
 // The host hands over each segment un-stuffed (FF 00 -> FF), 4-byte aligned and zero padded, so a bit position is a
 // plain offset and the reader can take 32 bits at a time.
+// Index of staged word j in shared memory: one word of skew per 16, so that lanes whose chunks start a multiple of
+// 16 words apart (512-bit chunks) do not all hit the same bank.
+__device__ __forceinline__ uint32_t stage_index(uint32_t j) { return j + (j >> 4); }
+
 struct BitReader {
     const uint32_t* __restrict__ words;   // big-endian bit order inside each byte-swapped word
     uint32_t nwords;
     uint32_t next;                        // index of the next word to take
     uint64_t win;                         // bit 63 = next unread bit
     int have;                             // valid bits in win
+    // The CTA's part of the stream staged in shared memory, already byte-swapped (stage_count == 0: not staged).
+    // A refill is a dependent load on the critical path of every ~32 bits decoded: from shared memory it costs
+    // ~30 cycles, from global memory (L2) several hundred.
+    const uint32_t* stage;
+    uint32_t stage_w0, stage_count;
 
     __device__ __forceinline__ uint32_t word(uint32_t i) const {
+        const uint32_t j = i - stage_w0;
+        if (j < stage_count) return stage[stage_index(j)];
         return i < nwords ? __byte_perm(__ldg(words + i), 0, 0x0123) : 0u;
     }
     __device__ __forceinline__ void seek(uint32_t bitpos) {
@@ -152,6 +163,8 @@ struct SegmentCtx {
     uint32_t nwords;
     const uint16_t* look;       // shared memory: [component][0 = DC, 1 = AC][512] lookahead entries
     const uint8_t* zigzag;      // shared memory copy of c_zigzag (divergent indices serialise in the constant cache)
+    const uint32_t* stage;      // shared memory: this CTA's words of the stream (see BitReader), or nullptr
+    uint32_t stage_w0, stage_count;
 };
 
 // Address of block `b` (segment-relative, decode order) in the coefficient planes.
@@ -183,6 +196,9 @@ __device__ __forceinline__ void decode_range(const SegmentCtx& c, DecodeState& s
     BitReader br;
     br.words = c.words;
     br.nwords = c.nwords;
+    br.stage = c.stage;
+    br.stage_w0 = c.stage_w0;
+    br.stage_count = c.stage_count;
     br.seek(st.pos);
     int blk = st.blk, k = st.k;
     int done = 0;
@@ -304,7 +320,9 @@ template <bool CLUSTER>
 __global__ void __launch_bounds__(HUFF_MAX_THREADS)
 huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ images,
                const SegmentDev* __restrict__ segments, const HuffDev* __restrict__ tables,
-               int16_t* __restrict__ coef, int32_t* __restrict__ status, int min_chunk_bits, int debug_rounds) {
+               int16_t* __restrict__ coef, int32_t* __restrict__ status, int min_chunk_bits, int debug_rounds,
+               int stage_words) {
+    extern __shared__ uint32_t s_stream[];          // stage_words (+ skew) words: this CTA's part of the stream
     __shared__ uint32_t s_pos[HUFF_MAX_THREADS];
     __shared__ int s_state[HUFF_MAX_THREADS];        // blk << 8 | k
     __shared__ int s_warp[HUFF_MAX_THREADS / 32];
@@ -343,6 +361,22 @@ huffman_kernel(const uint8_t* __restrict__ scan, const ImageDev* __restrict__ im
     chunk = max((chunk + 31u) & ~31u, static_cast<uint32_t>(min_chunk_bits));
     const uint32_t my_begin = static_cast<uint32_t>(min(static_cast<uint64_t>(gt) * chunk, static_cast<uint64_t>(c.nbits)));
     const uint32_t my_end = min(my_begin + chunk, c.nbits);
+    // stage the words this CTA's threads will read (their chunks + the few words a symbol may reach past a chunk end)
+    c.stage = nullptr;
+    c.stage_w0 = 0;
+    c.stage_count = 0;
+    if (stage_words > 0) {
+        const uint64_t cta_begin = min(static_cast<uint64_t>(rank) * P * chunk, static_cast<uint64_t>(c.nbits));
+        const uint64_t cta_end = min(cta_begin + static_cast<uint64_t>(P) * chunk, static_cast<uint64_t>(c.nbits));
+        const uint32_t w0 = static_cast<uint32_t>(cta_begin >> 5);
+        const uint32_t w1 = min(c.nwords, static_cast<uint32_t>((cta_end + 31u) >> 5) + 4u);
+        const uint32_t count = min(w1 > w0 ? w1 - w0 : 0u, static_cast<uint32_t>(stage_words));
+        for (uint32_t i = t; i < count; i += P) s_stream[stage_index(i)] = __byte_perm(__ldg(c.words + w0 + i), 0, 0x0123);
+        c.stage = s_stream;
+        c.stage_w0 = w0;
+        c.stage_count = count;
+        __syncthreads();
+    }
 
     // ---- 1 + 2: find every chunk's true entry state
     DecodeState in = {my_begin, 0, 0};
@@ -1240,15 +1274,41 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
         }();
         int cluster = 1;
         while (cluster < max_cluster && want > static_cast<int64_t>(cluster) * HUFF_MAX_THREADS) cluster *= 2;
+        const int threads = cluster > 1 ? HUFF_MAX_THREADS
+                                        : static_cast<int>(want < 32 ? 32 : (want > HUFF_MAX_THREADS ? HUFF_MAX_THREADS : want));
+        // shared-memory staging of the stream: as many words as the largest CTA share needs, capped by what fits
+        static const int stage_on = [] { const char* e = getenv("B2P_JPEG_STAGE"); return e ? atoi(e) : 1; }();
+        int stage_words = 0;
+        size_t stage_bytes = 0;
+        if (stage_on) {
+            const int64_t pt = static_cast<int64_t>(cluster) * threads;
+            int64_t chunk = (max_seg_bits + pt - 1) / pt;
+            chunk = (chunk + 31) / 32 * 32;
+            if (chunk < min_chunk) chunk = min_chunk;
+            int64_t words = static_cast<int64_t>(threads) * chunk / 32 + 8;
+            const int64_t cap = (188 * 1024 / 4) * 16 / 17 - 32;          // dynamic shared memory left beside the tables
+            if (words > cap) words = cap;
+            stage_words = static_cast<int>(words);
+            stage_bytes = static_cast<size_t>(words + words / 16 + 16) * 4;
+            static std::atomic<bool> attr_set[64][2];
+            int dev_id = 0;
+            cudaGetDevice(&dev_id);
+            const int which = cluster > 1 ? 1 : 0;
+            if (dev_id >= 0 && dev_id < 64 && !attr_set[dev_id][which].load(std::memory_order_acquire)) {
+                if (which) JPEG_CUDA(d, cudaFuncSetAttribute(huffman_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024));
+                else JPEG_CUDA(d, cudaFuncSetAttribute(huffman_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 190 * 1024));
+                attr_set[dev_id][which].store(true, std::memory_order_release);
+            }
+        }
         if (cluster == 1) {
-            const int threads = static_cast<int>(want < 32 ? 32 : (want > HUFF_MAX_THREADS ? HUFF_MAX_THREADS : want));
-            huffman_kernel<false><<<static_cast<unsigned>(n_segments), threads, 0, stream>>>(
-                dev + off_scan, images_dev, segs_dev, tabs_dev, d->coef, status, min_chunk, debug_rounds);
+            huffman_kernel<false><<<static_cast<unsigned>(n_segments), threads, stage_bytes, stream>>>(
+                dev + off_scan, images_dev, segs_dev, tabs_dev, d->coef, status, min_chunk, debug_rounds, stage_words);
             JPEG_CUDA(d, cudaGetLastError());
         } else {
             cudaLaunchConfig_t cfg = {};
             cfg.gridDim = dim3(static_cast<unsigned>(n_segments * cluster));
             cfg.blockDim = dim3(HUFF_MAX_THREADS);
+            cfg.dynamicSmemBytes = stage_bytes;
             cfg.stream = stream;
             cudaLaunchAttribute attr[1];
             attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -1260,7 +1320,7 @@ int32_t b2p_jpeg_decode(b2p_jpeg* d, const uint8_t* const* files, const int64_t*
             const uint8_t* scan_dev = dev + off_scan;
             int16_t* coef_dev = d->coef;
             JPEG_CUDA(d, cudaLaunchKernelEx(&cfg, huffman_kernel<true>, scan_dev, images_dev, segs_dev, tabs_dev, coef_dev,
-                                            status, min_chunk, debug_rounds));
+                                            status, min_chunk, debug_rounds, stage_words));
         }
         JPEG_CUDA(d, cudaEventRecord(d->ev[2], stream));
     }
