@@ -127,204 +127,24 @@ __global__ void layernorm_kernel(const uint4* __restrict__ x, const float* __res
 }
 
 // ------------------------------------------------------------------------------ attention
-constexpr int ATT_THREADS = 320;       // warp 0 loads, warp 1 issues the MMAs, warps 2-9 = softmax / epilogue (two per TMEM lane quadrant)
 constexpr int HD = 64;                 // head dimension
 constexpr int KV_ROWS = 208;           // keys padded to a multiple of 16 (UMMA N / K granularity), >= 197
 constexpr int Q_BYTES = 128 * 128;     // 128 queries x 64 dims bf16, 128B swizzle
 constexpr int KV_BYTES = 256 * 128;    // room for 208 key (value) rows of 128 bytes
 constexpr int P_CHUNK_BYTES = 128 * 128;
 // P (4 chunks of 16 KB) is written only after S = QK^T has completed, when Q and K are dead: chunks 0-1
-// overlay K, chunk 2 overlays Q, chunk 3 gets its own 16 KB.  ~99 KB per CTA, so two CTAs share an SM and
-// one's softmax overlaps the other's loads and MMAs.  The softmax is the long pole of a CTA (208 exp2 per row),
-// so eight warps share it: two per TMEM lane quadrant, each taking half of the keys.
-constexpr int ATT_XCHG_BYTES = 2 * 2 * 128 * 4;      // row max and row sum halves exchanged between the two warps of a row
-constexpr int ATT_SMEM = 1024 + Q_BYTES + 2 * KV_BYTES + P_CHUNK_BYTES + 128 + ATT_XCHG_BYTES;
+// overlay K, chunk 2 overlays Q, chunk 3 gets its own 16 KB.
 
 // tcgen05 instruction descriptor, bf16 x bf16 -> fp32, A K-major, B MN-major (bit 16).
 __host__ __device__ constexpr uint32_t umma_idesc_bf16_b_mn(uint32_t m, uint32_t n) {
     return umma_idesc_bf16(m, n) | (1u << 16);
 }
 
-__global__ void __launch_bounds__(ATT_THREADS, 2)
-attention_kernel(const __grid_constant__ CUtensorMap tmap_q, const __grid_constant__ CUtensorMap tmap_kv,
-                 uint16_t* __restrict__ out, int seq, int dim, float scale_log2e) {
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-    uint8_t* smem_q = smem;
-    uint8_t* smem_k = smem_q + Q_BYTES;
-    uint8_t* smem_v = smem_k + KV_BYTES;
-    uint8_t* smem_p3 = smem_v + KV_BYTES;
-    uint64_t* load_bar = reinterpret_cast<uint64_t*>(smem_p3 + P_CHUNK_BYTES);
-    // P chunk c (keys 64c .. 64c+63): {K, K + 16 KB, Q, own}
-    const uint32_t pk = smem_u32(smem_k), pq = smem_u32(smem_q), p3 = smem_u32(smem_p3);
-    auto p_chunk_addr = [&](int c) -> uint32_t { return c == 0 ? pk : (c == 1 ? pk + P_CHUNK_BYTES : (c == 2 ? pq : p3)); };
-    uint64_t* s_bar = load_bar + 1;
-    uint64_t* p_bar = s_bar + 1;
-    uint64_t* o_bar = p_bar + 1;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_bar + 1);
-    float* x_max = reinterpret_cast<float*>(smem_p3 + P_CHUNK_BYTES + 128);      // [2][128]
-    float* x_sum = x_max + 2 * 128;                                               // [2][128]
-
-    const int warp_idx = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
-    const int mt = blockIdx.x, head = blockIdx.y, img = blockIdx.z;
-    const int row0 = img * seq;                    // first token row of this image in the [n*seq, 3*dim] matrix
-
-    if (warp_idx == 0) {
-        if (elect_one()) {
-            tma_prefetch_desc(&tmap_q);
-            tma_prefetch_desc(&tmap_kv);
-        }
-    } else if (warp_idx == 1) {
-        if (elect_one()) {
-            mbar_init(load_bar, 1);
-            mbar_init(s_bar, 1);
-            mbar_init(p_bar, 8);
-            mbar_init(o_bar, 1);
-            fence_mbar_init();
-        }
-        __syncwarp();
-        tmem_alloc(tmem_slot, 256);
-        tmem_relinquish();
-    }
-    pdl_launch_dependents();
-    tc_fence_before();
-    __syncthreads();
-    tc_fence_after();
-    const uint32_t tmem_base = *tmem_slot;
-    pdl_wait();
-
-    if (warp_idx == 0) {
-        if (elect_one()) {
-            mbar_arrive_expect_tx(load_bar, Q_BYTES + 2 * KV_ROWS * 128);
-            tma_load_2d(&tmap_q, load_bar, smem_q, head * HD, row0 + mt * 128);
-            tma_load_2d(&tmap_kv, load_bar, smem_k, dim + head * HD, row0);
-            tma_load_2d(&tmap_kv, load_bar, smem_v, 2 * dim + head * HD, row0);
-        }
-    } else if (warp_idx == 1) {
-        if (elect_one()) {
-            // ---- S = Q K^T  (M=128, N=208, K=64)
-            mbar_wait(load_bar, 0);
-            tc_fence_after();
-            const uint64_t q_desc = umma_desc_kmajor(smem_u32(smem_q), 128);
-            const uint64_t k_desc = umma_desc_kmajor(smem_u32(smem_k), 128);
-            constexpr uint32_t idesc_s = umma_idesc_bf16(128, KV_ROWS);
-#pragma unroll
-            for (int k = 0; k < HD / 16; ++k)
-                umma_bf16(tmem_base, q_desc + static_cast<uint64_t>(2 * k), k_desc + static_cast<uint64_t>(2 * k), idesc_s,
-                          static_cast<uint32_t>(k != 0));
-            umma_commit(s_bar);
-            // ---- O = P V  (M=128, N=64, K=208): P K-major from the softmax warps, V MN-major as loaded
-            mbar_wait(p_bar, 0);
-            tc_fence_after();
-            constexpr uint32_t idesc_o = umma_idesc_bf16_b_mn(128, HD);
-            const uint32_t v_addr = smem_u32(smem_v);
-#pragma unroll
-            for (int ks = 0; ks < KV_ROWS / 16; ++ks) {
-                const uint64_t p_desc = umma_desc_kmajor(p_chunk_addr(ks >> 2), 128) + static_cast<uint64_t>(2 * (ks & 3));
-                // MN-major, 128B swizzle: each K index is one 128-byte row; 8-row groups are 1024 B apart (SBO)
-                const uint64_t v_desc = umma_desc_kmajor(v_addr + ks * 2048, 128);
-                umma_bf16(tmem_base, p_desc, v_desc, idesc_o, static_cast<uint32_t>(ks != 0));
-            }
-            umma_commit(o_bar);
-        }
-    } else {
-        // Two warps share every TMEM lane quadrant (a warp may only read lanes 32 * (warp_idx % 4) ...): the first
-        // set takes keys 0..127 (column chunks 0-3), the second keys 128..207 (chunks 4-6); row maxima and row
-        // sums are combined through shared memory, and the O epilogue is split the same way (dims 0-31 / 32-63).
-        const int quad = warp_idx & 3;
-        const int half = (warp_idx - 2) >> 2;
-        const int lane = static_cast<int>(lane_id());
-        const int r = quad * 32 + lane;                         // query row inside the tile
-        const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
-        const int c_lo = half ? 4 : 0, c_hi = half ? 7 : 4;
-        mbar_wait(s_bar, 0);
-        tc_fence_after();
-        // pass 1: row maximum over the valid keys of this half, then over both halves
-        float mx = -FLT_MAX;
-#pragma unroll 1
-        for (int c = c_lo; c < c_hi; ++c) {
-            uint32_t v[32];
-            tmem_ld_32x32(t_addr + c * 32, v);
-            tmem_ld_wait();
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-                if (c * 32 + j < seq) mx = fmaxf(mx, __uint_as_float(v[j]));
-        }
-        x_max[half * 128 + r] = mx;
-        named_bar_sync(1, 256);
-        mx = fmaxf(mx, x_max[(half ^ 1) * 128 + r]);
-        // pass 2: p = exp((s - max) * scale), unnormalised bf16 into the K-major swizzled P tiles; row sum in fp32
-        float sum = 0.f;
-        const uint32_t p_row = static_cast<uint32_t>(r * 128);
-#pragma unroll 1
-        for (int c = c_lo; c < c_hi; ++c) {
-            uint32_t v[32];
-            tmem_ld_32x32(t_addr + c * 32, v);
-            tmem_ld_wait();
-            float p[32];
-#pragma unroll
-            for (int j = 0; j < 32; ++j) {
-                const float e = exp2f((__uint_as_float(v[j]) - mx) * scale_log2e);
-                p[j] = (c * 32 + j < seq) ? e : 0.f;
-            }
-            const int chunk = c >> 1;                          // 64-key chunk
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                uint4 o;
-                o.x = pack_bf16x2(p[8 * j + 0], p[8 * j + 1]); o.y = pack_bf16x2(p[8 * j + 2], p[8 * j + 3]);
-                o.z = pack_bf16x2(p[8 * j + 4], p[8 * j + 5]); o.w = pack_bf16x2(p[8 * j + 6], p[8 * j + 7]);
-                // sum what the tensor core will actually see (the bf16-rounded values)
-                sum += bf16_lo(o.x) + bf16_hi(o.x) + bf16_lo(o.y) + bf16_hi(o.y) + bf16_lo(o.z) + bf16_hi(o.z) +
-                       bf16_lo(o.w) + bf16_hi(o.w);
-                const int piece = ((c & 1) * 4 + j) ^ (r & 7);
-                st_shared_v4(p_chunk_addr(chunk) + p_row + static_cast<uint32_t>(piece * 16), o);
-            }
-        }
-        // (the PV MMA reads keys 0..207 only; chunk 6 wrote keys 192..223 of P chunk 3, zeros beyond `seq`)
-        x_sum[half * 128 + r] = sum;
-        fence_proxy_async_smem();          // P must be visible to the tensor core's async proxy
-        tc_fence_before();                 // and all S reads are done before the accumulator is overwritten
-        __syncwarp();
-        if (lane == 0) mbar_arrive(p_bar);
-        // ---- O epilogue
-        mbar_wait(o_bar, 0);
-        tc_fence_after();
-        named_bar_sync(1, 256);            // both halves of every row sum are in shared memory
-        const float inv = 1.0f / (sum + x_sum[(half ^ 1) * 128 + r]);
-        const int token = mt * 128 + r;
-        uint4 packed[4];
-        {
-            uint32_t v[32];
-            tmem_ld_32x32(t_addr + half * 32, v);
-            tmem_ld_wait();
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                packed[j].x = pack_bf16x2(__uint_as_float(v[8 * j + 0]) * inv, __uint_as_float(v[8 * j + 1]) * inv);
-                packed[j].y = pack_bf16x2(__uint_as_float(v[8 * j + 2]) * inv, __uint_as_float(v[8 * j + 3]) * inv);
-                packed[j].z = pack_bf16x2(__uint_as_float(v[8 * j + 4]) * inv, __uint_as_float(v[8 * j + 5]) * inv);
-                packed[j].w = pack_bf16x2(__uint_as_float(v[8 * j + 6]) * inv, __uint_as_float(v[8 * j + 7]) * inv);
-            }
-        }
-        if (token < seq) {
-            uint4* o = reinterpret_cast<uint4*>(out + (static_cast<size_t>(row0 + token) * dim + head * HD + half * 32));
-#pragma unroll
-            for (int j = 0; j < 4; ++j) st_v4(o + j, packed[j]);
-        }
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (warp_idx == 1) {
-        tc_fence_after();
-        tmem_dealloc(tmem_base, 256);
-    }
-}
-
-// ------------------------------------------------------------------------------ attention, persistent version
 // One CTA per SM walks the (image, head, query tile) items.  Two items are in flight at any time, in two slots
 // (slot = item parity): each slot has its own Q/K/V/P shared-memory stage, its own 256 TMEM columns (S, later
 // overwritten by O) and its own group of four softmax warps, so the softmax of one item runs under the loads, the
-// MMAs and the epilogue of the other, and none of the per-CTA costs of the first version (TMEM allocation, barrier
-// set-up, cold first load) is paid per item.
+// MMAs and the epilogue of the other, and the per-CTA costs (TMEM allocation, barrier set-up, cold first load) are
+// paid once per SM instead of once per item (the first version, one item per CTA, was 15 % slower at batch 64).
 //   warp 0   TMA producer:  Q / K / V of item i into stage i % 2 as soon as PV(i - 2) has released it
 //   warp 1   MMA issuer:    S(i) = Q K^T, then O(i - 1) = P V as soon as the softmax of i - 1 has published P
 //   warps 2-5 / 6-9  softmax + O epilogue of the even / odd items
@@ -618,8 +438,8 @@ cudaError_t launch_layernorm(const void* x, const float* gamma, const float* bet
 
 bool attention_plan_init(AttentionPlan& p, const void* qkv, int batch_cap, int seq, int dim, int heads, char* err,
                          size_t err_len) {
-    if (dim != heads * HD || seq > KV_ROWS - 0 || seq > 256 || seq < 1) {
-        snprintf(err, err_len, "attention supports head_dim 64 and sequence length <= %d", KV_ROWS);
+    if (dim != heads * HD || seq > KV_ROWS || seq <= 128) {
+        snprintf(err, err_len, "attention supports head_dim 64 and sequence lengths 129..%d (two query tiles)", KV_ROWS);
         return false;
     }
     p.seq = seq;
@@ -640,31 +460,17 @@ cudaError_t attention_plan_launch(const AttentionPlan& p, void* out, int n, cuda
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
     if (!attr_set[dev].load(std::memory_order_acquire)) {
-        cudaError_t e = cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM);
+        cudaError_t e = cudaFuncSetAttribute(attention_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, A2_SMEM);
         if (e != cudaSuccess) return e;
         attr_set[dev].store(true, std::memory_order_release);
     }
     const float scale_log2e = 1.4426950408889634f / sqrtf(static_cast<float>(HD));
-    // persistent two-slot kernel unless B2P_ATT_V1 is set (the one-item-per-CTA version, kept for A/B runs) or the
-    // sequence needs other than two query tiles
-    static const bool use_v1 = getenv("B2P_ATT_V1") != nullptr;
-    if (!use_v1 && p.seq > 128 && p.seq <= 256) {
-        static bool attr2_set[64] = {};
-        if (!attr2_set[dev]) {
-            cudaError_t e = cudaFuncSetAttribute(attention_persistent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, A2_SMEM);
-            if (e != cudaSuccess) return e;
-            attr2_set[dev] = true;
-        }
-        int sms = 0;
-        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        const int n_items = n * p.heads * 2;
-        const int grid2 = n_items < sms ? n_items : sms;
-        return launch_pdl(attention_persistent_kernel, dim3(grid2), dim3(A2_THREADS), A2_SMEM, s, p.tmap_q, p.tmap_kv,
-                          static_cast<uint16_t*>(out), p.seq, p.dim, p.heads, n_items, scale_log2e);
-    }
-    dim3 grid((p.seq + 127) / 128, p.heads, n);
-    return launch_pdl(attention_kernel, grid, dim3(ATT_THREADS), ATT_SMEM, s, p.tmap_q, p.tmap_kv,
-                      static_cast<uint16_t*>(out), p.seq, p.dim, scale_log2e);
+    int sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int n_items = n * p.heads * 2;            // two 128-query tiles per (image, head)
+    const int grid = n_items < sms ? n_items : sms;
+    return launch_pdl(attention_persistent_kernel, dim3(grid), dim3(A2_THREADS), A2_SMEM, s, p.tmap_q, p.tmap_kv,
+                      static_cast<uint16_t*>(out), p.seq, p.dim, p.heads, n_items, scale_log2e);
 }
 
 }  // namespace b2p

@@ -38,7 +38,9 @@ def _run_conv(n, hwc, oc, k, stride, pad, relu, residual, seed, pad_hi=None, sub
     got = out.float().cpu()
     rep.close()
     err = (got - ref).abs()
-    tol = 2.0 ** -7 * ref.abs() + 2e-2      # one bf16 ulp of the result + accumulation-order slack
+    # the result is fp32-accumulated and rounded ONCE to bf16: half a bf16 ulp (<= 2^-8 |ref|) plus accumulation-order
+    # noise near zero
+    tol = 2.0 ** -8 * ref.abs() + 2e-3
     bad = (err > tol).sum().item()
     print(f"conv n={n} hwc={hwc} oc={oc} k={k} s={stride} p={pad}: max_err={err.max().item():.4g} "
           f"max_ref={ref.abs().max().item():.4g} bad={bad}/{err.numel()}")
@@ -150,6 +152,9 @@ def test_conv_pair_fused(k1, n2, hw, n, cuda_device):
     e1, e2 = (outs[0] - ref1).abs(), (outs[1] - ref2).abs()
     print(f"pair k1={k1} n2={n2}: out1 max_err={e1.max().item():.4g} out2 max_err={e2.max().item():.4g}")
     assert not torch.isnan(outs[0]).any() and not torch.isnan(outs[1]).any()
+    # the residual operand is itself a bf16-rounded conv output (|idn| up to ~5): where the GPU and torch round it to
+    # different neighbours (fp32 accumulation order at a tie) the sum moves by one ulp OF THE OPERAND, 1.6e-2 at 2-4,
+    # whatever the size of the sum - hence the absolute term
     assert (e1 > 2.0 ** -7 * ref1.abs() + 2e-2).sum().item() == 0
     assert (e2 > 2.0 ** -6 * ref2.abs() + 3e-2).sum().item() == 0      # second conv sees a bf16-rounded input
 
@@ -183,7 +188,7 @@ def test_conv_with_folded_shortcut(c_main, c_sc, oc, hw_out, stride2, n, cuda_de
     ref = (F.conv2d(t2_ref, w3, b3) + F.conv2d(xin, wd, bd, stride=stride2)).relu().permute(0, 2, 3, 1)
     err = (out.float().cpu() - ref).abs()
     print(f"dual-source conv {c_main}+{c_sc}->{oc} s{stride2}: max_err={err.max().item():.4g}")
-    assert (err > 2.0 ** -7 * ref.abs() + 2e-2).sum().item() == 0
+    assert (err > 2.0 ** -8 * ref.abs() + 2e-3).sum().item() == 0
 
 
 def test_conv_sub_batched(cuda_device):
