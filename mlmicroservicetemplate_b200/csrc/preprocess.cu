@@ -22,6 +22,7 @@
 // the horizontal pass for output column ox (3 channels) and feeds BAND x 3 register accumulators
 // of the vertical pass, so the fp32 intermediate never leaves the SM.
 #include <cstdio>
+#include <cstdlib>
 #include <cuda_bf16.h>
 #include "kernels.h"
 #include "ptx.cuh"
@@ -31,7 +32,7 @@ namespace {
 
 constexpr int OUT = B2P_OUT_HW;      // 224
 constexpr int BAND = 8;              // output rows per CTA
-constexpr int THREADS = 256;         // 224 compute lanes + 32 that only help copying
+constexpr int THREADS = 256;         // widest CTA: 224 compute lanes + 32 that only help copying (narrower CTAs: 128 / 64)
 constexpr int RING = 2;              // raw source rows in flight per CTA (deeper rings were measured: no gain,
                                      // the kernel is issue-bound, and they cost occupancy on wide images)
 
@@ -82,6 +83,7 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait_pending() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 // Copies `nbytes` from global `g` into shared `buf + (g & 15)` so that 16-byte vectors line up.
+template <int NT>
 __device__ __forceinline__ void stage_row(uint8_t* buf, const uint8_t* g, int nbytes) {
     const int shift = static_cast<int>(reinterpret_cast<uintptr_t>(g) & 15u);
     uint8_t* dst = buf + shift;
@@ -89,9 +91,9 @@ __device__ __forceinline__ void stage_row(uint8_t* buf, const uint8_t* g, int nb
     head = head < nbytes ? head : nbytes;
     const int nvec = (nbytes - head) >> 4;
     const int tail0 = head + (nvec << 4);
-    for (int i = threadIdx.x; i < nvec; i += THREADS) cp_async_16(dst + head + (i << 4), g + head + (i << 4));
-    for (int i = threadIdx.x; i < head; i += THREADS) dst[i] = __ldg(g + i);
-    for (int i = tail0 + threadIdx.x; i < nbytes; i += THREADS) dst[i] = __ldg(g + i);
+    for (int i = threadIdx.x; i < nvec; i += NT) cp_async_16(dst + head + (i << 4), g + head + (i << 4));
+    for (int i = threadIdx.x; i < head; i += NT) dst[i] = __ldg(g + i);
+    for (int i = tail0 + threadIdx.x; i < nbytes; i += NT) dst[i] = __ldg(g + i);
 }
 
 // Packed fp32x2 arithmetic (sm_100): one instruction rounds two independent IEEE fp32 results exactly as
@@ -130,14 +132,14 @@ __device__ __forceinline__ void lds_pixel(uint32_t addr, f32x2& rg, f32x2& bx) {
     asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(rg), "=l"(bx) : "r"(addr));
 }
 
-template <bool OUT_F32>
-__global__ void __launch_bounds__(THREADS)
+template <bool OUT_F32, int NT>
+__global__ void __launch_bounds__(NT)
 preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict__ imgs, void* __restrict__ out,
                   int wh_taps, int wv_taps, int rowbuf_bytes, int frow_bytes, float one_f, int cols, int skip_identity) {
     extern __shared__ __align__(16) uint8_t smem[];
     const f32x2 one = pack2(one_f, one_f);
-    float* wh = reinterpret_cast<float*>(smem);                       // [wh_taps][OUT]
-    float* wv = wh + wh_taps * OUT;                                   // [BAND][wv_taps]
+    float* wh = reinterpret_cast<float*>(smem);                       // [wh_taps][cols]
+    float* wv = wh + wh_taps * cols;                                   // [BAND][wv_taps]
     int* vmeta = reinterpret_cast<int*>(wv + BAND * wv_taps);         // ymin[BAND], ysize[BAND]
     uint8_t* rowbuf = reinterpret_cast<uint8_t*>(vmeta + 2 * BAND);   // RING x rowbuf_bytes raw uint8 rows (16B aligned)
     float4* frow = reinterpret_cast<float4*>(rowbuf + RING * rowbuf_bytes);   // the current row as fp32 (R,G,B,0) pixels
@@ -167,11 +169,11 @@ preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict_
         float total = 0.f;
         for (int j = 0; j < xsize; ++j) {
             const float w = axis_raw_weight(g, center, xmin, j);
-            wh[j * OUT + tid] = w;
+            wh[j * cols + tid] = w;
             total = __fadd_rn(total, w);
         }
         if (total != 0.f)
-            for (int j = 0; j < xsize; ++j) wh[j * OUT + tid] = __fdiv_rn(wh[j * OUT + tid], total);
+            for (int j = 0; j < xsize; ++j) wh[j * cols + tid] = __fdiv_rn(wh[j * cols + tid], total);
     }
     // ---- vertical weights for the band's rows
     if (tid < BAND) {
@@ -209,7 +211,7 @@ preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict_
     // consumed, so the ~1 us global-memory latency is overlapped instead of paid once per row
 #pragma unroll
     for (int k = 0; k < RING; ++k) {
-        if (iy0 + k < iy1) stage_row(rowbuf + k * rowbuf_bytes, src + static_cast<size_t>(iy0 + k) * row_bytes, win_bytes);
+        if (iy0 + k < iy1) stage_row<NT>(rowbuf + k * rowbuf_bytes, src + static_cast<size_t>(iy0 + k) * row_bytes, win_bytes);
         cp_async_commit();
     }
 
@@ -220,13 +222,13 @@ preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict_
         {   // uint8 -> fp32 once per source sample (exact), all 256 threads
             const uint8_t* g = src + static_cast<size_t>(iy) * row_bytes;
             const uint8_t* raw = rowbuf + cur * rowbuf_bytes + (reinterpret_cast<uintptr_t>(g) & 15u);
-            for (int px = tid; px < win_px; px += THREADS)
+            for (int px = tid; px < win_px; px += NT)
                 frow[px] = make_float4(static_cast<float>(raw[3 * px]), static_cast<float>(raw[3 * px + 1]),
                                        static_cast<float>(raw[3 * px + 2]), 0.f);
         }
         __syncthreads();                     // frow complete, raw buffer `cur` free again
         if (iy + RING < iy1)
-            stage_row(rowbuf + cur * rowbuf_bytes, src + static_cast<size_t>(iy + RING) * row_bytes, win_bytes);
+            stage_row<NT>(rowbuf + cur * rowbuf_bytes, src + static_cast<size_t>(iy + RING) * row_bytes, win_bytes);
         cp_async_commit();
 
         if (active) {
@@ -239,7 +241,7 @@ preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict_
             for (; j <= hmain; j += 4) {        // hmain is a multiple of 4: the un-fused taps come in fours
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
-                    w = wh[(j + u) * OUT + tid];
+                    w = wh[(j + u) * cols + tid];
                     w2 = pack2(w, w);
                     lds_pixel(frow_base + static_cast<uint32_t>(j + u) * 16u, prg, pb);
                     hrg = add2(mul2(prg, w2), hrg, one);
@@ -247,7 +249,7 @@ preprocess_kernel(const uint8_t* __restrict__ slab, const b2p_image* __restrict_
                 }
             }
             for (; j < xsize; ++j) {
-                w = wh[j * OUT + tid];
+                w = wh[j * cols + tid];
                 w2 = pack2(w, w);
                 lds_pixel(frow_base + static_cast<uint32_t>(j) * 16u, prg, pb);
                 hrg = fma2(prg, w2, hrg);
@@ -505,10 +507,15 @@ cudaError_t launch_preprocess(const uint8_t* slab, const b2p_image* imgs_dev, co
         wh_taps = th > wh_taps ? th : wh_taps;
         wv_taps = tv > wv_taps ? tv : wv_taps;
     }
+    // Columns per CTA: 224 (one 256-thread CTA per band) whenever the staged window fits; very wide sources get
+    // 112 / 56 / ... columns on 128- / 64-thread CTAs.  B2P_K1_COLS forces a narrower value (A/B runs: narrower chunks
+    // raise occupancy but were measured 0-15 % slower, profiles/r02u_k1_ablation.txt).
+    static const int forced_cols = [] { const char* e = getenv("B2P_K1_COLS"); return e ? atoi(e) : 0; }();
     const int col_choices[6] = {224, 112, 56, 32, 16, 8};
     int cols = 0, rowbuf_bytes = 0, frow_bytes = 0;
     size_t smem = 0;
     for (int c : col_choices) {
+        if (forced_cols && c > forced_cols) continue;
         int max_win = 1;
         for (int i = 0; i < n; ++i) {
             const b2p_image& im = imgs_host[i];
@@ -522,26 +529,28 @@ cudaError_t launch_preprocess(const uint8_t* slab, const b2p_image* imgs_dev, co
         }
         rowbuf_bytes = ((max_win * 3 + 15) / 16) * 16 + 32;
         frow_bytes = max_win * 16 + 16;
-        smem = static_cast<size_t>(wh_taps) * OUT * 4 + static_cast<size_t>(BAND) * wv_taps * 4 + 2 * BAND * 4 +
+        smem = static_cast<size_t>(wh_taps) * c * 4 + static_cast<size_t>(BAND) * wv_taps * 4 + 2 * BAND * 4 +
                RING * static_cast<size_t>(rowbuf_bytes) + frow_bytes;
-        if (smem <= 200 * 1024) { cols = c; break; }
+        if (smem <= 200 * 1024) { cols = c; break; }      // widest chunk that fits (narrower ones measured 0-15 % slower)
     }
     if (cols == 0) return cudaErrorInvalidValue;     // not reachable for images below ~1.4 M pixels per row
     dim3 grid(OUT / BAND, n, OUT / cols);
-    cudaError_t e;
+    const int nt = cols > 112 ? 256 : (cols > 56 ? 128 : 64);
+    cudaError_t e = cudaSuccess;
+#define B2P_K1_LAUNCH(F32, NT)                                                                                          \
+    do {                                                                                                                \
+        e = cudaFuncSetAttribute(preprocess_kernel<F32, NT>, cudaFuncAttributeMaxDynamicSharedMemorySize,               \
+                                 static_cast<int>(smem));                                                               \
+        if (e != cudaSuccess) return e;                                                                                 \
+        preprocess_kernel<F32, NT><<<grid, NT, smem, s>>>(slab, imgs_dev, out, wh_taps, wv_taps, rowbuf_bytes,          \
+                                                          frow_bytes, 1.0f, cols, lut_path ? 1 : 0);                    \
+    } while (0)
     if (out_f32) {
-        e = cudaFuncSetAttribute(preprocess_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 static_cast<int>(smem));
-        if (e != cudaSuccess) return e;
-        preprocess_kernel<true><<<grid, THREADS, smem, s>>>(slab, imgs_dev, out, wh_taps, wv_taps, rowbuf_bytes, frow_bytes,
-                                                             1.0f, cols, lut_path ? 1 : 0);
+        if (nt == 256) B2P_K1_LAUNCH(true, 256); else if (nt == 128) B2P_K1_LAUNCH(true, 128); else B2P_K1_LAUNCH(true, 64);
     } else {
-        e = cudaFuncSetAttribute(preprocess_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 static_cast<int>(smem));
-        if (e != cudaSuccess) return e;
-        preprocess_kernel<false><<<grid, THREADS, smem, s>>>(slab, imgs_dev, out, wh_taps, wv_taps, rowbuf_bytes, frow_bytes,
-                                                              1.0f, cols, lut_path ? 1 : 0);
+        if (nt == 256) B2P_K1_LAUNCH(false, 256); else if (nt == 128) B2P_K1_LAUNCH(false, 128); else B2P_K1_LAUNCH(false, 64);
     }
+#undef B2P_K1_LAUNCH
     if (launches) *launches += 1;
     return cudaGetLastError();
 }
