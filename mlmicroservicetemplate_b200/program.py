@@ -266,6 +266,10 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
                 n1 = w3.shape[0]
                 can_pair = (fuse_pairs and isinstance(nxt, Bottleneck) and nxt.conv1.kernel_size == (1, 1)
                             and not fusable(nxt, (hwc2[0], hwc2[1], w3.shape[0]))     # a fused next block has its own conv1
+                            # a STRIDED folded shortcut stays out of the pair kernel: its gathered (stride-2 im2col) operand
+                            # loads starve the pair's two-stage ring - measured 170 us paired vs 73 + 40 us as conv3(+shortcut)
+                            # and a separate conv1 for ResNet-50's first 28x28 block (profiles/r02v_pair_shortcut_ab.txt)
+                            and not (shortcut is not None and shortcut[3] != 1)
                             and nxt.conv1.stride == (1, 1) and nxt.conv1.out_channels in (64, 128)
                             and n1 % 128 == 0 and w3.shape[1] in (64, 128) and tuple(blk.conv3.kernel_size) == (1, 1))
                 # (wider pairs - K1 >= 256 or N2 = 256, i.e. ResNet-50's stage 3 - were measured slower than the two
