@@ -22,7 +22,7 @@ Environment knobs (defaults in brackets):
     CHECKPOINT          path of a torch.save'd torchvision state_dict for MODEL (default: seeded random init)
     LABELS              text file with one class name per line (default: positional names)
     ENGINE_SOCKET       path of a GPU dispatcher's Unix socket (src/server/serve.py starts both): this process then
-                        builds no replica; uploads go to the dispatcher through a shared-memory ring of INGEST_SHM_MB [256]
+                        builds no replica; uploads go to the dispatcher through a shared-memory ring of INGEST_SHM_MB [64]
     DECODE [gpu]        gpu: uploads that are baseline JPEGs (b2p_jpeg_inspect) are decoded on the GPU, bit-exact
                         with Pillow; everything else (PNG, progressive / CMYK JPEG, ...) is decoded by Pillow
                         as in the reference.  host: every upload goes through Pillow.
@@ -66,7 +66,7 @@ def init() -> None:
             # Front-end process of a multi-process deployment (ingest.py): the replicas live in
             # the dispatcher process; this process parses uploads and hands their bytes over through shared memory.
             from ...ingest import RemoteEngine
-            engine = RemoteEngine(os.environ["ENGINE_SOCKET"], ring_bytes=int(os.getenv("INGEST_SHM_MB", "256")) << 20)
+            engine = RemoteEngine(os.environ["ENGINE_SOCKET"], ring_bytes=int(os.getenv("INGEST_SHM_MB", "64")) << 20)
             _state["engine"] = engine
             _state["decode"] = engine.info.get("decode", "gpu")
             _state["classes"] = list(engine.info["classes"])
