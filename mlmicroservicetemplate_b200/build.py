@@ -18,7 +18,7 @@ PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 LIB_DIR = PKG / "lib"
 LIB_PATH = LIB_DIR / "libb200predict.so"
-SOURCES = ["api.cu", "bottleneck56.cu", "conv3x3_c64.cu", "conv_gemm.cu", "conv_pair.cu", "head_static.cu", "jpeg.cu", "misc_kernels.cu", "preprocess.cu", "stem.cu", "vit.cu"]
+SOURCES = ["api.cu", "bottleneck56.cu", "conv3x3_c128.cu", "conv3x3_c64.cu", "conv_gemm.cu", "conv_pair.cu", "head_static.cu", "jpeg.cu", "misc_kernels.cu", "preprocess.cu", "stem.cu", "vit.cu"]
 HEADERS = [CSRC / "kernels.h", CSRC / "ptx.cuh", PKG.parent / "include" / "b200predict.h"]
 
 NVCC_FLAGS = [

@@ -25,6 +25,8 @@ struct OpPlan {
     Conv3x3Plan c3;       // valid for CONV ops taken by the patch-resident 3x3 kernel
     BneckPlan bneck;      // valid for BOTTLENECK
     bool use_c3 = false;
+    Conv3x3bPlan c3b;     // same idea for 28x28x128 -> 128
+    bool use_c3b = false;
     void* stem_image = nullptr;
     bool is_gemm = false;
     bool src_external = false;
@@ -214,6 +216,17 @@ int run_program(b2p_handle* h, const void* x, int n, void* out, cudaStream_t st,
                             }
                         }
                         e = conv3x3_c64_launch(p.c3, nb, o.relu, op_dir, h->num_sms, st);
+                        break;
+                    }
+                    if (p.use_c3b) {
+                        if (p.src_external || p.dst_external) {
+                            char eb[256] = "";
+                            if (!conv3x3_c128_plan_set(p.c3b, src, dst, nb, eb, sizeof eb)) {
+                                set_error(h, "%s", eb);
+                                return B2P_E_CUDA;
+                            }
+                        }
+                        e = conv3x3_c128_launch(p.c3b, nb, o.relu, op_dir, h->num_sms, st);
                         break;
                     }
                     if (p.src_external) {
@@ -477,6 +490,17 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
                         B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
                 }
             }
+            if (conv3x3_c128_supported(o) && h->blob_bytes[o.weight] == 128 * 9 * 128 * 2 && getenv("B2P_NO_C3B") == nullptr) {
+                // 28x28x128 3x3: the patch is fetched once as tiled boxes instead of nine im2col gathers
+                p.c3b.weight = h->blobs[o.weight];
+                p.c3b.bias = static_cast<const float*>(h->blobs[o.bias]);
+                p.use_c3b = true;
+                if (o.src != B2P_SLOT_INPUT && o.dst != B2P_SLOT_OUTPUT) {
+                    if (!h->slots[o.src] || !h->slots[o.dst]) B2P_FAIL(B2P_E_ARG, "op %d uses an empty slot", i);
+                    if (!conv3x3_c128_plan_set(p.c3b, h->slots[o.src], h->slots[o.dst], h->chunk, eb, sizeof eb))
+                        B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
+                }
+            }
             if (p.gemm.src2_c > 0) {
                 if (!h->slots[o.src2]) B2P_FAIL(B2P_E_ARG, "op %d reads an empty second source", i);
                 if (!gemm_plan_set_src2(p.gemm, h->slots[o.src2], h->chunk, eb, sizeof eb))
@@ -641,7 +665,7 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
         for (int i = 0; i < desc->n_ops && level > 0; ++i) {
             OpPlan& p = h->ops[i];
             const b2p_op& o = p.op;
-            if (!p.is_gemm || p.use_c3) continue;
+            if (!p.is_gemm || p.use_c3 || p.use_c3b) continue;
             if (o.res != B2P_SLOT_NONE && last_use(i, o.res)) p.gemm.pol_res = EVICT_FIRST;
             if (!p.gemm.im2col && o.src != o.res && last_use(i, o.src)) p.gemm.pol_a = EVICT_FIRST;
             if (level >= 2 && o.kind == B2P_OP_CONV &&

@@ -102,6 +102,17 @@ bool conv3x3_c64_plan_set(Conv3x3Plan& p, const void* src, void* dst, const void
                           size_t err_len);
 cudaError_t conv3x3_c64_launch(const Conv3x3Plan& p, int n, int relu, int reverse, int num_sms, cudaStream_t s);
 
+// ------------------------------------------------------------------ patch-resident 3x3 conv, 28x28x128 -> 128
+struct Conv3x3bPlan {
+    CUtensorMap tmap_in, tmap_w;
+    const void* weight = nullptr;        // packed [128][3][3][128] bf16 (device); each CTA of a pair keeps 64 rows resident
+    void* out = nullptr;                 // NHWC bf16, written with plain stores
+    const float* bias = nullptr;
+};
+bool conv3x3_c128_supported(const b2p_op& o);
+bool conv3x3_c128_plan_set(Conv3x3bPlan& p, const void* src, void* dst, int batch_cap, char* err, size_t err_len);
+cudaError_t conv3x3_c128_launch(const Conv3x3bPlan& p, int n, int relu, int reverse, int num_sms, cudaStream_t s);
+
 // ------------------------------------------------------------------ fused conv3(+res+ReLU) -> next conv1(+ReLU)
 struct PairPlan {
     CUtensorMap tmap_a, tmap_w3, tmap_res, tmap_out1, tmap_w1, tmap_out2, tmap_a2;

@@ -57,6 +57,9 @@ CONV_CASES = [
     (3, (56, 56, 64), 64, 3, 1, 1, True, True),           # same + residual (ResNet-18 BasicBlock conv2)
     (1, (56, 56, 64), 64, 3, 1, 1, False, False),
     (2, (28, 28, 64), 64, 3, 1, 1, True, False),          # 3x3 generic im2col path
+    (2, (28, 28, 128), 128, 3, 1, 1, True, False),        # 3x3, 28x28x128: patch-resident kernel (streamed weights)
+    (1, (28, 28, 128), 128, 3, 1, 1, False, False),
+    (45, (28, 28, 128), 128, 3, 1, 1, True, False),       # 315 tiles: every CTA wraps its patch / weight / TMEM rings
     (2, (56, 56, 128), 128, 3, 2, 1, True, False),        # 3x3 stride 2
     (2, (56, 56, 256), 512, 1, 2, 0, False, False),       # 1x1 stride 2 downsample
     (5, (7, 7, 512), 512, 3, 1, 1, True, True),           # tiny spatial, tiles span images, M tail
