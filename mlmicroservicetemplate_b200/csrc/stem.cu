@@ -13,10 +13,14 @@
 // K=16 MMAs per conv row accumulate the 4x4 window in TMEM; the 32 KB of weights (no-swizzle layout:
 // 8 x 16 B core matrices, SBO 128 B, LBO 1 KB) sit in shared memory for the lifetime of the CTA.
 //
-// Fused pooling: conv rows 2j-1, 2j, 2j+1 live in three TMEM accumulators; the epilogue takes the
-// vertical max in registers, applies bias+ReLU (both commute with max), rounds to bf16, exchanges
-// columns through shared memory for the horizontal 3-tap max and TMA-stores the pooled row
-// [56][64].  The 411 MB/256-image stem activation never reaches HBM.
+// Fused pooling: pooled row j needs conv rows 2j-1, 2j, 2j+1.  A CTA walks SEGMENTS of consecutive pooled rows of
+// one image and keeps every conv row in one of eight 64-column TMEM slots (a ring indexed by the CTA's running
+// conv-row count), so row 2j+1 is computed once and read by pooled rows j and j+1: two new conv rows per tile
+// instead of three (the kernel is bound by its N = 64 MMAs - 48 cycles each, the shared-memory read rate - so the
+// recomputed row was a third of its time).  Only the first tile of a segment computes three.  The epilogue takes
+// the vertical max in registers, applies bias+ReLU (both commute with max), rounds to bf16, exchanges columns
+// through shared memory for the horizontal 3-tap max and TMA-stores the pooled row [56][64].  The 411 MB/256-image
+// stem activation never reaches HBM.
 #include <atomic>
 #include <cstdio>
 #include <cuda_bf16.h>
@@ -41,8 +45,9 @@ struct StemCfg {
     static constexpr int PATCH_ROWS = ROWS + 3;
     static constexpr int PLANE_BYTES = PATCH_ROWS * PATCH_W * 16;
     static constexpr int STAGE_BYTES = 2 * PLANE_BYTES;
-    static constexpr int ACC_COLS = POOL ? 256 : 64;            // TMEM columns per accumulator set (3 x 64 -> 256)
-    static constexpr int TMEM_COLS = 2 * ACC_COLS;              // double buffered: 512 / 128
+    static constexpr int SLOTS = POOL ? 8 : 2;                  // 64-column TMEM slots, one conv row each
+    static constexpr int TMEM_COLS = SLOTS * OUT_C;             // 512 / 128
+    static constexpr int RING = POOL ? 3 : 2;                   // tiles between the MMA warp and the epilogue
     static constexpr int COLBUF_BYTES = POOL ? 128 * 128 : 0;   // conv columns x 64 ch bf16, swizzled (per group)
     static constexpr int OUTBUF_BYTES = 128 * 128;              // staging for the TMA store (per group)
     static constexpr int OUT_ROWS = POOL ? 56 : 112;            // rows of the store box
@@ -82,9 +87,10 @@ __device__ __forceinline__ uint32_t bf16x2_max(uint32_t a, uint32_t b) {
 template <bool POOL>
 __global__ void __launch_bounds__(STEM_THREADS, 1)
 stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__ CUtensorMap tmap_out,
-            const uint8_t* __restrict__ w_image, const float* __restrict__ bias, int n_imgs, int relu) {
+            const uint8_t* __restrict__ w_image, const float* __restrict__ bias, int n_imgs, int relu, int seg_len) {
     using C = StemCfg<POOL>;
     constexpr int ROWS = C::ROWS;
+    constexpr int RING = C::RING;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                                ~static_cast<uintptr_t>(1023));
@@ -96,13 +102,24 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem_out + 2 * C::OUTBUF_BYTES);
     uint64_t* empty_bar = full_bar + STEM_STAGES;
     uint64_t* tmem_full_bar = empty_bar + STEM_STAGES;
-    uint64_t* tmem_empty_bar = tmem_full_bar + 2;
-    uint64_t* w_bar = tmem_empty_bar + 2;
+    uint64_t* tmem_empty_bar = tmem_full_bar + RING;
+    uint64_t* w_bar = tmem_empty_bar + RING;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_bar + 1);
 
     const int warp_idx = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
     const int tiles_per_img = POOL ? 56 : 112;
-    const int total_tiles = n_imgs * tiles_per_img;
+    // a CTA's k-th tile: segment (k / seg_len) of its round-robin share, row (k % seg_len) of that segment
+    const int segs_per_img = tiles_per_img / seg_len;
+    const int total_segs = n_imgs * segs_per_img;
+    auto tile_of = [&](int k, int& img, int& t, bool& first) -> bool {
+        const int si = k / seg_len, within = k - si * seg_len;
+        const int seg = static_cast<int>(blockIdx.x) + si * static_cast<int>(gridDim.x);
+        if (seg >= total_segs) return false;
+        img = seg / segs_per_img;
+        t = (seg - img * segs_per_img) * seg_len + within;
+        first = within == 0;
+        return true;
+    };
 
     if (warp_idx == 0) {
         if (elect_one()) {
@@ -115,7 +132,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
                 mbar_init(&full_bar[i], 1);
                 mbar_init(&empty_bar[i], 1);
             }
-            for (int i = 0; i < 2; ++i) {
+            for (int i = 0; i < RING; ++i) {
                 mbar_init(&tmem_full_bar[i], 1);
                 mbar_init(&tmem_empty_bar[i], 4);
             }
@@ -140,11 +157,11 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
             bulk_load_1d(smem_w, w_image, W_IMAGE_BYTES, w_bar);
             int stage = 0;
             uint32_t phase = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                const int img = tile / tiles_per_img;
-                const int t = tile - img * tiles_per_img;
-                // first conv row of the tile, then the first s2d row its 4x4 window touches (pad 2 before)
-                const int conv_row0 = POOL ? 2 * t - 1 : t;
+            int img, t;
+            bool first;
+            for (int k = 0; tile_of(k, img, t, first); ++k) {
+                // first NEW conv row of the tile, then the first s2d row its 4x4 window touches (pad 2 before)
+                const int conv_row0 = POOL ? (first ? 2 * t - 1 : 2 * t) : t;
                 const int in_row0 = conv_row0 - 2;
                 mbar_wait(&empty_bar[stage], phase ^ 1u);
                 mbar_arrive_expect_tx(&full_bar[stage], C::STAGE_BYTES);
@@ -161,16 +178,24 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
             const uint32_t w_addr = smem_u32(smem_w);
             int stage = 0;
             uint32_t phase = 0;
-            int acc = 0;
-            uint32_t acc_phase = 0;
-            for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u);
+            uint32_t crow = 0;                                 // conv rows this CTA has computed so far
+            // The slots written by tile k held rows that tiles <= k - dist read: with two new rows per tile (three at
+            // a segment start, segments >= 2 tiles) any three consecutive tiles keep at most 8 rows alive, so the
+            // epilogue may lag three tiles; one-tile segments (3 rows each) and the un-pooled variant (2 slots): two.
+            const int dist = (POOL && seg_len > 1) ? 3 : 2;
+            int img, t;
+            bool first;
+            for (int k = 0; tile_of(k, img, t, first); ++k) {
+                const int wk = k - dist;
+                if (wk >= 0) mbar_wait(&tmem_empty_bar[wk % RING], static_cast<uint32_t>((wk / RING) & 1));
                 mbar_wait(&full_bar[stage], phase);
                 tc_fence_after();
                 const uint32_t patch = smem_u32(smem_patch + stage * C::STAGE_BYTES);
+                const int nrows = POOL ? (first ? 3 : 2) : 1;
 #pragma unroll
                 for (int ri = 0; ri < ROWS; ++ri) {
-                    const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * C::ACC_COLS + ri * OUT_C);
+                    if (ri >= nrows) break;
+                    const uint32_t d_tmem = tmem_base + ((crow + static_cast<uint32_t>(ri)) & (C::SLOTS - 1)) * OUT_C;
 #pragma unroll
                     for (int a = 0; a < 4; ++a) {
 #pragma unroll
@@ -184,10 +209,10 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
                         }
                     }
                 }
+                crow += static_cast<uint32_t>(nrows);
                 umma_commit(&empty_bar[stage]);
-                umma_commit(&tmem_full_bar[acc]);
+                umma_commit(&tmem_full_bar[k % RING]);
                 if (++stage == STEM_STAGES) { stage = 0; phase ^= 1u; }
-                if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
             }
         }
     } else {
@@ -203,17 +228,19 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
         smem_col += group * C::COLBUF_BYTES;
         smem_out += group * C::OUTBUF_BYTES;
         const uint32_t swz = static_cast<uint32_t>(q & 7);
-        const int acc = group;
-        uint32_t acc_phase = 0;
-        int tile_iter = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tile_iter) {
-            if ((tile_iter & 1) != group) continue;
-            const int img = tile / tiles_per_img;
-            const int t = tile - img * tiles_per_img;
-            mbar_wait(&tmem_full_bar[acc], acc_phase);
+        uint32_t crow = 0;
+        int img, t;
+        bool first;
+        for (int k = 0; tile_of(k, img, t, first); ++k) {
+            const int nrows = POOL ? (first ? 3 : 2) : 1;
+            // TMEM slots of the tile's conv rows: the new ones, preceded by the previous tile's last row
+            const uint32_t row0 = POOL ? (first ? crow : crow - 1u) : crow;
+            crow += static_cast<uint32_t>(nrows);
+            if ((k & 1) != group) continue;
+            const int my_ring = k % RING;
+            mbar_wait(&tmem_full_bar[my_ring], static_cast<uint32_t>((k / RING) & 1));
             tc_fence_after();
-            const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) +
-                                    static_cast<uint32_t>(acc * C::ACC_COLS);
+            const uint32_t t_lane = tmem_base + (static_cast<uint32_t>(quad * 32) << 16);
             uint4 packed[8];
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
@@ -221,7 +248,8 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
                 // issue the TMEM loads of all conv rows first, wait once (the loads overlap each other)
                 uint32_t v[ROWS][32];
 #pragma unroll
-                for (int ri = 0; ri < ROWS; ++ri) tmem_ld_32x32(t_addr + static_cast<uint32_t>(ri * OUT_C + h * 32), v[ri]);
+                for (int ri = 0; ri < ROWS; ++ri)
+                    tmem_ld_32x32(t_lane + ((row0 + static_cast<uint32_t>(ri)) & (C::SLOTS - 1)) * OUT_C + static_cast<uint32_t>(h * 32), v[ri]);
                 tmem_ld_wait();
 #pragma unroll
                 for (int ri = 0; ri < ROWS; ++ri) {
@@ -256,8 +284,7 @@ stem_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__
             // accumulators are in registers now: give the TMEM stage back to the MMA warp
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(&tmem_empty_bar[acc]);
-            acc_phase ^= 1u;
+            if (lane == 0) mbar_arrive(&tmem_empty_bar[my_ring]);
 
             // the previous tile's TMA store must have finished reading the staging buffer
             if (leader) tma_store_wait_read<0>();
@@ -364,7 +391,19 @@ bool stem_plan_init(StemPlan& p, const void* src_s2d, void* dst, int batch_cap, 
 }
 
 cudaError_t stem_plan_launch(const StemPlan& p, int n, int relu, int num_sms, cudaStream_t stream) {
-    const int total = n * (p.pool ? 56 : 112);
+    // Segment length (pooled rows a CTA walks inside one image): longer segments recompute fewer conv rows
+    // (2L + 1 per L pooled rows) but quantise worse over the SMs; small batches keep one row per CTA.
+    int seg_len = 1;
+    if (p.pool && n > 0) {
+        double best = 0.0;
+        for (int len : {1, 2, 4, 7, 14, 28}) {
+            const int segs = n * (56 / len);
+            const int rounds = (segs + num_sms - 1) / num_sms;
+            const double cost = static_cast<double>(rounds) * (2 * len + 1);     // conv rows on the busiest SM
+            if (best == 0.0 || cost < best) { best = cost; seg_len = len; }
+        }
+    }
+    const int total = n * ((p.pool ? 56 : 112) / seg_len);
     const int grid = total < num_sms ? total : num_sms;
     static std::atomic<bool> attr_set[64][2];   // zero-initialised; replicas of different GPUs launch from different threads
     int dev = 0;
@@ -378,7 +417,7 @@ cudaError_t stem_plan_launch(const StemPlan& p, int n, int relu, int num_sms, cu
             attr_set[dev][1].store(true, std::memory_order_release);
         }
         return launch_pdl(stem_kernel<true>, dim3(grid), dim3(STEM_THREADS), StemCfg<true>::SMEM_BYTES, stream, p.tmap_in,
-                          p.tmap_out, p.w_image, p.bias, n, relu);
+                          p.tmap_out, p.w_image, p.bias, n, relu, seg_len);
     } else {
         if (!attr_set[dev][0].load(std::memory_order_acquire)) {
             cudaError_t e = cudaFuncSetAttribute(stem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -387,7 +426,7 @@ cudaError_t stem_plan_launch(const StemPlan& p, int n, int relu, int num_sms, cu
             attr_set[dev][0].store(true, std::memory_order_release);
         }
         return launch_pdl(stem_kernel<false>, dim3(grid), dim3(STEM_THREADS), StemCfg<false>::SMEM_BYTES, stream, p.tmap_in,
-                          p.tmap_out, p.w_image, p.bias, n, relu);
+                          p.tmap_out, p.w_image, p.bias, n, relu, 1);
     }
     return cudaGetLastError();
 }
