@@ -60,6 +60,118 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int iters, int a_stride_ti
     }
 }
 
+// The same MMA stream (single CTA, N = 128 or pair N = 256 style operand footprints) while eight other warps of the CTA
+// move `side_bytes_per_mma` bytes per MMA slot through (1) st.shared + ld.shared, (2) st.global (128 B per thread,
+// one line each, like a row-per-thread epilogue), (3) ld.global.nc of lines that hit the L2, (4) TMA bulk loads
+// global -> shared.  Shows which epilogue / refill paths steal the tensor pipe's shared-memory reads.
+template <int N>
+__global__ void __launch_bounds__(384, 1) contend_kernel(int iters, int mode, int side_iters, uint4* gbuf, long long* out) {
+    extern __shared__ uint8_t raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(raw) + 1023) & ~uintptr_t(1023));
+    __shared__ uint64_t bar, tbar;
+    __shared__ uint32_t slot;
+    for (int i = threadIdx.x; i < 192 * 1024 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+    if (threadIdx.x < 32) {
+        if (threadIdx.x == 0) { mbar_init(&bar, 1); mbar_init(&tbar, 1); fence_mbar_init(); }
+        __syncwarp();
+        tmem_alloc(&slot, 256);
+        tmem_relinquish();
+    }
+    fence_proxy_async_smem();
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tm = slot;
+    const int warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) {
+        constexpr uint32_t idesc = umma_idesc_bf16(128, N);
+        const uint32_t a0 = smem_u32(smem), b0 = smem_u32(smem + 64 * 1024);
+        uint64_t ad[4], bd[2];
+        for (int i = 0; i < 4; ++i) ad[i] = umma_desc_kmajor(a0 + static_cast<uint32_t>(i * 16384), 128);
+        for (int i = 0; i < 2; ++i) bd[i] = umma_desc_kmajor(b0 + static_cast<uint32_t>(i * 32768), 128);
+        const long long t0 = clock64();
+        for (int it = 0; it < iters; it += 4) {
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_bf16(tm, ad[u] + 2 * k, bd[u & 1] + 2 * k, idesc, 1u);
+        }
+        umma_commit(&bar);
+        mbar_wait(&bar, 0);
+        out[blockIdx.x] = clock64() - t0;
+    } else if (warp >= 4 && mode > 0) {
+        // side traffic: thread-private 128-byte rows
+        const int tid = threadIdx.x - 128;                     // 0..255
+        uint8_t* sside = smem + 128 * 1024;                    // 32 KB scratch for modes 1 / 4
+        uint4* grow = gbuf + (static_cast<size_t>(blockIdx.x) * 256 + tid) * 8;      // 128 B per thread per sweep
+        const size_t sweep = static_cast<size_t>(gridDim.x) * 256 * 8;               // uint4 per sweep of the grid
+        uint4 acc4 = make_uint4(tid, 1, 2, 3);
+        const long long s0 = clock64();
+        for (int it = 0; it < side_iters; ++it) {
+            if (mode == 1) {
+                const uint32_t base = smem_u32(sside) + static_cast<uint32_t>(tid * 128);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) st_shared_v4(base + ((static_cast<uint32_t>(j) ^ (tid & 7)) << 4), acc4);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { const uint4 r = ld_shared_v4(base + ((static_cast<uint32_t>(j) ^ (tid & 7)) << 4)); acc4.x ^= r.y; }
+            } else if (mode == 2) {
+                uint4* dstp = grow + (it & 7) * sweep;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) st_v4(dstp + j, acc4);
+            } else if (mode == 3) {
+                const uint4* srcp = grow + (it & 7) * sweep;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) { const uint4 r = ld_nc_v4(srcp + j); acc4.x ^= r.y; }
+            } else if (mode == 4) {
+                if (tid == 0) {                                 // one 32 KB bulk copy global -> shared per iteration
+                    mbar_arrive_expect_tx(&tbar, 32768);
+                    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                                     smem_u32(sside)), "l"(gbuf + (static_cast<size_t>(blockIdx.x) * 8 + (it & 7)) * 2048), "r"(32768u),
+                                 "r"(smem_u32(&tbar)) : "memory");
+                    mbar_wait(&tbar, static_cast<uint32_t>(it & 1));
+                }
+            }
+        }
+        if (tid == 0) out[gridDim.x + blockIdx.x] = clock64() - s0;
+        if (acc4.x == 0x12345678u) out[2 * gridDim.x + threadIdx.x] = acc4.x;   // keep the loads alive
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        tc_fence_after();
+        tmem_dealloc(tm, 256);
+    }
+}
+
+template <int N>
+void run_contend(int sms, int iters, int mode, int side_iters, const char* what) {
+    auto k = contend_kernel<N>;
+    const int smem = 193 * 1024 + 1024;
+    cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    long long* d;
+    cudaMalloc(&d, sizeof(long long) * (2 * sms + 512));
+    uint4* g;
+    const size_t gbytes = static_cast<size_t>(sms) * 256 * 128 * 8;   // 8 sweeps of 128 B per side thread: 38 MB, L2 resident
+    cudaMalloc(&g, gbytes);
+    cudaMemset(g, 1, gbytes);
+    for (int rep = 0; rep < 2; ++rep) {
+        k<<<sms, 384, smem>>>(iters, mode, side_iters, g, d);
+        cudaError_t e = cudaDeviceSynchronize();
+        if (e != cudaSuccess) { printf("contend: %s\n", cudaGetErrorString(e)); return; }
+    }
+    long long h[512] = {0};
+    cudaMemcpy(h, d, sizeof(long long) * 2 * sms, cudaMemcpyDeviceToHost);
+    long long mx = 0, smx = 1;
+    for (int i = 0; i < sms; ++i) mx = h[i] > mx ? h[i] : mx;
+    for (int i = 0; i < sms; ++i) smx = h[sms + i] > smx ? h[sms + i] : smx;
+    const double total = static_cast<double>(mx);
+    const double side_bytes = mode == 4 ? 32768.0 * side_iters : (mode == 1 ? 2.0 : 1.0) * 256 * 128.0 * side_iters;
+    printf("single M=128 N=%3d + %-34s: %6.1f cycles per MMA over %7.0f cycles; side traffic ran %7.0f cycles at %5.1f B/clk/SM\n", N, what,
+           total / (4.0 * iters), total, mode ? static_cast<double>(smx) : 0.0, mode ? side_bytes / static_cast<double>(smx) : 0.0);
+    cudaFree(d);
+    cudaFree(g);
+}
+
 template <int N, bool PAIR>
 void run(int sms, int iters, int shift = 0) {
     auto k = rate_kernel<N, PAIR>;
@@ -115,5 +227,15 @@ int main() {
     for (int shift : {1, 2, 8}) run<64, false>(sms, iters, shift);
     for (int shift : {1, 2}) run<128, false>(sms, iters, shift);
     run<256, true>(sms, iters);
+    // side traffic sized to roughly 32-64 B/clk if it ran unhindered for the MMA stream's duration
+    for (int n : {128, 256}) {
+        const int side = n == 128 ? 1500 : 3000;
+        auto go = [&](int mode, int si, const char* w) { if (n == 128) run_contend<128>(sms, iters, mode, si, w); else run_contend<256>(sms, iters, mode, si, w); };
+        go(0, 0, "nothing");
+        go(1, side, "st.shared + ld.shared rows");
+        go(2, side * 2, "st.global rows (128 B / thread)");
+        go(3, side * 2, "ld.global.nc rows (L2 hits)");
+        go(4, side * 2, "bulk copy global->shared 32 KB");
+    }
     return 0;
 }
