@@ -56,6 +56,15 @@ __device__ __forceinline__ void tma_load_4d_tiled(const CUtensorMap* m, uint64_t
 // WRONG results (tests/test_gpu_layers.py caught it), leaving it 0 is bit-correct.
 __device__ __forceinline__ uint64_t desc_sw128_rowshift(uint32_t smem_addr) { return umma_desc_kmajor(smem_addr, 128); }
 
+#ifdef C3_TRACE
+__device__ long long g_c3_trace[256][8];
+#define C3_T0(v) const long long v = clock64()
+#define C3_ACC(slot, v) g_acc[slot] += clock64() - (v)
+#else
+#define C3_T0(v)
+#define C3_ACC(slot, v)
+#endif
+
 template <bool HAS_RES>
 __global__ void __launch_bounds__(C3_THREADS, 1)
 conv3x3_c64_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_constant__ CUtensorMap tmap_out,
@@ -151,9 +160,13 @@ conv3x3_c64_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_con
             uint32_t phase = 0;
             int acc = 0;
             uint32_t acc_phase = 0;
+#ifdef C3_TRACE
+            long long g_acc[4] = {0, 0, 0, 0};
+            C3_T0(t_all);
+#endif
             for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-                mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u);
-                mbar_wait(&full_bar[stage], phase);
+                { C3_T0(tw); mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1u); C3_ACC(0, tw); }
+                { C3_T0(tw); mbar_wait(&full_bar[stage], phase); C3_ACC(1, tw); }
                 tc_fence_after();
                 const uint32_t patch = smem_u32(smem_patch + stage * STAGE_BYTES);
                 const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(acc * CH);
@@ -174,7 +187,14 @@ conv3x3_c64_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_con
                 umma_commit(&tmem_full_bar[acc]);
                 if (++stage == STAGES) { stage = 0; phase ^= 1u; }
                 if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+#ifdef C3_TRACE
+                ++g_acc[2];
+#endif
             }
+#ifdef C3_TRACE
+            g_acc[3] = clock64() - t_all;
+            for (int i = 0; i < 4; ++i) g_c3_trace[blockIdx.x][i] = g_acc[i];
+#endif
         }
     } else {
         // ========================================================================= epilogue (group g <-> TMEM stage g)
@@ -195,7 +215,13 @@ conv3x3_c64_kernel(const __grid_constant__ CUtensorMap tmap_in, const __grid_con
             const int tt = reverse ? total_tiles - 1 - tile : tile;
             const int img = tt / tiles_per_img;
             const int t = tt - img * tiles_per_img;
+#ifdef C3_TRACE
+            const long long tw_full = clock64();
+#endif
             mbar_wait(&tmem_full_bar[acc], acc_phase);
+#ifdef C3_TRACE
+            if (threadIdx.x == 64 || threadIdx.x == 192) g_c3_trace[blockIdx.x][4 + group] += clock64() - tw_full;
+#endif
             tc_fence_after();
             if (HAS_RES) mbar_wait(&res_full_bar[acc], acc_phase);
             const uint32_t t_addr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + static_cast<uint32_t>(acc * CH);
