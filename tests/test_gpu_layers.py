@@ -79,8 +79,11 @@ def test_conv_stem_s2d_shape(cuda_device):
     _run_conv(2, (112, 112, 16), 64, 4, 1, 2, True, False, seed=7, pad_hi=1)
 
 
-@pytest.mark.parametrize("pool", [False, True], ids=["conv", "conv+maxpool"])
-@pytest.mark.parametrize("n", [1, 3])
+# Batch sizes for the pooled variant pick every segment length of the launcher's cost model on a 148-SM part
+# (1, 2, 4, 7, 14 and 28 pooled rows per segment for n = 1, 3, 8, 18, 37 and 74): the TMEM slot ring wraps differently
+# in each.
+@pytest.mark.parametrize("pool,n", [(False, 1), (False, 3), (True, 1), (True, 3), (True, 8), (True, 18), (True, 37), (True, 74)],
+                         ids=lambda v: f"pool{int(v)}" if isinstance(v, bool) else f"n{v}")
 def test_stem_dedicated_kernel(pool, n, cuda_device):
     """OP_STEM_CONV: 4x4/pad(2,1) conv over the s2d image + bias + ReLU (+ fused 3x3/s2/p1 max pool)."""
     from mlmicroservicetemplate_b200 import backend as B, program as P
