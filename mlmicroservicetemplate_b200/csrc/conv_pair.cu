@@ -14,8 +14,14 @@
 // each).  TMEM: two 128-column accumulators for GEMM1 (double buffered) + N2 columns for GEMM2.
 // Warps: 0 = TMA producer (A, W3), 1 = TMEM owner + MMA issuer (both GEMMs), 2 = loader for the
 // residual chunks and W1 tiles, 3 = idle, 4..7 / 8..11 = two epilogue groups (left / right 64 columns of a sub-tile).
+//
+// WRES variant (56x56 stage: N1 = 256, N2 = 64, K <= 128): both weight matrices - 64-96 KB - are loaded ONCE per CTA and
+// stay in shared memory; the operand ring then carries only the 16 KB A tiles.  These kernels run at the L2's
+// throughput (profiles/r02zb_l2_smem_bounds.txt) and the weights were 64-96 KB of the ~240 KB every 128-pixel tile
+// pulled through it.
 #include <atomic>
 #include <cstdio>
+#include <cstdlib>
 #include <cudaTypedefs.h>
 #include "kernels.h"
 #include "ptx.cuh"
@@ -46,7 +52,9 @@ struct PairArgs {
     const float* bias2;   // [N2]
 };
 
-template <int N2>
+constexpr int WRES_A_STAGES = 3;         // WRES: A-only operand ring
+
+template <int N2, bool WRES>
 __global__ void __launch_bounds__(PAIR_THREADS, 1)
 conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w3,
                  const __grid_constant__ CUtensorMap tmap_res, const __grid_constant__ CUtensorMap tmap_out1,
@@ -60,15 +68,19 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-    uint8_t* smem_g1 = smem;                                           // G1_STAGES x (A | W3)
-    uint8_t* smem_stg = smem_g1 + G1_STAGES * G1_STAGE_BYTES;          // STG_BUFS staging / A2 tiles
+    static_assert(!WRES || N2 == 64, "resident weights: the 64-channel conv1 only");
+    const int kblocks = args.k1_blocks + args.k2_blocks;
+    uint8_t* smem_g1 = smem;                                           // G1_STAGES x (A | W3);  WRES: WRES_A_STAGES x A
+    uint8_t* smem_stg = smem_g1 + (WRES ? WRES_A_STAGES * TILE16K : G1_STAGES * G1_STAGE_BYTES);   // STG_BUFS staging / A2 tiles
     uint8_t* smem_stg2 = smem_stg + STG_BUFS * TILE16K;                // staging for out2
     uint8_t* smem_res = smem_stg2 + TILE16K;
-    uint8_t* smem_w2 = smem_res + RES_BUFS * TILE16K;
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem_w2 + W2_BUFS * TILE16K);
-    uint64_t* full_bar = bars;                          // [G1_STAGES]
-    uint64_t* empty_bar = full_bar + G1_STAGES;
-    uint64_t* acc1_full = empty_bar + G1_STAGES;        // [2]
+    uint8_t* smem_w2 = smem_res + ((WRES && !args.has_res) ? 0 : RES_BUFS * TILE16K);   // W1 ring;  WRES: all of W1 (32 KB)
+    uint8_t* smem_w3 = smem_w2 + 2 * TILE16K;                          // WRES only: n1_tiles x kblocks tiles of W3
+    uint64_t* bars = reinterpret_cast<uint64_t*>(WRES ? smem_w3 + args.n1_tiles * kblocks * TILE16K : smem_w2 + W2_BUFS * TILE16K);
+    constexpr int RING = WRES ? WRES_A_STAGES : G1_STAGES;
+    uint64_t* full_bar = bars;                          // [RING]
+    uint64_t* empty_bar = full_bar + RING;
+    uint64_t* acc1_full = empty_bar + RING;             // [2]
     uint64_t* acc1_empty = acc1_full + 2;
     uint64_t* res_full = acc1_empty + 2;                // [RES_BUFS]
     uint64_t* res_empty = res_full + RES_BUFS;
@@ -78,7 +90,9 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     uint64_t* a2_free = a2_full + STG_BUFS;             // [STG_BUFS] MMA -> epilogue: GEMM2 finished reading
     uint64_t* acc2_full = a2_free + STG_BUFS;           // [1]
     uint64_t* acc2_empty = acc2_full + 1;               // [1]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc2_empty + 1);
+    uint64_t* w3_bar = acc2_empty + 1;                  // WRES: resident W3 / W1 have landed
+    uint64_t* w1_bar = w3_bar + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w1_bar + 1);
 
     const int warp_idx = __shfl_sync(0xffffffffu, static_cast<int>(threadIdx.x >> 5), 0);
 
@@ -89,13 +103,15 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
     } else if (warp_idx == 1) {
         if (elect_one()) {
-            for (int i = 0; i < G1_STAGES; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
+            for (int i = 0; i < RING; ++i) { mbar_init(&full_bar[i], 1); mbar_init(&empty_bar[i], 1); }
             for (int i = 0; i < 2; ++i) { mbar_init(&acc1_full[i], 1); mbar_init(&acc1_empty[i], 8); }
             for (int i = 0; i < RES_BUFS; ++i) { mbar_init(&res_full[i], 1); mbar_init(&res_empty[i], 4); }
             for (int i = 0; i < W2_BUFS; ++i) { mbar_init(&w2_full[i], 1); mbar_init(&w2_empty[i], 1); }
             for (int i = 0; i < STG_BUFS; ++i) { mbar_init(&a2_full[i], 1); mbar_init(&a2_free[i], 1); }
             mbar_init(acc2_full, 1);
             mbar_init(acc2_empty, 4);
+            mbar_init(w3_bar, 1);
+            mbar_init(w1_bar, 1);
             fence_mbar_init();
         }
         __syncwarp();
@@ -117,6 +133,12 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             int stage = 0;
             uint32_t phase = 0;
             const int pq = args.out_h * args.out_w;
+            if (WRES) {
+                mbar_arrive_expect_tx(w3_bar, static_cast<uint32_t>(args.n1_tiles * kblocks * TILE16K));
+                for (int nt = 0; nt < args.n1_tiles; ++nt)
+                    for (int kb = 0; kb < kblocks; ++kb)
+                        tma_load_2d_hint(&tmap_w3, w3_bar, smem_w3 + (nt * kblocks + kb) * TILE16K, kb * 64, nt * BN1, L2_EVICT_LAST);
+            }
             for (int t = blockIdx.x; t < args.m_tiles; t += gridDim.x) {
                 const int m0 = (args.reverse ? args.m_tiles - 1 - t : t) * BM;
                 int img = 0, base_w2 = 0, base_h2 = 0;
@@ -130,15 +152,15 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 for (int nt = 0; nt < args.n1_tiles; ++nt) {
                     for (int kb = 0; kb < args.k1_blocks + args.k2_blocks; ++kb) {
                         mbar_wait(&empty_bar[stage], phase ^ 1u);
-                        mbar_arrive_expect_tx(&full_bar[stage], G1_STAGE_BYTES);
-                        uint8_t* dst = smem_g1 + stage * G1_STAGE_BYTES;
+                        mbar_arrive_expect_tx(&full_bar[stage], WRES ? TILE16K : G1_STAGE_BYTES);
+                        uint8_t* dst = smem_g1 + stage * (WRES ? TILE16K : G1_STAGE_BYTES);
                         if (kb < args.k1_blocks)
                             tma_load_2d(&tmap_a, &full_bar[stage], dst, kb * 64, m0);
                         else
                             tma_load_im2col_4d(&tmap_a2, &full_bar[stage], dst, (kb - args.k1_blocks) * 64, base_w2, base_h2,
                                                img, 0, 0);
-                        tma_load_2d(&tmap_w3, &full_bar[stage], dst + TILE16K, kb * 64, nt * BN1);
-                        if (++stage == G1_STAGES) { stage = 0; phase ^= 1u; }
+                        if (!WRES) tma_load_2d(&tmap_w3, &full_bar[stage], dst + TILE16K, kb * 64, nt * BN1);
+                        if (++stage == RING) { stage = 0; phase ^= 1u; }
                     }
                 }
             }
@@ -170,22 +192,30 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     const uint64_t a_desc = umma_desc_kmajor(smem_u32(smem_stg + sb * TILE16K), 128);
 #pragma unroll
                     for (int u = 0; u < W2_UNITS; ++u) {
-                        mbar_wait(&w2_full[wb], wb_phase);
+                        if (!WRES) mbar_wait(&w2_full[wb], wb_phase);
                         tc_fence_after();
-                        const uint64_t b_desc = umma_desc_kmajor(smem_u32(smem_w2 + wb * TILE16K), 128);
+                        // WRES: chunk q of out1 = K block q of GEMM2, its [64 x 64] weight tile lies at q * 8 KB
+                        const uint64_t b_desc = umma_desc_kmajor(WRES ? smem_u32(smem_w2 + q * W2_UNIT_BYTES) : smem_u32(smem_w2 + wb * TILE16K), 128);
                         const uint32_t d = tmem_base + ACC2_COL + static_cast<uint32_t>(u * 128);
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
                             umma_bf16(d, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k), idesc2,
                                       static_cast<uint32_t>((q | k) != 0));
-                        umma_commit(&w2_empty[wb]);
-                        if (++wb == W2_BUFS) { wb = 0; wb_phase ^= 1u; }
+                        if (!WRES) {
+                            umma_commit(&w2_empty[wb]);
+                            if (++wb == W2_BUFS) { wb = 0; wb_phase ^= 1u; }
+                        }
                     }
                     umma_commit(&a2_free[sb]);
                     if (++sb == STG_BUFS) { sb = 0; sb_phase ^= 1u; }
                 }
             };
 
+            if (WRES) {
+                mbar_wait(w3_bar, 0);
+                mbar_wait(w1_bar, 0);
+                tc_fence_after();
+            }
             for (int t = blockIdx.x; t < args.m_tiles; t += gridDim.x) {
                 for (int nt = 0; nt < args.n1_tiles; ++nt) {
                     mbar_wait(&acc1_empty[slot], slot_phase ^ 1u);
@@ -194,15 +224,15 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     for (int kb = 0; kb < args.k1_blocks + args.k2_blocks; ++kb) {
                         mbar_wait(&full_bar[stage], phase);
                         tc_fence_after();
-                        const uint32_t base = smem_u32(smem_g1 + stage * G1_STAGE_BYTES);
+                        const uint32_t base = smem_u32(smem_g1 + stage * (WRES ? TILE16K : G1_STAGE_BYTES));
                         const uint64_t a_desc = umma_desc_kmajor(base, 128);
-                        const uint64_t b_desc = umma_desc_kmajor(base + TILE16K, 128);
+                        const uint64_t b_desc = umma_desc_kmajor(WRES ? smem_u32(smem_w3 + (nt * kblocks + kb) * TILE16K) : base + TILE16K, 128);
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
                             umma_bf16(d1, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k), idesc1,
                                       static_cast<uint32_t>((kb | k) != 0));
                         umma_commit(&empty_bar[stage]);
-                        if (++stage == G1_STAGES) { stage = 0; phase ^= 1u; }
+                        if (++stage == RING) { stage = 0; phase ^= 1u; }
                     }
                     umma_commit(&acc1_full[slot]);
                     if (++slot == 2) { slot = 0; slot_phase ^= 1u; }
@@ -222,6 +252,11 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             // The residual of a chunk is needed at the START of that chunk's epilogue, its W1 tile only afterwards (by
             // the second GEMM), and both come from this one thread: so the residual loads run RES_BUFS - 1 chunks
             // ahead of the W1 loads instead of waiting behind them.
+            if (WRES) {
+                mbar_arrive_expect_tx(w1_bar, static_cast<uint32_t>(chunks_per_tile * W2_UNIT_BYTES));
+                for (int q = 0; q < chunks_per_tile; ++q)
+                    tma_load_2d_hint(&tmap_w1, w1_bar, smem_w2 + q * W2_UNIT_BYTES, q * 64, 0, L2_EVICT_LAST);
+            }
             const int my_tiles = (args.m_tiles - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
             const int total_chunks = my_tiles * chunks_per_tile;
             int res_issued = 0;
@@ -239,6 +274,7 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     const int ahead = c + RES_BUFS - 1 < total_chunks - 1 ? c + RES_BUFS - 1 : total_chunks - 1;
                     while (res_issued <= ahead) issue_res(res_issued++);
                 }
+                if (WRES) continue;
                 const int q = c % chunks_per_tile;
                 for (int u = 0; u < W2_UNITS; ++u) {
                     mbar_wait(&w2_empty[wb], wb_phase ^ 1u);
@@ -410,19 +446,29 @@ bool pair_encode(CUtensorMap* m, const void* base, uint64_t cols, uint64_t rows,
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-template <int N2>
+template <int N2, bool WRES>
 cudaError_t launch_pair(const PairPlan& p, const PairArgs& a, int grid, cudaStream_t s) {
     static std::atomic<bool> attr_set[64];   // zero-initialised; replicas of different GPUs launch from different threads
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
     if (!attr_set[dev].load(std::memory_order_acquire)) {
-        cudaError_t e = cudaFuncSetAttribute(conv_pair_kernel<N2>, cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM);
+        cudaError_t e = cudaFuncSetAttribute(conv_pair_kernel<N2, WRES>, cudaFuncAttributeMaxDynamicSharedMemorySize, PAIR_SMEM);
         if (e != cudaSuccess) return e;
         attr_set[dev].store(true, std::memory_order_release);
     }
-    return launch_pdl(conv_pair_kernel<N2>, dim3(grid), dim3(PAIR_THREADS), PAIR_SMEM, s, p.tmap_a, p.tmap_w3, p.tmap_res,
+    return launch_pdl(conv_pair_kernel<N2, WRES>, dim3(grid), dim3(PAIR_THREADS), PAIR_SMEM, s, p.tmap_a, p.tmap_w3, p.tmap_res,
                       p.tmap_out1, p.tmap_w1, p.tmap_out2, p.tmap_a2, a);
+}
+
+// Resident weights fit when (A ring + staging + residual tiles + W1 + W3) stay inside the kernel's fixed allocation.
+bool pair_weights_fit(const PairPlan& p, const PairArgs& a) {
+    if (p.n2 != 64) return false;
+    static const char* off = getenv("B2P_PAIR_WRES");
+    if (off && off[0] == '0') return false;
+    const int tiles = WRES_A_STAGES + STG_BUFS + 1 + (a.has_res ? RES_BUFS : 0) + 2 /*W1: 4 x 8 KB*/ +
+                      a.n1_tiles * (a.k1_blocks + a.k2_blocks);
+    return a.n1_tiles * 2 * 8192 <= 2 * TILE16K && 1024 + tiles * TILE16K + 512 <= PAIR_SMEM;
 }
 
 }  // namespace
@@ -515,9 +561,9 @@ cudaError_t pair_plan_launch(const PairPlan& p, int m_rows, int reverse, int num
     a.bias2 = p.bias2;
     if (a.m_tiles <= 0) return cudaSuccess;
     const int grid = a.m_tiles < num_sms ? a.m_tiles : num_sms;
-    if (p.n2 == 64) return launch_pair<64>(p, a, grid, s);
-    if (p.n2 == 128) return launch_pair<128>(p, a, grid, s);
-    if (p.n2 == 256) return launch_pair<256>(p, a, grid, s);
+    if (p.n2 == 64) return pair_weights_fit(p, a) ? launch_pair<64, true>(p, a, grid, s) : launch_pair<64, false>(p, a, grid, s);
+    if (p.n2 == 128) return launch_pair<128, false>(p, a, grid, s);
+    if (p.n2 == 256) return launch_pair<256, false>(p, a, grid, s);
     return cudaErrorInvalidConfiguration;
 }
 
