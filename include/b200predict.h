@@ -69,7 +69,10 @@ enum b2p_op_kind {
     B2P_OP_CONV_PAIR = 12, /* two chained 1x1/s1 convs in one kernel (a bottleneck's conv3 and the next block's
                               conv1): dst = relu(conv(src) + bias + res) as OP_CONV, and additionally
                               slot reserved[0] = relu(conv(dst) + bias2) with weight blob reserved[1] and bias blob
-                              reserved[2], reserved[3] = its output channels (64, 128 or 256)                 */
+                              reserved[2], reserved[3] = its output channels (64, 128 or 256).  reserved2 = 2: dst keeps only
+                              the pixels with even row and column, as a compact [n, out_h/2, out_w/2, out_c] tensor - for a
+                              dst whose only other reader is a 1x1/stride-2 conv (ResNet's projection shortcut), which then
+                              reads it with stride 1                                                                    */
     B2P_OP_BOTTLENECK = 13 /* a whole identity bottleneck block of the 56x56 stage in one kernel
                               (SP/torchvision/models/resnet.py:143-163): t1 = relu(conv1x1(src)), t2 = relu(conv3x3(t1)),
                               dst = relu(conv1x1(t2) + src).  in_c = 256, reserved2 = bottleneck width (64), out_c = 256,

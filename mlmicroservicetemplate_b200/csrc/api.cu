@@ -163,7 +163,12 @@ int validate_desc(const b2p_model_desc* d) {
         int64_t out_need = static_cast<int64_t>(o.out_h) * o.out_w * o.out_c;
         if (o.kind == B2P_OP_TOKENS) in_need = static_cast<int64_t>(o.in_h - 1) * o.in_w * o.in_c;   // the class token is added
         if (o.kind == B2P_OP_ATTENTION) in_need *= 3;                                               // packed Q | K | V
-        if (!holds(o.src, in_need) || !holds(o.dst, out_need)) return B2P_E_ARG;
+        int64_t dst_need = out_need;
+        if (o.kind == B2P_OP_CONV_PAIR && o.reserved2 == 2) {      // dst keeps the even rows / columns only
+            if ((o.out_h | o.out_w) & 1) return B2P_E_ARG;
+            dst_need = static_cast<int64_t>(o.out_h / 2) * (o.out_w / 2) * o.out_c;
+        }
+        if (!holds(o.src, in_need) || !holds(o.dst, dst_need)) return B2P_E_ARG;
         if (o.res != B2P_SLOT_NONE && !holds(o.res, out_need)) return B2P_E_ARG;
         if (o.src2_c > 0) {
             const int64_t st = o.src2_stride > 0 ? o.src2_stride : 1;
@@ -604,13 +609,16 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
             void* s_src2 = k2 > 0 ? h->slots[o.src2] : nullptr;
             if (!s_src || (o.res != B2P_SLOT_NONE && !s_res) || !s_dst || !s_dst2 || (k2 > 0 && !s_src2))
                 B2P_FAIL(B2P_E_ARG, "op %d uses an empty slot", i);
-            if (h->slot_elems[o.dst] < static_cast<int64_t>(o.out_h) * o.out_w * o.out_c ||
+            const int sub = o.reserved2 == 2 ? 2 : 1;     // 2: dst keeps the even rows / columns only
+            if (o.reserved2 != 0 && o.reserved2 != 1 && o.reserved2 != 2) B2P_FAIL(B2P_E_ARG, "op %d: CONV_PAIR reserved2 must be 0, 1 or 2", i);
+            if (sub == 2 && ((o.out_h | o.out_w) & 1)) B2P_FAIL(B2P_E_ARG, "op %d: a subsampled CONV_PAIR output needs even out_h / out_w", i);
+            if (h->slot_elems[o.dst] < static_cast<int64_t>(o.out_h / sub) * (o.out_w / sub) * o.out_c ||
                 h->slot_elems[o.reserved[0]] < static_cast<int64_t>(o.out_h) * o.out_w * n2)
                 B2P_FAIL(B2P_E_ARG, "op %d: destination slot too small", i);
             if (!pair_plan_init(p.pair, o.in_c, k2, o.out_c, n2, h->blobs[o.weight], static_cast<const float*>(h->blobs[o.bias]),
                                 h->blobs[o.reserved[1]], static_cast<const float*>(h->blobs[o.reserved[2]]), eb, sizeof eb) ||
                 !pair_plan_set_src2(p.pair, s_src2, h->chunk, o.out_h, o.out_w, o.src2_stride > 0 ? o.src2_stride : 1, eb, sizeof eb) ||
-                !pair_plan_set_buffers(p.pair, s_src, s_res, s_dst, s_dst2, static_cast<int>(rows_cap), eb, sizeof eb))
+                !pair_plan_set_buffers(p.pair, s_src, s_res, s_dst, s_dst2, static_cast<int>(rows_cap), sub, eb, sizeof eb))
                 B2P_FAIL(B2P_E_CUDA, "op %d: %s", i, eb);
         } else if (o.kind == B2P_OP_BOTTLENECK) {
             const bool proj = o.res == B2P_SLOT_NONE;

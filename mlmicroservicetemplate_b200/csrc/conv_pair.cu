@@ -48,6 +48,9 @@ struct PairArgs {
     int has_res;          // 0: no residual tensor (the shortcut is part of GEMM1)
     int n1_tiles;         // N1 / 128
     int reverse;
+    int sub;              // 2: only the pixels with even row and column of out1 are kept (compact [n, H/2, W/2, N1] tensor)
+    uint8_t* out1;        // sub == 2: base of that tensor (plain stores instead of the TMA store)
+    int n1;
     const float* bias1;   // [N1]
     const float* bias2;   // [N2]
 };
@@ -305,6 +308,19 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         uint32_t acc2_phase = 0;
         for (int t = blockIdx.x; t < args.m_tiles; t += gridDim.x) {
             const int m0 = (args.reverse ? args.m_tiles - 1 - t : t) * BM;
+            // sub == 2: out1 is only ever read through a stride-2 1x1 conv (the next block's projection shortcut; its
+            // conv1 is this kernel's second GEMM), so three quarters of it need not exist: the thread of an even-row /
+            // even-column pixel writes its 128 bytes of every chunk straight to the compact tensor, nobody else stores.
+            uint8_t* sub_dst = nullptr;
+            if (args.sub == 2) {
+                const int pix = m0 + row;
+                const int pq = args.out_h * args.out_w;
+                const int img = pix / pq, rem = pix - img * pq;
+                const int oh = rem / args.out_w, ow = rem - oh * args.out_w;
+                if (pix < args.m_rows && ((oh | ow) & 1) == 0)
+                    sub_dst = args.out1 + (static_cast<size_t>((img * (args.out_h >> 1) + (oh >> 1)) * (args.out_w >> 1) + (ow >> 1))) *
+                                              static_cast<size_t>(args.n1) * 2;
+            }
             for (int nt = 0; nt < args.n1_tiles; ++nt) {
                 mbar_wait(&acc1_full[slot], slot_phase);
                 tc_fence_after();
@@ -365,9 +381,15 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     for (int j = 0; j < 8; ++j) st_shared_v4(o_row + ((static_cast<uint32_t>(j) ^ swz) << 4), packed[j]);
                     fence_proxy_async_smem();
                     named_bar_sync(bar_id, 128);
+                    if (sub_dst) {
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) st_v4(sub_dst + col0 * 2 + j * 16, packed[j]);
+                    }
                     if (leader) {
-                        tma_store_2d(&tmap_out1, smem_stg + sb * TILE16K, col0, m0);
-                        tma_store_commit();
+                        if (args.sub != 2) {
+                            tma_store_2d(&tmap_out1, smem_stg + sb * TILE16K, col0, m0);
+                            tma_store_commit();
+                        }
                         mbar_arrive(&a2_full[sb]);          // the tile is also GEMM2's A operand now
                     }
                     ++mloc;
@@ -533,9 +555,21 @@ bool pair_plan_set_src2(PairPlan& p, const void* src2, int batch_cap, int out_h,
     return true;
 }
 
-bool pair_plan_set_buffers(PairPlan& p, const void* a, const void* res, void* out1, void* out2, int rows, char* err,
+bool pair_plan_set_buffers(PairPlan& p, const void* a, const void* res, void* out1, void* out2, int rows, int sub, char* err,
                            size_t err_len) {
     p.has_res = res != nullptr;
+    p.sub = sub == 2 ? 2 : 1;
+    p.out1 = out1;
+    if (p.sub == 2) {
+        // out1 is the compact [n, H/2, W/2, N1] tensor: no tensor map over it (the residual map falls back to `a`'s rows)
+        if (!pair_encode(&p.tmap_a, a, p.k1, rows, 64, 128) ||
+            !pair_encode(&p.tmap_res, res ? res : a, res ? p.n1 : p.k1, rows, 64, 128) ||
+            !pair_encode(&p.tmap_out1, a, p.k1, rows, 64, 128) || !pair_encode(&p.tmap_out2, out2, p.n2, rows, 64, 128)) {
+            snprintf(err, err_len, "conv pair activation tensor maps failed");
+            return false;
+        }
+        return true;
+    }
     if (!pair_encode(&p.tmap_a, a, p.k1, rows, 64, 128) ||
         !pair_encode(&p.tmap_res, res ? res : out1, p.n1, rows, 64, 128) ||
         !pair_encode(&p.tmap_out1, out1, p.n1, rows, 64, 128) || !pair_encode(&p.tmap_out2, out2, p.n2, rows, 64, 128)) {
@@ -557,6 +591,9 @@ cudaError_t pair_plan_launch(const PairPlan& p, int m_rows, int reverse, int num
     a.has_res = p.has_res;
     a.n1_tiles = p.n1 / BN1;
     a.reverse = reverse;
+    a.sub = p.sub;
+    a.out1 = static_cast<uint8_t*>(p.out1);
+    a.n1 = p.n1;
     a.bias1 = p.bias1;
     a.bias2 = p.bias2;
     if (a.m_tiles <= 0) return cudaSuccess;

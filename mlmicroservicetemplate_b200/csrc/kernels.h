@@ -118,6 +118,8 @@ struct PairPlan {
     CUtensorMap tmap_a, tmap_w3, tmap_res, tmap_out1, tmap_w1, tmap_out2, tmap_a2;
     int k1 = 0, k2 = 0, n1 = 0, n2 = 0;
     int stride2 = 1, out_h = 1, out_w = 1, has_res = 1;
+    int sub = 1;            // 2: out1 keeps only even rows / columns (compact tensor at out1)
+    void* out1 = nullptr;
     const float* bias1 = nullptr;
     const float* bias2 = nullptr;
 };
@@ -127,7 +129,8 @@ bool pair_plan_init(PairPlan& p, int k1, int k2, int n1, int n2, const void* w3,
 // Second GEMM1 source (folded projection shortcut): NHWC [batch_cap, out_h*stride2, out_w*stride2, k2] bf16.
 bool pair_plan_set_src2(PairPlan& p, const void* src2, int batch_cap, int out_h, int out_w, int stride2, char* err,
                         size_t err_len);
-bool pair_plan_set_buffers(PairPlan& p, const void* a, const void* res, void* out1, void* out2, int rows, char* err,
+// sub = 2: out1 is a compact [n, out_h/2, out_w/2, n1] tensor holding the even rows / columns only.
+bool pair_plan_set_buffers(PairPlan& p, const void* a, const void* res, void* out1, void* out2, int rows, int sub, char* err,
                            size_t err_len);
 cudaError_t pair_plan_launch(const PairPlan& p, int m_rows, int reverse, int num_sms, cudaStream_t s);
 

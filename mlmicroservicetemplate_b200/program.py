@@ -108,11 +108,11 @@ def stem_s2d_weight(w: torch.Tensor) -> torch.Tensor:
 
 
 def _mk_op(kind, src, dst, res=B.SLOT_NONE, in_hwc=(0, 0, 0), out_hwc=(0, 0, 0), k=(1, 1), stride=1, pad=(0, 0),
-           relu=0, weight=-1, bias=-1, flag0=0, reserved=None, src2=B.SLOT_NONE, src2_c=0, src2_stride=1) -> B.Op:
+           relu=0, weight=-1, bias=-1, flag0=0, reserved=None, src2=B.SLOT_NONE, src2_c=0, src2_stride=1, reserved2=0) -> B.Op:
     r = reserved if reserved is not None else (flag0, 0, 0, 0)
     return B.Op(kind, src, dst, res, in_hwc[0], in_hwc[1], in_hwc[2], out_hwc[0], out_hwc[1], out_hwc[2],
                 k[0], k[1], stride, pad[0], pad[1], relu, weight, bias, (B.C.c_int32 * 4)(*[int(v) for v in r]),
-                src2, src2_c, src2_stride, 0)
+                src2, src2_c, src2_stride, int(reserved2))
 
 
 class _Builder:
@@ -173,9 +173,13 @@ def bottleneck_op(p: Program, src: int, dst: int, hw: int, cin: int, w1, b1, w2,
 
 
 def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_stem: bool = True,
-                         fuse_pairs: bool = True, fold_shortcut: bool = True, fuse_blocks: Optional[bool] = None) -> Program:
+                         fuse_pairs: bool = True, fold_shortcut: bool = True, fuse_blocks: Optional[bool] = None,
+                         subsample_pair_out: Optional[bool] = None) -> Program:
     """Walks a torchvision ResNet (SP/torchvision/models/resnet.py:266-282: conv1-bn1-relu-maxpool,
     layer1..4, avgpool, fc) and emits the program.  Works for BasicBlock and Bottleneck nets."""
+    import os
+    if subsample_pair_out is None:
+        subsample_pair_out = os.getenv("B2P_PAIR_SUBSAMPLE", "1") != "0"
     from torchvision.models.resnet import BasicBlock, Bottleneck
 
     model = model.eval()
@@ -222,6 +226,7 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
 
     blocks = [blk for layer in (model.layer1, model.layer2, model.layer3, model.layer4) for blk in layer]
     carry = None          # (t1 slot, hwc1) when the previous block's CONV_PAIR already computed this block's conv1
+    x_sub = 1             # 2: x holds only the even rows / columns of the block input (see the CONV_PAIR branch)
     for bi_, blk in enumerate(blocks):
         if True:
             # A 56x56 bottleneck (ResNet-50/101/152 layer1) runs as ONE kernel: only the block input is read and the
@@ -245,13 +250,17 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
                 shortcut = None
                 if blk.downsample is not None:
                     wd, bd = fold_bn(blk.downsample[0].weight, blk.downsample[1])
+                    ds_stride = blk.downsample[0].stride[0] // x_sub      # a pre-subsampled x is read with stride 1
+                    ds_presub = x_sub != 1
                     if fold_shortcut and wd.shape[1] % 64 == 0 and tuple(blk.downsample[0].kernel_size) == (1, 1):
-                        shortcut = (x, wd, bd, blk.downsample[0].stride[0])
+                        shortcut = (x, wd, bd, ds_stride)
                         idn = B.SLOT_NONE
                     else:
-                        idn, _ = bld.conv(x, hwc, wd, bd, blk.downsample[0].stride[0], 0, False)
+                        idn, _ = bld.conv(x, hwc, wd, bd, ds_stride, 0, False)
                 else:
+                    assert x_sub == 1
                     idn = x
+                x_sub = 1
                 if carry is not None:
                     t1, hwc1 = carry
                     carry = None
@@ -269,7 +278,8 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
                             # a STRIDED folded shortcut stays out of the pair kernel: its gathered (stride-2 im2col) operand
                             # loads starve the pair's two-stage ring - measured 170 us paired vs 73 + 40 us as conv3(+shortcut)
                             # and a separate conv1 for ResNet-50's first 28x28 block (profiles/r02v_pair_shortcut_ab.txt)
-                            and not (shortcut is not None and shortcut[3] != 1)
+                            and not (shortcut is not None and (shortcut[3] != 1 or
+                                                               (ds_presub and os.getenv("B2P_PAIR_AFTER_SUB", "0") == "0")))
                             and nxt.conv1.stride == (1, 1) and nxt.conv1.out_channels in (64, 128)
                             and n1 % 128 == 0 and w3.shape[1] in (64, 128) and tuple(blk.conv3.kernel_size) == (1, 1))
                 # (wider pairs - K1 >= 256 or N2 = 256, i.e. ResNet-50's stage 3 - were measured slower than the two
@@ -289,14 +299,24 @@ def build_resnet_program(model: torch.nn.Module, name: str = "resnet", fused_ste
                     bi = p.add_blob(pad_bias(b3p, n1))
                     wi2 = p.add_blob(pack_conv_weight(wn))
                     bi2 = p.add_blob(pad_bias(bn_, n2))
-                    out = p.alloc(oh * ow * n1)
+                    # When the next block downsamples, its conv1 (this kernel's second GEMM) is the only full-resolution
+                    # reader of this block's output; the other one is the 1x1/stride-2 projection shortcut.  So only the
+                    # even rows / columns are written (a quarter of the tensor: 103 instead of 411 MB per 256 images at
+                    # 56x56x256) and the shortcut reads the compact tensor with stride 1.
+                    sub = 1
+                    if (subsample_pair_out and nxt.downsample is not None and tuple(nxt.downsample[0].kernel_size) == (1, 1)
+                            and tuple(nxt.downsample[0].stride) == (2, 2) and nxt.conv2.stride == (2, 2)
+                            and oh % 2 == 0 and ow % 2 == 0):
+                        sub = 2
+                    out = p.alloc((oh // sub) * (ow // sub) * n1)
                     t1n = p.alloc(oh * ow * n2)
                     p.ops.append(_mk_op(B.OP_CONV_PAIR, t2, out, idn, hwc2, (oh, ow, n1), (1, 1), 1, (0, 0), 1, wi, bi,
-                                        reserved=(t1n, wi2, bi2, n2), **sc_kw))
+                                        reserved=(t1n, wi2, bi2, n2), reserved2=sub, **sc_kw))
+                    x_sub = sub
                     if shortcut is not None:
                         p.release(x)
                     p.flops_per_image += 2.0 * oh * ow * n1 * w3.shape[1] + 2.0 * oh * ow * n2 * n1
-                    hwc3 = (oh, ow, n1)
+                    hwc3 = (oh // sub, ow // sub, n1)
                     carry = (t1n, (oh, ow, n2))
                 elif shortcut is not None:
                     out, hwc3 = bld.conv(t2, hwc2, w3, b3, 1, 0, True, second=shortcut)

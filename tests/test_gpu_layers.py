@@ -109,8 +109,9 @@ def test_stem_dedicated_kernel(pool, n, cuda_device):
     assert bad == 0
 
 
-@pytest.mark.parametrize("k1,n2,hw,n", [(64, 64, 56, 2), (128, 128, 28, 3), (256, 256, 14, 5), (64, 128, 56, 1)])
-def test_conv_pair_fused(k1, n2, hw, n, cuda_device):
+@pytest.mark.parametrize("k1,n2,hw,n,sub", [(64, 64, 56, 2, 1), (128, 128, 28, 3, 1), (256, 256, 14, 5, 1), (64, 128, 56, 1, 1),
+                                              (64, 128, 56, 3, 2), (128, 128, 28, 2, 2)])
+def test_conv_pair_fused(k1, n2, hw, n, sub, cuda_device):
     """OP_CONV_PAIR (conv3 + residual + ReLU -> next conv1 + ReLU in one kernel) against the two convs in torch.
     Both outputs are exported through an identity 1x1 conv (exact in bf16) because a program has one output."""
     from mlmicroservicetemplate_b200 import backend as B, program as P
@@ -131,13 +132,15 @@ def test_conv_pair_fused(k1, n2, hw, n, cuda_device):
         t2s, _ = bld.conv(B.SLOT_INPUT, (hw, hw, k1), torch.eye(k1).view(k1, k1, 1, 1), torch.zeros(k1), 1, 0, False)
         wi, bi = p.add_blob(P.pack_conv_weight(w3)), p.add_blob(P.pad_bias(b3, n1))
         wi2, bi2 = p.add_blob(P.pack_conv_weight(w1)), p.add_blob(P.pad_bias(b1, n2))
-        out1, out2 = p.alloc(hw * hw * n1), p.alloc(hw * hw * n2)
+        # sub = 2: the first output keeps only its even rows / columns (a compact [hw/2, hw/2, n1] tensor)
+        out1, out2 = p.alloc((hw // sub) * (hw // sub) * n1), p.alloc(hw * hw * n2)
         p.ops.append(P._mk_op(B.OP_CONV_PAIR, t2s, out1, idn, (hw, hw, k1), (hw, hw, n1), (1, 1), 1, (0, 0), 1, wi, bi,
-                              reserved=(out2, wi2, bi2, n2)))
+                              reserved=(out2, wi2, bi2, n2), reserved2=sub))
         c = n2 if export_second else n1
-        bld.conv(out2 if export_second else out1, (hw, hw, c), torch.eye(c).view(c, c, 1, 1), torch.zeros(c), 1, 0, False,
+        side = hw if export_second else hw // sub
+        bld.conv(out2 if export_second else out1, (side, side, c), torch.eye(c).view(c, c, 1, 1), torch.zeros(c), 1, 0, False,
                  dst=B.SLOT_OUTPUT)
-        p.out_elems = hw * hw * c
+        p.out_elems = side * side * c
         return p
 
     x = t2.to(torch.bfloat16).cuda()
@@ -145,7 +148,8 @@ def test_conv_pair_fused(k1, n2, hw, n, cuda_device):
     for second in (False, True):
         rep = B.Replica(0, build(second), max_batch=n)
         c = n2 if second else n1
-        out = torch.full((n, hw, hw, c), float("nan"), dtype=torch.bfloat16, device="cuda")
+        side = hw if second else hw // sub
+        out = torch.full((n, side, side, c), float("nan"), dtype=torch.bfloat16, device="cuda")
         rep.forward(x, n, out)
         torch.cuda.synchronize()
         outs.append(out.float().cpu())
@@ -154,7 +158,7 @@ def test_conv_pair_fused(k1, n2, hw, n, cuda_device):
     idn = _bf16r(F.conv2d(xin, w_id))
     ref1 = (F.conv2d(xin, w3, b3) + idn).relu()
     ref2 = F.conv2d(_bf16r(ref1), w1, b1).relu().permute(0, 2, 3, 1)
-    ref1 = ref1.permute(0, 2, 3, 1)
+    ref1 = ref1.permute(0, 2, 3, 1)[:, ::sub, ::sub, :]
     e1, e2 = (outs[0] - ref1).abs(), (outs[1] - ref2).abs()
     print(f"pair k1={k1} n2={n2}: out1 max_err={e1.max().item():.4g} out2 max_err={e2.max().item():.4g}")
     assert not torch.isnan(outs[0]).any() and not torch.isnan(outs[1]).any()

@@ -55,6 +55,8 @@ def interpret(prog: P.Program, x_nchw: torch.Tensor) -> torch.Tensor:
             y2 = F.conv2d(y.permute(0, 3, 1, 2), w2.permute(0, 3, 1, 2), prog.blobs[bi2][:n2]).relu().permute(0, 2, 3, 1)
             assert y2[0].numel() <= prog.slot_elems[dst2]
             slots[dst2] = y2
+            if op.reserved2 == 2:          # only the even rows / columns of the first result are kept
+                y = y[:, ::2, ::2, :].contiguous()
         elif op.kind == B.OP_BOTTLENECK:
             mid = op.reserved2
             xin = src.permute(0, 3, 1, 2)
@@ -98,7 +100,8 @@ def interpret(prog: P.Program, x_nchw: torch.Tensor) -> torch.Tensor:
             y = src @ prog.blobs[op.weight].float()[: op.out_c].t() + prog.blobs[op.bias][: op.out_c]
         else:
             raise AssertionError(op.kind)
-        assert tuple(y.shape[1:]) in ((op.out_h, op.out_w, op.out_c), (op.out_c,)), (op.kind, tuple(y.shape))
+        sub = 2 if (op.kind == B.OP_CONV_PAIR and op.reserved2 == 2) else 1
+        assert tuple(y.shape[1:]) in ((op.out_h // sub, op.out_w // sub, op.out_c), (op.out_c,)), (op.kind, tuple(y.shape))
         if op.dst == B.SLOT_OUTPUT:
             out = y
         else:
