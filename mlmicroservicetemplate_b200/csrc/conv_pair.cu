@@ -36,9 +36,9 @@ constexpr int G1_STAGES = 2;
 constexpr int G1_STAGE_BYTES = 2 * TILE16K;      // A (128 x 64) + W3 (128 x 64)
 constexpr int STG_BUFS = 4;              // staging tiles that double as GEMM2 A operands: two per epilogue group
 constexpr int RES_BUFS = 2;              // one residual tile per epilogue group
-constexpr int W2_BUFS = 3;               // W1 units of (<=128 rows) x 64 columns
+constexpr int W2_BUFS_MAX = 3;           // W1 units of (<=128 rows) x 64 columns (two when a second out2 staging tile takes the room)
 constexpr int PAIR_THREADS = 384;         // TMA, MMA, loader, (idle), two epilogue groups of four warps
-constexpr int PAIR_SMEM = 1024 + G1_STAGES * G1_STAGE_BYTES + (STG_BUFS + 1 + RES_BUFS + W2_BUFS) * TILE16K + 512;
+constexpr int PAIR_SMEM = 1024 + G1_STAGES * G1_STAGE_BYTES + (STG_BUFS + 1 + RES_BUFS + W2_BUFS_MAX) * TILE16K + 512;
 
 struct PairArgs {
     int m_rows, m_tiles;
@@ -55,7 +55,7 @@ struct PairArgs {
     const float* bias2;   // [N2]
 };
 
-constexpr int WRES_A_STAGES = 3;         // WRES: A-only operand ring
+constexpr int WRES_A_STAGES = 2;         // WRES: A-only operand ring
 
 template <int N2, bool WRES>
 __global__ void __launch_bounds__(PAIR_THREADS, 1)
@@ -72,11 +72,17 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
     static_assert(!WRES || N2 == 64, "resident weights: the 64-channel conv1 only");
+    // ALT: the second epilogue (out2) of a tile is taken by epilogue group (tile & 1) instead of always group 0, which
+    // had 3-4 epilogue units per tile against group 1's 2 and set the tile period of the kernels that are not DRAM-bound
+    // (profiles/r02zb_l2_smem_bounds.txt, section 9).  Costs a second out2 staging tile (one W1 ring slot / A stage less).
+    constexpr bool ALT = N2 <= 128;
+    constexpr int W2_BUFS = ALT ? 2 : 3;
+    constexpr int STG2_BUFS = ALT ? 2 : 1;
     const int kblocks = args.k1_blocks + args.k2_blocks;
     uint8_t* smem_g1 = smem;                                           // G1_STAGES x (A | W3);  WRES: WRES_A_STAGES x A
     uint8_t* smem_stg = smem_g1 + (WRES ? WRES_A_STAGES * TILE16K : G1_STAGES * G1_STAGE_BYTES);   // STG_BUFS staging / A2 tiles
     uint8_t* smem_stg2 = smem_stg + STG_BUFS * TILE16K;                // staging for out2
-    uint8_t* smem_res = smem_stg2 + TILE16K;
+    uint8_t* smem_res = smem_stg2 + STG2_BUFS * TILE16K;
     uint8_t* smem_w2 = smem_res + ((WRES && !args.has_res) ? 0 : RES_BUFS * TILE16K);   // W1 ring;  WRES: all of W1 (32 KB)
     uint8_t* smem_w3 = smem_w2 + 2 * TILE16K;                          // WRES only: n1_tiles x kblocks tiles of W3
     uint64_t* bars = reinterpret_cast<uint64_t*>(WRES ? smem_w3 + args.n1_tiles * kblocks * TILE16K : smem_w2 + W2_BUFS * TILE16K);
@@ -91,8 +97,8 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     uint64_t* w2_empty = w2_full + W2_BUFS;
     uint64_t* a2_full = w2_empty + W2_BUFS;             // [STG_BUFS] epilogue -> MMA: chunk staged
     uint64_t* a2_free = a2_full + STG_BUFS;             // [STG_BUFS] MMA -> epilogue: GEMM2 finished reading
-    uint64_t* acc2_full = a2_free + STG_BUFS;           // [1]
-    uint64_t* acc2_empty = acc2_full + 1;               // [1]
+    uint64_t* acc2_full = a2_free + STG_BUFS;           // [2] (ALT: tile parity; else only [0])
+    uint64_t* acc2_empty = acc2_full + 2;               // [1]
     uint64_t* w3_bar = acc2_empty + 1;                  // WRES: resident W3 / W1 have landed
     uint64_t* w1_bar = w3_bar + 1;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w1_bar + 1);
@@ -111,7 +117,8 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             for (int i = 0; i < RES_BUFS; ++i) { mbar_init(&res_full[i], 1); mbar_init(&res_empty[i], 4); }
             for (int i = 0; i < W2_BUFS; ++i) { mbar_init(&w2_full[i], 1); mbar_init(&w2_empty[i], 1); }
             for (int i = 0; i < STG_BUFS; ++i) { mbar_init(&a2_full[i], 1); mbar_init(&a2_free[i], 1); }
-            mbar_init(acc2_full, 1);
+            mbar_init(&acc2_full[0], 1);
+            mbar_init(&acc2_full[1], 1);
             mbar_init(acc2_empty, 4);
             mbar_init(w3_bar, 1);
             mbar_init(w1_bar, 1);
@@ -219,7 +226,8 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 mbar_wait(w1_bar, 0);
                 tc_fence_after();
             }
-            for (int t = blockIdx.x; t < args.m_tiles; t += gridDim.x) {
+            int it = 0;
+            for (int t = blockIdx.x; t < args.m_tiles; t += gridDim.x, ++it) {
                 for (int nt = 0; nt < args.n1_tiles; ++nt) {
                     mbar_wait(&acc1_empty[slot], slot_phase ^ 1u);
                     tc_fence_after();
@@ -242,7 +250,7 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     if (nt >= 1) gemm2_subtile(nt - 1);       // consume the chunks the epilogue produced meanwhile
                 }
                 gemm2_subtile(args.n1_tiles - 1);
-                umma_commit(acc2_full);
+                umma_commit(&acc2_full[ALT ? (it & 1) : 0]);
             }
         }
     } else if (warp_idx == 2) {
@@ -295,7 +303,7 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const uint32_t swz = static_cast<uint32_t>(row & 7);
         // Two groups of four warps: group g takes the g-th 64-column chunk of every 128-column GEMM1 sub-tile (so the
         // left and right halves of an accumulator stage are drained at the same time), owns residual tile g and the
-        // staging tiles g and g + 2; group 0 also runs the second epilogue (out2) of every tile.
+        // staging tiles g and g + 2; the second epilogue (out2) of a tile is run by group (tile & 1) (ALT) or always by group 0.
         const int group = (warp_idx - 4) >> 2;
         const bool leader = (warp_idx == 4 + 4 * group) && (lane == 0);
         const uint32_t bar_id = 1u + static_cast<uint32_t>(group);
@@ -306,7 +314,9 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         uint32_t rb_phase = 0;
         uint32_t mloc = 0;              // this group's chunk counter: staging tile group + 2 * (mloc & 1)
         uint32_t acc2_phase = 0;
+        int it = -1;
         for (int t = blockIdx.x; t < args.m_tiles; t += gridDim.x) {
+            ++it;
             const int m0 = (args.reverse ? args.m_tiles - 1 - t : t) * BM;
             // sub == 2: out1 is only ever read through a stride-2 1x1 conv (the next block's projection shortcut; its
             // conv1 is this kernel's second GEMM), so three quarters of it need not exist: the thread of an even-row /
@@ -397,9 +407,10 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                 if (++slot == 2) { slot = 0; slot_phase ^= 1u; }
             }
             // ---- second epilogue: out2 = relu(acc2 + bias2), group 0 only (group 1 is already on the next tile)
-            if (group != 0) continue;
-            mbar_wait(acc2_full, acc2_phase);
+            if (group != (ALT ? (it & 1) : 0)) continue;
+            mbar_wait(&acc2_full[ALT ? (it & 1) : 0], acc2_phase);
             acc2_phase ^= 1u;
+            uint8_t* my_stg2 = smem_stg2 + (ALT ? group : 0) * TILE16K;
             tc_fence_after();
 #pragma unroll 1
             for (int c2 = 0; c2 < N2 / 64; ++c2) {
@@ -424,15 +435,15 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     __syncwarp();
                     if (lane == 0) mbar_arrive(acc2_empty);
                 }
-                if (leader) tma_store_wait_read<0>();      // smem_stg2 is single-buffered
-                named_bar_sync(1, 128);
-                const uint32_t o_row = smem_u32(smem_stg2) + static_cast<uint32_t>(row * 128);
+                if (leader) tma_store_wait_read<0>();      // one out2 staging tile per group
+                named_bar_sync(bar_id, 128);
+                const uint32_t o_row = smem_u32(my_stg2) + static_cast<uint32_t>(row * 128);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) st_shared_v4(o_row + ((static_cast<uint32_t>(j) ^ swz) << 4), packed[j]);
                 fence_proxy_async_smem();
-                named_bar_sync(1, 128);
+                named_bar_sync(bar_id, 128);
                 if (leader) {
-                    tma_store_2d(&tmap_out2, smem_stg2, c2 * 64, m0);
+                    tma_store_2d(&tmap_out2, my_stg2, c2 * 64, m0);
                     tma_store_commit();
                 }
             }
@@ -488,7 +499,7 @@ bool pair_weights_fit(const PairPlan& p, const PairArgs& a) {
     if (p.n2 != 64) return false;
     static const char* off = getenv("B2P_PAIR_WRES");
     if (off && off[0] == '0') return false;
-    const int tiles = WRES_A_STAGES + STG_BUFS + 1 + (a.has_res ? RES_BUFS : 0) + 2 /*W1: 4 x 8 KB*/ +
+    const int tiles = WRES_A_STAGES + STG_BUFS + 2 /*out2 staging*/ + (a.has_res ? RES_BUFS : 0) + 2 /*W1: 4 x 8 KB*/ +
                       a.n1_tiles * (a.k1_blocks + a.k2_blocks);
     return a.n1_tiles * 2 * 8192 <= 2 * TILE16K && 1024 + tiles * TILE16K + 512 <= PAIR_SMEM;
 }
