@@ -679,7 +679,7 @@ bool gemm_plan_init(GemmPlan& p, const b2p_op& op, const void* weight_dev, int64
         if (p.force_block_n && bn != p.force_block_n) continue;
         if (p.n_pad % bn != 0) continue;
         if (p.block_k == 16 && bn != 64) continue;
-        if (p.out_f32 && bn != 128) continue;
+        if (p.out_f32 && bn == 256) continue;      // fp32 logits: 128- or 64-wide tiles (the FC layer has 16 / 32 of them)
         const double tile_cost = bn + 32;           // +32: fixed per-tile overhead in "column" units
         // single CTAs; a nearly empty last wave is cut into 64-column pieces (see gemm_tail_split)
         {
@@ -852,6 +852,7 @@ cudaError_t gemm_plan_launch(const GemmPlan& p, int m_rows, bool has_res, void* 
     }
     if (p.out_f32) {
         if (p.block_n == 128 && !p.im2col && !has_res) B2P_LAUNCH(128, 64, false, true, false);
+        if (p.block_n == 64 && !p.im2col && !has_res) B2P_LAUNCH(64, 64, false, true, false);
         return cudaErrorInvalidConfiguration;
     }
 #define B2P_PICK(BN)                                                   \
