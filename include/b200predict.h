@@ -132,8 +132,11 @@ typedef struct b2p_image {
 typedef struct b2p_stats {
     float ms_h2d, ms_preprocess, ms_forward, ms_epilogue, ms_d2h;
                                     /* CUDA-event times.  ms_preprocess / ms_forward / ms_epilogue (K1 / K2 / K3): the
-                                       MEAN over the b2p_predict and b2p_predict_host calls issued since the previous
-                                       b2p_stats_get whose work has completed (at most the 64 most recent);
+                                       MEAN over the SAMPLED b2p_predict and b2p_predict_host calls issued since the
+                                       previous b2p_stats_get whose work has completed (at most the 64 most recent).
+                                       Every 4th call is sampled, the first one included (environment B2P_STATS_EVERY=n
+                                       at create; 1 = every call): the events that delimit the stages sit between
+                                       kernels and cost those kernels their launch overlap;
                                        ms_h2d / ms_d2h: the most recent b2p_predict_host call                        */
     int64_t calls;
     int64_t kernel_launches;        /* kernels launched by this handle since create                */

@@ -75,7 +75,7 @@ struct b2p_handle {
     float* norm_lut = nullptr;           // [3][256] normalisation table for K1's crop-only path
     float* probs_dev = nullptr;
     int32_t* idx_dev = nullptr;
-    cudaEvent_t ev[7] = {};   // [0],[1] copy begin/end (copy stream), [6] D2H end (caller's stream); [2..5] unused
+    cudaEvent_t ev[7] = {};   // [0],[1] copy begin/end (copy stream), [5] D2H begin, [6] D2H end (caller's stream); [2..4] unused
     bool ev_valid = false;
     // per-stage events of the predict chains: K1 begin, K1 / K2 / K3 end, one set per call in a ring, so that
     // b2p_stats_get can average the stages over every call since the previous read
@@ -84,6 +84,11 @@ struct b2p_handle {
     int sev_pos = 0;          // next set to record into
     int sev_unread = 0;       // sets recorded since the last b2p_stats_get (saturates at SRING)
     int sev_last = -1;
+    // Stage events sit BETWEEN kernels of the chain and keep the next kernel's programmatic launch from overlapping
+    // its predecessor's tail, so only every stage_every-th call records them (B2P_STATS_EVERY, default 4; 1 = every
+    // call); b2p_stats_get averages over the sampled calls.
+    int stage_every = 4;
+    long predict_calls = 0;
     b2p_stats stats = {};
     char err[512] = "";
 };
@@ -431,6 +436,7 @@ int32_t b2p_create(int32_t device, const b2p_model_desc* desc, b2p_handle** out)
     h->in_elems = desc->in_elems_per_image;
     h->out_elems = desc->out_elems_per_image;
     h->alternate = getenv("B2P_NO_ALTERNATE") == nullptr;
+    if (const char* e = getenv("B2P_STATS_EVERY")) h->stage_every = atoi(e) > 0 ? atoi(e) : 1;
 
 #define B2P_FAIL(code, ...)                         \
     do {                                            \
@@ -753,7 +759,7 @@ int32_t b2p_stats_get(b2p_handle* h, b2p_stats* out) {
     if (h->ev_valid && h->stats.calls > 0 && h->sev_last >= 0) {
         float a = 0.f, b = 0.f;
         if (cudaEventElapsedTime(&a, h->ev[0], h->ev[1]) == cudaSuccess &&
-            cudaEventElapsedTime(&b, h->sev[h->sev_last][3], h->ev[6]) == cudaSuccess) {
+            cudaEventElapsedTime(&b, h->ev[5], h->ev[6]) == cudaSuccess) {
             h->stats.ms_h2d = a;
             h->stats.ms_d2h = b;
         } else {
@@ -823,19 +829,22 @@ int32_t b2p_predict(b2p_handle* h, const uint8_t* slab, const b2p_image* imgs, i
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     B2P_CUDA(h, cudaSetDevice(h->device));
     cudaEvent_t* sev = h->sev[h->sev_pos];
-    B2P_CUDA(h, cudaEventRecord(sev[0], st));
+    const bool sample = (h->predict_calls++ % h->stage_every) == 0;
+    if (sample) B2P_CUDA(h, cudaEventRecord(sev[0], st));
     size_t first_op = 0;
     int rc = chain_preprocess(h, slab, imgs, n, stream, &first_op);
     if (rc != B2P_OK) return rc;
-    B2P_CUDA(h, cudaEventRecord(sev[1], st));
+    if (sample) B2P_CUDA(h, cudaEventRecord(sev[1], st));
     rc = run_program(h, h->x_dev, n, h->logits_dev, st, first_op);
     if (rc != B2P_OK) return rc;
-    B2P_CUDA(h, cudaEventRecord(sev[2], st));
+    if (sample) B2P_CUDA(h, cudaEventRecord(sev[2], st));
     rc = b2p_softmax_topk(h, h->logits_dev, n, h->classes, k, probs, idx, stream);
     if (rc != B2P_OK) return rc;
-    B2P_CUDA(h, cudaEventRecord(sev[3], st));
-    h->sev_pos = (h->sev_pos + 1) % b2p_handle::SRING;
-    if (h->sev_unread < b2p_handle::SRING) ++h->sev_unread;
+    if (sample) {
+        B2P_CUDA(h, cudaEventRecord(sev[3], st));
+        h->sev_pos = (h->sev_pos + 1) % b2p_handle::SRING;
+        if (h->sev_unread < b2p_handle::SRING) ++h->sev_unread;
+    }
     return B2P_OK;
 }
 
@@ -882,22 +891,28 @@ int32_t b2p_predict_host(b2p_handle* h, const uint8_t* slab_host, int64_t slab_b
     B2P_CUDA(h, cudaEventRecord(h->ev_copied[si], h->copy_stream));
     B2P_CUDA(h, cudaStreamWaitEvent(st, h->ev_copied[si], 0));
     cudaEvent_t* sev = h->sev[h->sev_pos];
-    B2P_CUDA(h, cudaEventRecord(sev[0], st));
+    const bool sample = (h->predict_calls++ % h->stage_every) == 0;
+    if (sample) B2P_CUDA(h, cudaEventRecord(sev[0], st));
     size_t first_op = 0;
     int rc = chain_preprocess(h, h->slab_dev[si], imgs, n, stream, &first_op);
     if (rc != B2P_OK) return rc;
-    B2P_CUDA(h, cudaEventRecord(sev[1], st));
+    if (sample) B2P_CUDA(h, cudaEventRecord(sev[1], st));
+    // "K1 has read slab si": the copy of two calls later waits for this.  (Signalling it after the whole chain instead,
+    // to keep K1 -> stem launch overlap, cost 12 % of the end-to-end rate: the copies then run one step ahead, not two.)
     B2P_CUDA(h, cudaEventRecord(h->ev_consumed[si], st));
     h->slab_used[si] = true;
     rc = run_program(h, h->x_dev, n, h->logits_dev, st, first_op);
     if (rc != B2P_OK) return rc;
-    B2P_CUDA(h, cudaEventRecord(sev[2], st));
+    if (sample) B2P_CUDA(h, cudaEventRecord(sev[2], st));
     rc = b2p_softmax_topk(h, h->logits_dev, n, h->classes, k, h->probs_dev, h->idx_dev, stream);
     if (rc != B2P_OK) return rc;
-    B2P_CUDA(h, cudaEventRecord(sev[3], st));
-    h->sev_last = h->sev_pos;
-    h->sev_pos = (h->sev_pos + 1) % b2p_handle::SRING;
-    if (h->sev_unread < b2p_handle::SRING) ++h->sev_unread;
+    if (sample) {
+        B2P_CUDA(h, cudaEventRecord(sev[3], st));
+        h->sev_pos = (h->sev_pos + 1) % b2p_handle::SRING;
+        if (h->sev_unread < b2p_handle::SRING) ++h->sev_unread;
+    }
+    h->sev_last = 0;
+    B2P_CUDA(h, cudaEventRecord(h->ev[5], st));
     B2P_CUDA(h, cudaMemcpyAsync(probs_host, h->probs_dev, sizeof(float) * static_cast<size_t>(n) * k,
                                 cudaMemcpyDeviceToHost, st));
     B2P_CUDA(h, cudaMemcpyAsync(idx_host, h->idx_dev, sizeof(int32_t) * static_cast<size_t>(n) * k,

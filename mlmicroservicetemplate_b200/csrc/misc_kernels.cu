@@ -159,6 +159,8 @@ constexpr int MAX_PER_LANE = 40;   // up to 1280 classes
 
 __global__ void softmax_topk_kernel(const float* __restrict__ logits, int n, int classes, int k,
                                     float* __restrict__ probs, int32_t* __restrict__ idx) {
+    pdl_launch_dependents();
+    pdl_wait();                                         // the logits come from the kernel before this one
     const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (warp >= n) return;
@@ -248,8 +250,7 @@ cudaError_t launch_softmax_topk(const float* logits, int n, int classes, int k, 
     if (classes > 32 * MAX_PER_LANE) return cudaErrorInvalidValue;
     const int warps_per_block = 4;
     const int grid = (n + warps_per_block - 1) / warps_per_block;
-    softmax_topk_kernel<<<grid, warps_per_block * 32, 0, s>>>(logits, n, classes, k, probs, idx);
-    return cudaGetLastError();
+    return launch_pdl(softmax_topk_kernel, dim3(grid), dim3(warps_per_block * 32), 0, s, logits, n, classes, k, probs, idx);
 }
 
 }  // namespace b2p

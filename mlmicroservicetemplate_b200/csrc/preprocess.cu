@@ -374,7 +374,9 @@ preprocess_identity_s2d_kernel(const uint8_t* __restrict__ slab, const b2p_image
                                uint4* __restrict__ out, const float* __restrict__ lut_g, int n) {
     __shared__ float lut[3 * 256];
     __shared__ uint4 stage[256 * 8];                 // 32 KB: one 4 KB transposition buffer per warp
-    for (int i = threadIdx.x; i < 3 * 256; i += 256) lut[i] = __ldg(lut_g + i);
+    pdl_launch_dependents();
+    for (int i = threadIdx.x; i < 3 * 256; i += 256) lut[i] = __ldg(lut_g + i);     // written once at create
+    pdl_wait();                                      // the slot written below may still be read by the previous step
     __syncthreads();
     constexpr int HALF = OUT / 2;                    // 112 s2d pixels per row
     constexpr int GROUPS = HALF / 4;                 // 28 groups of 4
@@ -459,9 +461,8 @@ bool preprocess_all_identity(const b2p_image* imgs_host, int n) {
 cudaError_t launch_preprocess_s2d(const uint8_t* slab, const b2p_image* imgs_dev, int n, void* out_s2d,
                                   const float* norm_lut, cudaStream_t s) {
     const long threads = static_cast<long>(n) * (OUT / 2) * (OUT / 8);
-    preprocess_identity_s2d_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, s>>>(
-        slab, imgs_dev, static_cast<uint4*>(out_s2d), norm_lut, n);
-    return cudaGetLastError();
+    return launch_pdl(preprocess_identity_s2d_kernel, dim3(static_cast<unsigned>((threads + 255) / 256)), dim3(256), 0, s, slab,
+                      imgs_dev, static_cast<uint4*>(out_s2d), norm_lut, n);
 }
 
 // Host mirror of axis_range(): first source index and one-past-last of the taps of output index i.
