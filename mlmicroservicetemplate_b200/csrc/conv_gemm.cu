@@ -694,7 +694,10 @@ bool gemm_plan_init(GemmPlan& p, const b2p_op& op, const void* weight_dev, int64
         if (cta2_ok && (cta2_all ? bn >= 128 : (bn == 256 && !has_res_op))) {
             const long pairs = num_sms / 2;
             const long tiles = static_cast<long>((m_tiles + 1) / 2) * (p.n_pad / bn);
-            const double cost = static_cast<double>((tiles + pairs - 1) / pairs) * tile_cost;
+            // a pair tile pulls half of the weight bytes per CTA through the L2, which is what bounds these layers: worth
+            // an extra partly filled wave (ResNet-50's 7x7 layers; A/B profiles/r02zb_l2_smem_bounds.txt, section 13)
+            static const double pair_bias = getenv("B2P_PAIR_BIAS") ? atof(getenv("B2P_PAIR_BIAS")) : 0.8;
+            const double cost = static_cast<double>((tiles + pairs - 1) / pairs) * tile_cost * pair_bias;
             if (best == 0 || cost <= best_cost) { best = bn; best_cost = cost; best_cta2 = 1; }
         }
     }
