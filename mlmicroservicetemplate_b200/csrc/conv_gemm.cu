@@ -691,7 +691,8 @@ bool gemm_plan_init(GemmPlan& p, const b2p_op& op, const void* weight_dev, int64
             if (best == 0 || cost < best_cost) { best = bn; best_cost = cost; best_cta2 = 0; }
         }
         // CTA pairs: measured 7 % cheaper per tile for the layers the policy admits, no tail splitting
-        if (cta2_ok && (cta2_all ? bn >= 128 : (bn == 256 && !has_res_op))) {
+        static const bool cta2_res = getenv("B2P_CTA2_RES") != nullptr;     // experiment: pairs for residual layers too
+        if (cta2_ok && (cta2_all ? bn >= 128 : (bn == 256 && (!has_res_op || cta2_res)))) {
             const long pairs = num_sms / 2;
             const long tiles = static_cast<long>((m_tiles + 1) / 2) * (p.n_pad / bn);
             // a pair tile pulls half of the weight bytes per CTA through the L2, which is what bounds these layers: worth
