@@ -209,3 +209,34 @@ def test_fold_bn_and_packing_layout():
     assert packed.shape == (64, 3, 3, 8) and packed.dtype == torch.bfloat16
     assert torch.equal(packed[:16].float(), w.permute(0, 2, 3, 1).to(torch.bfloat16).float())
     assert packed[16:].abs().sum().item() == 0
+
+
+def test_resnet50_transition_output_is_subsampled_once(monkeypatch):
+    """The stage-1 -> stage-2 CONV_PAIR keeps only the even rows / columns of its first output (its other reader is the
+    next block's stride-2 shortcut, which then reads the compact tensor with stride 1); B2P_PAIR_SUBSAMPLE=0 restores the
+    full tensor and the stride-2 read.  Both programs compute the same network (the interpreter test above runs the
+    default one)."""
+    from mlmicroservicetemplate_b200.runtime import seeded_model
+    model = seeded_model("resnet50", 0)
+    prog = P.build_program(model, "resnet50")
+    pairs = [op for op in prog.ops if op.kind == B.OP_CONV_PAIR]
+    sub = [op for op in pairs if op.reserved2 == 2]
+    assert len(pairs) == 5 and len(sub) == 1
+    op = sub[0]
+    assert (op.out_h, op.out_w, op.out_c, op.reserved[3]) == (56, 56, 256, 128)
+    assert prog.slot_elems[op.dst] >= 28 * 28 * 256
+    # the ops that see this tensor: from the pair op to the next writer of its slot (slot ids are recycled)
+    i0 = list(prog.ops).index(op)
+    live = []
+    for o in prog.ops[i0 + 1:]:
+        if o.dst == op.dst or (o.kind == B.OP_CONV_PAIR and o.reserved[0] == op.dst):
+            break
+        live.append(o)
+    readers = [o for o in live if o.src2_c > 0 and o.src2 == op.dst]
+    assert len(readers) == 1 and readers[0].src2_stride == 1 and readers[0].src2_c == 256 and readers[0].out_h == 28
+    assert not any(o.src == op.dst or o.res == op.dst for o in live), "nobody reads the compact tensor at full resolution"
+    monkeypatch.setenv("B2P_PAIR_SUBSAMPLE", "0")
+    full = P.build_program(model, "resnet50")
+    assert not any(o.kind == B.OP_CONV_PAIR and o.reserved2 == 2 for o in full.ops)
+    strided = [o for o in full.ops if o.src2_c == 256 and o.out_h == 28]
+    assert len(strided) == 1 and strided[0].src2_stride == 2
