@@ -15,8 +15,8 @@
 // Warps: 0 = TMA producer (A, W3), 1 = TMEM owner + MMA issuer (both GEMMs), 2 = loader for the
 // residual chunks and W1 tiles, 3 = idle, 4..7 / 8..11 = two epilogue groups (left / right 64 columns of a sub-tile).
 //
-// WRES variant (56x56 stage: N1 = 256, N2 = 64, K <= 128): both weight matrices - 64-96 KB - are loaded ONCE per CTA and
-// stay in shared memory; the operand ring then carries only the 16 KB A tiles.  These kernels run at the L2's
+// WRES variant (56x56 stage: N1 = 256, K <= 128): W3 - and for N2 = 64 also W1, 64-96 KB together - is loaded ONCE per
+// CTA and stays in shared memory; the operand ring then carries only the 16 KB A tiles.  These kernels run at the L2's
 // throughput (profiles/r02zb_l2_smem_bounds.txt) and the weights were 64-96 KB of the ~240 KB every 128-pixel tile
 // pulled through it.
 #include <atomic>
@@ -71,7 +71,8 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-    static_assert(!WRES || N2 == 64, "resident weights: the 64-channel conv1 only");
+    static_assert(!WRES || N2 <= 128, "resident W3: N2 = 64 (W1 resident too) or 128 (W1 streamed through its ring)");
+    constexpr bool W1RES = WRES && N2 == 64;            // W1 (N2 x N1) resident as well: 32 KB for N1 = 256
     // ALT: the second epilogue (out2) of a tile is taken by epilogue group (tile & 1) instead of always group 0, which
     // had 3-4 epilogue units per tile against group 1's 2 and set the tile period of the kernels that are not DRAM-bound
     // (profiles/r02zb_l2_smem_bounds.txt, section 9).  Costs a second out2 staging tile (one W1 ring slot / A stage less).
@@ -202,16 +203,16 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     const uint64_t a_desc = umma_desc_kmajor(smem_u32(smem_stg + sb * TILE16K), 128);
 #pragma unroll
                     for (int u = 0; u < W2_UNITS; ++u) {
-                        if (!WRES) mbar_wait(&w2_full[wb], wb_phase);
+                        if (!W1RES) mbar_wait(&w2_full[wb], wb_phase);
                         tc_fence_after();
                         // WRES: chunk q of out1 = K block q of GEMM2, its [64 x 64] weight tile lies at q * 8 KB
-                        const uint64_t b_desc = umma_desc_kmajor(WRES ? smem_u32(smem_w2 + q * W2_UNIT_BYTES) : smem_u32(smem_w2 + wb * TILE16K), 128);
+                        const uint64_t b_desc = umma_desc_kmajor(W1RES ? smem_u32(smem_w2 + q * W2_UNIT_BYTES) : smem_u32(smem_w2 + wb * TILE16K), 128);
                         const uint32_t d = tmem_base + ACC2_COL + static_cast<uint32_t>(u * 128);
 #pragma unroll
                         for (int k = 0; k < 4; ++k)
                             umma_bf16(d, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k), idesc2,
                                       static_cast<uint32_t>((q | k) != 0));
-                        if (!WRES) {
+                        if (!W1RES) {
                             umma_commit(&w2_empty[wb]);
                             if (++wb == W2_BUFS) { wb = 0; wb_phase ^= 1u; }
                         }
@@ -223,7 +224,7 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 
             if (WRES) {
                 mbar_wait(w3_bar, 0);
-                mbar_wait(w1_bar, 0);
+                if (W1RES) mbar_wait(w1_bar, 0);
                 tc_fence_after();
             }
             int it = 0;
@@ -263,7 +264,7 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             // The residual of a chunk is needed at the START of that chunk's epilogue, its W1 tile only afterwards (by
             // the second GEMM), and both come from this one thread: so the residual loads run RES_BUFS - 1 chunks
             // ahead of the W1 loads instead of waiting behind them.
-            if (WRES) {
+            if (W1RES) {
                 mbar_arrive_expect_tx(w1_bar, static_cast<uint32_t>(chunks_per_tile * W2_UNIT_BYTES));
                 for (int q = 0; q < chunks_per_tile; ++q)
                     tma_load_2d_hint(&tmap_w1, w1_bar, smem_w2 + q * W2_UNIT_BYTES, q * 64, 0, L2_EVICT_LAST);
@@ -285,7 +286,7 @@ conv_pair_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
                     const int ahead = c + RES_BUFS - 1 < total_chunks - 1 ? c + RES_BUFS - 1 : total_chunks - 1;
                     while (res_issued <= ahead) issue_res(res_issued++);
                 }
-                if (WRES) continue;
+                if (W1RES) continue;
                 const int q = c % chunks_per_tile;
                 for (int u = 0; u < W2_UNITS; ++u) {
                     mbar_wait(&w2_empty[wb], wb_phase ^ 1u);
@@ -496,12 +497,13 @@ cudaError_t launch_pair(const PairPlan& p, const PairArgs& a, int grid, cudaStre
 
 // Resident weights fit when (A ring + staging + residual tiles + W1 + W3) stay inside the kernel's fixed allocation.
 bool pair_weights_fit(const PairPlan& p, const PairArgs& a) {
-    if (p.n2 != 64) return false;
+    if (p.n2 != 64 && p.n2 != 128) return false;      // 64: W3 and W1 resident; 128: W3 resident, W1 through its two-slot ring
     static const char* off = getenv("B2P_PAIR_WRES");
     if (off && off[0] == '0') return false;
     const int tiles = WRES_A_STAGES + STG_BUFS + 2 /*out2 staging*/ + (a.has_res ? RES_BUFS : 0) + 2 /*W1: 4 x 8 KB*/ +
                       a.n1_tiles * (a.k1_blocks + a.k2_blocks);
-    return a.n1_tiles * 2 * 8192 <= 2 * TILE16K && 1024 + tiles * TILE16K + 512 <= PAIR_SMEM;
+    if (p.n2 == 64 && a.n1_tiles * 2 * 8192 > 2 * TILE16K) return false;
+    return 1024 + tiles * TILE16K + 512 <= PAIR_SMEM;
 }
 
 }  // namespace
@@ -610,7 +612,7 @@ cudaError_t pair_plan_launch(const PairPlan& p, int m_rows, int reverse, int num
     if (a.m_tiles <= 0) return cudaSuccess;
     const int grid = a.m_tiles < num_sms ? a.m_tiles : num_sms;
     if (p.n2 == 64) return pair_weights_fit(p, a) ? launch_pair<64, true>(p, a, grid, s) : launch_pair<64, false>(p, a, grid, s);
-    if (p.n2 == 128) return launch_pair<128, false>(p, a, grid, s);
+    if (p.n2 == 128) return pair_weights_fit(p, a) ? launch_pair<128, true>(p, a, grid, s) : launch_pair<128, false>(p, a, grid, s);
     if (p.n2 == 256) return launch_pair<256, false>(p, a, grid, s);
     return cudaErrorInvalidConfiguration;
 }
