@@ -142,3 +142,68 @@ def test_blocking_predict_keeps_the_reference_signature(client):
     assert list(sig.parameters) == ["image_file"] and inspect.signature(plugin.init).parameters == {}
     out = plugin.predict(SimpleNamespace(file=io.BytesIO(_jpeg())))
     assert out == CASES["POST /predict ready"]["body"]["result"]
+
+
+def _mp(parts, boundary="XbOuNdArY"):
+    """parts: [(header lines, payload bytes)] -> (body, content type)"""
+    out = b""
+    for headers, payload in parts:
+        out += b"--" + boundary.encode() + b"\r\n" + "\r\n".join(headers).encode() + b"\r\n\r\n" + payload + b"\r\n"
+    return out + b"--" + boundary.encode() + b"--\r\n", f"multipart/form-data; boundary={boundary}"
+
+
+def test_single_image_part_recognises_only_the_plain_upload():
+    from mlmicroservicetemplate_b200.src.server.main import single_image_part
+    data = bytes(range(256)) * 40 + b"\r\n--not-the-boundary\r\n"
+    cd = 'Content-Disposition: form-data; name="image_file"; filename="a.jpg"'
+    body, ct = _mp([([cd, "Content-Type: image/jpeg"], data)])
+    assert single_image_part(body, ct) == (data, "a.jpg", "image/jpeg")
+    assert single_image_part(body, ct.replace("boundary=", 'boundary="') + '"') == (data, "a.jpg", "image/jpeg")
+    assert single_image_part(body[:-2], ct)[0] == data                       # no CRLF after the closing delimiter
+    body2, _ = _mp([([cd], data)])
+    assert single_image_part(body2, ct) == (data, "a.jpg", "application/octet-stream")
+    # everything else goes to the framework's parser
+    for parts in ([(['Content-Disposition: form-data; name="other"; filename="a.jpg"'], data)],
+                  [(['Content-Disposition: form-data; name="image_file"'], data)],                    # a field, not a file
+                  [([cd], data), (['Content-Disposition: form-data; name="x"'], b"1")],               # two parts
+                  [(["Content-Disposition: form-data; name=\"image_file\"; filename*=UTF-8''a.jpg"], data)],
+                  [(['Content-Disposition: form-data; name=image_file; filename="a.jpg"'], data)],     # unquoted
+                  [([cd, "X-Extra: 1"], data)]):
+        b, c = _mp(parts)
+        assert single_image_part(b, c) is None, parts[0][0]
+    assert single_image_part(body, "application/json") is None
+    assert single_image_part(body, "multipart/form-data") is None
+    assert single_image_part(body[:-8], ct) is None                           # closing delimiter cut off
+    assert single_image_part(b"junk" + body, ct) is None
+
+
+def test_fast_path_answers_exactly_like_the_router(client, monkeypatch):
+    """The same uploads through FastPredict and, with the fast path bypassed, through the framework's parser: status,
+    body bytes and headers are identical; requests the fast path does not recognise reach the router untouched."""
+    c, main, dep, plugin = client
+    _wait_ready(dep)
+    taken = []
+    real = main.single_image_part
+    monkeypatch.setattr(main, "single_image_part", lambda b, t: (taken.append(1), real(b, t))[1])
+    jpeg = _jpeg(3)
+
+    def drop(h):
+        return {k: v for k, v in h.items() if k.lower() not in ("date",)}
+    fast = c.post("/predict", files={"image_file": ("a.jpg", jpeg, "image/jpeg")}, headers={"Origin": "http://localhost:3000"})
+    assert fast.status_code == 200 and taken
+    monkeypatch.setattr(main, "single_image_part", lambda b, t: None)
+    slow = c.post("/predict", files={"image_file": ("a.jpg", jpeg, "image/jpeg")}, headers={"Origin": "http://localhost:3000"})
+    assert (fast.status_code, fast.content, drop(fast.headers)) == (slow.status_code, slow.content, drop(slow.headers))
+    monkeypatch.setattr(main, "single_image_part", real)
+    # not recognised -> the router's own answers
+    r = c.post("/predict", files={"wrong_name": ("a.jpg", jpeg, "image/jpeg")})
+    assert r.status_code == 422 and r.json()["detail"][0]["loc"] == ["body", "image_file"]
+    r = c.post("/predict", data={"image_file": "not a file"})
+    assert r.status_code == 422
+    r = c.post("/predict", files={"image_file": ("a.jpg", jpeg, "image/jpeg")}, data={"extra": "1"})
+    assert r.status_code == 200
+    bad = c.post("/predict", files={"image_file": ("a.jpg", b"these are not image bytes", "image/jpeg")})
+    assert bad.status_code == 500                                              # undecodable upload, as in the reference
+    dep.model_settings.ready_to_predict = False
+    r = c.post("/predict", files={"image_file": ("a.jpg", jpeg, "image/jpeg")})
+    assert r.status_code == 503 and r.json() == main.NOT_READY
