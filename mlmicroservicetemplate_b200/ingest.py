@@ -273,7 +273,16 @@ class DispatcherServer:
             try:
                 ready = wait(conns, timeout=0.05)
             except (OSError, ValueError):
-                ready = conns                      # a connection died between the snapshot and the wait: find it below
+                # a connection was closed between the snapshot and the wait: drop the dead ones, read nothing (a read
+                # on a healthy connection that has no data would block every front end)
+                ready = []
+                for c in conns:
+                    try:
+                        dead = c.closed or c.fileno() < 0
+                    except (OSError, ValueError):
+                        dead = True
+                    if dead:
+                        self._drop(c)
             for conn in ready:
                 fe = self.fronts.get(conn)
                 if fe is None:
