@@ -21,6 +21,8 @@ from __future__ import annotations
 
 import os
 import pickle
+import socket
+import struct
 import threading
 import time
 from concurrent.futures import Future
@@ -34,6 +36,7 @@ import numpy as np
 AUTHKEY = b"b2p-ingest"
 SLOT_BYTES = 256 << 10          # allocation granule of a ring
 KIND_JPEG, KIND_PIXELS = 1, 2
+SEND_TIMEOUT_S = 2.0            # dispatcher -> front end; a front end that does not read for this long is dropped
 
 
 @dataclass
@@ -188,10 +191,14 @@ class RemoteEngine:
 
 class _FrontEnd:
     """One connected front-end process: its connection, its mapped ring and the answers waiting to be sent."""
-    __slots__ = ("conn", "shm", "base", "base_addr", "outbox", "rx")
+    __slots__ = ("conn", "shm", "base", "base_addr", "outbox", "rx", "sock")
 
     def __init__(self, conn, shm, base):
         self.conn = conn
+        # answers go out through a socket object over the same descriptor so that a send can TIME OUT: one sender
+        # thread serves every front end, and a front end that stopped reading must not stall the others for ever
+        self.sock = socket.socket(fileno=os.dup(conn.fileno()))
+        self.sock.settimeout(SEND_TIMEOUT_S)
         self.shm = shm
         self.base = base
         self.base_addr = base.ctypes.data
@@ -290,7 +297,10 @@ class DispatcherServer:
                 try:
                     # one read takes everything the front end has sent so far; the connection's framing is a 4-byte
                     # big-endian length followed by a pickle (multiprocessing.connection), parsed here in bulk
-                    chunk = os.read(conn.fileno(), 1 << 18)
+                    try:
+                        chunk = os.read(conn.fileno(), 1 << 18)
+                    except BlockingIOError:          # (the send timeout makes the descriptor non-blocking)
+                        continue
                     if not chunk:
                         raise EOFError
                     rx = fe.rx
@@ -345,9 +355,10 @@ class DispatcherServer:
                     fe.outbox = []
             for fe, items in work:
                 try:
-                    fe.conn.send(("res", items))
-                except (OSError, ValueError):
-                    pass                           # the front end went away; the receive loop cleans up
+                    payload = pickle.dumps(("res", items), protocol=pickle.HIGHEST_PROTOCOL)
+                    fe.sock.sendall(struct.pack("!i", len(payload)) + payload)     # multiprocessing.connection framing
+                except (OSError, ValueError):        # gone, or not reading (socket.timeout is an OSError)
+                    self._drop(fe.conn)
             if self.stopping and not work:
                 return
 
@@ -356,10 +367,11 @@ class DispatcherServer:
             fe = self.fronts.pop(conn, None)
         if fe is None:
             return
-        try:
-            conn.close()
-        except OSError:
-            pass
+        for closer in (conn.close, fe.sock.close):
+            try:
+                closer()
+            except OSError:
+                pass
         fe.base = None
         try:
             fe.shm.close()
