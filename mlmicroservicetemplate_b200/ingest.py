@@ -51,12 +51,13 @@ class HostView:
 
 
 class ShmRing:
-    """A shared-memory segment handed out in runs of SLOT_BYTES granules (first fit; payloads are short-lived)."""
+    """A shared-memory segment handed out in runs of SLOT_BYTES granules (first fit; payloads are short-lived).
+    The free map is a bytearray (1 = free), so finding a run of n granules is one C-speed substring search."""
 
     def __init__(self, nbytes: int):
         self.slots = max(4, nbytes // SLOT_BYTES)
         self.shm = shared_memory.SharedMemory(create=True, size=self.slots * SLOT_BYTES)
-        self.free = np.ones(self.slots, dtype=bool)
+        self.free = bytearray(b"\x01" * self.slots)
         self.lock = threading.Lock()
         self.cursor = 0
 
@@ -67,26 +68,20 @@ class ShmRing:
     def alloc(self, nbytes: int) -> Optional[Tuple[int, int]]:
         """-> (first granule, number of granules) or None when the ring is full."""
         need = max(1, -(-nbytes // SLOT_BYTES))
+        run = b"\x01" * need
         with self.lock:
-            n = self.slots
-            start = self.cursor
-            for _ in range(2):                      # from the cursor to the end, then from the beginning
-                i = start
-                while i + need <= n:
-                    run = self.free[i:i + need]
-                    if run.all():
-                        self.free[i:i + need] = False
-                        self.cursor = (i + need) % n
-                        return i, need
-                    i += int(np.argmin(run)) + 1    # jump past the first busy granule of the window
-                if start == 0:
-                    break
-                start = 0
-        return None
+            i = self.free.find(run, self.cursor)        # from the cursor to the end, then from the beginning
+            if i < 0 and self.cursor:
+                i = self.free.find(run)
+            if i < 0:
+                return None
+            self.free[i:i + need] = bytes(need)
+            self.cursor = (i + need) % self.slots
+            return i, need
 
     def release(self, first: int, count: int) -> None:
         with self.lock:
-            self.free[first:first + count] = True
+            self.free[first:first + count] = b"\x01" * count
 
     def close(self) -> None:
         try:

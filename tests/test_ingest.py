@@ -137,7 +137,7 @@ def test_remote_engine_in_process_round_trip_and_dispatcher_loss():
         im = np.full((10, 10, 3), 9, np.uint8)
         probs, idx = remote.submit(im).result(timeout=10)
         assert [int(v) for v in idx] == [9, im.size % 251]
-        assert remote.ring.free.all(), "the granules of an answered request go back to the ring"
+        assert all(remote.ring.free), "the granules of an answered request go back to the ring"
     finally:
         remote.close()
         srv.close()
